@@ -1,0 +1,200 @@
+/*
+ * b200_hotpath.h — C-ABI of the B200-native (sm_100a) SGLang per-layer hot path.
+ *
+ * This is the drop-in boundary: every entry point replaces one
+ * `torch.ops.sgl_kernel.*` op (or Triton kernel) that the reference's Python layers
+ * call on this path.  All pointers are raw DEVICE pointers owned by the caller
+ * (PyTorch's caching allocator in practice); sizes/strides are in ELEMENTS unless
+ * a name says bytes; `stream` is a `cudaStream_t` passed as `void*` (0 = legacy
+ * default stream).  Calls only enqueue work on `stream` — no host sync, no
+ * allocation — so all of them are CUDA-graph capturable.
+ *
+ * Return value: 0 (B200_OK) on success, otherwise a b200_status code;
+ * `b200_last_error()` returns a thread-local human-readable message.  The Python
+ * host layer (sglang_npu_b200/_cabi.py) turns non-zero codes into RuntimeError /
+ * NotImplementedError, mirroring TORCH_CHECK / TORCH_CHECK_NOT_IMPLEMENTED in the
+ * reference (sgl-kernel/csrc/gemm/int8_gemm_kernel.cu:670-695, :742-743).
+ *
+ * Reference citations are paths under /root/reference.
+ */
+#ifndef B200_HOTPATH_H_
+#define B200_HOTPATH_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  B200_OK = 0,
+  B200_ERR_INVALID_ARG = 1, /* shape / alignment / null-pointer violation      -> RuntimeError        */
+  B200_ERR_UNSUPPORTED = 2, /* valid request this build has no kernel for      -> NotImplementedError */
+  B200_ERR_CUDA = 3,        /* CUDA runtime / driver error at launch           -> RuntimeError        */
+  B200_ERR_WORKSPACE = 4    /* caller-provided workspace too small             -> RuntimeError        */
+} b200_status;
+
+typedef enum {
+  B200_BF16 = 0,
+  B200_F16 = 1,
+  B200_F32 = 2,
+  B200_FP8_E4M3 = 3,
+  B200_I8 = 4
+} b200_dtype;
+
+/* ---- library info ------------------------------------------------------------------- */
+int b200_abi_version(void);
+const char* b200_last_error(void);
+/* Fills SM count and compute capability of the current device. */
+int b200_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- KV-cache write -------------------------------------------------------------------
+ * Replaces MHATokenToKVPool.set_kv_buffer's two index_put_ launches
+ * (python/sglang/srt/mem_cache/memory_pool.py:369-407):
+ *     k_cache[loc[t], :, :] = k[t, :, :];  v_cache[loc[t], :, :] = v[t, :, :]
+ * Bit-exact copy.  k/v rows may be strided views (token stride given, [heads, dim]
+ * contiguous); cache rows are [num_kv_heads, head_dim] contiguous with the given
+ * token stride.  elem_bytes is the KV element size (2 = bf16/fp16, 1 = fp8 stored
+ * as uint8, memory_pool.py:114-118).  Row bytes must be a multiple of 16.
+ */
+int b200_set_kv_buffer(void* k_cache, void* v_cache, const void* k, const void* v,
+                       const void* loc, int loc_is_int64, int64_t num_tokens,
+                       int64_t k_row_elems, int64_t v_row_elems,
+                       int64_t k_token_stride, int64_t v_token_stride,
+                       int64_t k_cache_token_stride, int64_t v_cache_token_stride,
+                       int elem_bytes, void* stream);
+
+/* ---- decode attention -----------------------------------------------------------------
+ * Replaces decode_attention_fwd (python/sglang/srt/layers/attention/triton_ops/
+ * decode_attention.py:677-728; stage1 :241-401, stage2 :492-552) and the oracle's
+ * _run_sdpa_forward_decode (torch_native_backend.py:112-180):
+ *   o[b,h,:] = softmax(sm_scale * q[b,h,:] . K[idx_b, h/g, :]^T) . V[idx_b, h/g, :]
+ *   idx_b    = req_to_token[req_pool_indices[b], 0:seq_lens[b]]      (no causal mask)
+ * Split-KV: request b is cut into ceil(seq_len_b / kv_chunk) chunks; grid.x covers
+ * max_splits chunks, surplus CTAs exit.  Partials (fp32 o, lse) live in `workspace`
+ * and are merged by a second kernel.  A request with seq_len 0 produces zeros.
+ */
+int b200_decode_attn_workspace_bytes(int batch, int num_q_heads, int head_dim, int max_splits,
+                                     size_t* bytes);
+int b200_decode_attn(void* o, const void* q, const void* k_cache, const void* v_cache,
+                     const int32_t* req_to_token, int64_t req_to_token_stride,
+                     const void* req_pool_indices, const void* seq_lens, int index_is_int64,
+                     int batch, int num_q_heads, int num_kv_heads, int head_dim,
+                     int64_t q_token_stride, int64_t o_token_stride,
+                     int64_t kv_token_stride, float sm_scale, float logit_cap,
+                     int kv_chunk, int max_splits, void* workspace, size_t workspace_bytes,
+                     int dtype, void* stream);
+
+/* ---- extend (prefill) attention ------------------------------------------------------
+ * Replaces extend_attention_fwd (triton_ops/extend_attention.py:302-440) and the
+ * oracle's _run_sdpa_forward_extend (torch_native_backend.py:27-110).  Request b has
+ * prefix_lens[b] cached tokens and extend_lens[b] = qo_indptr[b+1]-qo_indptr[b] new
+ * ones; query i (0-based within the request) attends to all prefix slots plus new
+ * tokens 0..i (causal) or all new tokens (causal = 0).  Prefix keys come through the
+ * page table; new keys come from k_new/v_new when non-NULL (contiguous activations,
+ * token stride given) else also through the page table (they were written first).
+ */
+int b200_extend_attn(void* o, const void* q, const void* k_new, const void* v_new,
+                     const void* k_cache, const void* v_cache,
+                     const int32_t* req_to_token, int64_t req_to_token_stride,
+                     const void* req_pool_indices, int index_is_int64,
+                     const int32_t* qo_indptr, const int32_t* prefix_lens,
+                     int batch, int max_extend_len,
+                     int num_q_heads, int num_kv_heads, int head_dim,
+                     int64_t q_token_stride, int64_t o_token_stride,
+                     int64_t knew_token_stride, int64_t vnew_token_stride,
+                     int64_t kv_token_stride, float sm_scale, float logit_cap, int causal,
+                     int dtype, void* stream);
+
+/* ---- LSE merge ----------------------------------------------------------------------------
+ * Replaces merge_state / merge_state_v2 (sgl-kernel/csrc/attention/cascade.cu:20-55,
+ * merge_attn_states.cu:31-204): v_out = (v_a e^{s_a-m} + v_b e^{s_b-m}) / (e^{s_a-m}+e^{s_b-m}),
+ * s_out = m + log(...), m = max(s_a, s_b).  v_*: [T, H, D] (dtype), s_*: [T, H] fp32.
+ * s_out may be NULL.
+ */
+int b200_merge_state(void* v_out, float* s_out, const void* v_a, const float* s_a,
+                     const void* v_b, const float* s_b, int64_t num_tokens, int num_heads,
+                     int head_dim, int dtype, void* stream);
+
+/* ---- W8A8-int8 linear ------------------------------------------------------------------
+ * b200_per_token_quant_int8 replaces per_token_quant_int8 (python/sglang/srt/layers/
+ * quantization/int8_kernel.py:20-83): per row, absmax = max(|x|, 1e-10);
+ * scale = absmax/127; xq = rint(x * (127/absmax)) (round-half-even, the oracle's
+ * torch.round rule, test/srt/cpu/utils.py:24-32).
+ *
+ * b200_int8_scaled_mm replaces int8_scaled_mm (sgl-kernel/csrc/gemm/
+ * int8_gemm_kernel.cu:663-746): out[m,n] = cast((sum_k a[m,k]*b[n,k]) * scale_a[m]
+ * * scale_b[n] + bias[n]).  `a` is [M,K] row-major int8, `b` is the weight as the
+ * reference holds it after process_weights_after_loading — logical [K,N] column-major,
+ * i.e. N rows of K contiguous int8 (w8a8_int8.py:332-341).  K % 16 == 0, N % 8 == 0.
+ * If acc_out != NULL the raw int32 accumulators [M,N] are written too (parity hook:
+ * they must be bit-exact).  Workspace: b200_int8_scaled_mm_workspace_bytes.
+ */
+int b200_per_token_quant_int8(int8_t* xq, float* scale, const void* x, int64_t M, int64_t K,
+                              int64_t x_row_stride, int dtype, void* stream);
+int b200_int8_scaled_mm_workspace_bytes(int64_t M, int64_t N, int64_t K, size_t* bytes);
+int b200_int8_scaled_mm(void* out, const int8_t* a, const int8_t* b, const float* scale_a,
+                        const float* scale_b, const void* bias, int64_t M, int64_t N, int64_t K,
+                        int out_dtype, int32_t* acc_out, void* workspace, size_t workspace_bytes,
+                        void* stream);
+
+/* ---- block-scaled FP8 linear -----------------------------------------------------------
+ * b200_per_token_group_quant_fp8 replaces sgl_per_token_group_quant_fp8
+ * (sgl-kernel/csrc/gemm/per_token_group_quant_8bit.cu) / per_token_group_quant_fp8
+ * (fp8_kernel.py:116-297): per (row, group of `group_size`): s = max(absmax, eps)/448,
+ * xq = e4m3(clamp(x / s, +-448)); scales written as [M, K/group] with the given strides
+ * (row-major or column-major "TMA-aligned" layout).
+ *
+ * b200_fp8_blockwise_scaled_mm replaces fp8_blockwise_scaled_mm (sgl-kernel/csrc/gemm/
+ * fp8_blockwise_gemm_kernel.cu:345-423): out[m,n] = sum_kb (sum_{k in kb} a[m,k] b[n,k])
+ * * sa[m,kb] * sb[n/128,kb]; a [M,K] e4m3 row-major, b N rows of K contiguous e4m3;
+ * K % 128 == 0, N % 128 == 0 (fp8_utils.py:190-197).
+ */
+int b200_per_token_group_quant_fp8(void* xq, float* scales, const void* x, int64_t M, int64_t K,
+                                   int64_t x_row_stride, int group_size, float eps,
+                                   int64_t scale_row_stride, int64_t scale_col_stride,
+                                   int dtype, void* stream);
+int b200_per_token_quant_fp8(void* xq, float* scale, const void* x, int64_t M, int64_t K,
+                             int64_t x_row_stride, int dtype, void* stream);
+int b200_fp8_blockwise_scaled_mm(void* out, const void* a, const void* b, const float* scale_a,
+                                 int64_t sa_row_stride, int64_t sa_col_stride,
+                                 const float* scale_b, int64_t sb_row_stride, int64_t sb_col_stride,
+                                 const void* bias, int64_t M, int64_t N, int64_t K, int out_dtype,
+                                 void* stream);
+/* per-token x per-channel FP8 (sgl-kernel/csrc/gemm/fp8_gemm_kernel.cu:1110-1145). */
+int b200_fp8_scaled_mm(void* out, const void* a, const void* b, const float* scale_a,
+                       const float* scale_b, const void* bias, int64_t M, int64_t N, int64_t K,
+                       int out_dtype, void* stream);
+
+/* ---- AWQ-int4 linear -------------------------------------------------------------------
+ * b200_awq_dequantize replaces awq_dequantize (sgl-kernel/csrc/gemm/awq_kernel.cu:126-221):
+ * W[k, 8c+i] = (nib(qweight[k,c], ORDER[i]) - nib(qzeros[k/g,c], ORDER[i])) * scales[k/g, 8c+i],
+ * ORDER = [0,4,1,5,2,6,3,7], computed in the scale dtype (sub then mul).
+ * b200_awq_gemm fuses that dequantisation into out = x @ W (+bias)
+ * (python/sglang/srt/layers/quantization/awq.py:401-418) without materialising W.
+ */
+int b200_awq_dequantize(void* w_out, const int32_t* qweight, const void* scales,
+                        const int32_t* qzeros, int64_t K, int64_t N, int group_size,
+                        int dtype, void* stream);
+int b200_awq_gemm(void* out, const void* x, const int32_t* qweight, const void* scales,
+                  const int32_t* qzeros, const void* bias, int64_t M, int64_t N, int64_t K,
+                  int group_size, int dtype, void* stream);
+
+/* ---- elementwise steps either side of the path -----------------------------
+ * fused_add_rmsnorm (sgl-kernel/csrc/elementwise/fused_add_rms_norm_kernel.cu), silu_and_mul
+ * (activation.cu), neox rope with a cos/sin cache (rope.cu).  residual may be NULL (plain
+ * rmsnorm, out-of-place into `out`).  With residual: residual += x; out = norm(residual)*w.
+ */
+int b200_rmsnorm(void* out, void* residual, const void* x, const void* weight, int64_t M,
+                 int64_t H, float eps, int dtype, void* stream);
+int b200_silu_and_mul(void* out, const void* x, int64_t M, int64_t H, int dtype, void* stream);
+int b200_rope_neox(void* q, void* k, const float* cos_sin_cache, const int64_t* positions,
+                   int64_t num_tokens, int num_q_heads, int num_kv_heads, int head_dim,
+                   int rot_dim, int64_t q_token_stride, int64_t k_token_stride, int dtype,
+                   void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_HOTPATH_H_ */

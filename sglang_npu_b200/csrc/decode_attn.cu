@@ -1,0 +1,485 @@
+// Paged split-KV GQA flash-decode + LSE merge for sm_100a.
+//
+// Replaces decode_attention_fwd (reference python/sglang/srt/layers/attention/triton_ops/
+// decode_attention.py:677-728; grouped stage 1 :241-401, stage 2 :492-552).  Semantics follow
+// the oracle TorchNativeAttnBackend._run_sdpa_forward_decode (torch_native_backend.py:112-180):
+//   o[b,h] = softmax(sm_scale * q[b,h] . K[idx_b, h/g]^T) . V[idx_b, h/g],
+//   idx_b  = req_to_token[req_pool_indices[b], :seq_lens[b]],  no causal mask.
+//
+// Design (HBM-bound: 4 FLOP per KV byte):
+//  * grid = (max_splits, Hkv * head_blocks, batch).  One CTA owns one (request, KV head,
+//    KV chunk) and ALL q heads of that KV head's GQA group (<= 16 per head block), so every
+//    KV byte is read from HBM exactly once per step.
+//  * 4 warps per CTA; each warp streams its own 16-token blocks (block j of the chunk goes
+//    to warp j % 4) through a private STAGES-deep cp.async ring: 16-byte vectorised copies,
+//    a warp instruction covers 512 contiguous bytes of KV rows, XOR-swizzled in shared
+//    memory so ldmatrix is bank-conflict free.  No CTA-wide barrier in the main loop.
+//  * math on the legacy tensor path (mma.sync m16n8k16, fp32 accumulate): S = Q K^T with the
+//    group's q heads on the M axis, online softmax in the exp2 domain with warp shuffles,
+//    O += P V.  At 4 FLOP/B this is <10% of the tensor pipe; the kernel is judged on GB/s.
+//  * the 4 warps' (m, l, O) are merged through shared memory; with one chunk per request the
+//    CTA writes the final output, else fp32 partial (o, lse) go to the workspace and
+//    decode_merge_kernel combines the chunks (log-sum-exp merge).
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kDecWarps = 4;
+constexpr int kDecThreads = kDecWarps * 32;
+constexpr int kBlkTok = 16;  // tokens per warp block (one mma k-step of P.V, two n-tiles of Q.K^T)
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct DecodeArgs {
+  void* o;
+  const void* q;
+  const void* k_cache;
+  const void* v_cache;
+  const int32_t* req_to_token;
+  int64_t req_to_token_stride;
+  const void* req_pool_indices;
+  const void* seq_lens;
+  int index_is_int64;
+  int batch, num_q_heads, num_kv_heads, group, head_blocks;
+  int64_t q_token_stride, o_token_stride, kv_token_stride;
+  float scale_log2;   // sm_scale * log2(e)
+  float sm_scale;
+  float logit_cap;
+  int kv_chunk, max_splits;
+  float* part_o;    // [batch, Hq, max_splits, D]
+  float* part_lse;  // [batch, Hq, max_splits]   (log2 domain)
+};
+
+template <int D>
+struct DecodeSmem {
+  static constexpr int kChunks = D / 8;                       // 16-byte chunks per row
+  static constexpr int kBlkBytes = kBlkTok * D * 2;           // one K (or V) block of a warp
+  static constexpr int kStageBytes = 2 * kBlkBytes;           // K + V
+  static constexpr int kOPad = D + 8;                         // fp32 row stride for the merge
+  static constexpr int merge_bytes() { return kDecWarps * 16 * kOPad * 4 + 2 * kDecWarps * 16 * 4; }
+  static constexpr int pipe_bytes(int stages) { return kDecWarps * stages * kStageBytes; }
+};
+
+// Issue the cp.async copies of one 16-token block (K and V) owned by this warp.
+template <typename T, int D>
+__device__ __forceinline__ void issue_block(const T* __restrict__ k_cache, const T* __restrict__ v_cache,
+                                            int64_t kv_token_stride, int kv_head_off,
+                                            const int32_t* __restrict__ s_slots, int tok0, int n_tok,
+                                            uint32_t smem_k, uint32_t smem_v, int lane) {
+  constexpr int kChunks = D / 8;
+  constexpr int kRowsPerIter = 32 / kChunks;
+  const int c = lane % kChunks;
+  const int r0 = lane / kChunks;
+#pragma unroll
+  for (int it = 0; it < kBlkTok / kRowsPerIter; ++it) {
+    const int r = r0 + it * kRowsPerIter;
+    const int tok = tok0 + r;
+    const bool valid = tok < n_tok;
+    const int slot = valid ? s_slots[tok] : 0;
+    const int64_t off = (int64_t)slot * kv_token_stride + kv_head_off + c * 8;
+    const uint32_t so = (uint32_t)(r * (D * 2) + ((c ^ (r & 7)) << 4));
+    cp_async16_pred(smem_k + so, k_cache + off, valid);
+    cp_async16_pred(smem_v + so, v_cache + off, valid);
+  }
+}
+
+template <typename T, int D, int STAGES, bool UPPER>
+__global__ void __launch_bounds__(kDecThreads, 2) decode_attn_kernel(const DecodeArgs a) {
+  using S = DecodeSmem<D>;
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+
+  const int split = blockIdx.x;
+  const int kvh = blockIdx.y / a.head_blocks;
+  const int hb = blockIdx.y - kvh * a.head_blocks;
+  const int b = blockIdx.z;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int g = lane >> 2;
+  const int t = lane & 3;
+
+  const int seq_len = (int)load_index(a.seq_lens, b, a.index_is_int64);
+  const int start = split * a.kv_chunk;
+  if (start >= seq_len) return;
+  const int n_tok = min(seq_len - start, a.kv_chunk);
+  const int num_splits = (seq_len + a.kv_chunk - 1) / a.kv_chunk;
+
+  // carve shared memory: [pipeline | slots]; the merge scratch aliases the pipeline.
+  uint8_t* pipe = smem_raw;
+  int32_t* s_slots = reinterpret_cast<int32_t*>(smem_raw + S::pipe_bytes(STAGES));
+
+  // ---- 1. page-table slice of this chunk -> shared memory --------------------------------
+  {
+    const int64_t req = load_index(a.req_pool_indices, b, a.index_is_int64);
+    const int32_t* row = a.req_to_token + req * a.req_to_token_stride + start;
+    for (int i = threadIdx.x; i < n_tok; i += kDecThreads) s_slots[i] = __ldg(row + i);
+  }
+  __syncthreads();
+
+  const T* k_cache = reinterpret_cast<const T*>(a.k_cache);
+  const T* v_cache = reinterpret_cast<const T*>(a.v_cache);
+  const int kv_head_off = kvh * D;
+  const uint32_t warp_pipe = smem_u32(pipe) + warp * STAGES * S::kStageBytes;
+
+  const int n_blocks = (n_tok + kBlkTok - 1) / kBlkTok;            // blocks in the chunk
+  const int my_blocks = (n_blocks - warp + kDecWarps - 1) / kDecWarps;  // blocks warp, warp+4, ...
+
+  // ---- 2. pipeline prologue ---------------------------------------------------------------
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; ++s) {
+    if (s < my_blocks) {
+      const int tok0 = (warp + s * kDecWarps) * kBlkTok;
+      issue_block<T, D>(k_cache, v_cache, a.kv_token_stride, kv_head_off, s_slots, tok0, n_tok,
+                        warp_pipe + s * S::kStageBytes, warp_pipe + s * S::kStageBytes + S::kBlkBytes,
+                        lane);
+    }
+    cp_async_commit();
+  }
+
+  // ---- 3. Q fragments (rows = q heads of the group), overlapped with the first copies -----
+  const int head0 = kvh * a.group + hb * 16;
+  const int n_heads = min(16, a.group - hb * 16);
+  uint32_t qf[D / 16][4];
+  {
+    const T* qb = reinterpret_cast<const T*>(a.q) + (int64_t)b * a.q_token_stride + (int64_t)head0 * D;
+    const bool v0 = g < n_heads;
+    const bool v1 = UPPER && (g + 8 < n_heads);
+#pragma unroll
+    for (int ks = 0; ks < D / 16; ++ks) {
+      const int col = ks * 16 + 2 * t;
+      qf[ks][0] = v0 ? *reinterpret_cast<const uint32_t*>(qb + g * D + col) : 0u;
+      qf[ks][1] = v1 ? *reinterpret_cast<const uint32_t*>(qb + (g + 8) * D + col) : 0u;
+      qf[ks][2] = v0 ? *reinterpret_cast<const uint32_t*>(qb + g * D + col + 8) : 0u;
+      qf[ks][3] = v1 ? *reinterpret_cast<const uint32_t*>(qb + (g + 8) * D + col + 8) : 0u;
+    }
+  }
+
+  float o_acc[D / 8][4];
+#pragma unroll
+  for (int i = 0; i < D / 8; ++i) o_acc[i][0] = o_acc[i][1] = o_acc[i][2] = o_acc[i][3] = 0.f;
+  float m_run[2] = {-INFINITY, -INFINITY};  // running max (log2 domain), rows g and g+8
+  float l_run[2] = {0.f, 0.f};              // per-thread partial row sums
+
+  const bool use_cap = a.logit_cap > 0.f;
+  const float cap_in = use_cap ? a.sm_scale / a.logit_cap : 0.f;
+  const float cap_out = a.logit_cap * kLog2e;
+
+  // ldmatrix lane addressing (see header comment of each use)
+  const int lm_row = lane & 7;
+  const int lm_mat = lane >> 3;
+
+  // ---- 4. main loop over this warp's blocks ----------------------------------------------------
+  for (int i = 0; i < my_blocks; ++i) {
+    // prefetch block i + STAGES - 1
+    {
+      const int nb = i + STAGES - 1;
+      if (nb < my_blocks) {
+        const int st = nb % STAGES;
+        const int tok0 = (warp + nb * kDecWarps) * kBlkTok;
+        issue_block<T, D>(k_cache, v_cache, a.kv_token_stride, kv_head_off, s_slots, tok0, n_tok,
+                          warp_pipe + st * S::kStageBytes,
+                          warp_pipe + st * S::kStageBytes + S::kBlkBytes, lane);
+      }
+      cp_async_commit();
+    }
+    cp_async_wait<STAGES - 1>();
+    __syncwarp();
+
+    const int st = i % STAGES;
+    const uint32_t sk = warp_pipe + st * S::kStageBytes;
+    const uint32_t sv = sk + S::kBlkBytes;
+    const int tok0 = (warp + i * kDecWarps) * kBlkTok;
+
+    // S = Q K^T : [16 heads x 16 tokens] as two n-tiles of 8 tokens
+    float s[2][4];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < D / 16; ++ks) {
+      // matrices: 0:(tok 0-7, dims lo) 1:(tok 0-7, dims hi) 2:(tok 8-15, lo) 3:(tok 8-15, hi)
+      const int r = (lm_mat >> 1) * 8 + lm_row;
+      const int c = ks * 2 + (lm_mat & 1);
+      uint32_t b0, b1, b2, b3;
+      ldmatrix_x4(b0, b1, b2, b3, sk + r * (D * 2) + ((c ^ (r & 7)) << 4));
+      mma_16816<T>(s[0], qf[ks], b0, b1);
+      mma_16816<T>(s[1], qf[ks], b2, b3);
+    }
+
+    // scale (+ optional logit cap) into the log2 domain, mask the tail of the chunk
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float v = s[j][e];
+        if (use_cap) v = cap_out * tanh_approx(v * cap_in);
+        else v *= a.scale_log2;
+        const int tok = tok0 + j * 8 + 2 * t + (e & 1);
+        s[j][e] = tok < n_tok ? v : -INFINITY;
+      }
+    }
+
+    // online softmax, rows g (regs 0,1) and g+8 (regs 2,3)
+    float alpha[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      if (h == 1 && !UPPER) { alpha[1] = 1.f; break; }
+      float mx = fmaxf(fmaxf(s[0][2 * h], s[0][2 * h + 1]), fmaxf(s[1][2 * h], s[1][2 * h + 1]));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      const float m_new = fmaxf(m_run[h], mx);  // finite: every block has >= 1 valid token
+      alpha[h] = fast_exp2(m_run[h] - m_new);
+      m_run[h] = m_new;
+      float sum = 0.f;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        s[j][2 * h] = fast_exp2(s[j][2 * h] - m_new);
+        s[j][2 * h + 1] = fast_exp2(s[j][2 * h + 1] - m_new);
+        sum += s[j][2 * h] + s[j][2 * h + 1];
+      }
+      l_run[h] = l_run[h] * alpha[h] + sum;
+    }
+    if (!UPPER) { s[0][2] = s[0][3] = s[1][2] = s[1][3] = 0.f; }
+
+    // P as the A operand of P.V
+    uint32_t pf[4];
+    pf[0] = pack2<T>(s[0][0], s[0][1]);
+    pf[1] = pack2<T>(s[0][2], s[0][3]);
+    pf[2] = pack2<T>(s[1][0], s[1][1]);
+    pf[3] = pack2<T>(s[1][2], s[1][3]);
+
+#pragma unroll
+    for (int nt = 0; nt < D / 8; ++nt) {
+      o_acc[nt][0] *= alpha[0];
+      o_acc[nt][1] *= alpha[0];
+      if (UPPER) {
+        o_acc[nt][2] *= alpha[1];
+        o_acc[nt][3] *= alpha[1];
+      }
+    }
+#pragma unroll
+    for (int np = 0; np < D / 16; ++np) {
+      // matrices (transposed on load): 0:(tok 0-7, dims np*16..+7) 1:(tok 8-15, same dims)
+      //                                2:(tok 0-7, dims +8..+15)   3:(tok 8-15, dims +8..+15)
+      const int r = (lm_mat & 1) * 8 + lm_row;
+      const int c = np * 2 + (lm_mat >> 1);
+      uint32_t b0, b1, b2, b3;
+      ldmatrix_x4_trans(b0, b1, b2, b3, sv + r * (D * 2) + ((c ^ (r & 7)) << 4));
+      mma_16816<T>(o_acc[2 * np], pf, b0, b1);
+      mma_16816<T>(o_acc[2 * np + 1], pf, b2, b3);
+    }
+    __syncwarp();  // all lanes done reading this stage before it is refilled
+  }
+  cp_async_wait<0>();
+
+  // ---- 5. merge the 4 warps through shared memory ----------------------------------------------
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    l_run[h] += __shfl_xor_sync(0xffffffffu, l_run[h], 1);
+    l_run[h] += __shfl_xor_sync(0xffffffffu, l_run[h], 2);
+  }
+  __syncthreads();  // every warp is done with its pipeline buffers; reuse them
+  float* sm_o = reinterpret_cast<float*>(pipe);                        // [warps][16][kOPad]
+  float* sm_m = sm_o + kDecWarps * 16 * S::kOPad;                      // [warps][16]
+  float* sm_l = sm_m + kDecWarps * 16;                                 // [warps][16]
+  {
+    float* wo = sm_o + warp * 16 * S::kOPad;
+#pragma unroll
+    for (int nt = 0; nt < D / 8; ++nt) {
+      *reinterpret_cast<float2*>(wo + g * S::kOPad + nt * 8 + 2 * t) = make_float2(o_acc[nt][0], o_acc[nt][1]);
+      if (UPPER)
+        *reinterpret_cast<float2*>(wo + (g + 8) * S::kOPad + nt * 8 + 2 * t) =
+            make_float2(o_acc[nt][2], o_acc[nt][3]);
+    }
+    if (t == 0) {
+      sm_m[warp * 16 + g] = m_run[0];
+      sm_l[warp * 16 + g] = l_run[0];
+      sm_m[warp * 16 + g + 8] = UPPER ? m_run[1] : -INFINITY;
+      sm_l[warp * 16 + g + 8] = UPPER ? l_run[1] : 0.f;
+    }
+  }
+  __syncthreads();
+
+  // thread -> (row = head within block, 8 threads per row, D/8 consecutive dims each)
+  {
+    const int row = threadIdx.x >> 3;
+    const int seg = threadIdx.x & 7;
+    if (row < n_heads) {
+      float mw[kDecWarps], wgt[kDecWarps];
+      float M = -INFINITY;
+#pragma unroll
+      for (int w = 0; w < kDecWarps; ++w) {
+        mw[w] = sm_m[w * 16 + row];
+        M = fmaxf(M, mw[w]);
+      }
+      float L = 0.f;
+#pragma unroll
+      for (int w = 0; w < kDecWarps; ++w) {
+        wgt[w] = (mw[w] == -INFINITY) ? 0.f : fast_exp2(mw[w] - M);
+        L += sm_l[w * 16 + row] * wgt[w];
+      }
+      const float inv_l = 1.f / L;
+      const int head = head0 + row;
+      constexpr int kPer = D / 8;
+      float acc[kPer];
+#pragma unroll
+      for (int d = 0; d < kPer; ++d) acc[d] = 0.f;
+#pragma unroll
+      for (int w = 0; w < kDecWarps; ++w) {
+        const float* src = sm_o + (w * 16 + row) * S::kOPad + seg * kPer;
+#pragma unroll
+        for (int d = 0; d < kPer; ++d) acc[d] += src[d] * wgt[w];
+      }
+      if (num_splits == 1) {
+        T* dst = reinterpret_cast<T*>(a.o) + (int64_t)b * a.o_token_stride + (int64_t)head * D + seg * kPer;
+#pragma unroll
+        for (int d = 0; d < kPer; d += 2)
+          *reinterpret_cast<uint32_t*>(dst + d) = pack2<T>(acc[d] * inv_l, acc[d + 1] * inv_l);
+      } else {
+        const int64_t pidx = ((int64_t)b * a.num_q_heads + head) * a.max_splits + split;
+        float* dst = a.part_o + pidx * D + seg * kPer;
+#pragma unroll
+        for (int d = 0; d < kPer; d += 4)
+          *reinterpret_cast<float4*>(dst + d) =
+              make_float4(acc[d] * inv_l, acc[d + 1] * inv_l, acc[d + 2] * inv_l, acc[d + 3] * inv_l);
+        if (seg == 0) a.part_lse[pidx] = M + log2f(L);
+      }
+    }
+  }
+}
+
+// Stage 2: combine the chunks of each (request, q head).  One warp per (b, h); each lane owns
+// D/32 consecutive dims.  Requests with one chunk were finalised by stage 1; requests with
+// seq_len 0 get zeros.
+template <typename T, int D>
+__global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeArgs a) {
+  const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp_global >= a.batch * a.num_q_heads) return;
+  const int b = warp_global / a.num_q_heads;
+  const int h = warp_global - b * a.num_q_heads;
+  const int seq_len = (int)load_index(a.seq_lens, b, a.index_is_int64);
+  const int num_splits = (seq_len + a.kv_chunk - 1) / a.kv_chunk;
+  if (num_splits == 1) return;
+  constexpr int kPer = D / 32;
+  T* dst = reinterpret_cast<T*>(a.o) + (int64_t)b * a.o_token_stride + (int64_t)h * D + lane * kPer;
+  float acc[kPer];
+#pragma unroll
+  for (int d = 0; d < kPer; ++d) acc[d] = 0.f;
+  if (num_splits > 1) {
+    const int64_t base = ((int64_t)b * a.num_q_heads + h) * a.max_splits;
+    float M = -INFINITY;
+    for (int s = lane; s < num_splits; s += 32) M = fmaxf(M, a.part_lse[base + s]);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, off));
+    float L = 0.f;
+    for (int s = 0; s < num_splits; ++s) {
+      const float w = fast_exp2(a.part_lse[base + s] - M);
+      L += w;
+      const float* src = a.part_o + (base + s) * D + lane * kPer;
+      if (kPer == 4) {
+        const float4 v = *reinterpret_cast<const float4*>(src);
+        acc[0] += v.x * w; acc[1] += v.y * w; acc[2] += v.z * w; acc[3] += v.w * w;
+      } else {
+        const float2 v = *reinterpret_cast<const float2*>(src);
+        acc[0] += v.x * w; acc[1] += v.y * w;
+      }
+    }
+    const float inv = 1.f / L;
+#pragma unroll
+    for (int d = 0; d < kPer; ++d) acc[d] *= inv;
+  }
+#pragma unroll
+  for (int d = 0; d < kPer; d += 2) *reinterpret_cast<uint32_t*>(dst + d) = pack2<T>(acc[d], acc[d + 1]);
+}
+
+template <typename T, int D>
+static int launch_decode(const DecodeArgs& a, cudaStream_t stream) {
+  constexpr int STAGES = 3;
+  using S = DecodeSmem<D>;
+  const int pipe = S::pipe_bytes(STAGES);
+  static_assert(S::merge_bytes() <= S::pipe_bytes(STAGES), "merge scratch must fit in the pipeline buffers");
+  const int smem = pipe + a.kv_chunk * 4;
+  dim3 grid(a.max_splits, a.num_kv_heads * a.head_blocks, a.batch);
+  const bool upper = a.group > 8;
+  if (upper) {
+    auto kern = decode_attn_kernel<T, D, STAGES, true>;
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    kern<<<grid, kDecThreads, smem, stream>>>(a);
+  } else {
+    auto kern = decode_attn_kernel<T, D, STAGES, false>;
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    kern<<<grid, kDecThreads, smem, stream>>>(a);
+  }
+  B200_LAUNCH_OK();
+  const int warps = a.batch * a.num_q_heads;
+  decode_merge_kernel<T, D><<<(warps + 3) / 4, 128, 0, stream>>>(a);
+  B200_LAUNCH_OK();
+  return B200_OK;
+}
+
+}  // namespace b200
+
+B200_API int b200_decode_attn_workspace_bytes(int batch, int num_q_heads, int head_dim,
+                                                int max_splits, size_t* bytes) {
+  using namespace b200;
+  B200_REQUIRE(bytes != nullptr, "decode_attn_workspace_bytes: null out pointer");
+  B200_REQUIRE(batch >= 0 && num_q_heads > 0 && head_dim > 0 && max_splits > 0,
+               "decode_attn_workspace_bytes: bad sizes");
+  const size_t n = (size_t)batch * num_q_heads * max_splits;
+  *bytes = n * head_dim * sizeof(float) + n * sizeof(float) + 256;
+  return B200_OK;
+}
+
+B200_API int b200_decode_attn(void* o, const void* q, const void* k_cache, const void* v_cache,
+                                const int32_t* req_to_token, int64_t req_to_token_stride,
+                                const void* req_pool_indices, const void* seq_lens,
+                                int index_is_int64, int batch, int num_q_heads, int num_kv_heads,
+                                int head_dim, int64_t q_token_stride, int64_t o_token_stride,
+                                int64_t kv_token_stride, float sm_scale, float logit_cap,
+                                int kv_chunk, int max_splits, void* workspace,
+                                size_t workspace_bytes, int dtype, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(batch >= 0, "decode_attn: negative batch");
+  if (batch == 0) return B200_OK;
+  B200_REQUIRE(o && q && k_cache && v_cache && req_to_token && req_pool_indices && seq_lens,
+               "decode_attn: null pointer");
+  B200_REQUIRE(num_kv_heads > 0 && num_q_heads % num_kv_heads == 0,
+               "decode_attn: num_q_heads %d not a multiple of num_kv_heads %d", num_q_heads, num_kv_heads);
+  B200_REQUIRE(kv_chunk >= 16 && kv_chunk % 16 == 0 && kv_chunk <= 4096,
+               "decode_attn: kv_chunk %d must be a multiple of 16 in [16, 4096]", kv_chunk);
+  B200_REQUIRE(max_splits >= 1 && max_splits <= 65535, "decode_attn: max_splits %d", max_splits);
+  B200_REQUIRE(batch <= 65535, "decode_attn: batch %d exceeds grid.z", batch);
+  B200_REQUIRE(q_token_stride % 2 == 0 && o_token_stride % 2 == 0 && kv_token_stride % 8 == 0,
+               "decode_attn: strides must keep 4-byte (q/o) and 16-byte (kv) alignment");
+  B200_REQUIRE(((uintptr_t)k_cache | (uintptr_t)v_cache) % 16 == 0 && ((uintptr_t)q | (uintptr_t)o) % 4 == 0,
+               "decode_attn: pointer alignment");
+  size_t need = 0;
+  b200_decode_attn_workspace_bytes(batch, num_q_heads, head_dim, max_splits, &need);
+  if (max_splits > 1) {
+    if (workspace == nullptr || workspace_bytes < need)
+      return fail(B200_ERR_WORKSPACE, "decode_attn: workspace %zu B < required %zu B", workspace_bytes, need);
+    B200_REQUIRE((uintptr_t)workspace % 16 == 0, "decode_attn: workspace must be 16-byte aligned");
+  }
+  DecodeArgs a;
+  a.o = o; a.q = q; a.k_cache = k_cache; a.v_cache = v_cache;
+  a.req_to_token = req_to_token; a.req_to_token_stride = req_to_token_stride;
+  a.req_pool_indices = req_pool_indices; a.seq_lens = seq_lens; a.index_is_int64 = index_is_int64;
+  a.batch = batch; a.num_q_heads = num_q_heads; a.num_kv_heads = num_kv_heads;
+  a.group = num_q_heads / num_kv_heads;
+  a.head_blocks = (a.group + 15) / 16;
+  a.q_token_stride = q_token_stride; a.o_token_stride = o_token_stride; a.kv_token_stride = kv_token_stride;
+  a.sm_scale = sm_scale; a.scale_log2 = sm_scale * kLog2e; a.logit_cap = logit_cap;
+  a.kv_chunk = kv_chunk; a.max_splits = max_splits;
+  const size_t n = (size_t)batch * num_q_heads * max_splits;
+  a.part_o = reinterpret_cast<float*>(workspace);
+  a.part_lse = a.part_o ? a.part_o + n * head_dim : nullptr;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == B200_BF16) {
+    if (head_dim == 128) return launch_decode<__nv_bfloat16, 128>(a, st);
+    if (head_dim == 64) return launch_decode<__nv_bfloat16, 64>(a, st);
+  } else if (dtype == B200_F16) {
+    if (head_dim == 128) return launch_decode<__half, 128>(a, st);
+    if (head_dim == 64) return launch_decode<__half, 64>(a, st);
+  } else {
+    return fail(B200_ERR_UNSUPPORTED, "decode_attn: dtype %d not supported (bf16/f16 only)", dtype);
+  }
+  return fail(B200_ERR_UNSUPPORTED, "decode_attn: head_dim %d not supported (64, 128)", head_dim);
+}

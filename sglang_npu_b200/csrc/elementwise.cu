@@ -1,0 +1,189 @@
+// Element-wise steps either side of the hot path: fused add + RMSNorm,
+// SiLU-and-mul, NeoX RoPE with a cos/sin cache.  Reference: sgl-kernel/csrc/elementwise/
+// {fused_add_rms_norm_kernel,activation,rope}.cu; numerics follow the layers' forward_native
+// (python/sglang/srt/layers/layernorm.py:135-172, activation.py:60-62, rotary_embedding.py:50-75)
+// evaluated in fp32.  HBM-bound: 16-byte accesses, one row per CTA.
+#include "common.cuh"
+
+namespace b200 {
+
+template <typename T>
+__global__ void __launch_bounds__(256) rmsnorm_kernel(T* __restrict__ out, T* __restrict__ residual,
+                                                      const T* __restrict__ x, const T* __restrict__ w,
+                                                      int64_t H, float eps) {
+  extern __shared__ float row_f[];  // H floats
+  __shared__ float red[8];
+  const int64_t row = blockIdx.x;
+  const T* xr = x + row * H;
+  T* rr = residual ? residual + row * H : nullptr;
+  float ss = 0.f;
+  for (int64_t c = threadIdx.x * 8; c < H; c += 256 * 8) {
+    const int4 xv = *reinterpret_cast<const int4*>(xr + c);
+    const uint32_t* xu = reinterpret_cast<const uint32_t*>(&xv);
+    float f[8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 a = unpack2<T>(xu[i]);
+      f[2 * i] = a.x;
+      f[2 * i + 1] = a.y;
+    }
+    if (rr) {
+      const int4 rv = *reinterpret_cast<const int4*>(rr + c);
+      const uint32_t* ru = reinterpret_cast<const uint32_t*>(&rv);
+      int4 nv;
+      uint32_t* nu = reinterpret_cast<uint32_t*>(&nv);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 b = unpack2<T>(ru[i]);
+        f[2 * i] += b.x;
+        f[2 * i + 1] += b.y;
+        nu[i] = pack2<T>(f[2 * i], f[2 * i + 1]);
+      }
+      *reinterpret_cast<int4*>(rr + c) = nv;  // residual = (x + residual) rounded to T
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      row_f[c + i] = f[i];
+      ss += f[i] * f[i];
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) tot += red[i];
+  const float rstd = rsqrtf(tot / (float)H + eps);
+  T* orow = out + row * H;
+  for (int64_t c = threadIdx.x * 8; c < H; c += 256 * 8) {
+    const int4 wv = *reinterpret_cast<const int4*>(w + c);
+    const uint32_t* wu = reinterpret_cast<const uint32_t*>(&wv);
+    int4 ov;
+    uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 ww = unpack2<T>(wu[i]);
+      ou[i] = pack2<T>(row_f[c + 2 * i] * rstd * ww.x, row_f[c + 2 * i + 1] * rstd * ww.y);
+    }
+    *reinterpret_cast<int4*>(orow + c) = ov;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) silu_and_mul_kernel(T* __restrict__ out, const T* __restrict__ x,
+                                                           int64_t M, int64_t H) {
+  const int64_t packs = H / 8;
+  const int64_t total = M * packs;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = i / packs;
+    const int64_t c = (i - row * packs) * 8;
+    const int4 gv = *reinterpret_cast<const int4*>(x + row * 2 * H + c);
+    const int4 uv = *reinterpret_cast<const int4*>(x + row * 2 * H + H + c);
+    const uint32_t* gu = reinterpret_cast<const uint32_t*>(&gv);
+    const uint32_t* uu = reinterpret_cast<const uint32_t*>(&uv);
+    int4 ov;
+    uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 g2 = unpack2<T>(gu[k]);
+      const float2 u2 = unpack2<T>(uu[k]);
+      // F.silu(gate) is rounded to T before the multiply in forward_native
+      const float s0 = DT<T>::to_f(DT<T>::from_f(g2.x / (1.f + __expf(-g2.x))));
+      const float s1 = DT<T>::to_f(DT<T>::from_f(g2.y / (1.f + __expf(-g2.y))));
+      ou[k] = pack2<T>(s0 * u2.x, s1 * u2.y);
+    }
+    *reinterpret_cast<int4*>(out + row * H + c) = ov;
+  }
+}
+
+// NeoX rotary embedding, in place on q and k.  One CTA per token; thread -> (head, pair index).
+template <typename T>
+__global__ void __launch_bounds__(256) rope_neox_kernel(T* __restrict__ q, T* __restrict__ k,
+                                                        const float* __restrict__ cos_sin, const int64_t* __restrict__ pos,
+                                                        int num_q_heads, int num_kv_heads, int head_dim, int rot_dim,
+                                                        int64_t q_stride, int64_t k_stride) {
+  const int64_t tok = blockIdx.x;
+  const int half = rot_dim / 2;
+  const float* cs = cos_sin + pos[tok] * rot_dim;
+  const int total = (num_q_heads + num_kv_heads) * half;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int h = i / half;
+    const int j = i - h * half;
+    T* base = h < num_q_heads ? q + tok * q_stride + (int64_t)h * head_dim
+                              : k + tok * k_stride + (int64_t)(h - num_q_heads) * head_dim;
+    const float c = cs[j], s = cs[half + j];
+    const float x1 = DT<T>::to_f(base[j]);
+    const float x2 = DT<T>::to_f(base[half + j]);
+    base[j] = DT<T>::from_f(x1 * c - x2 * s);
+    base[half + j] = DT<T>::from_f(x2 * c + x1 * s);
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+B200_API int b200_rmsnorm(void* out, void* residual, const void* x, const void* weight, int64_t M, int64_t H,
+                            float eps, int dtype, void* stream) {
+  B200_REQUIRE(M >= 0 && H > 0, "rmsnorm: bad sizes");
+  if (M == 0) return B200_OK;
+  B200_REQUIRE(out && x && weight, "rmsnorm: null pointer");
+  B200_REQUIRE(H % 8 == 0 && H <= 16384, "rmsnorm: H %lld must be a multiple of 8 and <= 16384", (long long)H);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t smem = (size_t)H * sizeof(float);
+  if (dtype == B200_BF16) {
+    auto kern = rmsnorm_kernel<__nv_bfloat16>;
+    if (smem > 48 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)M, 256, smem, st>>>((__nv_bfloat16*)out, (__nv_bfloat16*)residual, (const __nv_bfloat16*)x,
+                                        (const __nv_bfloat16*)weight, H, eps);
+  } else if (dtype == B200_F16) {
+    auto kern = rmsnorm_kernel<__half>;
+    if (smem > 48 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)M, 256, smem, st>>>((__half*)out, (__half*)residual, (const __half*)x, (const __half*)weight, H, eps);
+  } else {
+    return fail(B200_ERR_UNSUPPORTED, "rmsnorm: dtype %d not supported", dtype);
+  }
+  B200_LAUNCH_OK();
+  return B200_OK;
+}
+
+B200_API int b200_silu_and_mul(void* out, const void* x, int64_t M, int64_t H, int dtype, void* stream) {
+  B200_REQUIRE(M >= 0 && H > 0, "silu_and_mul: bad sizes");
+  if (M == 0) return B200_OK;
+  B200_REQUIRE(out && x, "silu_and_mul: null pointer");
+  B200_REQUIRE(H % 8 == 0, "silu_and_mul: H must be a multiple of 8");
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t blocks = ceil_div(M * (H / 8), 256);
+  const int64_t cap = (int64_t)sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  if (dtype == B200_BF16)
+    silu_and_mul_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>((__nv_bfloat16*)out, (const __nv_bfloat16*)x, M, H);
+  else if (dtype == B200_F16)
+    silu_and_mul_kernel<__half><<<(unsigned)blocks, 256, 0, st>>>((__half*)out, (const __half*)x, M, H);
+  else
+    return fail(B200_ERR_UNSUPPORTED, "silu_and_mul: dtype %d not supported", dtype);
+  B200_LAUNCH_OK();
+  return B200_OK;
+}
+
+B200_API int b200_rope_neox(void* q, void* k, const float* cos_sin_cache, const int64_t* positions,
+                              int64_t num_tokens, int num_q_heads, int num_kv_heads, int head_dim, int rot_dim,
+                              int64_t q_token_stride, int64_t k_token_stride, int dtype, void* stream) {
+  B200_REQUIRE(num_tokens >= 0, "rope_neox: bad sizes");
+  if (num_tokens == 0) return B200_OK;
+  B200_REQUIRE(q && k && cos_sin_cache && positions, "rope_neox: null pointer");
+  B200_REQUIRE(rot_dim % 2 == 0 && rot_dim <= head_dim, "rope_neox: rot_dim %d", rot_dim);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == B200_BF16)
+    rope_neox_kernel<__nv_bfloat16><<<(unsigned)num_tokens, 256, 0, st>>>((__nv_bfloat16*)q, (__nv_bfloat16*)k, cos_sin_cache,
+                                                                      positions, num_q_heads, num_kv_heads, head_dim, rot_dim,
+                                                                      q_token_stride, k_token_stride);
+  else if (dtype == B200_F16)
+    rope_neox_kernel<__half><<<(unsigned)num_tokens, 256, 0, st>>>((__half*)q, (__half*)k, cos_sin_cache, positions, num_q_heads,
+                                                               num_kv_heads, head_dim, rot_dim, q_token_stride, k_token_stride);
+  else
+    return fail(B200_ERR_UNSUPPORTED, "rope_neox: dtype %d not supported", dtype);
+  B200_LAUNCH_OK();
+  return B200_OK;
+}

@@ -1,0 +1,372 @@
+"""Python op wrappers over the C-ABI — the replacement for `sgl_kernel`'s Python layer
+(reference sgl-kernel/python/sgl_kernel/{gemm,attention,elementwise}.py).
+
+Names and argument meaning follow the reference ops so the layer code reads the same;
+outputs are allocated here with torch (ownership contract of SURVEY §8b) and the kernels
+are enqueued on the current CUDA stream.  No fallbacks: non-CUDA tensors raise.
+"""
+from __future__ import annotations
+
+from ctypes import byref, c_size_t
+from typing import Optional, Tuple
+
+import torch
+
+from . import _cabi
+from ._cabi import check, dtype_code, ptr, require_cuda, stream_ptr
+
+
+def _is64(t: torch.Tensor) -> int:
+    if t.dtype == torch.int64:
+        return 1
+    if t.dtype == torch.int32:
+        return 0
+    raise RuntimeError(f"index tensor must be int32 or int64, got {t.dtype}")
+
+
+# ---- KV write ------------------------------------------------------------------------------
+def set_kv_buffer(k_cache: torch.Tensor, v_cache: torch.Tensor, loc: torch.Tensor,
+                  cache_k: torch.Tensor, cache_v: torch.Tensor) -> None:
+    """k_cache[loc] = cache_k; v_cache[loc] = cache_v (memory_pool.py:369-407), one launch."""
+    require_cuda(k_cache, v_cache, loc, cache_k, cache_v)
+    lib = _cabi.load()
+    T = loc.numel()
+    if T == 0:
+        return
+    assert cache_k.shape[0] == T and cache_v.shape[0] == T
+    assert cache_k.dtype == k_cache.dtype and cache_v.dtype == v_cache.dtype
+    cache_k = cache_k.reshape(T, -1) if cache_k.dim() != 2 else cache_k
+    cache_v = cache_v.reshape(T, -1) if cache_v.dim() != 2 else cache_v
+    if cache_k.stride(-1) != 1:
+        cache_k = cache_k.contiguous()
+    if cache_v.stride(-1) != 1:
+        cache_v = cache_v.contiguous()
+    if not loc.is_contiguous():
+        loc = loc.contiguous()
+    kc = k_cache.view(k_cache.shape[0], -1)
+    vc = v_cache.view(v_cache.shape[0], -1)
+    assert kc.shape[1] == cache_k.shape[1] and vc.shape[1] == cache_v.shape[1]
+    check(lib.b200_set_kv_buffer(
+        ptr(kc), ptr(vc), ptr(cache_k), ptr(cache_v), ptr(loc), _is64(loc), T,
+        cache_k.shape[1], cache_v.shape[1], cache_k.stride(0), cache_v.stride(0),
+        kc.stride(0), vc.stride(0), k_cache.element_size(), stream_ptr(k_cache.device)),
+        "b200_set_kv_buffer")
+
+
+# ---- decode attention -------------------------------------------------------------------------
+def decode_attn_workspace_bytes(batch: int, num_q_heads: int, head_dim: int, max_splits: int) -> int:
+    lib = _cabi.load()
+    out = c_size_t(0)
+    check(lib.b200_decode_attn_workspace_bytes(batch, num_q_heads, head_dim, max_splits, byref(out)),
+          "b200_decode_attn_workspace_bytes")
+    return out.value
+
+
+def decode_attention_fwd(q: torch.Tensor, k_buffer: torch.Tensor, v_buffer: torch.Tensor,
+                         o: torch.Tensor, req_to_token: torch.Tensor,
+                         req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
+                         workspace: Optional[torch.Tensor], kv_chunk: int, max_splits: int,
+                         sm_scale: float, logit_cap: float = 0.0) -> None:
+    """q [bs, Hq, D]; k/v_buffer [slots, Hkv, D]; o [bs, Hq, D] (written)."""
+    require_cuda(q, k_buffer, v_buffer, o, req_to_token, req_pool_indices, seq_lens)
+    lib = _cabi.load()
+    bs, hq, d = q.shape
+    hkv = k_buffer.shape[1]
+    assert q.stride(2) == 1 and q.stride(1) == d and o.stride(2) == 1 and o.stride(1) == d
+    assert k_buffer.stride(2) == 1 and k_buffer.stride(1) == d and v_buffer.stride() == k_buffer.stride()
+    assert req_to_token.dtype == torch.int32 and req_to_token.stride(1) == 1
+    assert req_pool_indices.dtype == seq_lens.dtype
+    assert req_pool_indices.is_contiguous() and seq_lens.is_contiguous()
+    ws_bytes = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    check(lib.b200_decode_attn(
+        ptr(o), ptr(q), ptr(k_buffer), ptr(v_buffer), ptr(req_to_token), req_to_token.stride(0),
+        ptr(req_pool_indices), ptr(seq_lens), _is64(seq_lens), bs, hq, hkv, d,
+        q.stride(0), o.stride(0), k_buffer.stride(0), float(sm_scale), float(logit_cap),
+        int(kv_chunk), int(max_splits), ptr(workspace), ws_bytes, dtype_code(q.dtype),
+        stream_ptr(q.device)), "b200_decode_attn")
+
+
+# ---- extend attention -------------------------------------------------------------------------
+def extend_attention_fwd(q: torch.Tensor, k_new: Optional[torch.Tensor], v_new: Optional[torch.Tensor],
+                         o: torch.Tensor, k_buffer: torch.Tensor, v_buffer: torch.Tensor,
+                         req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+                         qo_indptr: torch.Tensor, prefix_lens: torch.Tensor, max_extend_len: int,
+                         sm_scale: float, logit_cap: float = 0.0, causal: bool = True) -> None:
+    """q [T, Hq, D]; k_new/v_new [T, Hkv, D] or None (read new keys from the cache)."""
+    require_cuda(q, o, k_buffer, v_buffer, req_to_token, req_pool_indices, qo_indptr, prefix_lens)
+    lib = _cabi.load()
+    T, hq, d = q.shape
+    hkv = k_buffer.shape[1]
+    bs = req_pool_indices.numel()
+    assert qo_indptr.dtype == torch.int32 and prefix_lens.dtype == torch.int32
+    assert q.stride(2) == 1 and q.stride(1) == d and o.stride(2) == 1 and o.stride(1) == d
+    kn_stride = vn_stride = 0
+    if k_new is not None:
+        assert k_new.stride(2) == 1 and k_new.stride(1) == d and v_new.stride(2) == 1 and v_new.stride(1) == d
+        kn_stride, vn_stride = k_new.stride(0), v_new.stride(0)
+    check(lib.b200_extend_attn(
+        ptr(o), ptr(q), ptr(k_new), ptr(v_new), ptr(k_buffer), ptr(v_buffer), ptr(req_to_token),
+        req_to_token.stride(0), ptr(req_pool_indices), _is64(req_pool_indices), ptr(qo_indptr),
+        ptr(prefix_lens), bs, int(max_extend_len), hq, hkv, d, q.stride(0), o.stride(0),
+        kn_stride, vn_stride, k_buffer.stride(0), float(sm_scale), float(logit_cap), int(causal),
+        dtype_code(q.dtype), stream_ptr(q.device)), "b200_extend_attn")
+
+
+# ---- LSE merge ---------------------------------------------------------------------------------
+def merge_state_v2(v_a: torch.Tensor, s_a: torch.Tensor, v_b: torch.Tensor, s_b: torch.Tensor,
+                   v_merged: Optional[torch.Tensor] = None, s_merged: Optional[torch.Tensor] = None
+                   ) -> Tuple[torch.Tensor, torch.Tensor]:
+    """sgl_kernel.merge_state_v2 (sgl-kernel/python/sgl_kernel/attention.py)."""
+    require_cuda(v_a, s_a, v_b, s_b)
+    lib = _cabi.load()
+    s_a = s_a.to(torch.float32).contiguous()
+    s_b = s_b.to(torch.float32).contiguous()
+    v_a, v_b = v_a.contiguous(), v_b.contiguous()
+    if v_merged is None:
+        v_merged = torch.empty_like(v_a)
+    if s_merged is None:
+        s_merged = torch.empty_like(s_a)
+    T, H, D = v_a.shape
+    check(lib.b200_merge_state(ptr(v_merged), ptr(s_merged), ptr(v_a), ptr(s_a), ptr(v_b), ptr(s_b),
+                               T, H, D, dtype_code(v_a.dtype), stream_ptr(v_a.device)), "b200_merge_state")
+    return v_merged, s_merged
+
+
+merge_state = merge_state_v2
+
+
+# ---- int8 ------------------------------------------------------------------------------------------
+def per_token_quant_int8(x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """int8_kernel.py:53-83 — returns (x_q int8 like x, scales fp32 [..., 1])."""
+    require_cuda(x)
+    lib = _cabi.load()
+    K = x.shape[-1]
+    x2 = x.reshape(-1, K)
+    if x2.stride(-1) != 1:
+        x2 = x2.contiguous()
+    M = x2.shape[0]
+    x_q = torch.empty((M, K), device=x.device, dtype=torch.int8)
+    scales = torch.empty((M, 1), device=x.device, dtype=torch.float32)
+    check(lib.b200_per_token_quant_int8(ptr(x_q), ptr(scales), ptr(x2), M, K, x2.stride(0),
+                                        dtype_code(x.dtype), stream_ptr(x.device)),
+          "b200_per_token_quant_int8")
+    return x_q.view(x.shape), scales.view(x.shape[:-1] + (1,))
+
+
+_INT8_WS = {}
+
+
+def _int8_workspace(device, nbytes: int) -> torch.Tensor:
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _INT8_WS.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.zeros(max(nbytes, 1), device=device, dtype=torch.uint8)
+        _INT8_WS[key] = ws
+    return ws
+
+
+def int8_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tensor,
+                   scales_b: torch.Tensor, out_dtype: torch.dtype,
+                   bias: Optional[torch.Tensor] = None, return_acc: bool = False):
+    """sgl_kernel.int8_scaled_mm (sgl-kernel/python/sgl_kernel/gemm.py:20-29).
+
+    mat_a [M,K] int8 row-major; mat_b [K,N] int8 COLUMN-major (weight.t()); scales fp32.
+    """
+    require_cuda(mat_a, mat_b, scales_a, scales_b)
+    lib = _cabi.load()
+    assert mat_a.dtype == torch.int8 and mat_b.dtype == torch.int8
+    if mat_a.dim() != 2 or mat_b.dim() != 2:
+        raise RuntimeError("int8_scaled_mm: mat_a and mat_b must be 2-D")
+    M, K = mat_a.shape
+    if mat_b.shape[0] != K:
+        raise RuntimeError("int8_scaled_mm: inner dimensions differ")
+    N = mat_b.shape[1]
+    if mat_a.stride(1) != 1 or mat_a.stride(0) != K:
+        raise RuntimeError("int8_scaled_mm: mat_a must be row-major contiguous")
+    if mat_b.stride(0) != 1 or mat_b.stride(1) != K:
+        raise RuntimeError("int8_scaled_mm: mat_b must be column-major (pass weight.t())")
+    if scales_a.numel() != M or scales_b.numel() != N:
+        raise RuntimeError("int8_scaled_mm: scale sizes do not match M / N")
+    scales_a = scales_a.to(torch.float32).contiguous()
+    scales_b = scales_b.to(torch.float32).contiguous()
+    if bias is not None:
+        assert bias.numel() == N and bias.dtype == out_dtype
+        bias = bias.contiguous()
+    out = torch.empty((M, N), device=mat_a.device, dtype=out_dtype)
+    acc = torch.empty((M, N), device=mat_a.device, dtype=torch.int32) if return_acc else None
+    need = c_size_t(0)
+    check(lib.b200_int8_scaled_mm_workspace_bytes(M, N, K, byref(need)), "b200_int8_scaled_mm_workspace_bytes")
+    ws = _int8_workspace(mat_a.device, need.value)
+    check(lib.b200_int8_scaled_mm(ptr(out), ptr(mat_a), ptr(mat_b), ptr(scales_a), ptr(scales_b),
+                                  ptr(bias), M, N, K, dtype_code(out_dtype), ptr(acc), ptr(ws),
+                                  ws.numel(), stream_ptr(mat_a.device)), "b200_int8_scaled_mm")
+    return (out, acc) if return_acc else out
+
+
+# ---- fp8 ---------------------------------------------------------------------------------------------
+def sgl_per_token_group_quant_fp8(x: torch.Tensor, group_size: int = 128, eps: float = 1e-10,
+                                  column_major_scales: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
+    """per_token_group_quant_fp8 (fp8_kernel.py:209-297): returns (x_q e4m3, x_s fp32 [M, K/G])."""
+    require_cuda(x)
+    lib = _cabi.load()
+    K = x.shape[-1]
+    x2 = x.reshape(-1, K)
+    if x2.stride(-1) != 1:
+        x2 = x2.contiguous()
+    M = x2.shape[0]
+    G = K // group_size
+    x_q = torch.empty((M, K), device=x.device, dtype=torch.float8_e4m3fn)
+    if column_major_scales:
+        x_s = torch.empty((G, M), device=x.device, dtype=torch.float32).t()
+    else:
+        x_s = torch.empty((M, G), device=x.device, dtype=torch.float32)
+    check(lib.b200_per_token_group_quant_fp8(ptr(x_q), ptr(x_s), ptr(x2), M, K, x2.stride(0), group_size,
+                                             float(eps), x_s.stride(0), x_s.stride(1), dtype_code(x.dtype),
+                                             stream_ptr(x.device)), "b200_per_token_group_quant_fp8")
+    return x_q.view(x.shape), x_s.view(x.shape[:-1] + (G,)) if not column_major_scales else x_s
+
+
+def sgl_per_token_quant_fp8(x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    require_cuda(x)
+    lib = _cabi.load()
+    K = x.shape[-1]
+    x2 = x.reshape(-1, K)
+    if x2.stride(-1) != 1:
+        x2 = x2.contiguous()
+    M = x2.shape[0]
+    x_q = torch.empty((M, K), device=x.device, dtype=torch.float8_e4m3fn)
+    x_s = torch.empty((M, 1), device=x.device, dtype=torch.float32)
+    check(lib.b200_per_token_quant_fp8(ptr(x_q), ptr(x_s), ptr(x2), M, K, x2.stride(0), dtype_code(x.dtype),
+                                       stream_ptr(x.device)), "b200_per_token_quant_fp8")
+    return x_q.view(x.shape), x_s
+
+
+def fp8_blockwise_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tensor,
+                            scales_b: torch.Tensor, out_dtype: torch.dtype,
+                            bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """sgl_kernel.fp8_blockwise_scaled_mm (gemm.py:32-42): mat_a [M,K] e4m3 row-major, mat_b [K,N]
+    e4m3 column-major (weight.T), scales_a [M, K/128], scales_b [K/128, N/128] (weight_scale.T)."""
+    require_cuda(mat_a, mat_b, scales_a, scales_b)
+    lib = _cabi.load()
+    M, K = mat_a.shape
+    N = mat_b.shape[1]
+    if mat_b.shape[0] != K or mat_b.stride(0) != 1 or mat_b.stride(1) != K:
+        raise RuntimeError("fp8_blockwise_scaled_mm: mat_b must be [K,N] column-major")
+    if mat_a.stride(1) != 1 or mat_a.stride(0) != K:
+        raise RuntimeError("fp8_blockwise_scaled_mm: mat_a must be row-major contiguous")
+    if scales_a.shape != (M, K // 128) or scales_b.shape != (K // 128, N // 128):
+        raise RuntimeError("fp8_blockwise_scaled_mm: scale shapes must be [M,K/128] and [K/128,N/128]")
+    assert scales_a.dtype == torch.float32 and scales_b.dtype == torch.float32
+    out = torch.empty((M, N), device=mat_a.device, dtype=out_dtype)
+    if bias is not None:
+        bias = bias.to(out_dtype).contiguous()
+    # kernel wants scale_b indexed [n_block, k_block]
+    check(lib.b200_fp8_blockwise_scaled_mm(
+        ptr(out), ptr(mat_a), ptr(mat_b), ptr(scales_a), scales_a.stride(0), scales_a.stride(1),
+        ptr(scales_b), scales_b.stride(1), scales_b.stride(0), ptr(bias), M, N, K,
+        dtype_code(out_dtype), stream_ptr(mat_a.device)), "b200_fp8_blockwise_scaled_mm")
+    return out
+
+
+def fp8_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tensor,
+                  scales_b: torch.Tensor, out_dtype: torch.dtype,
+                  bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """sgl_kernel.fp8_scaled_mm: per-token x per-channel scaled e4m3 GEMM."""
+    require_cuda(mat_a, mat_b, scales_a, scales_b)
+    lib = _cabi.load()
+    M, K = mat_a.shape
+    N = mat_b.shape[1]
+    if mat_b.shape[0] != K or mat_b.stride(0) != 1 or mat_b.stride(1) != K:
+        raise RuntimeError("fp8_scaled_mm: mat_b must be [K,N] column-major")
+    scales_a = scales_a.to(torch.float32).contiguous()
+    scales_b = scales_b.to(torch.float32).contiguous()
+    out = torch.empty((M, N), device=mat_a.device, dtype=out_dtype)
+    if bias is not None:
+        bias = bias.to(out_dtype).contiguous()
+    check(lib.b200_fp8_scaled_mm(ptr(out), ptr(mat_a), ptr(mat_b), ptr(scales_a), ptr(scales_b), ptr(bias),
+                                 M, N, K, dtype_code(out_dtype), stream_ptr(mat_a.device)), "b200_fp8_scaled_mm")
+    return out
+
+
+# ---- AWQ -----------------------------------------------------------------------------------------------
+def awq_dequantize(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> torch.Tensor:
+    """sgl_kernel.awq_dequantize (gemm.py:7-10): returns W [K, N] in the dtype of `scales`."""
+    require_cuda(qweight, scales, qzeros)
+    lib = _cabi.load()
+    K, n8 = qweight.shape
+    N = n8 * 8
+    G = K // qzeros.shape[0]
+    assert qweight.dtype == torch.int32 and qzeros.dtype == torch.int32
+    assert qweight.is_contiguous() and qzeros.is_contiguous() and scales.is_contiguous()
+    out = torch.empty((K, N), device=qweight.device, dtype=scales.dtype)
+    check(lib.b200_awq_dequantize(ptr(out), ptr(qweight), ptr(scales), ptr(qzeros), K, N, G,
+                                  dtype_code(scales.dtype), stream_ptr(qweight.device)), "b200_awq_dequantize")
+    return out
+
+
+def awq_gemm(x: torch.Tensor, qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor,
+             bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Fused dequant + matmul: x [M,K] @ W(qweight, scales, qzeros) [K,N] (+bias) (awq.py:401-418)."""
+    require_cuda(x, qweight, scales, qzeros)
+    lib = _cabi.load()
+    K, n8 = qweight.shape
+    N = n8 * 8
+    G = K // qzeros.shape[0]
+    x2 = x.reshape(-1, K).contiguous()
+    M = x2.shape[0]
+    assert x.dtype == scales.dtype
+    out = torch.empty((M, N), device=x.device, dtype=x.dtype)
+    if bias is not None:
+        bias = bias.to(x.dtype).contiguous()
+    check(lib.b200_awq_gemm(ptr(out), ptr(x2), ptr(qweight), ptr(scales), ptr(qzeros), ptr(bias), M, N, K, G,
+                            dtype_code(x.dtype), stream_ptr(x.device)), "b200_awq_gemm")
+    return out
+
+
+# ---- element-wise ----------------------------------------------------------------------------------------
+def rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float) -> torch.Tensor:
+    require_cuda(x, weight)
+    lib = _cabi.load()
+    H = x.shape[-1]
+    x2 = x.reshape(-1, H).contiguous()
+    out = torch.empty_like(x2)
+    check(lib.b200_rmsnorm(ptr(out), None, ptr(x2), ptr(weight), x2.shape[0], H, float(eps),
+                           dtype_code(x.dtype), stream_ptr(x.device)), "b200_rmsnorm")
+    return out.view(x.shape)
+
+
+def fused_add_rmsnorm(x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, eps: float) -> None:
+    """In place like sgl_kernel.fused_add_rmsnorm: residual += x; x = rmsnorm(residual) * weight."""
+    require_cuda(x, residual, weight)
+    lib = _cabi.load()
+    H = x.shape[-1]
+    assert x.is_contiguous() and residual.is_contiguous()
+    check(lib.b200_rmsnorm(ptr(x), ptr(residual), ptr(x), ptr(weight), x.numel() // H, H, float(eps),
+                           dtype_code(x.dtype), stream_ptr(x.device)), "b200_rmsnorm")
+
+
+def silu_and_mul(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    require_cuda(x)
+    lib = _cabi.load()
+    H = x.shape[-1] // 2
+    x2 = x.reshape(-1, 2 * H).contiguous()
+    if out is None:
+        out = torch.empty(x.shape[:-1] + (H,), device=x.device, dtype=x.dtype)
+    check(lib.b200_silu_and_mul(ptr(out), ptr(x2), x2.shape[0], H, dtype_code(x.dtype), stream_ptr(x.device)),
+          "b200_silu_and_mul")
+    return out
+
+
+def apply_rope_neox_inplace(positions: torch.Tensor, q: torch.Tensor, k: torch.Tensor, head_dim: int,
+                            cos_sin_cache: torch.Tensor) -> None:
+    """q [T, Hq*D], k [T, Hkv*D] (may be strided views of a fused qkv), rotated in place."""
+    require_cuda(positions, q, k, cos_sin_cache)
+    lib = _cabi.load()
+    assert positions.dtype == torch.int64 and cos_sin_cache.dtype == torch.float32
+    T = q.shape[0]
+    hq = q.shape[-1] // head_dim
+    hkv = k.shape[-1] // head_dim
+    rot = cos_sin_cache.shape[-1]
+    assert q.stride(-1) == 1 and k.stride(-1) == 1
+    check(lib.b200_rope_neox(ptr(q), ptr(k), ptr(cos_sin_cache), ptr(positions), T, hq, hkv, head_dim, rot,
+                             q.stride(0), k.stride(0), dtype_code(q.dtype), stream_ptr(q.device)), "b200_rope_neox")

@@ -1,0 +1,214 @@
+"""B200AttnBackend — the drop-in `AttentionBackend` for `--attention-backend b200`.
+
+Boundary: reference python/sglang/srt/layers/attention/base_attn_backend.py:14-117 (interface),
+triton_backend.py:41-122 / :160-336 / :338-627 / :632-732 (the backend this replaces on GPU),
+torch_native_backend.py:182-267 (the oracle's semantics).
+
+Differences from the Triton backend that matter to a maintainer:
+  * no CSR `kv_indices` rebuild per step: the kernels read `req_to_token` rows directly, so
+    `init_forward_metadata` for decode only picks the split-KV chunking (no kernel launch,
+    no host sync) and CUDA-graph replay needs no metadata refresh at all;
+  * `set_kv_buffer` is one fused scatter launch;
+  * there is no Triton / FlashInfer / CPU fallback: tensors must live on a CUDA device.
+"""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from .... import kernels
+from .base_attn_backend import AttentionBackend
+
+_NUM_RESIDENT_CTAS_PER_SM = 2  # decode kernel: __launch_bounds__(128, 2), ~100 KiB smem per CTA
+
+
+@dataclass
+class ForwardMetadata:
+    # decode
+    kv_chunk: int = 0
+    max_splits: int = 0
+    workspace: Optional[torch.Tensor] = None
+    # extend
+    qo_indptr: Optional[torch.Tensor] = None
+    prefix_lens: Optional[torch.Tensor] = None
+    max_extend_len: int = 0
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+def plan_decode_splits(batch: int, num_kv_heads: int, group: int, max_len: int, sm_count: int,
+                       forced_chunk: int = 0):
+    """Pick (kv_chunk, max_splits) for the split-KV decode kernel.
+
+    One CTA handles one (request, KV head, <=16 q heads, chunk); aim for ~8 waves of the
+    2 x SM-count resident CTAs, with chunks of 256..2048 tokens (multiples of 16), and
+    make the chunks of the longest request even.  Pure host arithmetic (graph-safe).
+    """
+    max_len = max(int(max_len), 1)
+    if forced_chunk > 0:
+        chunk = _round_up(forced_chunk, 16)
+    else:
+        units = max(batch * num_kv_heads * ((group + 15) // 16), 1)
+        target = sm_count * _NUM_RESIDENT_CTAS_PER_SM * 8
+        chunk = _round_up(max(max_len * units // target, 1), 64)
+        chunk = min(max(chunk, 256), 2048)
+        splits = (max_len + chunk - 1) // chunk
+        chunk = min(_round_up((max_len + splits - 1) // splits, 16), 2048)
+    chunk = max(16, min(chunk, 4096))
+    return chunk, (max_len + chunk - 1) // chunk
+
+
+class B200AttnBackend(AttentionBackend):
+    def __init__(self, model_runner, skip_prefill: bool = False):
+        super().__init__()
+        self.device = torch.device(model_runner.device)
+        if self.device.type != "cuda":
+            raise RuntimeError("B200AttnBackend requires a CUDA device (no CPU fallback in this backend)")
+        kernels._cabi.load()  # fail loudly at construction if the extension is missing
+        self.skip_prefill = skip_prefill
+        self.req_to_token = model_runner.req_to_token_pool.req_to_token
+        tp = getattr(model_runner, "tp_size", 1) or 1
+        cfg = model_runner.model_config
+        self.num_head = cfg.num_attention_heads // tp
+        self.num_kv_head = cfg.get_num_kv_heads(tp)
+        self.max_context_len = cfg.context_len
+        self.sliding_window_size = getattr(model_runner, "sliding_window_size", None)
+        self.head_dim = model_runner.token_to_kv_pool.get_key_buffer(0).shape[-1]
+        self.v_head_dim = model_runner.token_to_kv_pool.get_value_buffer(0).shape[-1]
+        if self.v_head_dim != self.head_dim:
+            raise NotImplementedError("B200AttnBackend: v_head_dim != head_dim (MLA-style) is out of scope")
+        self.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
+        self.forced_chunk = int(os.environ.get("B200_DECODE_KV_CHUNK", "0"))
+        self.forward_metadata: Optional[ForwardMetadata] = None
+        self._workspace: Optional[torch.Tensor] = None
+        self._graph_workspace: Optional[torch.Tensor] = None
+        self._graph_max_bs = 0
+        max_bs = model_runner.req_to_token_pool.size
+        self.qo_indptr = torch.zeros((max_bs + 1,), dtype=torch.int32, device=self.device)
+
+    # ---- metadata -------------------------------------------------------------------------
+    def _decode_workspace(self, bs: int, max_splits: int, graph: bool = False) -> Optional[torch.Tensor]:
+        if max_splits <= 1:
+            return None
+        need = kernels.decode_attn_workspace_bytes(bs, self.num_head, self.head_dim, max_splits)
+        cur = self._graph_workspace if graph else self._workspace
+        if cur is None or cur.numel() < need:
+            cur = torch.empty(need, dtype=torch.uint8, device=self.device)
+            if graph:
+                self._graph_workspace = cur
+            else:
+                self._workspace = cur
+        return cur
+
+    def init_forward_metadata(self, forward_batch):
+        mode = forward_batch.forward_mode
+        bs = forward_batch.batch_size
+        group = self.num_head // self.num_kv_head
+        if mode.is_decode_or_idle():
+            if forward_batch.seq_lens_cpu is not None:
+                max_len = int(forward_batch.seq_lens_cpu.max()) if bs > 0 else 1
+            else:
+                max_len = self.max_context_len  # no host sync: plan for the worst case
+            chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, max_len, self.sm_count,
+                                               self.forced_chunk)
+            self.forward_metadata = ForwardMetadata(kv_chunk=chunk, max_splits=splits,
+                                                    workspace=self._decode_workspace(bs, splits))
+        else:
+            ext = forward_batch.extend_seq_lens
+            qo_indptr = self.qo_indptr[: bs + 1]
+            qo_indptr[1:] = torch.cumsum(ext, dim=0)
+            if forward_batch.extend_seq_lens_cpu is not None:
+                max_extend = max(forward_batch.extend_seq_lens_cpu) if bs > 0 else 0
+            else:
+                max_extend = int(ext.max().item())  # same host sync as triton_backend.py:325
+            self.forward_metadata = ForwardMetadata(
+                qo_indptr=qo_indptr,
+                prefix_lens=forward_batch.extend_prefix_lens.to(torch.int32),
+                max_extend_len=int(max_extend))
+
+    # ---- CUDA graphs (base_attn_backend.py:22-55; cuda_graph_runner.py:283-288, :642, :773) --------
+    def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
+        self._graph_max_bs = max_bs
+        group = self.num_head // self.num_kv_head
+        _, splits = plan_decode_splits(1, self.num_kv_head, group, self.max_context_len, self.sm_count,
+                                       self.forced_chunk)
+        self._decode_workspace(max_bs, max(splits, 2), graph=True)
+
+    def init_forward_metadata_capture_cuda_graph(self, bs: int, num_tokens: int, req_pool_indices, seq_lens,
+                                                 encoder_lens, forward_mode, spec_info):
+        if not forward_mode.is_decode_or_idle():
+            raise NotImplementedError("B200AttnBackend: CUDA graphs are captured for DECODE only")
+        group = self.num_head // self.num_kv_head
+        chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, self.max_context_len, self.sm_count,
+                                           self.forced_chunk)
+        self.forward_metadata = ForwardMetadata(kv_chunk=chunk, max_splits=splits,
+                                                workspace=self._decode_workspace(bs, splits, graph=True))
+
+    def init_forward_metadata_replay_cuda_graph(self, bs: int, req_pool_indices, seq_lens, seq_lens_sum: int,
+                                                encoder_lens, forward_mode, spec_info, seq_lens_cpu):
+        # Nothing to refresh: the captured kernels read req_pool_indices / seq_lens / req_to_token
+        # from the graph runner's static tensors, and the chunking was fixed at capture.
+        return
+
+    def get_cuda_graph_seq_len_fill_value(self):
+        return 1
+
+    # ---- per-layer entry points -----------------------------------------------------------------
+    def _save_kv(self, layer, forward_batch, k, v):
+        pool = forward_batch.token_to_kv_pool
+        kb = pool.get_key_buffer(layer.layer_id)
+        if k.dtype == kb.dtype and layer.k_scale is None:
+            kernels.set_kv_buffer(kb, pool.get_value_buffer(layer.layer_id), forward_batch.out_cache_loc, k, v)
+        else:  # dtype conversion / scaling rules live in the pool (memory_pool.py:385-391)
+            pool.set_kv_buffer(layer, forward_batch.out_cache_loc, k, v, layer.k_scale, layer.v_scale)
+
+    def _check_layer(self, layer):
+        if layer.sliding_window_size is not None and layer.sliding_window_size > -1:
+            raise NotImplementedError("B200AttnBackend: sliding-window attention is out of scope")
+        if layer.qk_head_dim != layer.v_head_dim:
+            raise NotImplementedError("B200AttnBackend: qk_head_dim != v_head_dim is out of scope")
+
+    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+        self._check_layer(layer)
+        q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
+        o = torch.empty_like(q)
+        if save_kv_cache:
+            self._save_kv(layer, forward_batch, k, v)
+        md = self.forward_metadata
+        pool = forward_batch.token_to_kv_pool
+        kernels.decode_attention_fwd(
+            q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
+            pool.get_key_buffer(layer.layer_id), pool.get_value_buffer(layer.layer_id),
+            o.view(-1, layer.tp_q_head_num, layer.v_head_dim),
+            forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
+            forward_batch.seq_lens, md.workspace, md.kv_chunk, md.max_splits,
+            layer.scaling, layer.logit_cap or 0.0)
+        return o
+
+    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+        self._check_layer(layer)
+        q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
+        o = torch.empty_like(q)
+        if save_kv_cache:
+            self._save_kv(layer, forward_batch, k, v)
+        md = self.forward_metadata
+        pool = forward_batch.token_to_kv_pool
+        causal = not (layer.is_cross_attention or getattr(layer.attn_type, "value", "") == "encoder_only")
+        kernels.extend_attention_fwd(
+            q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
+            None if save_kv_cache else k.view(-1, layer.tp_k_head_num, layer.qk_head_dim),
+            None if save_kv_cache else v.view(-1, layer.tp_v_head_num, layer.v_head_dim),
+            o.view(-1, layer.tp_q_head_num, layer.v_head_dim),
+            pool.get_key_buffer(layer.layer_id), pool.get_value_buffer(layer.layer_id),
+            forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
+            md.qo_indptr, md.prefix_lens, md.max_extend_len,
+            layer.scaling, layer.logit_cap or 0.0, causal)
+        return o
+
+    def support_triton(self):
+        return False
