@@ -5,12 +5,6 @@ using namespace b200;
 #define PENDING(name) return fail(B200_ERR_UNSUPPORTED, name ": kernel not built in this revision")
 #define API B200_API
 
-B200_API int b200_int8_scaled_mm_workspace_bytes(int64_t, int64_t, int64_t, size_t* bytes) {
-  if (bytes) *bytes = 0;
-  return B200_OK;
-}
-B200_API int b200_int8_scaled_mm(void*, const int8_t*, const int8_t*, const float*, const float*, const void*, int64_t,
-                            int64_t, int64_t, int, int32_t*, void*, size_t, void*) { PENDING("int8_scaled_mm"); }
 B200_API int b200_fp8_blockwise_scaled_mm(void*, const void*, const void*, const float*, int64_t, int64_t, const float*,
                                      int64_t, int64_t, const void*, int64_t, int64_t, int64_t, int, void*) {
   PENDING("fp8_blockwise_scaled_mm");

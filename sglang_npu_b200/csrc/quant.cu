@@ -57,7 +57,9 @@ __global__ void __launch_bounds__(256) per_token_quant_int8_kernel(int8_t* __res
     for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(f[i]));
   }
   amax = fmaxf(block_max<256>(amax, sm), 1e-10f);
-  const float inv = __fdiv_rn(127.f, amax);
+  // torch evaluates `127 / absmax` as reciprocal(absmax) * 127 (Tensor.__rtruediv__), i.e. two
+  // roundings; the oracle (test/srt/cpu/utils.py:24-32 run by torch) fixes that rule, so do the same.
+  const float inv = __fmul_rn(__frcp_rn(amax), 127.f);
   if (threadIdx.x == 0) scale[row] = __fdiv_rn(amax, 127.f);
   int8_t* qr = xq + row * K;
   for (int64_t c = threadIdx.x * 8; c < K; c += 256 * 8) {

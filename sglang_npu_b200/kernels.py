@@ -157,7 +157,9 @@ _INT8_WS = {}
 
 
 def _int8_workspace(device, nbytes: int) -> torch.Tensor:
-    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    # One self-cleaning split-K workspace per device: int8 GEMMs of one process are stream-ordered on the
+    # forward stream (as in the reference's single-threaded TP worker); allocate it before graph capture.
+    key = device.index
     ws = _INT8_WS.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.zeros(max(nbytes, 1), device=device, dtype=torch.uint8)

@@ -1,0 +1,58 @@
+"""Tensor-parallel group state and the TP collectives the hot path calls
+(reference python/sglang/srt/distributed/parallel_state.py:463-567, communication_op.py:11-13).
+
+One process per GPU; the group is `torch.distributed`'s default (NCCL over NVLink/NVSwitch on the
+GPU box, gloo in the CPU tests).  At decode sizes the o_proj/down_proj all-reduce is latency bound;
+NCCL's in-place ncclAllReduce on the compute stream is CUDA-graph capturable like the reference's
+PyNccl path.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+_TP_GROUP = None
+_TP_RANK = 0
+_TP_SIZE = 1
+
+
+def init_tensor_parallel(group=None):
+    """Adopt an initialised torch.distributed process group as the TP group."""
+    global _TP_GROUP, _TP_RANK, _TP_SIZE
+    if not dist.is_initialized():
+        _TP_GROUP, _TP_RANK, _TP_SIZE = None, 0, 1
+        return
+    _TP_GROUP = group if group is not None else dist.group.WORLD
+    _TP_RANK = dist.get_rank(_TP_GROUP)
+    _TP_SIZE = dist.get_world_size(_TP_GROUP)
+
+
+def destroy_tensor_parallel():
+    global _TP_GROUP, _TP_RANK, _TP_SIZE
+    _TP_GROUP, _TP_RANK, _TP_SIZE = None, 0, 1
+
+
+def get_tensor_model_parallel_rank() -> int:
+    return _TP_RANK
+
+
+def get_tensor_model_parallel_world_size() -> int:
+    return _TP_SIZE
+
+
+def tensor_model_parallel_all_reduce(x: torch.Tensor) -> torch.Tensor:
+    """In-place sum over the TP group (communication_op.py:11-13)."""
+    if _TP_SIZE == 1:
+        return x
+    dist.all_reduce(x, op=dist.ReduceOp.SUM, group=_TP_GROUP)
+    return x
+
+
+def tensor_model_parallel_all_gather(x: torch.Tensor, dim: int = -1) -> torch.Tensor:
+    if _TP_SIZE == 1:
+        return x
+    if dim < 0:
+        dim += x.dim()
+    parts = [torch.empty_like(x) for _ in range(_TP_SIZE)]
+    dist.all_gather(parts, x.contiguous(), group=_TP_GROUP)
+    return torch.cat(parts, dim=dim)

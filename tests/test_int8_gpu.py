@@ -1,0 +1,80 @@
+"""GPU parity for the W8A8-int8 linear path: per-token quant codes and int32 accumulators bit-exact,
+bf16 outputs within the north_star tolerance (shape grid after sgl-kernel/tests/test_int8_gemm.py:36-42
+and test/srt/cpu/test_gemm.py:83-126)."""
+import pytest
+import torch
+
+from oracle import quant_oracle as qo
+from sglang_npu_b200 import kernels, synth
+from tests.util import assert_close_path
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("M,K", [(1, 512), (7, 896), (64, 4096), (33, 14336), (300, 1024)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_per_token_quant_int8_bit_exact(cuda_device, M, K, dtype):
+    x = synth.activations(M, K, dtype, seed=M + K)
+    x[0, :8] = 0  # exercise exact zeros / ties
+    if M > 2:
+        x[2] = 0  # all-zero row -> absmax clamp 1e-10
+    xq, xs = kernels.per_token_quant_int8(x.to(cuda_device))
+    rq, rs = qo.per_token_quant_int8(x)
+    assert torch.equal(xq.cpu(), rq)
+    assert torch.equal(xs.cpu().view(torch.int32), rs.view(torch.int32))
+
+
+def _run_mm(dev, M, N, K, with_bias, out_dtype, seed=0):
+    g = torch.Generator().manual_seed(seed + M * 7 + N * 3 + K)
+    a = torch.randint(-127, 128, (M, K), generator=g, dtype=torch.int32).to(torch.int8)
+    w = torch.randint(-127, 128, (N, K), generator=g, dtype=torch.int32).to(torch.int8)
+    sa = torch.rand((M,), generator=g) * 1e-2
+    sb = torch.rand((N,), generator=g) * 1e-2
+    bias = (torch.randn((N,), generator=g) * 10).to(out_dtype) if with_bias else None
+    out, acc = kernels.int8_scaled_mm(a.to(dev), w.to(dev).t(), sa.to(dev), sb.to(dev), out_dtype,
+                                      bias.to(dev) if with_bias else None, return_acc=True)
+    torch.cuda.synchronize()
+    ref_acc = qo.int8_accumulate(a, w)
+    ref = qo.int8_scaled_mm(a, w, sa, sb, out_dtype, bias)
+    return out.cpu(), acc.cpu(), ref, ref_acc
+
+
+# decode (weight-streaming, split-K) shapes incl. ragged M / N / K tails
+@pytest.mark.parametrize("M", [1, 5, 16, 17, 64, 100, 128, 256])
+@pytest.mark.parametrize("N,K", [(16, 512), (1152, 896), (896, 4864), (6144, 4096), (4096, 14336), (136, 144)])
+def test_int8_scaled_mm_decode_shapes(cuda_device, M, N, K):
+    out, acc, ref, ref_acc = _run_mm(cuda_device, M, N, K, with_bias=(M % 2 == 1), out_dtype=torch.bfloat16)
+    assert torch.equal(acc, ref_acc), "int32 accumulators must be bit-exact"
+    # fp32 epilogue in the oracle's order, one rounding to bf16: bit-exact as well
+    assert torch.equal(out.view(torch.int16), ref.view(torch.int16))
+
+
+@pytest.mark.parametrize("M", [257, 512, 1000, 2048])
+@pytest.mark.parametrize("N,K", [(128, 512), (6144, 4096), (264, 1040), (28672, 4096)])
+def test_int8_scaled_mm_prefill_shapes(cuda_device, M, N, K):
+    out, acc, ref, ref_acc = _run_mm(cuda_device, M, N, K, with_bias=(N == 264), out_dtype=torch.float16)
+    assert torch.equal(acc, ref_acc), "int32 accumulators must be bit-exact"
+    assert torch.equal(out.view(torch.int16), ref.view(torch.int16))
+
+
+def test_int8_split_k_workspace_is_self_cleaning(cuda_device):
+    """Back-to-back calls reuse the split-K workspace; results must not drift."""
+    for i in range(3):
+        out, acc, ref, ref_acc = _run_mm(cuda_device, 64, 4096, 4096, False, torch.bfloat16, seed=i)
+        assert torch.equal(acc, ref_acc)
+
+
+def test_int8_argument_errors(cuda_device):
+    dev = cuda_device
+    a = torch.zeros((4, 24), dtype=torch.int8, device=dev)
+    w = torch.zeros((16, 24), dtype=torch.int8, device=dev)
+    s = torch.ones(4, device=dev)
+    with pytest.raises(RuntimeError, match="multiple of 16"):
+        kernels.int8_scaled_mm(a, w.t(), s, torch.ones(16, device=dev), torch.bfloat16)
+    a = torch.zeros((4, 32), dtype=torch.int8, device=dev)
+    with pytest.raises(RuntimeError, match="column-major"):
+        kernels.int8_scaled_mm(a, torch.zeros((32, 16), dtype=torch.int8, device=dev), s, torch.ones(16, device=dev),
+                               torch.bfloat16)
+    with pytest.raises(NotImplementedError):
+        kernels.int8_scaled_mm(a, torch.zeros((16, 32), dtype=torch.int8, device=dev).t(), s,
+                               torch.ones(16, device=dev), torch.float32)
