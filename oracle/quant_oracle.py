@@ -58,11 +58,15 @@ def w8a8_int8_linear(x: torch.Tensor, w_q: torch.Tensor, w_scale: torch.Tensor,
 # ---- block-scaled FP8 ----------------------------------------------------------------------------
 def per_token_group_quant_fp8(x: torch.Tensor, group_size: int = 128, eps: float = 1e-10,
                               dtype: torch.dtype = torch.float8_e4m3fn) -> Tuple[torch.Tensor, torch.Tensor]:
-    """native_per_token_group_quant_fp8 (python/sglang/test/test_block_fp8.py:24-49)."""
+    """native_per_token_group_quant_fp8 (python/sglang/test/test_block_fp8.py:24-49), with ONE rule fixed:
+    the eps clamp is applied in fp32 as the reference's kernels do (fp8_kernel.py:145-150 loads y as fp32 and
+    takes max(absmax, eps); per_token_group_quant_8bit.cu likewise).  The test restatement clamps in the input
+    dtype, which only differs for all-zero groups (bf16 rounds eps to 1.0004e-10; fp16 flushes it to 0 and the
+    restatement then produces NaN codes)."""
     assert x.shape[-1] % group_size == 0 and x.is_contiguous()
     finfo = torch.finfo(dtype)
     x_ = x.reshape(x.numel() // group_size, group_size)
-    amax = x_.abs().max(dim=-1, keepdim=True)[0].clamp(min=eps).to(torch.float32)
+    amax = x_.abs().max(dim=-1, keepdim=True)[0].to(torch.float32).clamp(min=eps)
     x_s = amax / finfo.max
     x_q = (x_ / x_s).clamp(min=finfo.min, max=finfo.max).to(dtype)
     return x_q.reshape(x.shape), x_s.reshape(x.shape[:-1] + (x.shape[-1] // group_size,))

@@ -5,12 +5,6 @@ using namespace b200;
 #define PENDING(name) return fail(B200_ERR_UNSUPPORTED, name ": kernel not built in this revision")
 #define API B200_API
 
-B200_API int b200_fp8_blockwise_scaled_mm(void*, const void*, const void*, const float*, int64_t, int64_t, const float*,
-                                     int64_t, int64_t, const void*, int64_t, int64_t, int64_t, int, void*) {
-  PENDING("fp8_blockwise_scaled_mm");
-}
-B200_API int b200_fp8_scaled_mm(void*, const void*, const void*, const float*, const float*, const void*, int64_t, int64_t,
-                           int64_t, int, void*) { PENDING("fp8_scaled_mm"); }
 B200_API int b200_awq_dequantize(void*, const int32_t*, const void*, const int32_t*, int64_t, int64_t, int, int, void*) {
   PENDING("awq_dequantize");
 }

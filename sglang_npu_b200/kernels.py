@@ -13,7 +13,33 @@ from typing import Optional, Tuple
 import torch
 
 from . import _cabi
-from ._cabi import check, dtype_code, ptr, require_cuda, stream_ptr
+from ._cabi import check as _check, dtype_code, ptr, require_cuda, stream_ptr
+
+
+_LAUNCHES = 0
+_KERNELS_PER_CALL = {"b200_decode_attn": 2, "b200_decode_attn_workspace_bytes": 0,
+                     "b200_int8_scaled_mm_workspace_bytes": 0}
+
+
+def check(status: int, what: str) -> None:
+    _check(status, what)
+    _count(_KERNELS_PER_CALL.get(what, 1))
+
+
+
+def reset_launch_count() -> None:
+    global _LAUNCHES
+    _LAUNCHES = 0
+
+
+def launch_count() -> int:
+    """Number of kernels of THIS library launched through the wrappers since the last reset."""
+    return _LAUNCHES
+
+
+def _count(n: int = 1) -> None:
+    global _LAUNCHES
+    _LAUNCHES += n
 
 
 def _is64(t: torch.Tensor) -> int:
