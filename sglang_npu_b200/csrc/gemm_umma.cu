@@ -388,7 +388,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 struct TmapKey {
   const void* p;
   uint64_t rows, kbytes;
-  uint32_t box;
+  uint32_t box;  // box_rows | box_bytes << 12 | swizzle << 20
   bool operator==(const TmapKey& o) const { return p == o.p && rows == o.rows && kbytes == o.kbytes && box == o.box; }
 };
 struct TmapKeyHash {
@@ -397,15 +397,16 @@ struct TmapKeyHash {
   }
 };
 
-int cached_tmap(CUtensorMap* out, const void* base, uint64_t rows, uint64_t kbytes, uint32_t box_rows) {
+int cached_tmap(CUtensorMap* out, const void* base, uint64_t rows, uint64_t kbytes, uint32_t box_rows, uint32_t box_bytes,
+                uint32_t swizzle_bytes) {
   static thread_local std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> cache;
-  TmapKey key{base, rows, kbytes, box_rows};
+  TmapKey key{base, rows, kbytes, box_rows | (box_bytes << 12) | (swizzle_bytes << 20)};
   auto it = cache.find(key);
   if (it != cache.end()) {
     *out = it->second;
     return B200_OK;
   }
-  int st = make_tmap_2d_bytes(out, base, rows, kbytes, kbytes, box_rows);
+  int st = make_tmap_2d_bytes(out, base, rows, kbytes, kbytes, box_rows, box_bytes, swizzle_bytes);
   if (st != B200_OK) return st;
   if (cache.size() > 4096) cache.clear();
   cache.emplace(key, *out);

@@ -172,8 +172,12 @@ typedef CUresult (*cuTensorMapEncodeTiled_t)(CUtensorMap*, CUtensorMapDataType, 
                                              CUtensorMapFloatOOBfill);
 cuTensorMapEncodeTiled_t get_tensor_map_encoder();
 
-// 2-D row-major byte matrix [rows, row_bytes] (row pitch `pitch_bytes`), box = [box_rows, 128 B], 128B swizzle.
+// 2-D row-major byte matrix [rows, row_bytes] (row pitch `pitch_bytes`), box = [box_rows, box_bytes],
+// swizzle span 128 / 64 / 32 bytes (0 = none).  Default: the UMMA operand tile (128 B rows, 128B swizzle).
 int make_tmap_2d_bytes(CUtensorMap* out, const void* base, uint64_t rows, uint64_t row_bytes, uint64_t pitch_bytes,
-                       uint32_t box_rows);
+                       uint32_t box_rows, uint32_t box_bytes = 128, uint32_t swizzle_bytes = 128);
+// Per-thread cache of encoded descriptors keyed by (pointer, shape, box): weights are long-lived.
+int cached_tmap(CUtensorMap* out, const void* base, uint64_t rows, uint64_t kbytes, uint32_t box_rows,
+                uint32_t box_bytes = 128, uint32_t swizzle_bytes = 128);
 
 }  // namespace b200
