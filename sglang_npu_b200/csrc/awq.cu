@@ -17,13 +17,18 @@
 // Fused GEMM (`awq_gemm_kernel`), weight-streaming at 0.5 B/weight, one orientation for decode and prefill:
 //   D[n, m] (TMEM, 128 channels x BN tokens) += W^T[n, k] * x[m, k]^T   per 64-wide K block
 //   * raw packed words: TMA (64-byte swizzle) into a RAW-deep ring — 4 KB per K block per CTA, evict-first;
-//   * 8 dequant warps turn one K block into the fp16 A operand in shared memory, MN-major SWIZZLE_128B
-//     atoms (64 channels x 8 k), one 16-byte store per packed word, bank-conflict free;
+//   * the group's scales / zero points of the tile ride in the same ring as 1-D bulk copies (no global-latency
+//     stall in the dequant loop);
+//   * 4 dequant groups x 2 warps own alternate K blocks (block i -> group i % 4), so four blocks are being
+//     dequantised concurrently; each turns its block into the fp16 A operand in shared memory, MN-major
+//     SWIZZLE_128B atoms (64 channels x 8 k), one 16-byte store per packed word, bank-conflict free;
 //   * tokens x[m, k]: TMA, K-major SWIZZLE_128B (B operand), evict-last;
 //   * one thread issues tcgen05.mma kind::f16 (M=128, N=BN, K=16) with fp32 accumulators in TMEM;
 //   * split-K over a thread-block cluster (1,1,S): partial accumulators are reduce-scattered through
 //     distributed shared memory and summed in rank order (deterministic, no workspace);
 //   * epilogue: (+bias) -> fp16/bf16 -> out[m, n].
+#include <cstdlib>
+
 #include "sm100.cuh"
 
 namespace b200 {
@@ -33,6 +38,8 @@ using namespace sm100;
 constexpr int kAwqThreads = 384;   // warp 0 raw-W TMA, 1 MMA, 2 TMEM alloc, 3 x TMA, 4-11 dequant + epilogue
 constexpr int kAwqDqThreads = 256;
 constexpr int kAwqBK = 64;         // K elements per pipeline stage
+constexpr int kAwqMaxGps = 2;      // quantisation groups per K block: group_size >= 32
+constexpr int kAwqGroups = 4;      // dequant warp groups (2 warps each) working on different K blocks
 
 template <typename T> struct AwqMagic;
 template <> struct AwqMagic<__half> { static constexpr uint32_t kOr = 0x64006400u; static constexpr int kFmt = 0; };
@@ -94,6 +101,7 @@ struct AwqArgs {
   const void* bias;       // [N] or null
   int M, N, K, group_size;
   int num_kb, kb_per_split, splits;
+  int cl;  // CTAs along n that share (multicast) the token tile: cluster dims (cl, 1, splits)
 };
 
 template <int BN, int STAGES, int RAW>
@@ -103,7 +111,10 @@ struct AwqSmem {
   static constexpr int kStage = kA + kB;
   static constexpr int kRawStage = kAwqBK * 64;  // 64 k rows x 16 packed words
   static constexpr int kRawOff = STAGES * kStage;
-  static constexpr int kBarOff = kRawOff + RAW * kRawStage;
+  // per raw stage: up to kAwqMaxGps groups x (128 scales (256 B) + 16 zero-point words (64 B))
+  static constexpr int kConstStage = kAwqMaxGps * 320;
+  static constexpr int kConstOff = kRawOff + RAW * kRawStage;
+  static constexpr int kBarOff = kConstOff + RAW * kConstStage;
   static constexpr int kNumBars = 2 * STAGES + 2 * RAW + 1;
   static constexpr int kBytes = kBarOff + kNumBars * 8 + 1024;
   static_assert(BN * 128 * 4 <= STAGES * kStage, "split-K receive buffer must fit in the operand stages");
@@ -120,7 +131,7 @@ __device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
 }
 
 template <typename T, int BN, int STAGES, int RAW>
-__global__ void __launch_bounds__(kAwqThreads, 1)
+__global__ void __launch_bounds__(kAwqThreads, (AwqSmem<BN, STAGES, RAW>::kBytes <= 113 * 1024) ? 2 : 1)
 awq_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x, const AwqArgs g) {
   using L = AwqSmem<BN, STAGES, RAW>;
   constexpr int kTmemCols = BN < 32 ? 32 : BN;
@@ -143,21 +154,30 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constan
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(op_full(s), 1 + kAwqDqThreads / 32);  // x TMA (expect_tx arrive) + one arrive per dequant warp
-      mbar_init(op_empty(s), 1);
+      mbar_init(op_full(s), 1 + 2);  // x TMA (expect_tx arrive) + the two warps of the owning dequant group
+      mbar_init(op_empty(s), g.cl);  // one tcgen05.commit per CTA sharing the token tile
     }
     for (int s = 0; s < RAW; ++s) {
       mbar_init(raw_full(s), 1);
-      mbar_init(raw_empty(s), kAwqDqThreads / 32);
+      mbar_init(raw_empty(s), 2);
     }
     mbar_init(tmem_full, 1);
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<kTmemCols>(smem_u32(&s_tmem_base));
+  if (warp >= 4) {  // scales / zero points of channels past N (partial last tile) stay zero
+    uint32_t* cz = reinterpret_cast<uint32_t*>(smem_raw + (base - smem_u32(smem_raw)) + L::kConstOff);
+    for (int i = threadIdx.x - 128; i < RAW * L::kConstStage / 4; i += kAwqDqThreads) cz[i] = 0u;
+    fence_proxy_async();
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = s_tmem_base;
+  const int CL = g.cl;
+  if (CL * g.splits > 1) cluster_sync();  // peers' barriers are initialised before anything is multicast to them
+  const int cx = (int)blockIdx.x % CL;                                        // position among the tile sharers
+  const uint16_t mc_mask = (uint16_t)(((1u << CL) - 1u) << (CL * blockIdx.z));  // cluster ranks cx' + CL * z
 
   const int n0 = blockIdx.x * 128;   // first output channel of this CTA
   const int m0 = blockIdx.y * BN;    // first token
@@ -166,14 +186,29 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constan
   const int kb0 = rank * g.kb_per_split;
   const int nkb = min(g.kb_per_split, g.num_kb - kb0);
 
+  // quantisation groups per K block (1 when group_size >= 64, else 64 / group_size) and valid channels of the tile
+  const int gps = g.group_size >= kAwqBK ? 1 : kAwqBK / g.group_size;
+  const int nv = max(0, min(128, g.N - n0));  // 0 for a surplus CTA that only feeds the multicast
+  const int num_groups = g.K / g.group_size;
+
   if (warp == 0) {
     if (lane == 0) {
+      const uint8_t* scales_b = reinterpret_cast<const uint8_t*>(g.scales);
+      const uint8_t* zeros_b = reinterpret_cast<const uint8_t*>(g.qzeros);
       for (int i = 0; i < nkb; ++i) {
         const int rs = i % RAW;
         mbar_wait(raw_empty(rs), ((i / RAW) & 1) ^ 1);
-        mbar_expect_tx(raw_full(rs), L::kRawStage);
-        tma_load_2d(base + L::kRawOff + rs * L::kRawStage, &tmap_w, raw_full(rs), n0 / 2 /* bytes: n0/8 words */,
-                    (kb0 + i) * kAwqBK, kEvictFirst);
+        const int k0 = (kb0 + i) * kAwqBK;
+        const int grp0 = k0 / g.group_size;
+        const int ng = nv > 0 ? min(gps, num_groups - grp0) : 0;  // groups of this block that exist (K tail)
+        mbar_expect_tx(raw_full(rs), L::kRawStage + ng * (nv * 2 + nv / 2));
+        tma_load_2d(base + L::kRawOff + rs * L::kRawStage, &tmap_w, raw_full(rs), n0 / 2 /* bytes: n0/8 words */, k0,
+                    kEvictFirst);
+        for (int gi = 0; gi < ng; ++gi) {
+          const uint32_t dst = base + L::kConstOff + rs * L::kConstStage + gi * 320;
+          bulk_load_1d(dst, scales_b + ((int64_t)(grp0 + gi) * g.N + n0) * 2, nv * 2, raw_full(rs));
+          bulk_load_1d(dst + 256, zeros_b + ((int64_t)(grp0 + gi) * g.N + n0) / 2, nv / 2, raw_full(rs));
+        }
       }
     }
   } else if (warp == 3) {
@@ -182,7 +217,13 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constan
         const int s = i % STAGES;
         mbar_wait(op_empty(s), ((i / STAGES) & 1) ^ 1);
         mbar_expect_tx(op_full(s), L::kB);
-        tma_load_2d(base + s * L::kStage + L::kA, &tmap_x, op_full(s), (kb0 + i) * kAwqBK * 2, m0, kEvictLast);
+        if (CL == 1) {
+          tma_load_2d(base + s * L::kStage + L::kA, &tmap_x, op_full(s), (kb0 + i) * kAwqBK * 2, m0, kEvictLast);
+        } else {  // this CTA fetches rows [cx, cx+1) * BN/CL of the tile and multicasts them to all sharers
+          const int rows = BN / CL;
+          tma_load_2d_mc(base + s * L::kStage + L::kA + cx * rows * 128, &tmap_x, op_full(s), (kb0 + i) * kAwqBK * 2,
+                         m0 + cx * rows, mc_mask, kEvictLast);
+        }
       }
     }
   } else if (warp == 1) {
@@ -198,54 +239,61 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constan
 #pragma unroll
         for (int k = 0; k < kAwqBK / 16; ++k)  // UMMA K = 16 elements: A advances 2 k-atoms (4096 B), B 32 bytes
           umma<kKindF16>(tmem_base, da + 256 * k, db + 2 * k, idesc, (i | k) != 0);
-        tc_commit(op_empty(s));
+        if (CL == 1) tc_commit(op_empty(s));
+        else tc_commit_mc(op_empty(s), mc_mask);  // the stage is free once EVERY sharer's MMAs have read it
       }
       tc_commit(tmem_full);
     }
   } else if (warp >= 4) {
-    // ---- dequant producers: thread -> (k row of the block, 4 consecutive packed words = 32 channels) ----------
-    using T2 = typename DT<T>::T2;
-    const int td = threadIdx.x - 128;
-    const int krow = td & 63;
-    const int quad = td >> 6;
-    const int n_thread = n0 + quad * 32;  // first channel of this thread's words
-    const bool n_ok = n_thread < g.N;     // N % 8 == 0; a word is either fully in or fully out — checked per word
-    const int n8 = g.N / 8;
-    const T* scales = reinterpret_cast<const T*>(g.scales);
-    uint32_t zm[4][4];
-    uint4 sc[4];
-    int cur_grp = -1;
-    // raw tile: row = krow (64 B), 16-byte chunk = quad, 64-byte swizzle: chunk ^= (row >> 1) & 3
-    const uint32_t raw_off = (uint32_t)(krow * 64 + ((quad ^ ((krow >> 1) & 3)) << 4));
-    // A operand: atom = (krow >> 3) * 2 + (quad >> 1); row r = krow & 7; chunk c = (quad & 1) * 4 + w, swizzled by r
-    const int r = krow & 7;
-    const uint32_t a_off = (uint32_t)((((krow >> 3) * 2 + (quad >> 1)) << 10) + (r << 7));
+    // ---- dequant producers: group = (warp - 4) / 2 owns K blocks i % 4 == group; within a group the two
+    //      warps take alternate 8-row k-atoms; lane -> (row of the atom, 4 consecutive packed words) ------------
+    const int dw = warp - 4;
+    const int grp_id = dw >> 1;
+    const int wsub = dw & 1;
+    const int r = lane & 7;
+    const int quad = lane >> 3;
     const int c_base = (quad & 1) * 4;
-    for (int i = 0; i < nkb; ++i) {
+    for (int i = grp_id; i < nkb; i += kAwqGroups) {
       const int rs = i % RAW;
       const int s = i % STAGES;
-      const int k = min((kb0 + i) * kAwqBK + krow, g.K - 1);
-      const int grp = k / g.group_size;
-      if (grp != cur_grp) {
-        cur_grp = grp;
-#pragma unroll
-        for (int w = 0; w < 4; ++w) {
-          const bool ok = n_thread + w * 8 < g.N;
-          const uint32_t z = ok ? __ldg(g.qzeros + (int64_t)grp * n8 + (n_thread >> 3) + w) : 0u;
-          sc[w] = ok ? __ldg(reinterpret_cast<const uint4*>(scales + (int64_t)grp * g.N + n_thread + w * 8))
-                     : make_uint4(0u, 0u, 0u, 0u);
-#pragma unroll
-          for (int p = 0; p < 4; ++p) zm[w][p] = nib_pair<T>(z, p);
-        }
-      }
       mbar_wait(raw_full(rs), (i / RAW) & 1);
-      const uint4 q = lds128(base + L::kRawOff + rs * L::kRawStage + raw_off);
+      const uint32_t raw_base = base + L::kRawOff + rs * L::kRawStage;
+      const uint32_t const_base = base + L::kConstOff + rs * L::kConstStage;
+      uint4 q[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        // raw tile: row (64 B), 16-byte chunk = quad, 64-byte swizzle: chunk ^= (row >> 1) & 3
+        const int krow = (wsub + 2 * j) * 8 + r;
+        q[j] = lds128(raw_base + (uint32_t)(krow * 64 + ((quad ^ ((krow >> 1) & 3)) << 4)));
+      }
+      uint32_t zm[4][4];
+      uint4 sc[4];
+      int cur_slot = -1;
       mbar_wait(op_empty(s), ((i / STAGES) & 1) ^ 1);
-      const uint32_t sa = base + s * L::kStage + a_off;
-      sts128(sa + (((c_base + 0) ^ r) << 4), dequant_word<T>(q.x, zm[0], sc[0]));
-      sts128(sa + (((c_base + 1) ^ r) << 4), dequant_word<T>(q.y, zm[1], sc[1]));
-      sts128(sa + (((c_base + 2) ^ r) << 4), dequant_word<T>(q.z, zm[2], sc[2]));
-      sts128(sa + (((c_base + 3) ^ r) << 4), dequant_word<T>(q.w, zm[3], sc[3]));
+      const uint32_t a_stage = base + s * L::kStage;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int katom = wsub + 2 * j;
+        const int slot = gps == 1 ? 0 : (katom * 8 * gps) >> 6;
+        if (slot != cur_slot) {
+          cur_slot = slot;
+          const uint32_t cb = const_base + slot * 320;
+          const uint4 z = lds128(cb + 256 + quad * 16);
+          const uint32_t zw[4] = {z.x, z.y, z.z, z.w};
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            sc[w] = lds128(cb + quad * 64 + w * 16);
+#pragma unroll
+            for (int p = 0; p < 4; ++p) zm[w][p] = nib_pair<T>(zw[w], p);
+          }
+        }
+        // A operand: atom = katom * 2 + (quad >> 1); row r; chunk c = (quad & 1) * 4 + w, swizzled by r
+        const uint32_t sa = a_stage + (uint32_t)(((katom * 2 + (quad >> 1)) << 10) + (r << 7));
+        sts128(sa + (((c_base + 0) ^ r) << 4), dequant_word<T>(q[j].x, zm[0], sc[0]));
+        sts128(sa + (((c_base + 1) ^ r) << 4), dequant_word<T>(q[j].y, zm[1], sc[1]));
+        sts128(sa + (((c_base + 2) ^ r) << 4), dequant_word<T>(q[j].z, zm[2], sc[2]));
+        sts128(sa + (((c_base + 3) ^ r) << 4), dequant_word<T>(q[j].w, zm[3], sc[3]));
+      }
       fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
       __syncwarp();
       if (lane == 0) {
@@ -253,7 +301,6 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constan
         mbar_arrive(raw_empty(rs));
       }
     }
-    (void)n_ok;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
   }
@@ -282,7 +329,7 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constan
       const uint32_t my_slot = base + (uint32_t)(rank * C * 128 + row) * 4;  // receive buffer [src rank][col][row]
       uint32_t dst[8];
 #pragma unroll
-      for (int d = 0; d < 8; ++d) dst[d] = d < S ? mapa(my_slot, d) : 0;
+      for (int d = 0; d < 8; ++d) dst[d] = d < S ? mapa(my_slot, cx + CL * d) : 0;
 #pragma unroll 1
       for (int c0 = half * kColsPerHalf; c0 < (half + 1) * kColsPerHalf; c0 += 16) {
         if (m0 + c0 >= g.M) break;
@@ -338,6 +385,7 @@ awq_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync();  // no CTA exits while a sharer may still signal its barriers
   if (warp == 2) tmem_dealloc<kTmemCols>(tmem_base);
 }
 
@@ -353,7 +401,7 @@ static int launch_awq(const CUtensorMap& tw, const CUtensorMap& tx, const AwqArg
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 1;
+  attr[0].val.clusterDim.x = g.cl;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = g.splits;
   cfg.attrs = attr;
@@ -378,17 +426,27 @@ static int run_awq_gemm(AwqArgs g, const void* x, const void* qweight, cudaStrea
     g.splits /= 2;
     g.kb_per_split = (int)ceil_div(g.num_kb, g.splits);
   }
+  // token-tile sharing: the tile is BN * 128 B per K block against 4 KB of packed weights, so at BN >= 64 the L2 ->
+  // SM traffic is dominated by tokens; cl CTAs along n fetch 1/cl of it each and multicast (cl * splits <= 8)
+  // Measured on B200 (profiles/awq_r01.md): sharing does not pay at these sizes — the kernel is bound by the
+  // packed-word stream, not by L2 -> SM token traffic — so it stays off unless B200_AWQ_CLUSTER_N asks for it.
+  static const int cl_env = [] { const char* e = getenv("B200_AWQ_CLUSTER_N"); return e ? atoi(e) : 1; }();
+  g.cl = (cl_env == 2 || cl_env == 4) && bn >= 64 ? cl_env : 1;
+  while (g.cl > 1 && (g.cl * g.splits > 8 || tiles < g.cl)) g.cl /= 2;
+  const int tiles_padded = (int)ceil_div(tiles, g.cl) * g.cl;  // surplus CTAs only feed the multicast
   CUtensorMap tw, tx;
   int rc;
   // packed weights [K rows, N/2 bytes]: box 64 rows x 64 bytes (16 words = 128 channels), 64-byte swizzle
   if ((rc = cached_tmap(&tw, qweight, (uint64_t)K, (uint64_t)(N / 2), kAwqBK, 64, 64)) != B200_OK) return rc;
-  if ((rc = cached_tmap(&tx, x, (uint64_t)M, (uint64_t)(K * 2), (uint32_t)bn)) != B200_OK) return rc;
-  dim3 grid(tiles, mtiles, g.splits);
+  if ((rc = cached_tmap(&tx, x, (uint64_t)M, (uint64_t)(K * 2), (uint32_t)(bn / g.cl))) != B200_OK) return rc;
+  dim3 grid(tiles_padded, mtiles, g.splits);
   switch (bn) {
-    case 16: return launch_awq<T, 16, 4, 8>(tw, tx, g, grid, st);
-    case 32: return launch_awq<T, 32, 4, 8>(tw, tx, g, grid, st);
-    case 64: return launch_awq<T, 64, 4, 8>(tw, tx, g, grid, st);
-    case 128: return launch_awq<T, 128, 4, 8>(tw, tx, g, grid, st);
+    // operand stages >= dequant groups + 1 (one being consumed by the MMA); the raw ring holds the bytes in flight
+    // BN <= 64: two CTAs per SM (<= 113 KB each) so one CTA's prologue / epilogue hides under the other's stream
+    case 16: return launch_awq<T, 16, 3, 8>(tw, tx, g, grid, st);
+    case 32: return launch_awq<T, 32, 3, 8>(tw, tx, g, grid, st);
+    case 64: return launch_awq<T, 64, 3, 8>(tw, tx, g, grid, st);
+    case 128: return launch_awq<T, 128, 4, 16>(tw, tx, g, grid, st);
     default: return launch_awq<T, 256, 4, 4>(tw, tx, g, grid, st);
   }
 }
@@ -430,6 +488,8 @@ B200_API int b200_awq_gemm(void* out, const void* x, const int32_t* qweight, con
   // the TMA row pitch additionally needs N % 32 == 0 (16-byte rows of packed words) and K % 8 == 0
   B200_REQUIRE(group_size > 0 && K % group_size == 0, "awq_gemm: K %lld is not a multiple of group_size %d", (long long)K,
                group_size);
+  if (group_size < 32 || (group_size < kAwqBK ? kAwqBK % group_size != 0 : group_size % kAwqBK != 0))
+    return fail(B200_ERR_UNSUPPORTED, "awq_gemm: group_size %d not supported (32, or a multiple of 64)", group_size);
   B200_REQUIRE(N % 32 == 0, "awq_gemm: N %lld must be a multiple of 32", (long long)N);
   B200_REQUIRE(K % 8 == 0, "awq_gemm: K %lld must be a multiple of 8", (long long)K);
   B200_REQUIRE(((uintptr_t)out % 2) == 0 && ((uintptr_t)scales % 16) == 0, "awq_gemm: pointer alignment");
