@@ -50,6 +50,17 @@ class LinearBase(nn.Module):
             self.quant_method = quant_config.get_quant_method(self, prefix=prefix) or UnquantizedLinearMethod()
 
 
+def _block_scale_units(layer, param, offset: int, size: int):
+    """Block-quantised scales hold one entry per `block_n` output rows: convert a logical (offset, size) into
+    block units (reference linear.py weight_loader_v2: `(x + block_n - 1) // block_n`)."""
+    from .parameter import BlockQuantScaleParameter
+
+    if isinstance(param, BlockQuantScaleParameter):
+        block_n = layer.quant_method.quant_config.weight_block_size[0]
+        return (offset + block_n - 1) // block_n, (size + block_n - 1) // block_n
+    return offset, size
+
+
 class ColumnParallelLinear(LinearBase):
     """Y = XA + b with A split along its output dim: A = [A_1, ..., A_p] (linear.py:242-415)."""
 
@@ -104,6 +115,7 @@ class MergedColumnParallelLinear(ColumnParallelLinear):
         assert loaded_shard_id is not None and loaded_shard_id < len(self.output_sizes)
         shard_offset = sum(self.output_sizes[:loaded_shard_id]) // self.tp_size
         shard_size = self.output_sizes[loaded_shard_id] // self.tp_size
+        shard_offset, shard_size = _block_scale_units(self, param, shard_offset, shard_size)
         param.load_merged_column_weight(loaded_weight, shard_offset, shard_size, self.tp_rank)
 
 
@@ -139,6 +151,7 @@ class QKVParallelLinear(ColumnParallelLinear):
         offset = {"q": 0, "k": q_sz, "v": q_sz + kv_sz}[loaded_shard_id]
         size = q_sz if loaded_shard_id == "q" else kv_sz
         rank = self.tp_rank if loaded_shard_id == "q" else self.tp_rank // self.num_kv_head_replicas
+        offset, size = _block_scale_units(self, param, offset, size)
         param.load_merged_column_weight(loaded_weight, offset, size, rank)
 
 

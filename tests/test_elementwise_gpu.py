@@ -1,0 +1,90 @@
+"""Parity of the LSE-merge primitive and the element-wise steps either side of the path
+against the oracle restatements; shape grids follow the reference's kernel tests
+(sgl-kernel/tests/test_merge_state_v2.py, test_norm.py, test_activation.py, test_rotary_embedding.py)."""
+import math
+
+import pytest
+import torch
+
+from oracle import attention_oracle as ao
+from oracle import quant_oracle as qo
+from sglang_npu_b200 import kernels
+from sglang_npu_b200.srt.model_executor.layer_stack import compute_cos_sin_cache
+from tests.util import assert_close_path
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("T,H,D", [(1, 1, 64), (7, 14, 64), (64, 32, 128), (513, 40, 128), (3, 8, 256)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_merge_state_v2(cuda_device, T, H, D, dtype):
+    g = torch.Generator().manual_seed(T * 131 + H)
+    va, vb = torch.randn(T, H, D, generator=g).to(dtype), torch.randn(T, H, D, generator=g).to(dtype)
+    sa, sb = torch.randn(T, H, generator=g) * 3, torch.randn(T, H, generator=g) * 3
+    if T > 2:  # the reference test also feeds +-inf LSEs (empty partial states)
+        sa[0, 0] = -math.inf
+        sb[1, 0] = -math.inf
+    ref_v, ref_s = ao.merge_state(va, sa, vb, sb)
+    out_v, out_s = kernels.merge_state_v2(va.to(cuda_device), sa.to(cuda_device), vb.to(cuda_device), sb.to(cuda_device))
+    assert_close_path(out_v, ref_v, "merge_state v")
+    torch.testing.assert_close(out_s.cpu(), ref_s, rtol=1e-4, atol=1e-4)
+
+
+def test_merge_state_is_associative_with_decode_splits(cuda_device):
+    """merging the states of two halves of a KV range equals attention over the whole range (cascade.cu use)."""
+    g = torch.Generator().manual_seed(5)
+    T, H, D, N = 4, 8, 128, 96
+    q = torch.randn(T, H, D, generator=g)
+    k = torch.randn(T, N, H, D, generator=g)
+    v = torch.randn(T, N, H, D, generator=g)
+
+    def part(lo, hi):
+        s = torch.einsum("thd,tnhd->thn", q, k[:, lo:hi]) * D ** -0.5
+        lse = torch.logsumexp(s, dim=-1)
+        return torch.einsum("thn,tnhd->thd", torch.softmax(s, -1), v[:, lo:hi]), lse
+
+    (oa, sa), (ob, sb), (full, _) = part(0, 40), part(40, N), part(0, N)
+    out, _ = kernels.merge_state_v2(oa.bfloat16().to(cuda_device), sa.to(cuda_device), ob.bfloat16().to(cuda_device),
+                                    sb.to(cuda_device))
+    assert_close_path(out, full.bfloat16(), "merge of halves")
+
+
+@pytest.mark.parametrize("M,H", [(1, 896), (64, 4096), (37, 5120), (300, 8192), (5, 128)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_rmsnorm_and_fused_add(cuda_device, M, H, dtype):
+    g = torch.Generator().manual_seed(M + H)
+    x = torch.randn(M, H, generator=g).to(dtype)
+    r = torch.randn(M, H, generator=g).to(dtype)
+    w = (1 + 0.1 * torch.randn(H, generator=g)).to(dtype)
+    out = kernels.rmsnorm(x.to(cuda_device), w.to(cuda_device), 1e-6)
+    assert_close_path(out, qo.rmsnorm(x, w, 1e-6), "rmsnorm", max_abs=4e-2)
+    xd, rd = x.to(cuda_device).clone(), r.to(cuda_device).clone()
+    kernels.fused_add_rmsnorm(xd, rd, w.to(cuda_device), 1e-6)
+    ref_x, ref_r = qo.rmsnorm(x, w, 1e-6, r)
+    assert torch.equal(rd.cpu().view(torch.int16), ref_r.view(torch.int16)), "residual = bf16(x + residual) must be exact"
+    assert_close_path(xd, ref_x, "fused_add_rmsnorm", max_abs=4e-2)
+
+
+@pytest.mark.parametrize("M,H", [(1, 4864), (64, 14336), (129, 27648), (3, 64)])
+def test_silu_and_mul(cuda_device, M, H):
+    x = torch.randn(M, 2 * H, generator=torch.Generator().manual_seed(H)).bfloat16()
+    out = kernels.silu_and_mul(x.to(cuda_device))
+    assert_close_path(out, qo.silu_and_mul(x.float()).bfloat16(), "silu_and_mul", max_abs=4e-2)
+
+
+@pytest.mark.parametrize("hq,hkv,d", [(32, 8, 128), (14, 2, 64), (5, 1, 128)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_rope_neox_on_strided_qkv(cuda_device, hq, hkv, d, dtype):
+    T = 33
+    g = torch.Generator().manual_seed(hq)
+    qkv = torch.randn(T, (hq + 2 * hkv) * d, generator=g).to(dtype)
+    pos = torch.randint(0, 4000, (T,), generator=g)
+    cache = compute_cos_sin_cache(d, 4096, 1e6)
+    q, k, v = qkv.split([hq * d, hkv * d, hkv * d], dim=-1)
+    ref_q, ref_k = qo.rope_neox(pos, q, k, d, cache)
+    dq = qkv.to(cuda_device)
+    q2, k2, v2 = dq.split([hq * d, hkv * d, hkv * d], dim=-1)
+    kernels.apply_rope_neox_inplace(pos.to(cuda_device), q2, k2, d, cache.to(cuda_device))
+    assert_close_path(q2, ref_q, "rope q", max_abs=4e-2)
+    assert_close_path(k2, ref_k, "rope k", max_abs=4e-2)
+    assert torch.equal(v2.cpu(), v), "rope must not touch v"

@@ -1,0 +1,117 @@
+"""Whole-path parity on random-init weights (north_star: "greedy-decoded tokens on random-init weights must match"):
+the layer stack on the B200 kernels vs oracle/model_oracle.py (torch_native attention + quant restatements on CPU),
+same seeded quantised weights on both sides (SURVEY §7.3 "dummy-weight parity": the reference's dummy loader leaves
+integer weights uninitialised, so the harness generates them).
+
+Tokens are compared where the oracle's top-2 logit margin exceeds the measured numeric noise of the bf16 path
+(argmax ties flip under 1-ulp differences on near-uniform random-init logits); every compared token
+must be identical, and most tokens must be comparable."""
+import copy
+
+import pytest
+import torch
+
+from oracle.model_oracle import OracleStack
+from sglang_npu_b200 import synth
+from sglang_npu_b200.srt.layers.quantization import get_quantization_config
+from sglang_npu_b200.srt.model_executor.layer_stack import CONFIGS
+from sglang_npu_b200.srt.model_executor.model_runner import HotPathRunner
+
+pytestmark = pytest.mark.gpu
+
+QCFG = {"weight_block_size": [128, 128], "activation_scheme": "dynamic", "quant_method": "fp8", "bits": 4,
+        "group_size": 128, "zero_point": True, "w_bit": 4, "q_group_size": 128}
+
+
+def _run(dev, model, quant, bs, max_prompt, page, layers, steps, vocab=4096, dtype=torch.bfloat16, gain=4.0, graph=False):
+    cfg = copy.deepcopy(CONFIGS[model])
+    cfg.vocab_size = vocab
+    g = torch.Generator().manual_seed(11)
+    prompts = torch.randint(max_prompt // 2, max_prompt + 1, (bs,), generator=g).tolist()
+    pb = synth.make_paged_batch(prompts, page, seed=5, reserve_tokens=steps + 1)
+    qc = get_quantization_config(quant).from_config(QCFG)
+    runner = HotPathRunner(cfg, qc, max_reqs=pb.req_to_token.shape[0], max_total_tokens=pb.num_slots, page_size=page,
+                           context_len=pb.req_to_token.shape[1] - 4, device=dev, num_layers=layers, weight_gain=gain,
+                           dtype=dtype)
+    runner.req_to_token_pool.req_to_token.copy_(pb.req_to_token)
+    oracle = OracleStack(runner.model)
+    kc = [torch.zeros_like(b, device="cpu") for b in runner.token_to_kv_pool.k_buffer]
+    vc = [torch.zeros_like(b, device="cpu") for b in runner.token_to_kv_pool.v_buffer]
+    rpi = pb.req_pool_indices
+    ids = torch.randint(0, vocab, (sum(prompts),), generator=g)
+    pos = torch.cat([torch.arange(e) for e in prompts])
+    loc = torch.cat([pb.req_to_token[rpi[i], : prompts[i]] for i in range(bs)]).long()
+    seq = torch.tensor(prompts, dtype=torch.int64)
+    zero = torch.zeros(bs, dtype=torch.int64)
+    logits = runner.forward_extend(ids.to(dev), rpi.to(dev), seq.to(dev), zero.to(dev), loc.to(dev), pos.to(dev),
+                                   seq_lens_cpu=seq, extend_seq_lens_cpu=prompts)
+    h = oracle.forward(ids, pos, kc, vc, pb.req_to_token, rpi, seq, loc, prefix_lens=zero)
+    ref = oracle.logits(h[torch.cumsum(seq, 0) - 1])
+    # KV written by the device path == KV written by the oracle, layer 0 (inputs identical there): bit-exact slots
+    k0 = runner.token_to_kv_pool.k_buffer[0].cpu()
+    touched = torch.zeros(k0.shape[0], dtype=torch.bool)
+    touched[loc] = True
+    assert not k0[~touched].any(), "KV write touched slots outside out_cache_loc"
+    stats = dict(compared=0, total=0, max_abs=0.0)
+    if graph:
+        runner.capture_decode_graph(bs)
+
+    def compare(dev_logits, ref_logits):
+        d = dev_logits.float().cpu()
+        r = ref_logits.float()
+        noise = (d - r).abs().max().item()
+        stats["max_abs"] = max(stats["max_abs"], noise)
+        top2 = r.topk(2, dim=-1).values
+        margin = top2[:, 0] - top2[:, 1]
+        sure = margin > 2.5 * noise
+        stats["compared"] += int(sure.sum())
+        stats["total"] += r.shape[0]
+        assert torch.equal(d.argmax(-1)[sure], r.argmax(-1)[sure]), \
+            f"greedy tokens differ where the oracle margin {margin[sure].min():.4f} exceeds 2.5 x noise {noise:.4f}"
+        cos = torch.nn.functional.cosine_similarity(d.flatten(), r.flatten(), dim=0).item()
+        assert cos > 0.999, f"logit cosine {cos}"
+        return r.argmax(-1)  # continue both sides from the ORACLE's token so the trajectories stay aligned
+
+    nxt = compare(logits, ref)
+    for s in range(steps):
+        seq = seq + 1
+        loc = torch.stack([pb.req_to_token[rpi[i], seq[i] - 1] for i in range(bs)]).long()
+        if graph:
+            runner.replay_decode(nxt.to(dev), rpi.to(dev), seq.to(dev), loc.to(dev))
+            # the graph returns token ids; re-run eagerly for logits of the same state is not needed: compare ids
+            dev_ids = runner._static["next_token_ids"].cpu()
+            h = oracle.forward(nxt, seq - 1, kc, vc, pb.req_to_token, rpi, seq, loc)
+            r = oracle.logits(h).float()
+            top2 = r.topk(2, dim=-1).values
+            sure = (top2[:, 0] - top2[:, 1]) > 2.5 * max(stats["max_abs"], 1e-3)
+            stats["compared"] += int(sure.sum())
+            stats["total"] += bs
+            assert torch.equal(dev_ids[sure], r.argmax(-1)[sure]), "CUDA-graph greedy ids differ from the oracle"
+            nxt = r.argmax(-1)
+        else:
+            lg = runner.forward_decode(nxt.to(dev), rpi.to(dev), seq.to(dev), loc.to(dev), seq_lens_cpu=seq)
+            h = oracle.forward(nxt, seq - 1, kc, vc, pb.req_to_token, rpi, seq, loc)
+            nxt = compare(lg, oracle.logits(h))
+    assert stats["compared"] >= 0.6 * stats["total"], f"too few comparable tokens: {stats}"
+    return stats
+
+
+def test_cfg1_qwen05b_int8_bs8_ctx512_page1(cuda_device):
+    """BASELINE configs[0]: Qwen2.5-0.5B W8A8-int8, bs 8, 512-token context, page_size 1 (all 24 layers)."""
+    st = _run(cuda_device, "qwen2.5-0.5b", "b200_w8a8_int8", bs=8, max_prompt=508, page=1, layers=24, steps=4)
+    print(st)
+
+
+def test_llama8b_shape_int8_page16_with_cuda_graph(cuda_device):
+    """configs[1] layer shapes (Llama-3.1-8B, page 16), 2 layers, decode through the captured CUDA graph."""
+    _run(cuda_device, "llama-3.1-8b", "b200_w8a8_int8", bs=5, max_prompt=200, page=16, layers=2, steps=3, graph=True)
+
+
+def test_llama8b_shape_block_fp8(cuda_device):
+    """configs[2] arithmetic: block-scaled FP8 linears."""
+    _run(cuda_device, "llama-3.1-8b", "b200_fp8", bs=3, max_prompt=150, page=16, layers=2, steps=2)
+
+
+def test_qwen32b_shape_awq_fp16(cuda_device):
+    """configs[3] arithmetic: AWQ-int4 linears (fp16 activations, awq.py:111-112)."""
+    _run(cuda_device, "qwen2.5-32b", "b200_awq", bs=3, max_prompt=100, page=16, layers=1, steps=2, dtype=torch.float16)

@@ -1,0 +1,59 @@
+"""CPU known-answer tests of oracle/quant_oracle.py (no GPU): hand-computable cases of the rules the reference's
+own tests define (test/srt/cpu/utils.py:24-32,:91-115; python/sglang/test/test_block_fp8.py:24-49,:274-330;
+sgl-kernel/tests/test_awq_dequant.py:9-61)."""
+import torch
+
+from oracle import quant_oracle as qo
+
+
+def test_per_token_quant_int8_known_answer():
+    x = torch.tensor([[1.0, -2.0, 0.5, 127.0], [0.0, 0.0, 0.0, 0.0]])
+    q, s = qo.per_token_quant_int8(x)
+    assert q.dtype == torch.int8 and s.shape == (2, 1)
+    assert q[0].tolist() == [1, -2, 0, 127]  # 0.5 -> round-half-even -> 0
+    assert abs(s[0, 0].item() - 1.0) < 1e-7
+    assert q[1].tolist() == [0, 0, 0, 0] and s[1, 0].item() > 0  # absmax clamp keeps the scale finite
+
+
+def test_int8_accumulator_is_exact_integer_matmul():
+    g = torch.Generator().manual_seed(0)
+    a = torch.randint(-127, 128, (5, 64), generator=g, dtype=torch.int32).to(torch.int8)
+    w = torch.randint(-127, 128, (7, 64), generator=g, dtype=torch.int32).to(torch.int8)
+    acc = qo.int8_accumulate(a, w)
+    assert acc.dtype == torch.int32
+    assert torch.equal(acc.long(), a.long() @ w.long().t())
+
+
+def test_block_fp8_group_quant_known_answer():
+    x = torch.zeros(1, 256)
+    x[0, 0], x[0, 128] = 448.0, -2.0
+    q, s = qo.per_token_group_quant_fp8(x, 128)
+    assert s.shape == (1, 2) and abs(s[0, 0].item() - 1.0) < 1e-6 and abs(s[0, 1].item() - 2.0 / 448) < 1e-9
+    assert q.dtype == torch.float8_e4m3fn and q.float()[0, 0].item() == 448.0 and q.float()[0, 128].item() == -448.0
+
+
+def test_block_fp8_matmul_applies_scales_per_128_block():
+    M, N, K = 2, 128, 256
+    a = torch.ones(M, K).to(torch.float8_e4m3fn)
+    w = torch.ones(N, K).to(torch.float8_e4m3fn)
+    a_s = torch.tensor([[1.0, 2.0], [3.0, 4.0]])
+    w_s = torch.tensor([[0.5, 0.25]])
+    out = qo.w8a8_block_fp8_matmul(a, w, a_s, w_s, [128, 128], torch.float32)
+    assert torch.allclose(out[0], torch.full((N,), 128 * 1.0 * 0.5 + 128 * 2.0 * 0.25))
+    assert torch.allclose(out[1], torch.full((N,), 128 * 3.0 * 0.5 + 128 * 4.0 * 0.25))
+
+
+def test_awq_nibble_order_known_answer():
+    # packed word with nibble j holding value j: logical column i reads nibble ORDER[i] = [0,4,1,5,2,6,3,7]
+    word = sum(j << (4 * j) for j in range(8))
+    qweight = torch.tensor([[word]], dtype=torch.int64).to(torch.int32)
+    qzeros = torch.zeros(1, 1, dtype=torch.int32)
+    scales = torch.ones(1, 8, dtype=torch.float16)
+    w = qo.awq_dequantize(qweight, scales, qzeros, 1)
+    assert w.flatten().tolist() == [0, 4, 1, 5, 2, 6, 3, 7]
+
+
+def test_rmsnorm_silu_rope_shapes():
+    x = torch.randn(3, 16)
+    assert qo.rmsnorm(x, torch.ones(16), 1e-6).shape == x.shape
+    assert qo.silu_and_mul(x).shape == (3, 8)
