@@ -194,6 +194,26 @@ int b200_rope_neox(void* q, void* k, const float* cos_sin_cache, const int64_t* 
                    int rot_dim, int64_t q_token_stride, int64_t k_token_stride, int dtype,
                    void* stream);
 
+/* ---- fused steps ("fused_add_rmsnorm + emit per-token int8 quant for the following GEMM,
+ * RoPE + fused KV-cache write, silu_and_mul + quant for down_proj") ---------------------------------------------
+ * Each is bit-identical to the two un-fused entry points run back to back; they remove one launch and one
+ * activation round-trip per linear at decode sizes.
+ *   b200_rmsnorm_quant_int8:      residual (optional, in place) += x; y = T(rmsnorm(residual) * weight);
+ *                                 (xq, scale) = per_token_quant_int8(y); y_out (optional) receives y.
+ *   b200_silu_and_mul_quant_int8: y = T(T(silu(x[:, :H])) * x[:, H:]); (xq, scale) = per_token_quant_int8(y).
+ *   b200_rope_neox_set_kv:        NeoX RoPE on q, k in place (b200_rope_neox), then
+ *                                 k_cache[loc] = k, v_cache[loc] = v (b200_set_kv_buffer); caches may be NULL.
+ */
+int b200_rmsnorm_quant_int8(int8_t* xq, float* scale, void* y_out, void* residual, const void* x,
+                            const void* weight, int64_t M, int64_t H, float eps, int dtype, void* stream);
+int b200_silu_and_mul_quant_int8(int8_t* xq, float* scale, const void* x, int64_t M, int64_t H, int dtype,
+                                 void* stream);
+int b200_rope_neox_set_kv(void* q, void* k, const void* v, const float* cos_sin_cache, const int64_t* positions,
+                          void* k_cache, void* v_cache, const void* loc, int loc_is_int64, int64_t num_tokens,
+                          int num_q_heads, int num_kv_heads, int head_dim, int rot_dim, int64_t q_token_stride,
+                          int64_t k_token_stride, int64_t v_token_stride, int64_t k_cache_token_stride,
+                          int64_t v_cache_token_stride, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

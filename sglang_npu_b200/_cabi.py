@@ -64,6 +64,10 @@ _SIGNATURES = {
     "b200_silu_and_mul": [_P, _P, c_int64, c_int64, c_int, _P],
     "b200_rope_neox": [_P, _P, _P, _P, c_int64, c_int, c_int, c_int, c_int, c_int64, c_int64,
                        c_int, _P],
+    "b200_rmsnorm_quant_int8": [_P, _P, _P, _P, _P, _P, c_int64, c_int64, c_float, c_int, _P],
+    "b200_silu_and_mul_quant_int8": [_P, _P, _P, c_int64, c_int64, c_int, _P],
+    "b200_rope_neox_set_kv": [_P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int64, c_int, c_int, c_int, c_int,
+                              c_int64, c_int64, c_int64, c_int64, c_int64, c_int, _P],
 }
 
 EXPORTED_SYMBOLS = sorted(list(_SIGNATURES) + ["b200_last_error"])

@@ -44,6 +44,49 @@ int fail(b200_status code, const char* fmt, ...);
 
 int sm_count();
 
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------
+// Every kernel of the decode chain is launched with cudaLaunchAttributeProgrammaticStreamSerialization, so
+// its CTAs may become resident while the previous kernel in the stream is still draining.  The contract
+// inside each kernel:
+//   * pdl_trigger() early: dependents may be scheduled once every CTA of this grid has started;
+//   * pdl_wait() before the first access to ANYTHING a previous kernel may have written (or may still
+//     be reading, for buffers this kernel overwrites) — it returns when all earlier grids have completed
+//     and their writes are visible.  Only launch-invariant data (weights, cos/sin tables, the page table
+//     of the step) may be touched before it: that is what lets a GEMM stream its first weight tiles, and
+//     set up barriers / TMEM, under the tail of its predecessor.
+// Every thread calls pdl_wait() on every path (also early-exit ones): a grid's completion must imply
+// the completion of its predecessors, or the NEXT grid's pdl_wait() would not cover them.
+// Both instructions are no-ops when the kernel was launched without the attribute (B200_PDL=0).
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+static inline int launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                           unsigned cluster_z, bool pdl, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  if (cluster_z > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = 1;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = cluster_z;
+    ++n;
+  }
+  if (pdl && pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, KArgs(args)...));
+  return B200_OK;
+}
+
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 // ---- dtype traits ----------------------------------------------------------------------
@@ -78,6 +121,9 @@ __device__ __forceinline__ float2 unpack2(uint32_t u) {
 }
 
 // ---- small PTX wrappers ----------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;\n" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory"); }
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

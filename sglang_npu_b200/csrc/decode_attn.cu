@@ -96,6 +96,8 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_attn_kernel(const Decod
   const int g = lane >> 2;
   const int t = lane & 3;
 
+  pdl_trigger();
+  pdl_wait();
   const int seq_len = (int)load_index(a.seq_lens, b, a.index_is_int64);
   const int start = split * a.kv_chunk;
   if (start >= seq_len) return;
@@ -350,6 +352,8 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_attn_kernel(const Decod
 // seq_len 0 get zeros.
 template <typename T, int D>
 __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeArgs a) {
+  pdl_trigger();
+  pdl_wait();
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp_global >= a.batch * a.num_q_heads) return;
@@ -399,20 +403,19 @@ static int launch_decode(const DecodeArgs& a, cudaStream_t stream) {
   const int smem = pipe + a.kv_chunk * 4;
   dim3 grid(a.max_splits, a.num_kv_heads * a.head_blocks, a.batch);
   const bool upper = a.group > 8;
+  int rc;
   if (upper) {
     auto kern = decode_attn_kernel<T, D, STAGES, true>;
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    kern<<<grid, kDecThreads, smem, stream>>>(a);
+    rc = launch_k(kern, grid, dim3(kDecThreads), smem, stream, 1, true, a);
   } else {
     auto kern = decode_attn_kernel<T, D, STAGES, false>;
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    kern<<<grid, kDecThreads, smem, stream>>>(a);
+    rc = launch_k(kern, grid, dim3(kDecThreads), smem, stream, 1, true, a);
   }
-  B200_LAUNCH_OK();
+  if (rc != B200_OK) return rc;
   const int warps = a.batch * a.num_q_heads;
-  decode_merge_kernel<T, D><<<(warps + 3) / 4, 128, 0, stream>>>(a);
-  B200_LAUNCH_OK();
-  return B200_OK;
+  return launch_k(decode_merge_kernel<T, D>, dim3((warps + 3) / 4), dim3(128), 0, stream, 1, true, a);
 }
 
 }  // namespace b200

@@ -13,6 +13,8 @@ __global__ void __launch_bounds__(256) rmsnorm_kernel(T* __restrict__ out, T* __
                                                       int64_t H, float eps) {
   extern __shared__ float row_f[];  // H floats
   __shared__ float red[8];
+  pdl_trigger();
+  pdl_wait();
   const int64_t row = blockIdx.x;
   const T* xr = x + row * H;
   T* rr = residual ? residual + row * H : nullptr;
@@ -73,6 +75,8 @@ __global__ void __launch_bounds__(256) rmsnorm_kernel(T* __restrict__ out, T* __
 template <typename T>
 __global__ void __launch_bounds__(256) silu_and_mul_kernel(T* __restrict__ out, const T* __restrict__ x,
                                                            int64_t M, int64_t H) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t packs = H / 8;
   const int64_t total = M * packs;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -103,6 +107,8 @@ __global__ void __launch_bounds__(256) rope_neox_kernel(T* __restrict__ q, T* __
                                                         const float* __restrict__ cos_sin, const int64_t* __restrict__ pos,
                                                         int num_q_heads, int num_kv_heads, int head_dim, int rot_dim,
                                                         int64_t q_stride, int64_t k_stride) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t tok = blockIdx.x;
   const int half = rot_dim / 2;
   const float* cs = cos_sin + pos[tok] * rot_dim;
@@ -135,12 +141,13 @@ B200_API int b200_rmsnorm(void* out, void* residual, const void* x, const void* 
   if (dtype == B200_BF16) {
     auto kern = rmsnorm_kernel<__nv_bfloat16>;
     if (smem > 48 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)M, 256, smem, st>>>((__nv_bfloat16*)out, (__nv_bfloat16*)residual, (const __nv_bfloat16*)x,
-                                        (const __nv_bfloat16*)weight, H, eps);
+    return launch_k(kern, dim3((unsigned)M), dim3(256), smem, st, 1, true, (__nv_bfloat16*)out, (__nv_bfloat16*)residual,
+                    (const __nv_bfloat16*)x, (const __nv_bfloat16*)weight, H, eps);
   } else if (dtype == B200_F16) {
     auto kern = rmsnorm_kernel<__half>;
     if (smem > 48 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)M, 256, smem, st>>>((__half*)out, (__half*)residual, (const __half*)x, (const __half*)weight, H, eps);
+    return launch_k(kern, dim3((unsigned)M), dim3(256), smem, st, 1, true, (__half*)out, (__half*)residual, (const __half*)x,
+                    (const __half*)weight, H, eps);
   } else {
     return fail(B200_ERR_UNSUPPORTED, "rmsnorm: dtype %d not supported", dtype);
   }
@@ -158,13 +165,12 @@ B200_API int b200_silu_and_mul(void* out, const void* x, int64_t M, int64_t H, i
   const int64_t cap = (int64_t)sm_count() * 8;
   if (blocks > cap) blocks = cap;
   if (dtype == B200_BF16)
-    silu_and_mul_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>((__nv_bfloat16*)out, (const __nv_bfloat16*)x, M, H);
-  else if (dtype == B200_F16)
-    silu_and_mul_kernel<__half><<<(unsigned)blocks, 256, 0, st>>>((__half*)out, (const __half*)x, M, H);
-  else
-    return fail(B200_ERR_UNSUPPORTED, "silu_and_mul: dtype %d not supported", dtype);
-  B200_LAUNCH_OK();
-  return B200_OK;
+    return launch_k(silu_and_mul_kernel<__nv_bfloat16>, dim3((unsigned)blocks), dim3(256), 0, st, 1, true, (__nv_bfloat16*)out,
+                    (const __nv_bfloat16*)x, M, H);
+  if (dtype == B200_F16)
+    return launch_k(silu_and_mul_kernel<__half>, dim3((unsigned)blocks), dim3(256), 0, st, 1, true, (__half*)out,
+                    (const __half*)x, M, H);
+  return fail(B200_ERR_UNSUPPORTED, "silu_and_mul: dtype %d not supported", dtype);
 }
 
 B200_API int b200_rope_neox(void* q, void* k, const float* cos_sin_cache, const int64_t* positions,
@@ -176,14 +182,11 @@ B200_API int b200_rope_neox(void* q, void* k, const float* cos_sin_cache, const 
   B200_REQUIRE(rot_dim % 2 == 0 && rot_dim <= head_dim, "rope_neox: rot_dim %d", rot_dim);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == B200_BF16)
-    rope_neox_kernel<__nv_bfloat16><<<(unsigned)num_tokens, 256, 0, st>>>((__nv_bfloat16*)q, (__nv_bfloat16*)k, cos_sin_cache,
-                                                                      positions, num_q_heads, num_kv_heads, head_dim, rot_dim,
-                                                                      q_token_stride, k_token_stride);
-  else if (dtype == B200_F16)
-    rope_neox_kernel<__half><<<(unsigned)num_tokens, 256, 0, st>>>((__half*)q, (__half*)k, cos_sin_cache, positions, num_q_heads,
-                                                               num_kv_heads, head_dim, rot_dim, q_token_stride, k_token_stride);
-  else
-    return fail(B200_ERR_UNSUPPORTED, "rope_neox: dtype %d not supported", dtype);
-  B200_LAUNCH_OK();
-  return B200_OK;
+    return launch_k(rope_neox_kernel<__nv_bfloat16>, dim3((unsigned)num_tokens), dim3(256), 0, st, 1, true, (__nv_bfloat16*)q,
+                    (__nv_bfloat16*)k, cos_sin_cache, positions, num_q_heads, num_kv_heads, head_dim, rot_dim, q_token_stride,
+                    k_token_stride);
+  if (dtype == B200_F16)
+    return launch_k(rope_neox_kernel<__half>, dim3((unsigned)num_tokens), dim3(256), 0, st, 1, true, (__half*)q, (__half*)k,
+                    cos_sin_cache, positions, num_q_heads, num_kv_heads, head_dim, rot_dim, q_token_stride, k_token_stride);
+  return fail(B200_ERR_UNSUPPORTED, "rope_neox: dtype %d not supported", dtype);
 }

@@ -1,4 +1,6 @@
 // Error plumbing and library info for the C-ABI.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -18,6 +20,15 @@ int fail(b200_status code, const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
   return static_cast<int>(code);
+}
+
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("B200_PDL");
+    on = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  return on != 0;
 }
 
 int sm_count() {

@@ -79,8 +79,15 @@ __device__ __forceinline__ void store_out(void* out, int64_t idx, float v, int i
   else reinterpret_cast<__half*>(out)[idx] = __float2half_rn(v);
 }
 
+// CTAs per SM the shared-memory footprint allows (the decode tiles are small enough for 2: twice the bytes
+// in flight per SM and no half-empty second wave when the tile count is not a multiple of the SM count).
+template <int MODE, int BN, int STAGES>
+constexpr int gemm_ctas_per_sm() {
+  return (MODE != kModeF8Block && GemmSmemLayout<BN, STAGES>::kBytes <= 112 * 1024) ? 2 : 1;
+}
+
 template <int MODE, int BN, int STAGES, bool SWAP>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(kGemmThreads, gemm_ctas_per_sm<MODE, BN, STAGES>())
 gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const GemmArgs g) {
   using L = GemmSmemLayout<BN, STAGES>;
@@ -121,6 +128,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = s_tmem_base;
+  pdl_trigger();  // barriers / TMEM are set up: the next kernel of the stream may start its own prologue
 
   const int a_row0 = blockIdx.x * 128;
   const int b_row0 = blockIdx.y * BN;
@@ -140,7 +148,22 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       // weights are read once (evict-first); activations are re-read by every CTA (evict-last)
       const uint64_t pol_a = SWAP ? kEvictFirst : kEvictLast;
       const uint64_t pol_b = SWAP ? kEvictLast : kEvictFirst;
-      for (int i = 0; i < nkb; ++i) {
+      // The weight operand does not depend on the previous kernel: fill the whole ring with weight tiles
+      // BEFORE waiting on it, so weight streaming overlaps the predecessor's tail (PDL, common.cuh).
+      const int pre = min(nkb, STAGES);
+      for (int i = 0; i < pre; ++i) {
+        mbar_expect_tx(full_bar(i), L::kStage);
+        const uint32_t sa = base + i * L::kStage;
+        if (SWAP) tma_load_2d(sa, &tmap_a, full_bar(i), (kb0 + i) * kBK, a_row0, pol_a);
+        else tma_load_2d(sa + L::kA, &tmap_b, full_bar(i), (kb0 + i) * kBK, b_row0, pol_b);
+      }
+      pdl_wait();  // activations (and their scales) are written by the previous kernel
+      for (int i = 0; i < pre; ++i) {
+        const uint32_t sa = base + i * L::kStage;
+        if (SWAP) tma_load_2d(sa + L::kA, &tmap_b, full_bar(i), (kb0 + i) * kBK, b_row0, pol_b);
+        else tma_load_2d(sa, &tmap_a, full_bar(i), (kb0 + i) * kBK, a_row0, pol_a);
+      }
+      for (int i = pre; i < nkb; ++i) {
         const int s = i % STAGES;
         const uint32_t ph = (i / STAGES) & 1;
         mbar_wait(empty_bar(s), ph ^ 1);
@@ -149,8 +172,11 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         tma_load_2d(sa, &tmap_a, full_bar(s), (kb0 + i) * kBK, a_row0, pol_a);
         tma_load_2d(sa + L::kA, &tmap_b, full_bar(s), (kb0 + i) * kBK, b_row0, pol_b);
       }
+    } else {
+      pdl_wait();
     }
   } else if (warp == 1) {
+    pdl_wait();
     if (lane == 0) {
       constexpr uint32_t idesc = MODE == kModeI8 ? make_idesc(/*s32*/ 2, /*int8*/ 1, 1, 128, BN)
                                                  : make_idesc(/*f32*/ 1, /*e4m3*/ 0, 0, 128, BN);
@@ -173,6 +199,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       if (!kBlock) tc_commit(tmem_full_bar(0));
     }
   } else if (warp >= 4) {
+    pdl_wait();  // scales are read (and the output written) only after the previous kernels have completed
     if constexpr (kBlock) {
       // promote every 128-wide K block into fp32 registers while the next block's MMAs run
 #pragma unroll
@@ -211,6 +238,8 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       tc_fence_after();
     }
   }
+
+  if (warp == 2 || warp == 3) pdl_wait();
 
   // ---- split-K: reduce-scatter the partial accumulators across the cluster through DSMEM -----------------
   if constexpr (SWAP) {
@@ -426,20 +455,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmA
   using L = GemmSmemLayout<BN, STAGES>;
   auto kern = gemm_umma_kernel<MODE, BN, STAGES, SWAP>;
   B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = grid;
-  cfg.blockDim = dim3(kGemmThreads);
-  cfg.dynamicSmemBytes = L::kBytes;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 1;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = SWAP ? g.splits : 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, ta, tb, g));
-  return B200_OK;
+  return launch_k(kern, grid, dim3(kGemmThreads), L::kBytes, st, SWAP ? (unsigned)g.splits : 1u, true, ta, tb, g);
 }
 
 template <int MODE>

@@ -21,6 +21,8 @@ struct KvWriteArgs {
 };
 
 __global__ void __launch_bounds__(256) kv_write_kernel(const KvWriteArgs a) {
+  pdl_trigger();
+  pdl_wait();
   const bool isv = blockIdx.y != 0;
   uint8_t* const cache = isv ? a.cache[1] : a.cache[0];
   const uint8_t* const src = isv ? a.src[1] : a.src[0];
@@ -80,7 +82,5 @@ B200_API int b200_set_kv_buffer(void* k_cache, void* v_cache, const void* k, con
   int64_t blocks = ceil_div(total, 256);
   const int64_t cap = (int64_t)sm_count() * 16;
   if (blocks > cap) blocks = cap;
-  kv_write_kernel<<<dim3((unsigned)blocks, 2), 256, 0, (cudaStream_t)stream>>>(a);
-  B200_LAUNCH_OK();
-  return B200_OK;
+  return launch_k(kv_write_kernel, dim3((unsigned)blocks, 2), dim3(256), 0, (cudaStream_t)stream, 1, true, a);
 }

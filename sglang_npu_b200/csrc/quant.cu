@@ -47,6 +47,8 @@ __global__ void __launch_bounds__(256) per_token_quant_int8_kernel(int8_t* __res
                                                                    const T* __restrict__ x, int64_t K,
                                                                    int64_t x_row_stride) {
   __shared__ float sm[8];
+  pdl_trigger();
+  pdl_wait();
   const int64_t row = blockIdx.x;
   const T* xr = x + row * x_row_stride;
   float amax = 0.f;
@@ -166,13 +168,12 @@ B200_API int b200_per_token_quant_int8(int8_t* xq, float* scale, const void* x, 
   B200_REQUIRE((uintptr_t)x % 16 == 0 && (uintptr_t)xq % 8 == 0, "per_token_quant_int8: alignment");
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == B200_BF16)
-    per_token_quant_int8_kernel<__nv_bfloat16><<<(unsigned)M, 256, 0, st>>>(xq, scale, (const __nv_bfloat16*)x, K, x_row_stride);
-  else if (dtype == B200_F16)
-    per_token_quant_int8_kernel<__half><<<(unsigned)M, 256, 0, st>>>(xq, scale, (const __half*)x, K, x_row_stride);
-  else
-    return fail(B200_ERR_UNSUPPORTED, "per_token_quant_int8: dtype %d not supported", dtype);
-  B200_LAUNCH_OK();
-  return B200_OK;
+    return launch_k(per_token_quant_int8_kernel<__nv_bfloat16>, dim3((unsigned)M), dim3(256), 0, st, 1, true, xq, scale,
+                    (const __nv_bfloat16*)x, K, x_row_stride);
+  if (dtype == B200_F16)
+    return launch_k(per_token_quant_int8_kernel<__half>, dim3((unsigned)M), dim3(256), 0, st, 1, true, xq, scale,
+                    (const __half*)x, K, x_row_stride);
+  return fail(B200_ERR_UNSUPPORTED, "per_token_quant_int8: dtype %d not supported", dtype);
 }
 
 B200_API int b200_per_token_group_quant_fp8(void* xq, float* scales, const void* x, int64_t M, int64_t K,

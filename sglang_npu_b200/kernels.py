@@ -398,3 +398,79 @@ def apply_rope_neox_inplace(positions: torch.Tensor, q: torch.Tensor, k: torch.T
     assert q.stride(-1) == 1 and k.stride(-1) == 1
     check(lib.b200_rope_neox(ptr(q), ptr(k), ptr(cos_sin_cache), ptr(positions), T, hq, hkv, head_dim, rot,
                              q.stride(0), k.stride(0), dtype_code(q.dtype), stream_ptr(q.device)), "b200_rope_neox")
+
+
+# ---- fused steps ---------------------------------------------------------------------
+class Int8Activation(tuple):
+    """(x_q int8 [M, K], x_scale fp32 [M, 1]) produced by a fused producer kernel; accepted by
+    B200W8A8Int8LinearMethod.apply in place of the bf16 activation (skips its own quant launch)."""
+
+    __slots__ = ()
+
+    def __new__(cls, x_q: torch.Tensor, x_scale: torch.Tensor, out_dtype: torch.dtype):
+        return super().__new__(cls, (x_q, x_scale, out_dtype))
+
+    x_q = property(lambda self: self[0])
+    x_scale = property(lambda self: self[1])
+    out_dtype = property(lambda self: self[2])
+
+    @property
+    def shape(self):
+        return self[0].shape
+
+
+def rmsnorm_quant_int8(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: Optional[torch.Tensor] = None,
+                       return_normed: bool = False):
+    """(fused_add_)rmsnorm followed by per_token_quant_int8 in ONE launch.  `residual` is updated in place
+    (residual += x) like sgl_kernel.fused_add_rmsnorm; x itself is left untouched."""
+    require_cuda(x, weight, residual)
+    lib = _cabi.load()
+    H = x.shape[-1]
+    assert x.is_contiguous() and (residual is None or residual.is_contiguous())
+    M = x.numel() // H
+    x_q = torch.empty((M, H), device=x.device, dtype=torch.int8)
+    scale = torch.empty((M, 1), device=x.device, dtype=torch.float32)
+    y = torch.empty_like(x) if return_normed else None
+    check(lib.b200_rmsnorm_quant_int8(ptr(x_q), ptr(scale), ptr(y), ptr(residual), ptr(x), ptr(weight), M, H, float(eps),
+                                      dtype_code(x.dtype), stream_ptr(x.device)), "b200_rmsnorm_quant_int8")
+    act = Int8Activation(x_q, scale, x.dtype)
+    return (act, y) if return_normed else act
+
+
+def silu_and_mul_quant_int8(x: torch.Tensor) -> Int8Activation:
+    """silu_and_mul followed by per_token_quant_int8 in ONE launch; x is [M, 2H] gate|up."""
+    require_cuda(x)
+    lib = _cabi.load()
+    H = x.shape[-1] // 2
+    x2 = x.reshape(-1, 2 * H)
+    if not x2.is_contiguous():
+        x2 = x2.contiguous()
+    M = x2.shape[0]
+    x_q = torch.empty((M, H), device=x.device, dtype=torch.int8)
+    scale = torch.empty((M, 1), device=x.device, dtype=torch.float32)
+    check(lib.b200_silu_and_mul_quant_int8(ptr(x_q), ptr(scale), ptr(x2), M, H, dtype_code(x.dtype), stream_ptr(x.device)),
+          "b200_silu_and_mul_quant_int8")
+    return Int8Activation(x_q, scale, x.dtype)
+
+
+def rope_neox_set_kv(positions: torch.Tensor, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, head_dim: int,
+                     cos_sin_cache: torch.Tensor, k_cache: Optional[torch.Tensor], v_cache: Optional[torch.Tensor],
+                     loc: Optional[torch.Tensor]) -> None:
+    """NeoX RoPE on q / k in place (views of a fused qkv are fine) + set_kv_buffer(k_cache, v_cache, loc, k, v)."""
+    require_cuda(positions, q, k, v, cos_sin_cache, k_cache, v_cache, loc)
+    lib = _cabi.load()
+    assert positions.dtype == torch.int64 and cos_sin_cache.dtype == torch.float32
+    T = q.shape[0]
+    hq, hkv = q.shape[-1] // head_dim, k.shape[-1] // head_dim
+    assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1
+    if k_cache is not None:
+        assert k_cache.dtype == k.dtype and v_cache.dtype == v.dtype and loc.numel() == T and loc.is_contiguous()
+        kc, vc = k_cache.view(k_cache.shape[0], -1), v_cache.view(v_cache.shape[0], -1)
+        kcs, vcs, is64 = kc.stride(0), vc.stride(0), _is64(loc)
+    else:
+        kc = vc = None
+        kcs = vcs = is64 = 0
+    check(lib.b200_rope_neox_set_kv(ptr(q), ptr(k), ptr(v), ptr(cos_sin_cache), ptr(positions), ptr(kc), ptr(vc), ptr(loc),
+                                    is64, T, hq, hkv, head_dim, cos_sin_cache.shape[-1], q.stride(0), k.stride(0),
+                                    v.stride(0), kcs, vcs, dtype_code(q.dtype), stream_ptr(q.device)),
+          "b200_rope_neox_set_kv")

@@ -86,6 +86,10 @@ class B200W8A8Int8LinearMethod(LinearMethodBase):
         layer.weight_scale = Parameter(layer.weight_scale.data, requires_grad=False)
 
     def apply(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None):
+        if isinstance(x, kernels.Int8Activation):  # quantised by the producer kernel (fused rmsnorm / silu-mul)
+            out = kernels.int8_scaled_mm(x.x_q, layer.weight, x.x_scale, layer.weight_scale, out_dtype=x.out_dtype,
+                                         bias=bias)
+            return out
         x_q, x_scale = kernels.per_token_quant_int8(x)
         out = kernels.int8_scaled_mm(x_q.view(-1, x_q.shape[-1]), layer.weight, x_scale, layer.weight_scale,
                                      out_dtype=x.dtype, bias=bias)

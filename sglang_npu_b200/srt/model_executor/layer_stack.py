@@ -83,10 +83,16 @@ class DecoderLayer(nn.Module):
         self.q_size = self.num_heads * cfg.head_dim
         self.kv_size = self.num_kv_heads * cfg.head_dim
         self.attn = RadixAttention(self.num_heads, cfg.head_dim, cfg.head_dim ** -0.5, self.num_kv_heads, layer_id)
+        import os
+
+        self.fused_int8 = (type(self.qkv_proj.quant_method).__name__ == "B200W8A8Int8LinearMethod"
+                           and os.environ.get("B200_FUSE_STEPS", "1") != "0")
         self.input_layernorm = nn.Parameter(torch.ones(cfg.hidden_size, dtype=dtype), requires_grad=False)
         self.post_attention_layernorm = nn.Parameter(torch.ones(cfg.hidden_size, dtype=dtype), requires_grad=False)
 
     def forward(self, positions, hidden_states, forward_batch, residual, cos_sin_cache):
+        if self.fused_int8:
+            return self.forward_fused_int8(positions, hidden_states, forward_batch, residual, cos_sin_cache)
         eps = self.cfg.rms_norm_eps
         if residual is None:
             residual = hidden_states
@@ -103,6 +109,30 @@ class DecoderLayer(nn.Module):
         act = kernels.silu_and_mul(gate_up)
         hidden_states, _ = self.down_proj(act)
         return hidden_states, residual
+
+
+    def _forward_fused_int8(self, positions, hidden_states, forward_batch, residual, cos_sin_cache):
+        """Same layer with the §8f #2 fusions: norm+quant, rope+KV-write, silu-mul+quant (10 launches, not 15)."""
+        eps = self.cfg.rms_norm_eps
+        if residual is None:
+            residual = hidden_states
+            act = kernels.rmsnorm_quant_int8(hidden_states, self.input_layernorm, eps)
+        else:
+            act = kernels.rmsnorm_quant_int8(hidden_states, self.input_layernorm, eps, residual=residual)
+        qkv, _ = self.qkv_proj(act)
+        q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
+        pool = forward_batch.token_to_kv_pool
+        kernels.rope_neox_set_kv(positions, q, k, v, self.cfg.head_dim, cos_sin_cache,
+                                 pool.get_key_buffer(self.attn.layer_id), pool.get_value_buffer(self.attn.layer_id),
+                                 forward_batch.out_cache_loc)
+        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=False)
+        hidden_states, _ = self.o_proj(attn_out)
+        act = kernels.rmsnorm_quant_int8(hidden_states, self.post_attention_layernorm, eps, residual=residual)
+        gate_up, _ = self.gate_up_proj(act)
+        hidden_states, _ = self.down_proj(kernels.silu_and_mul_quant_int8(gate_up))
+        return hidden_states, residual
+
+    forward_fused_int8 = _forward_fused_int8
 
 
 class LayerStack(nn.Module):

@@ -88,3 +88,85 @@ def test_rope_neox_on_strided_qkv(cuda_device, hq, hkv, d, dtype):
     assert_close_path(q2, ref_q, "rope q", max_abs=4e-2)
     assert_close_path(k2, ref_k, "rope k", max_abs=4e-2)
     assert torch.equal(v2.cpu(), v), "rope must not touch v"
+
+
+# ---- fused steps: bit-identical to the two un-fused kernels run back to back ---------------------------------
+@pytest.mark.parametrize("M,H", [(1, 896), (64, 4096), (37, 5120), (130, 8192)])
+@pytest.mark.parametrize("with_residual", [False, True])
+def test_rmsnorm_quant_int8_equals_unfused_and_oracle(cuda_device, M, H, with_residual):
+    g = torch.Generator().manual_seed(M * 7 + H)
+    x = torch.randn(M, H, generator=g).bfloat16().to(cuda_device)
+    r = torch.randn(M, H, generator=g).bfloat16().to(cuda_device)
+    w = (1 + 0.1 * torch.randn(H, generator=g)).bfloat16().to(cuda_device)
+    # un-fused reference flow on the device
+    x1, r1 = x.clone(), r.clone()
+    if with_residual:
+        kernels.fused_add_rmsnorm(x1, r1, w, 1e-5)
+        y1 = x1
+    else:
+        y1 = kernels.rmsnorm(x1, w, 1e-5)
+    q1, s1 = kernels.per_token_quant_int8(y1)
+    r2 = r.clone()
+    act, y2 = kernels.rmsnorm_quant_int8(x, w, 1e-5, residual=r2 if with_residual else None, return_normed=True)
+    assert torch.equal(act.x_q, q1) and torch.equal(act.x_scale, s1) and torch.equal(y2, y1)
+    if with_residual:
+        assert torch.equal(r2, r1)
+    # and against the oracle: norm (tolerance) -> quant of the device's own normed activation (bit-exact)
+    qo_q, qo_s = qo.per_token_quant_int8(y2.cpu())
+    assert torch.equal(act.x_q.cpu(), qo_q) and torch.equal(act.x_scale.cpu().view(-1), qo_s.view(-1))
+
+
+@pytest.mark.parametrize("M,H", [(1, 4864), (64, 14336), (5, 27648), (300, 3584), (2, 64)])
+def test_silu_and_mul_quant_int8_equals_unfused(cuda_device, M, H):
+    x = torch.randn(M, 2 * H, generator=torch.Generator().manual_seed(H + M)).bfloat16().to(cuda_device)
+    y = kernels.silu_and_mul(x)
+    q1, s1 = kernels.per_token_quant_int8(y)
+    act = kernels.silu_and_mul_quant_int8(x)
+    assert torch.equal(act.x_q, q1) and torch.equal(act.x_scale, s1)
+
+
+@pytest.mark.parametrize("hq,hkv,d", [(32, 8, 128), (14, 2, 64), (5, 1, 128)])
+@pytest.mark.parametrize("loc_dtype", [torch.int64, torch.int32])
+def test_rope_neox_set_kv_equals_unfused(cuda_device, hq, hkv, d, loc_dtype):
+    T, slots = 41, 512
+    g = torch.Generator().manual_seed(hq * 3 + d)
+    qkv = torch.randn(T, (hq + 2 * hkv) * d, generator=g).bfloat16().to(cuda_device)
+    pos = torch.randint(0, 4000, (T,), generator=g).to(cuda_device)
+    loc = torch.randperm(slots - 16, generator=g)[:T].add(16).to(loc_dtype).to(cuda_device)
+    cache = compute_cos_sin_cache(d, 4096, 5e5).to(cuda_device)
+    a, b = qkv.clone(), qkv.clone()
+    kc1 = torch.zeros(slots, hkv, d, dtype=torch.bfloat16, device=cuda_device)
+    vc1, kc2, vc2 = torch.zeros_like(kc1), torch.zeros_like(kc1), torch.zeros_like(kc1)
+    q1, k1, v1 = a.split([hq * d, hkv * d, hkv * d], dim=-1)
+    kernels.apply_rope_neox_inplace(pos, q1, k1, d, cache)
+    kernels.set_kv_buffer(kc1, vc1, loc, k1, v1)
+    q2, k2, v2 = b.split([hq * d, hkv * d, hkv * d], dim=-1)
+    kernels.rope_neox_set_kv(pos, q2, k2, v2, d, cache, kc2, vc2, loc)
+    assert_close_path(q2, q1, "fused rope q", max_abs=1e-2)  # FMA contraction may differ by an ulp between kernels
+    assert_close_path(k2, k1, "fused rope k", max_abs=1e-2)
+    assert torch.equal(vc2, vc1), "v rows must be copied bit-exactly into the cache"
+    assert torch.equal(kc2.view(slots, -1)[loc.long()], k2), "cache rows must equal the rotated k bit-exactly"
+    touched = torch.zeros(slots, dtype=torch.bool, device=cuda_device)
+    touched[loc.long()] = True
+    assert not kc2[~touched].any() and not vc2[~touched].any()
+    # oracle
+    ref_q, ref_k = qo.rope_neox(pos.cpu(), qkv.cpu()[:, : hq * d], qkv.cpu()[:, hq * d: (hq + hkv) * d], d, cache.cpu())
+    assert_close_path(q2, ref_q, "fused rope q vs oracle", max_abs=4e-2)
+    assert_close_path(k2, ref_k, "fused rope k vs oracle", max_abs=4e-2)
+
+
+def test_int8_linear_accepts_prequantised_activation(cuda_device):
+    from sglang_npu_b200 import synth
+    from sglang_npu_b200.srt.layers.linear import RowParallelLinear
+    from sglang_npu_b200.srt.layers.quantization.w8a8_int8 import B200W8A8Int8Config
+
+    with torch.device(cuda_device):
+        lin = RowParallelLinear(1024, 512, bias=False, quant_config=B200W8A8Int8Config(), params_dtype=torch.bfloat16)
+    w, s = synth.int8_weight(512, 1024, 3)
+    lin.weight_loader(lin.weight, w.to(cuda_device))
+    lin.weight_loader(lin.weight_scale, s.view(-1, 1).to(cuda_device))
+    lin.quant_method.process_weights_after_loading(lin)
+    x = torch.randn(9, 2048, generator=torch.Generator().manual_seed(0)).bfloat16().to(cuda_device)
+    y_ref, _ = lin(kernels.silu_and_mul(x))
+    y_fused, _ = lin(kernels.silu_and_mul_quant_int8(x))
+    assert torch.equal(y_ref, y_fused)
