@@ -69,7 +69,9 @@ def test_rmsnorm_and_fused_add(cuda_device, M, H, dtype):
 def test_silu_and_mul(cuda_device, M, H):
     x = torch.randn(M, 2 * H, generator=torch.Generator().manual_seed(H)).bfloat16()
     out = kernels.silu_and_mul(x.to(cuda_device))
-    assert_close_path(out, qo.silu_and_mul(x.float()).bfloat16(), "silu_and_mul", max_abs=4e-2)
+    # forward_native on the bf16 tensor: silu rounded to bf16, then the product rounded (activation.py:60-62);
+    # one bf16 ulp (2^-8 relative) of slack for the fast-exp sigmoid
+    torch.testing.assert_close(out.cpu().float(), qo.silu_and_mul(x).float(), rtol=1.6e-2, atol=2e-3)
 
 
 @pytest.mark.parametrize("hq,hkv,d", [(32, 8, 128), (14, 2, 64), (5, 1, 128)])
