@@ -327,8 +327,7 @@ def main():
             pass
 
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        _finish(world, dev)
         return 0
 
     cpu_baseline = None
@@ -353,9 +352,25 @@ def main():
     if args.layers:
         line["invalid"] = f"debug run with {n_layers} layers"
     print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    _finish(world, dev)
     return 0
+
+
+def _finish(world, dev):
+    """Leave without tearing NCCL down: destroy_process_group() can block for minutes when captured CUDA graphs
+    still hold the communicator; the measurements are done, so synchronise, meet the other ranks and exit hard."""
+    if world <= 1:
+        return
+    import torch.distributed as dist
+
+    torch.cuda.synchronize(dev)
+    try:
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+    finally:
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
