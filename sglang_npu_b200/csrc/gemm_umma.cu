@@ -21,6 +21,7 @@
 // epilogue warps promote it into fp32 registers with sa[m,kb] * sb[n/128,kb] while the next block's MMAs run.
 // Warp roles: warp 0 = TMA producer (one lane), warp 1 = MMA issuer (one lane), warp 2 = TMEM allocator,
 // warps 4-7 = epilogue (TMEM lane quarter = warp % 4).
+#include <cstdlib>
 #include <unordered_map>
 
 #include "sm100.cuh"
@@ -413,6 +414,158 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (warp == 2) tmem_dealloc<kTmemCols>(tmem_base);
 }
 
+// ---- prefill: persistent CTAs, double-buffered TMEM accumulators -------------------------------------------------------
+// Tensor-bound orientation for M > 256 (int8 / per-channel FP8): one CTA per SM walks output tiles of 128 tokens x
+// 256 channels (tile t -> n_tile = t / tiles_m, m_tile = t % tiles_m: the CTAs running at any moment share two or
+// three weight tiles and the whole activation matrix stays in L2).  The 512 TMEM columns hold TWO 128x256 fp32/s32
+// accumulators: while the epilogue warps drain tile j (tcgen05.ld -> scales -> bf16 -> 32-byte row segments), the
+// MMA thread already accumulates tile j+1 into the other buffer and the TMA thread runs ahead through the smem ring
+// without draining it at tile boundaries — no per-tile prologue / epilogue bubbles.
+constexpr int kPfBN = 256;
+constexpr int kPfStages = 4;
+
+template <int MODE>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const GemmArgs g, const int tiles_m, const int num_tiles) {
+  using L = GemmSmemLayout<kPfBN, kPfStages>;
+  constexpr int kKind = MODE == kModeI8 ? kKindI8 : kKindF8;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint32_t s_tmem_base;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar = base + L::kBarOff;
+  auto full_bar = [&](int s) { return bar + s * 8; };
+  auto empty_bar = [&](int s) { return bar + (kPfStages + s) * 8; };
+  auto tmem_full_bar = [&](int b) { return bar + (2 * kPfStages + b) * 8; };
+  auto tmem_empty_bar = [&](int b) { return bar + (2 * kPfStages + 2 + b) * 8; };
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_a);
+    prefetch_tmap(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kPfStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(tmem_full_bar(b), 1);
+      mbar_init(tmem_empty_bar(b), 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<512>(smem_u32(&s_tmem_base));
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = s_tmem_base;
+  pdl_trigger();
+  pdl_wait();
+
+  const int nkb = g.num_kb;
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int n_tile = t / tiles_m;
+        const int a_row0 = (t - n_tile * tiles_m) * 128;
+        const int b_row0 = n_tile * kPfBN;
+        for (int i = 0; i < nkb; ++i, ++it) {
+          const int s = it % kPfStages;
+          mbar_wait(empty_bar(s), ((it / kPfStages) & 1) ^ 1);
+          mbar_expect_tx(full_bar(s), L::kStage);
+          const uint32_t sa = base + s * L::kStage;
+          tma_load_2d(sa, &tmap_a, full_bar(s), i * kBK, a_row0, kEvictLast);
+          tma_load_2d(sa + L::kA, &tmap_b, full_bar(s), i * kBK, b_row0, kEvictNormal);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = MODE == kModeI8 ? make_idesc(/*s32*/ 2, /*int8*/ 1, 1, 128, kPfBN)
+                                                 : make_idesc(/*f32*/ 1, /*e4m3*/ 0, 0, 128, kPfBN);
+      uint32_t it = 0;
+      int j = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++j) {
+        const int buf = j & 1;
+        mbar_wait(tmem_empty_bar(buf), ((j >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * kPfBN;
+        for (int i = 0; i < nkb; ++i, ++it) {
+          const int s = it % kPfStages;
+          mbar_wait(full_bar(s), (it / kPfStages) & 1);
+          tc_fence_after();
+          const uint32_t sa = base + s * L::kStage;
+          const uint64_t da = smem_desc_k_sw128(sa);
+          const uint64_t db = smem_desc_k_sw128(sa + L::kA);
+#pragma unroll
+          for (int k = 0; k < kBK / 32; ++k) umma<kKind>(d_tmem, da + 2 * k, db + 2 * k, idesc, (i | k) != 0);
+          tc_commit(empty_bar(s));
+        }
+        tc_commit(tmem_full_bar(buf));
+      }
+    }
+  } else if (warp >= 4) {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const bool has_bias = g.bias != nullptr;
+    int j = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++j) {
+      const int buf = j & 1;
+      const int n_tile = t / tiles_m;
+      const int m = (t - n_tile * tiles_m) * 128 + row;
+      const int b_row0 = n_tile * kPfBN;
+      const bool m_ok = m < g.M;
+      const float smv = m_ok ? g.scale_m[m] : 0.f;
+      mbar_wait(tmem_full_bar(buf), (j >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * kPfBN;
+#pragma unroll 2
+      for (int c0 = 0; c0 < kPfBN; c0 += 16) {
+        const int n0 = b_row0 + c0;
+        if (n0 >= g.N) break;  // warp-uniform
+        uint32_t r[16];
+        tmem_ld16(taddr + c0, r);
+        tmem_ld_wait();
+        if (m_ok) {
+          const int valid = min(16, g.N - n0);  // N % 8 == 0: a 16-column group is full or exactly half full
+          float v[16];
+#pragma unroll
+          for (int jj = 0; jj < 16; ++jj) {
+            float bias = 0.f, sn = 0.f;
+            if (jj < valid) {
+              sn = __ldg(g.scale_n + n0 + jj);
+              if (has_bias) bias = load_bias(g.bias, n0 + jj, g.out_is_bf16);
+            }
+            v[jj] = finalize<MODE>(r[jj], smv, sn, has_bias, bias);
+          }
+          uint32_t p[8];
+#pragma unroll
+          for (int jj = 0; jj < 8; ++jj)
+            p[jj] = g.out_is_bf16 ? pack2<__nv_bfloat16>(v[2 * jj], v[2 * jj + 1]) : pack2<__half>(v[2 * jj], v[2 * jj + 1]);
+          uint8_t* dstp = reinterpret_cast<uint8_t*>(g.out) + ((int64_t)m * g.N + n0) * 2;
+          *reinterpret_cast<uint4*>(dstp) = make_uint4(p[0], p[1], p[2], p[3]);
+          if (valid > 8) *reinterpret_cast<uint4*>(dstp + 16) = make_uint4(p[4], p[5], p[6], p[7]);
+          if (MODE == kModeI8 && g.acc_out) {
+            int32_t* ad = g.acc_out + (int64_t)m * g.N + n0;
+#pragma unroll
+            for (int jj = 0; jj < 16; jj += 4)
+              if (jj < valid) *reinterpret_cast<uint4*>(ad + jj) = make_uint4(r[jj], r[jj + 1], r[jj + 2], r[jj + 3]);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tmem_empty_bar(buf));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<512>(tmem_base);
+}
+
 // ---- host side -----------------------------------------------------------------------------------
 struct TmapKey {
   const void* p;
@@ -493,6 +646,20 @@ static int run_gemm(GemmArgs g, const void* a, const void* b, int64_t M, int64_t
   // prefill orientation: A = tokens [M, K], B = weights [N, K]
   g.splits = 1;
   g.kb_per_split = g.num_kb;
+  if constexpr (MODE != kModeF8Block) {
+    static const bool persist = getenv("B200_GEMM_PERSIST") == nullptr || getenv("B200_GEMM_PERSIST")[0] != '0';
+    if (N >= kPfBN && persist) {
+      if ((rc = cached_tmap(&ta, a, (uint64_t)M, (uint64_t)K, 128)) != B200_OK) return rc;
+      if ((rc = cached_tmap(&tb, b, (uint64_t)N, (uint64_t)K, (uint32_t)kPfBN)) != B200_OK) return rc;
+      const int tiles_m = (int)ceil_div(M, 128);
+      const int num_tiles = tiles_m * (int)ceil_div(N, kPfBN);
+      using L = GemmSmemLayout<kPfBN, kPfStages>;
+      auto kern = gemm_prefill_kernel<MODE>;
+      B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
+      const int ctas = num_tiles < sm_count() ? num_tiles : sm_count();
+      return launch_k(kern, dim3((unsigned)ctas), dim3(kGemmThreads), L::kBytes, st, 1, true, ta, tb, g, tiles_m, num_tiles);
+    }
+  }
   const int bn = (MODE != kModeF8Block && N >= 256) ? 256 : 128;
   if ((rc = cached_tmap(&ta, a, (uint64_t)M, (uint64_t)K, 128)) != B200_OK) return rc;
   if ((rc = cached_tmap(&tb, b, (uint64_t)N, (uint64_t)K, (uint32_t)bn)) != B200_OK) return rc;

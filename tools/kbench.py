@@ -128,6 +128,36 @@ def bench_awq(args):
                                   gbs=round(tot_b / tot_t / 1e6, 1), frac_hbm=round(tot_b / tot_t / 1e6 / HBM, 3))), flush=True)
 
 
+def bench_peak(args):
+    """Library ceilings measured the way MEASURED_PEAKS.json measures bf16: cuBLASLt int8 (torch._int_mm) and
+    fp8 (torch._scaled_mm) at 8192^3 and at the Llama-8B prefill shapes, plus SM clocks under load."""
+    import subprocess
+    dev = torch.device("cuda")
+    shapes = [(8192, 8192, 8192), (8192, 6144, 4096), (8192, 28672, 4096), (8192, 4096, 14336)]
+    for (m, n, k) in shapes:
+        a = torch.randint(-127, 128, (m, k), device=dev, dtype=torch.int8)
+        b = torch.randint(-127, 128, (n, k), device=dev, dtype=torch.int8)
+        row = dict(m=m, n=n, k=k)
+        try:
+            t = timeit_rot(lambda c: (lambda: torch._int_mm(a, b.t())), 1, iters=16)
+            row["cublaslt_int8_tops"] = round(2 * m * n * k / t / 1e9, 1)
+        except Exception as e:  # noqa: BLE001
+            row["cublaslt_int8_err"] = str(e)[:80]
+        try:
+            a8, b8 = a.to(torch.float8_e4m3fn), b.to(torch.float8_e4m3fn)
+            one = torch.ones((), device=dev)
+            t = timeit_rot(lambda c: (lambda: torch._scaled_mm(a8, b8.t(), one, one, out_dtype=torch.bfloat16)), 1, iters=16)
+            row["cublaslt_fp8_tflops"] = round(2 * m * n * k / t / 1e9, 1)
+        except Exception as e:  # noqa: BLE001
+            row["cublaslt_fp8_err"] = str(e)[:80]
+        sa, sb = torch.rand(m, device=dev), torch.rand(n, device=dev)
+        t = timeit_rot(lambda c: (lambda: kernels.int8_scaled_mm(a, b.t(), sa, sb, torch.bfloat16)), 1, iters=16)
+        row["b200_int8_tops"] = round(2 * m * n * k / t / 1e9, 1)
+        q = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,power.draw", "--format=csv,noheader"], capture_output=True, text=True)
+        row["smi_after"] = q.stdout.strip()
+        print(json.dumps(row), flush=True)
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("what")
@@ -141,4 +171,4 @@ if __name__ == "__main__":
     ap.add_argument("--m", type=int, default=0)
     ap.add_argument("--ragged", action="store_true")
     args = ap.parse_args()
-    {"decode": bench_decode, "gemm_int8": bench_gemm_int8, "awq": bench_awq}[args.what](args)
+    {"decode": bench_decode, "gemm_int8": bench_gemm_int8, "awq": bench_awq, "peak": bench_peak}[args.what](args)
