@@ -13,7 +13,9 @@
 // p is fetched from the cache slot req_to_token[req, p]; when k_new/v_new are given, positions
 // >= prefix come from those contiguous activations instead (save_kv_cache = False callers).
 // The tcgen05/TMEM version of this tile loop is the next step for this row.
-#include "common.cuh"
+#include <cstdlib>
+
+#include "extend_attn.cuh"
 
 namespace b200 {
 
@@ -21,26 +23,7 @@ constexpr int kExtWarps = 4;
 constexpr int kExtThreads = kExtWarps * 32;
 constexpr int kExtBM = 64;
 constexpr int kExtBN = 64;
-constexpr float kLog2eExt = 1.4426950408889634f;
 
-struct ExtendArgs {
-  void* o;
-  const void* q;
-  const void* k_new;
-  const void* v_new;
-  const void* k_cache;
-  const void* v_cache;
-  const int32_t* req_to_token;
-  int64_t req_to_token_stride;
-  const void* req_pool_indices;
-  int index_is_int64;
-  const int32_t* qo_indptr;
-  const int32_t* prefix_lens;
-  int batch, num_q_heads, num_kv_heads;
-  int64_t q_token_stride, o_token_stride, knew_token_stride, vnew_token_stride, kv_token_stride;
-  float scale_log2, sm_scale, logit_cap;
-  int causal;
-};
 
 // Load one [64 x D] K tile and V tile (KV positions kv0 .. kv0+63 of the request).
 template <typename T, int D>
@@ -315,6 +298,11 @@ B200_API int b200_extend_attn(
   a.kv_token_stride = kv_token_stride;
   a.sm_scale = sm_scale; a.scale_log2 = sm_scale * kLog2eExt; a.logit_cap = logit_cap; a.causal = causal;
   cudaStream_t st = (cudaStream_t)stream;
+  // tcgen05 / TMEM tiles (extend_attn_umma.cu) unless the whole batch is a handful of query rows, where 128-row
+  // MMA tiles would be mostly padding; B200_EXTEND_LEGACY=1 forces the mma.sync kernel (A/B measurements)
+  static const bool legacy = getenv("B200_EXTEND_LEGACY") != nullptr && getenv("B200_EXTEND_LEGACY")[0] == '1';
+  if (!legacy && max_extend_len > 16 && (head_dim == 128 || head_dim == 64) && (dtype == B200_BF16 || dtype == B200_F16))
+    return launch_extend_umma(a, max_extend_len, head_dim, dtype, st);
   if (dtype == B200_BF16) {
     if (head_dim == 128) return launch_extend<__nv_bfloat16, 128>(a, max_extend_len, st);
     if (head_dim == 64) return launch_extend<__nv_bfloat16, 64>(a, max_extend_len, st);
