@@ -15,10 +15,10 @@
 //   lazy rescale: O (and the running sum) is rescaled in TMEM only for warps where some row's max grew by more
 //               than 2^8 since the max it is normalised to; otherwise the stale max keeps being used (exact after
 //               the final 1/l), so the TMEM round-trip of O disappears from the steady state.
-// Warp roles: 0-3 KV gather (16-byte cp.async of 256-byte cache rows through req_to_token — any page_size —
-// placed directly in the UMMA swizzle), 4 = MMA issuer (one lane) + TMEM allocator, 8-11 softmax / correction /
-// epilogue (TMEM lane quarter = warp % 4).  mbarriers: kv_full/kv_empty per stage, s_full per S buffer,
-// p_full, pv_done.
+// Warp roles: 0-1 K gather, 2-3 V gather (16-byte cp.async of 256-byte cache rows through req_to_token — any
+// page_size — placed directly in the UMMA swizzle; independent 2-stage rings, page ids fetched a tile ahead),
+// 4 = MMA issuer (one lane) + TMEM allocator, 8-11 softmax / correction / epilogue (TMEM lane quarter = warp % 4).
+// mbarriers: k_full/k_empty and v_full/v_empty per stage, s_full per S buffer, p_full, pv_done.
 #include <type_traits>
 
 #include "extend_attn.cuh"
@@ -54,42 +54,135 @@ __device__ __forceinline__ uint32_t sw128_off(int r, int c, int half_bytes) {
   return (uint32_t)((c >> 3) * half_bytes + (r >> 3) * 1024 + (r & 7) * 128 + (((c & 7) ^ (r & 7)) << 4));
 }
 
-// Gather one K tile and one V tile (KV positions kv0 .. kv0+127) with 16-byte cp.async: 16 lanes cover one
-// 256-byte row, so a warp instruction reads two whole rows.
+// Gather one [128 x D] tile of K (or V) rows (KV positions kv0 .. kv0+127) with 16-byte cp.async.  A "stream" is
+// two warps; warp w of the stream owns rows 64w .. 64w+63.  D/8 lanes cover one row, so a warp instruction reads
+// 32 / (D/8) whole rows.  The rows' cache slots come from two coalesced page-table loads per warp (`slots`, loaded
+// ahead of time by ux_load_slots) and are handed round with shuffles — no dependent global load per row.
+struct UxSlots {
+  int32_t lo, hi;  // slot of row 64w + lane, 64w + 32 + lane
+};
+
+__device__ __forceinline__ UxSlots ux_load_slots(const int32_t* __restrict__ r2t_row, int kv0, int kv_end, int w, int lane) {
+  UxSlots s;
+  const int p0 = kv0 + 64 * w + lane;
+  s.lo = p0 < kv_end ? __ldg(r2t_row + p0) : 0;
+  s.hi = p0 + 32 < kv_end ? __ldg(r2t_row + p0 + 32) : 0;
+  return s;
+}
+
 template <typename T, int D>
-__device__ __forceinline__ void ux_load_kv(const ExtendArgs& a, const int32_t* __restrict__ r2t_row, int kv0, int kv_end,
-                                           int prefix, int64_t new_base_tok, int kvh, uint32_t smem_k, uint32_t smem_v,
-                                           int tid) {
-  constexpr int kChunks = D / 8;
-  constexpr int kRowsPerPass = kUxProducers / kChunks;
-  const int c = tid % kChunks;
-  const int r0 = tid / kChunks;
-  const T* k_cache = reinterpret_cast<const T*>(a.k_cache);
-  const T* v_cache = reinterpret_cast<const T*>(a.v_cache);
-  const T* k_new = reinterpret_cast<const T*>(a.k_new);
-  const T* v_new = reinterpret_cast<const T*>(a.v_new);
-#pragma unroll 4
-  for (int p = 0; p < kUxBN / kRowsPerPass; ++p) {
-    const int r = r0 + p * kRowsPerPass;
-    const int pos = kv0 + r;
-    const bool valid = pos < kv_end;
-    const T* ksrc = k_cache;
-    const T* vsrc = v_cache;
-    if (valid) {
-      if (k_new != nullptr && pos >= prefix) {
-        const int64_t tok = new_base_tok + (pos - prefix);
-        ksrc = k_new + tok * a.knew_token_stride + kvh * D + c * 8;
-        vsrc = v_new + tok * a.vnew_token_stride + kvh * D + c * 8;
-      } else {
-        const int64_t off = (int64_t)__ldg(r2t_row + pos) * a.kv_token_stride + kvh * D + c * 8;
-        ksrc = k_cache + off;
-        vsrc = v_cache + off;
-      }
-    }
-    const uint32_t so = sw128_off(r, c, UxSmem<D>::kHalf);
-    cp_async16_pred(smem_k + so, ksrc, valid);  // rows past kv_end are zero-filled (and masked in the softmax)
-    cp_async16_pred(smem_v + so, vsrc, valid);
+__device__ __forceinline__ void ux_load_tile(const T* __restrict__ cache, const T* __restrict__ fresh, int64_t kv_token_stride,
+                                             int64_t fresh_token_stride, const UxSlots& slots, int kv0, int kv_end, int prefix,
+                                             int64_t new_base_tok, int kvh, uint32_t smem_tile, int w, int lane) {
+  constexpr int kChunks = D / 8;             // 16-byte chunks per row
+  constexpr int kRpp = 32 / kChunks;         // rows per warp pass (2 for D=128, 4 for D=64)
+  constexpr int kPeriod = 8 / kRpp;          // passes per 8-row swizzle group
+  const int c = lane % kChunks;
+  const int rl = lane / kChunks;
+  // Everything that depends on the lane is hoisted: inside the fully unrolled loop one copy costs a shuffle (slot),
+  // a 64-bit multiply-add (address), a compare (tail) and the cp.async with an immediate shared-memory offset.
+  uint32_t lane_off[kPeriod];
+#pragma unroll
+  for (int bq = 0; bq < kPeriod; ++bq) {
+    const int r7 = bq * kRpp + rl;
+    lane_off[bq] = smem_tile + (uint32_t)((c >> 3) * UxSmem<D>::kHalf + (8 * w) * 1024 + r7 * 128 + (((c & 7) ^ r7) << 4));
   }
+  const T* cbase = cache + kvh * D + c * 8;
+  const int pos0 = kv0 + 64 * w + rl;
+  if (fresh == nullptr) {
+#pragma unroll
+    for (int p = 0; p < 64 / kRpp; ++p) {
+      const int32_t slot = __shfl_sync(0xffffffffu, (p * kRpp < 32) ? slots.lo : slots.hi, ((p * kRpp) & 31) + rl);
+      const bool valid = pos0 + p * kRpp < kv_end;
+      cp_async16_pred(lane_off[p % kPeriod] + (p / kPeriod) * 1024, cbase + (int64_t)slot * kv_token_stride, valid);
+    }
+  } else {  // save_kv_cache = False callers: positions >= prefix come from the contiguous new-token activations
+    const T* fbase = fresh + kvh * D + c * 8;
+#pragma unroll 4
+    for (int p = 0; p < 64 / kRpp; ++p) {
+      const int32_t slot = __shfl_sync(0xffffffffu, (p * kRpp < 32) ? slots.lo : slots.hi, ((p * kRpp) & 31) + rl);
+      const int pos = pos0 + p * kRpp;
+      const T* src = pos >= prefix ? fbase + (new_base_tok + (pos - prefix)) * fresh_token_stride
+                                   : cbase + (int64_t)slot * kv_token_stride;
+      cp_async16_pred(lane_off[p % kPeriod] + (p / kPeriod) * 1024, pos < kv_end ? src : cbase, pos < kv_end);
+    }
+  }
+}
+
+// ---- softmax row helpers: the calling thread owns one query row = one TMEM lane ----------------------------------
+// MODE 0: plain scale; 1: scale + causal / tail mask; 2: logit cap (tanh) + mask.  Scores are handled in the exp2
+// domain: t = s * (sm_scale * log2 e).
+struct SoftmaxCtx {
+  float scale_log2, cap_in, cap_out;
+  int lim, kv_end;
+};
+
+template <int MODE>
+__device__ __forceinline__ float ux_score(float s, const SoftmaxCtx& cx, int pos) {
+  float v = s;
+  if (MODE == 2) v = cx.cap_out * tanh_approx(s * cx.cap_in);
+  if (MODE >= 1 && (pos > cx.lim || pos >= cx.kv_end)) v = -INFINITY;
+  return v;
+}
+
+// max over the row's 128 scores of this tile (already in the exp2 domain)
+template <int MODE>
+__device__ __forceinline__ float ux_row_max(uint32_t t_s, const SoftmaxCtx& cx, int kv0) {
+  float mx = -INFINITY;
+  uint32_t ra[32], rb[32];
+  tmem_ld32(t_s, ra);
+  tmem_ld_wait();
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    tmem_ld32(t_s + 64 * h + 32, rb);  // in flight while the previous 32 columns are reduced
+#pragma unroll
+    for (int i = 0; i < 32; ++i) mx = fmaxf(mx, ux_score<MODE>(__uint_as_float(ra[i]), cx, kv0 + 64 * h + i));
+    tmem_ld_wait();
+    if (h == 0) tmem_ld32(t_s + 64, ra);
+#pragma unroll
+    for (int i = 0; i < 32; ++i) mx = fmaxf(mx, ux_score<MODE>(__uint_as_float(rb[i]), cx, kv0 + 64 * h + 32 + i));
+    if (h == 0) tmem_ld_wait();
+  }
+  return MODE == 2 ? mx : mx * cx.scale_log2;  // sm_scale > 0: max commutes with the scaling
+}
+
+// p = exp2(t - m) for the row's 128 scores, written as T into the K-major SWIZZLE_128B P tile; returns sum(p)
+template <typename T, int MODE>
+__device__ __forceinline__ void ux_exp_store32(const uint32_t (&r)[32], const SoftmaxCtx& cx, int pos0, float m_use, float& sum,
+                                               uint32_t sp, int row, int c0, int half_bytes) {
+  float p[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    const float v = ux_score<MODE>(__uint_as_float(r[i]), cx, pos0 + i);
+    p[i] = fast_exp2(MODE == 2 ? v - m_use : fmaf(v, cx.scale_log2, -m_use));  // masked: fma(-inf, +scale, .) = -inf -> 0
+    sum += p[i];
+  }
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    const uint32_t w0 = pack2<T>(p[8 * g + 0], p[8 * g + 1]), w1 = pack2<T>(p[8 * g + 2], p[8 * g + 3]);
+    const uint32_t w2 = pack2<T>(p[8 * g + 4], p[8 * g + 5]), w3 = pack2<T>(p[8 * g + 6], p[8 * g + 7]);
+    const uint32_t addr = sp + sw128_off(row, (c0 >> 3) + g, half_bytes);
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+  }
+}
+
+template <typename T, int MODE>
+__device__ __forceinline__ float ux_row_exp(uint32_t t_s, const SoftmaxCtx& cx, int kv0, float m_use, uint32_t sp, int row,
+                                            int half_bytes) {
+  float sum = 0.f;
+  uint32_t ra[32], rb[32];
+  tmem_ld32(t_s, ra);
+  tmem_ld_wait();
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    tmem_ld32(t_s + 64 * h + 32, rb);
+    ux_exp_store32<T, MODE>(ra, cx, kv0 + 64 * h, m_use, sum, sp, row, 64 * h, half_bytes);
+    tmem_ld_wait();
+    if (h == 0) tmem_ld32(t_s + 64, ra);
+    ux_exp_store32<T, MODE>(rb, cx, kv0 + 64 * h + 32, m_use, sum, sp, row, 64 * h + 32, half_bytes);
+    if (h == 0) tmem_ld_wait();
+  }
+  return sum;
 }
 
 }  // namespace
@@ -102,11 +195,13 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
   __shared__ uint32_t s_tmem_base;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar = base + L::kBar;
-  auto kv_full = [&](int s) { return bar + s * 8; };
-  auto kv_empty = [&](int s) { return bar + (2 + s) * 8; };
-  auto s_full = [&](int b) { return bar + (4 + b) * 8; };
-  const uint32_t p_full = bar + 6 * 8;
-  const uint32_t pv_done = bar + 7 * 8;
+  auto k_full = [&](int s) { return bar + s * 8; };
+  auto k_empty = [&](int s) { return bar + (2 + s) * 8; };
+  auto v_full = [&](int s) { return bar + (4 + s) * 8; };
+  auto v_empty = [&](int s) { return bar + (6 + s) * 8; };
+  auto s_full = [&](int b) { return bar + (8 + b) * 8; };
+  const uint32_t p_full = bar + 10 * 8;
+  const uint32_t pv_done = bar + 11 * 8;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -130,8 +225,10 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
   if (warp == 4) {
     if (lane == 0) {
       for (int s = 0; s < 2; ++s) {
-        mbar_init(kv_full(s), 4);  // one arrive per producer warp
-        mbar_init(kv_empty(s), 1);
+        mbar_init(k_full(s), 2);  // one arrive per warp of the stream
+        mbar_init(k_empty(s), 1);
+        mbar_init(v_full(s), 2);
+        mbar_init(v_empty(s), 1);
         mbar_init(s_full(s), 1);
       }
       mbar_init(p_full, 4);  // one arrive per softmax warp
@@ -148,15 +245,24 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
   constexpr uint32_t kOCol = 256;  // S buffers at columns 0 and 128, O at 256
 
   if (warp < 4) {
-    // ---- producers: Q once, then K/V tiles through a 2-stage ring -----------------------------------------
-    const int tid = threadIdx.x;
+    // ---- producers: warps 0-1 stream K tiles (and Q once), warps 2-3 stream V tiles; each stream runs its own
+    //      2-stage ring, so K of tile j+2 is fetched as soon as Q K^T of tile j has retired ---------------------------
+    const bool is_v = warp >= 2;
+    const int w = warp & 1;
     const int64_t req = load_index(a.req_pool_indices, b, a.index_is_int64);
     const int32_t* r2t_row = a.req_to_token + req * a.req_to_token_stride;
-    {
+    const T* cache = reinterpret_cast<const T*>(is_v ? a.v_cache : a.k_cache);
+    const T* fresh = reinterpret_cast<const T*>(is_v ? a.v_new : a.k_new);
+    const int64_t fresh_stride = is_v ? a.vnew_token_stride : a.knew_token_stride;
+    const uint32_t ring = base + (is_v ? L::kV : L::kK);
+    auto full = [&](int s) { return is_v ? v_full(s) : k_full(s); };
+    auto empty = [&](int s) { return is_v ? v_empty(s) : k_empty(s); };
+    if (!is_v) {
       constexpr int kChunks = D / 8;
-      constexpr int kRowsPerPass = kUxProducers / kChunks;
-      const int c = tid % kChunks;
-      const int r0 = tid / kChunks;
+      constexpr int kRowsPerPass = 64 / kChunks;
+      const int t64 = w * 32 + lane;
+      const int c = t64 % kChunks;
+      const int r0 = t64 / kChunks;
       const T* qb = reinterpret_cast<const T*>(a.q) + (int64_t)head * D;
 #pragma unroll 4
       for (int p = 0; p < kUxBM / kRowsPerPass; ++p) {
@@ -166,25 +272,28 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
         cp_async16_pred(base + L::kQ + sw128_off(r, c, L::kHalf), src, valid);
       }
     }
+    UxSlots slots = ux_load_slots(r2t_row, 0, kv_end, w, lane);
     for (int j = 0; j < n_tiles; ++j) {
       const int s = j & 1;
+      while (!mbar_try_wait(empty(s), ((j >> 1) & 1) ^ 1)) __nanosleep(64);  // do not steal issue slots from the softmax warp
+      ux_load_tile<T, D>(cache, fresh, a.kv_token_stride, fresh_stride, slots, j * kUxBN, kv_end, prefix, q_start, kvh,
+                         ring + s * L::kTile, w, lane);
+      cp_async_commit();
+      if (j + 1 < n_tiles) slots = ux_load_slots(r2t_row, (j + 1) * kUxBN, kv_end, w, lane);  // page ids of the next tile
       if (j > 0) {
-        // publish tile j-1 BEFORE waiting for a free stage: the MMA warp issues Q K^T of tile j-1 ahead of the
-        // P V that frees the stage of tile j
-        cp_async_wait<0>();
+        // tile j-1 has landed once at most one group is outstanding.  It is published only now, AFTER tile j was
+        // issued (copies of consecutive tiles overlap); the stage tile j+1 needs is freed by an MMA that depends
+        // on tile j-1, which is public by the time this loop waits for it — no cycle.
+        cp_async_wait<1>();
         fence_proxy_async();  // generic-proxy writes -> visible to the tensor core's async-proxy reads
         __syncwarp();
-        if (lane == 0) mbar_arrive(kv_full((j - 1) & 1));
+        if (lane == 0) mbar_arrive(full((j - 1) & 1));
       }
-      mbar_wait(kv_empty(s), ((j >> 1) & 1) ^ 1);
-      ux_load_kv<T, D>(a, r2t_row, j * kUxBN, kv_end, prefix, q_start, kvh, base + L::kK + s * L::kTile,
-                       base + L::kV + s * L::kTile, tid);
-      cp_async_commit();
     }
     cp_async_wait<0>();
     fence_proxy_async();
     __syncwarp();
-    if (lane == 0) mbar_arrive(kv_full((n_tiles - 1) & 1));
+    if (lane == 0) mbar_arrive(full((n_tiles - 1) & 1));
   } else if (warp == 4) {
     // ---- MMA issuer --------------------------------------------------------------------------------------------
     if (lane == 0) {
@@ -192,7 +301,7 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
       constexpr uint32_t idesc_o = make_idesc(/*f32*/ 1, kFmt, kFmt, 128, D, /*A K-major*/ 0, /*B MN-major*/ 1);
       auto issue_qk = [&](int j) {
         const int s = j & 1;
-        mbar_wait(kv_full(s), (j >> 1) & 1);
+        mbar_wait(k_full(s), (j >> 1) & 1);
         tc_fence_after();
         const uint32_t sq = base + L::kQ;
         const uint32_t sk = base + L::kK + s * L::kTile;
@@ -203,11 +312,13 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
           const uint64_t db = smem_desc_k_sw128(sk + (kk >> 2) * L::kHalf) + 2 * (kk & 3);
           umma<kKindF16>(d_tmem, da, db, idesc_s, kk != 0);
         }
+        tc_commit(k_empty(s));  // the K stage is free as soon as this Q K^T retires
         tc_commit(s_full(j & 1));
       };
       issue_qk(0);
       for (int j = 0; j < n_tiles; ++j) {
         if (j + 1 < n_tiles) issue_qk(j + 1);
+        mbar_wait(v_full(j & 1), (j >> 1) & 1);
         mbar_wait(p_full, j & 1);
         tc_fence_after();
         const uint32_t sp = base + L::kP;
@@ -219,7 +330,7 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
           const uint64_t db = smem_desc_mn_sw128(sv + kk * 2048, L::kHalf, 1024);
           umma<kKindF16>(tmem_base + kOCol, da, db, idesc_o, (j | kk) != 0);
         }
-        tc_commit(kv_empty(j & 1));  // K and V of this stage are free once these MMAs retire
+        tc_commit(v_empty(j & 1));
         tc_commit(pv_done);
       }
     }
@@ -230,37 +341,24 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
     const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
     const int lim = a.causal ? prefix + m0 + row : kv_total - 1;  // last KV position this row may see
     const bool use_cap = a.logit_cap > 0.f;
-    const float cap_in = use_cap ? a.sm_scale / a.logit_cap : 0.f;
-    const float cap_out = a.logit_cap * kLog2eExt;
     const uint32_t sp = base + L::kP;
     float m_used = -INFINITY;  // the max (log2 domain) the row's P and O are currently normalised to
     float l_run = 0.f;
+    const SoftmaxCtx cx{a.scale_log2, use_cap ? a.sm_scale / a.logit_cap : 0.f, a.logit_cap * kLog2eExt, lim, kv_end};
 
     for (int j = 0; j < n_tiles; ++j) {
       const int kv0 = j * kUxBN;
       const uint32_t t_s = t_lane + (uint32_t)(j & 1) * kUxBN;
       // tiles that touch the causal diagonal or the end of the sequence need per-element masks (CTA-uniform test)
       const bool need_mask = (kv0 + kUxBN > kv_end) || (a.causal && kv0 + kUxBN - 1 > prefix + m0);
+      const int mode = use_cap ? 2 : (need_mask ? 1 : 0);  // warp-uniform: the hot loops carry no per-element branches
       mbar_wait(s_full(j & 1), (j >> 1) & 1);
       tc_fence_after();
 
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c0 = 0; c0 < kUxBN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld32(t_s + c0, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float v = __uint_as_float(r[i]);
-          v = use_cap ? cap_out * tanh_approx(v * cap_in) : v * a.scale_log2;
-          if (need_mask) {
-            const int pos = kv0 + c0 + i;
-            if (pos > lim || pos >= kv_end) v = -INFINITY;
-          }
-          mx = fmaxf(mx, v);
-        }
-      }
+      float mx;
+      if (mode == 0) mx = ux_row_max<0>(t_s, cx, kv0);
+      else if (mode == 1) mx = ux_row_max<1>(t_s, cx, kv0);
+      else mx = ux_row_max<2>(t_s, cx, kv0);
       const float m_new = fmaxf(m_used, mx);
       if (j == 0) {
         m_used = m_new;
@@ -285,35 +383,9 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
         }
       }
       const float m_use = (m_used == -INFINITY) ? 0.f : m_used;
-
-#pragma unroll 1
-      for (int c0 = 0; c0 < kUxBN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld32(t_s + c0, r);
-        tmem_ld_wait();
-        float p[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float v = __uint_as_float(r[i]);
-          v = use_cap ? cap_out * tanh_approx(v * cap_in) : v * a.scale_log2;
-          if (need_mask) {
-            const int pos = kv0 + c0 + i;
-            if (pos > lim || pos >= kv_end) v = -INFINITY;
-          }
-          p[i] = fast_exp2(v - m_use);
-          l_run += p[i];
-        }
-#pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          uint4 w;
-          w.x = pack2<T>(p[8 * g + 0], p[8 * g + 1]);
-          w.y = pack2<T>(p[8 * g + 2], p[8 * g + 3]);
-          w.z = pack2<T>(p[8 * g + 4], p[8 * g + 5]);
-          w.w = pack2<T>(p[8 * g + 6], p[8 * g + 7]);
-          const uint32_t addr = sp + sw128_off(row, (c0 >> 3) + g, L::kHalf);
-          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(addr), "r"(w.x), "r"(w.y), "r"(w.z), "r"(w.w) : "memory");
-        }
-      }
+      if (mode == 0) l_run += ux_row_exp<T, 0>(t_s, cx, kv0, m_use, sp, row, L::kHalf);
+      else if (mode == 1) l_run += ux_row_exp<T, 1>(t_s, cx, kv0, m_use, sp, row, L::kHalf);
+      else l_run += ux_row_exp<T, 2>(t_s, cx, kv0, m_use, sp, row, L::kHalf);
       fence_proxy_async();  // P (generic-proxy stores) -> visible to the MMA's async-proxy reads
       tc_fence_before();    // orders this thread's TMEM loads / stores before the MMA warp's next tcgen05 ops
       __syncwarp();

@@ -128,6 +128,28 @@ def bench_awq(args):
                                   gbs=round(tot_b / tot_t / 1e6, 1), frac_hbm=round(tot_b / tot_t / 1e6 / HBM, 3))), flush=True)
 
 
+def bench_extend(args):
+    """cfg 3 layer shape: chunked prefill of an 8k prompt (chunks of `--chunk` tokens, prefix = what is cached)."""
+    dev = torch.device("cuda")
+    hq, hkv, d, page = args.hq, args.hkv, args.d, args.page
+    total = args.ctx
+    chunk = args.chunk or total
+    pb = synth.make_paged_batch([total], page, seed=1)
+    kc, vc = synth.randn_kv_device(pb.num_slots, page, hkv, d, torch.bfloat16, dev)
+    r2t, rpi = pb.req_to_token.to(dev), pb.req_pool_indices.to(dev)
+    for prefix in range(0, total, chunk):
+        e = min(chunk, total - prefix)
+        q = torch.randn(e, hq, d, device=dev).to(torch.bfloat16)
+        o = torch.empty_like(q)
+        qo = torch.tensor([0, e], dtype=torch.int32, device=dev)
+        pl = torch.tensor([prefix], dtype=torch.int32, device=dev)
+        fn = lambda: kernels.extend_attention_fwd(q, None, None, o, kc, vc, r2t, rpi, qo, pl, e, d ** -0.5, 0.0, True)
+        med, best = timeit(fn, iters=10, warmup=3, flush=False)
+        flops = 4 * d * hq * (e * prefix + e * (e + 1) / 2)
+        print(json.dumps(dict(kernel="extend_attn", legacy=os.environ.get("B200_EXTEND_LEGACY", "0"), extend=e, prefix=prefix,
+                              ms_med=round(med, 4), tflops=round(flops / med / 1e9, 1))), flush=True)
+
+
 def bench_peak(args):
     """Library ceilings measured the way MEASURED_PEAKS.json measures bf16: cuBLASLt int8 (torch._int_mm) and
     fp8 (torch._scaled_mm) at 8192^3 and at the Llama-8B prefill shapes, plus SM clocks under load."""
@@ -171,4 +193,4 @@ if __name__ == "__main__":
     ap.add_argument("--m", type=int, default=0)
     ap.add_argument("--ragged", action="store_true")
     args = ap.parse_args()
-    {"decode": bench_decode, "gemm_int8": bench_gemm_int8, "awq": bench_awq, "peak": bench_peak}[args.what](args)
+    {"decode": bench_decode, "gemm_int8": bench_gemm_int8, "awq": bench_awq, "peak": bench_peak, "extend": bench_extend}[args.what](args)
