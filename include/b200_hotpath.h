@@ -48,6 +48,10 @@ int b200_abi_version(void);
 const char* b200_last_error(void);
 /* Fills SM count and compute capability of the current device. */
 int b200_device_info(int* sm_count, int* cc_major, int* cc_minor);
+/* Diagnostics: when a device buffer is set, the GEMM kernels record per-CTA phase timestamps into it
+ * (16 x uint64 per CTA: [0]/[15] = %globaltimer ns at entry/exit, [1..14] = %clock64 at kernel-specific
+ * points; CTAs beyond bytes/128 record nothing).  NULL (the default) disables it.  Not thread-safe. */
+int b200_debug_set_trace(void* device_buffer, size_t bytes);
 
 /* ---- KV-cache write -------------------------------------------------------------------
  * Replaces MHATokenToKVPool.set_kv_buffer's two index_put_ launches
@@ -129,7 +133,10 @@ int b200_merge_state(void* v_out, float* s_out, const void* v_a, const float* s_
  * reference holds it after process_weights_after_loading — logical [K,N] column-major,
  * i.e. N rows of K contiguous int8 (w8a8_int8.py:332-341).  K % 16 == 0, N % 8 == 0.
  * If acc_out != NULL the raw int32 accumulators [M,N] are written too (parity hook:
- * they must be bit-exact).  Workspace: b200_int8_scaled_mm_workspace_bytes.
+ * they must be bit-exact).  Workspace (shared with b200_fp8_scaled_mm): b200_int8_scaled_mm_workspace_bytes
+ * bytes, zero-initialised ONCE by the caller, self-cleaning afterwards; it carries the per-CTA partial
+ * accumulators and flags of the persistent stream-K decode kernel (M <= 256).  One workspace per stream.
+ * workspace == NULL selects the cluster split-K kernel, which needs none.
  */
 int b200_per_token_quant_int8(int8_t* xq, float* scale, const void* x, int64_t M, int64_t K,
                               int64_t x_row_stride, int dtype, void* stream);
@@ -165,7 +172,7 @@ int b200_fp8_blockwise_scaled_mm(void* out, const void* a, const void* b, const 
 /* per-token x per-channel FP8 (sgl-kernel/csrc/gemm/fp8_gemm_kernel.cu:1110-1145). */
 int b200_fp8_scaled_mm(void* out, const void* a, const void* b, const float* scale_a,
                        const float* scale_b, const void* bias, int64_t M, int64_t N, int64_t K,
-                       int out_dtype, void* stream);
+                       int out_dtype, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- AWQ-int4 linear -------------------------------------------------------------------
  * b200_awq_dequantize replaces awq_dequantize (sgl-kernel/csrc/gemm/awq_kernel.cu:126-221):

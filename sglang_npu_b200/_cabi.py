@@ -38,6 +38,7 @@ _P = c_void_p
 _SIGNATURES = {
     "b200_abi_version": [],
     "b200_device_info": [POINTER(c_int), POINTER(c_int), POINTER(c_int)],
+    "b200_debug_set_trace": [_P, c_size_t],
     "b200_set_kv_buffer": [_P, _P, _P, _P, _P, c_int, c_int64, c_int64, c_int64, c_int64, c_int64,
                            c_int64, c_int64, c_int, _P],
     "b200_decode_attn_workspace_bytes": [c_int, c_int, c_int, c_int, POINTER(c_size_t)],
@@ -57,7 +58,7 @@ _SIGNATURES = {
     "b200_per_token_quant_fp8": [_P, _P, _P, c_int64, c_int64, c_int64, c_int, _P],
     "b200_fp8_blockwise_scaled_mm": [_P, _P, _P, _P, c_int64, c_int64, _P, c_int64, c_int64, _P,
                                      c_int64, c_int64, c_int64, c_int, _P],
-    "b200_fp8_scaled_mm": [_P, _P, _P, _P, _P, _P, c_int64, c_int64, c_int64, c_int, _P],
+    "b200_fp8_scaled_mm": [_P, _P, _P, _P, _P, _P, c_int64, c_int64, c_int64, c_int, _P, c_size_t, _P],
     "b200_awq_dequantize": [_P, _P, _P, _P, c_int64, c_int64, c_int, c_int, _P],
     "b200_awq_gemm": [_P, _P, _P, _P, _P, _P, c_int64, c_int64, c_int64, c_int, c_int, _P],
     "b200_rmsnorm": [_P, _P, _P, _P, c_int64, c_int64, c_float, c_int, _P],

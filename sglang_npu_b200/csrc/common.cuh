@@ -44,6 +44,11 @@ int fail(b200_status code, const char* fmt, ...);
 
 int sm_count();
 
+// Optional per-CTA phase trace (b200_debug_set_trace): 16 x u64 per CTA — slot 0 / 15 = %globaltimer at entry / exit,
+// slots 1..14 = %clock64 at kernel-specific points.  Null in normal operation (one predictable branch per point).
+extern unsigned long long* g_trace;
+extern size_t g_trace_slots;
+
 // ---- programmatic dependent launch (PDL) ---------------------------------------------------
 // Every kernel of the decode chain is launched with cudaLaunchAttributeProgrammaticStreamSerialization, so
 // its CTAs may become resident while the previous kernel in the stream is still draining.  The contract
@@ -123,6 +128,15 @@ __device__ __forceinline__ float2 unpack2(uint32_t u) {
 // ---- small PTX wrappers ----------------------------------------------------------------
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;\n" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory"); }
+
+__device__ __forceinline__ void trace_mark(unsigned long long* slot16, int i) {
+  if (slot16 != nullptr) {
+    unsigned long long t;
+    if (i == 0 || i == 15) asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
+    else asm volatile("mov.u64 %0, %%clock64;\n" : "=l"(t));
+    slot16[i] = t;
+  }
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

@@ -47,9 +47,20 @@ int sm_count() {
 
 }  // namespace b200
 
-B200_API int b200_abi_version(void) { return 1; }
+B200_API int b200_abi_version(void) { return 2; }
 
 B200_API const char* b200_last_error(void) { return b200::g_err; }
+
+namespace b200 {
+unsigned long long* g_trace = nullptr;
+size_t g_trace_slots = 0;
+}  // namespace b200
+
+B200_API int b200_debug_set_trace(void* device_buffer, size_t bytes) {
+  b200::g_trace = reinterpret_cast<unsigned long long*>(device_buffer);
+  b200::g_trace_slots = device_buffer ? bytes / (16 * sizeof(unsigned long long)) : 0;
+  return B200_OK;
+}
 
 B200_API int b200_device_info(int* sm_count, int* cc_major, int* cc_minor) {
   int dev = 0;

@@ -45,7 +45,14 @@ struct GemmArgs {
   int out_is_bf16;
   int64_t sm_rs, sm_cs;  // scale_m[m * sm_rs + kb * sm_cs]          (F8Block)
   int64_t sn_rs, sn_cs;  // scale_n[(n / 128) * sn_rs + kb * sn_cs]   (F8Block)
+  unsigned long long* trace;  // diagnostics (b200_debug_set_trace) or null
+  int trace_slots;
 };
+
+__device__ __forceinline__ unsigned long long* trace_slot(const GemmArgs& g) {
+  const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  return (g.trace != nullptr && cta < g.trace_slots) ? g.trace + (size_t)cta * 16 : nullptr;
+}
 
 constexpr int kGemmThreads = 256;
 constexpr int kBK = 128;  // bytes of K per pipeline stage = one 128B swizzle row
@@ -80,6 +87,27 @@ __device__ __forceinline__ void store_out(void* out, int64_t idx, float v, int i
   else reinterpret_cast<__half*>(out)[idx] = __float2half_rn(v);
 }
 
+// 16 consecutive token columns of one output channel: scales (+bias), one rounding to the output dtype, 2-byte
+// stores N elements apart (a warp covers 64 contiguous bytes per token).  Branch-free; per-token scales come from
+// shared memory.  p / ap point at (token c0, channel n).
+template <int MODE>
+__device__ __forceinline__ void finalize_store16(const uint32_t (&r)[16], const float* s_scale, float sn, bool has_bias,
+                                                 float bias, bool bf, uint16_t* p, int32_t* ap, int64_t N, int m_left,
+                                                 bool n_ok) {
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float v = finalize<MODE>(r[j], s_scale[j], sn, has_bias, bias);
+    const uint16_t hb = __half_as_ushort(__float2half_rn(v));
+    const uint16_t bb = __bfloat16_as_ushort(__float2bfloat16_rn(v));
+    if (n_ok && j < m_left) p[(int64_t)j * N] = bf ? bb : hb;
+  }
+  if (ap != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+      if (n_ok && j < m_left) ap[(int64_t)j * N] = (int32_t)r[j];
+  }
+}
+
 // CTAs per SM the shared-memory footprint allows (the decode tiles are small enough for 2: twice the bytes
 // in flight per SM and no half-empty second wave when the tile count is not a multiple of the SM count).
 template <int MODE, int BN, int STAGES>
@@ -108,6 +136,11 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  unsigned long long* const tr = trace_slot(g);
+  if (threadIdx.x == 0) {
+    trace_mark(tr, 0);
+    trace_mark(tr, 14);
+  }
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
@@ -130,6 +163,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   tc_fence_after();
   const uint32_t tmem_base = s_tmem_base;
   pdl_trigger();  // barriers / TMEM are set up: the next kernel of the stream may start its own prologue
+  if (threadIdx.x == 0) trace_mark(tr, 1);
 
   const int a_row0 = blockIdx.x * 128;
   const int b_row0 = blockIdx.y * BN;
@@ -159,6 +193,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         else tma_load_2d(sa + L::kA, &tmap_b, full_bar(i), (kb0 + i) * kBK, b_row0, pol_b);
       }
       pdl_wait();  // activations (and their scales) are written by the previous kernel
+      trace_mark(tr, 2);
       for (int i = 0; i < pre; ++i) {
         const uint32_t sa = base + i * L::kStage;
         if (SWAP) tma_load_2d(sa + L::kA, &tmap_b, full_bar(i), (kb0 + i) * kBK, b_row0, pol_b);
@@ -185,6 +220,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int s = i % STAGES;
         const uint32_t ph = (i / STAGES) & 1;
         mbar_wait(full_bar(s), ph);
+        if (i == 0) trace_mark(tr, 3);
         if (kBlock) mbar_wait(tmem_empty_bar(i & 1), ((i >> 1) & 1) ^ 1);  // epilogue drained this buffer
         tc_fence_after();
         const uint32_t sa = base + s * L::kStage;
@@ -198,6 +234,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (kBlock) tc_commit(tmem_full_bar(i & 1));
       }
       if (!kBlock) tc_commit(tmem_full_bar(0));
+      trace_mark(tr, 4);
     }
   } else if (warp >= 4) {
     pdl_wait();  // scales are read (and the output written) only after the previous kernels have completed
@@ -238,6 +275,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       mbar_wait(tmem_full_bar(0), 0);
       tc_fence_after();
     }
+    if (threadIdx.x == 128) trace_mark(tr, 5);
   }
 
   if (warp == 2 || warp == 3) pdl_wait();
@@ -247,6 +285,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (S > 1) {
       __syncwarp();
       cluster_sync();  // every CTA of the cluster has retired its MMAs: pipeline smem is free to reuse
+      if (threadIdx.x == 128) trace_mark(tr, 6);
       if (warp >= 4) {
         const int C = BN / S;  // token columns owned by each rank
         const int logC = 31 - __clz(C);
@@ -290,7 +329,9 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
       }
       __syncwarp();
+      if (threadIdx.x == 128) trace_mark(tr, 7);
       cluster_sync();  // all partials have landed
+      if (threadIdx.x == 128) trace_mark(tr, 8);
     }
   }
 
@@ -409,9 +450,11 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   }
 
+  if (threadIdx.x == 128) trace_mark(tr, 9);
   tc_fence_before();
   __syncthreads();
   if (warp == 2) tmem_dealloc<kTmemCols>(tmem_base);
+  if (threadIdx.x == 0) trace_mark(tr, 15);
 }
 
 // ---- prefill: persistent CTAs, double-buffered TMEM accumulators -------------------------------------------------------
@@ -566,6 +609,287 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   if (warp == 2) tmem_dealloc<512>(tmem_base);
 }
 
+// ---- decode: persistent stream-K weight streaming -----------------------------------------------------------------------
+// Weight-streaming orientation (weights on MMA-M, tokens on MMA-N, M <= 256) for int8 / per-channel FP8, balanced
+// to the byte: the work is U = (128-channel tiles) x (128-byte K blocks) "units" of one 16 KiB weight box each, and
+// CTA c of a one-CTA-per-SM grid streams the contiguous unit range [c*U/G, (c+1)*U/G) through a deep TMA ring, so
+// every SM pulls the same number of weight bytes whatever N and K are (the tile-per-CTA grid left 72 of 148 SMs with
+// half the work on gate_up).  A range is cut into segments at tile boundaries; segment j accumulates in TMEM buffer
+// j & 1 and is drained by the epilogue warps while the MMA thread is already on segment j+1.
+//   * a segment that covers the whole K range is finalised straight from TMEM;
+//   * a segment that does not start at K block 0 (always the FIRST of its CTA) is a contribution: the raw 32-bit
+//     accumulators go to this CTA's slot of the workspace and a release-flag is raised;
+//   * a segment that starts at K block 0 but stops early (always the LAST of its CTA) owns the tile: it waits for
+//     the flags of the following CTAs — which wrote their contributions at the very start of their own ranges —
+//     and adds their partials in CTA order.  int32 sums are exact and the fp32 order is fixed, so the result is
+//     bit-deterministic; the flags are reset by their consumer (self-cleaning workspace).
+// All G <= #SM CTAs are co-resident (one per SM by shared-memory footprint), so the flag wait cannot deadlock.
+template <int BN>
+struct StreamK {
+  static constexpr int kStageBytes = 128 * kBK + BN * kBK;
+  static constexpr int kStages = (200 * 1024) / kStageBytes > 10 ? 10 : (200 * 1024) / kStageBytes;
+  static constexpr int kBarOff = kStages * kStageBytes;
+  static constexpr int kBytes = kBarOff + (2 * kStages + 5) * 8 + 1024;
+  static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
+};
+constexpr int kSkFlagBytes = 1024;  // up to 256 CTAs
+
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;\n" ::: "memory"); }
+
+template <int MODE, int BN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
+                    const GemmArgs g, const int total_units, uint32_t* __restrict__ flags,
+                    uint32_t* __restrict__ partials) {
+  using L = StreamK<BN>;
+  constexpr int STAGES = L::kStages;
+  constexpr int kKind = MODE == kModeI8 ? kKindI8 : kKindF8;
+  constexpr int kWBytes = 128 * kBK;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint32_t s_tmem_base;
+  __shared__ float s_scale_m[BN];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar = base + L::kBarOff;
+  const uint32_t fix_bar = bar + (2 * STAGES + 4) * 8;
+  auto full_bar = [&](int s) { return bar + s * 8; };
+  auto empty_bar = [&](int s) { return bar + (STAGES + s) * 8; };
+  auto tmem_full_bar = [&](int b) { return bar + (2 * STAGES + b) * 8; };
+  auto tmem_empty_bar = [&](int b) { return bar + (2 * STAGES + 2 + b) * 8; };
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  unsigned long long* const tr = trace_slot(g);
+  if (threadIdx.x == 0) {
+    trace_mark(tr, 0);
+    trace_mark(tr, 14);
+  }
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_w);
+    prefetch_tmap(&tmap_x);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(tmem_full_bar(b), 1);
+      mbar_init(tmem_empty_bar(b), 4);
+    }
+    mbar_init(fix_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<L::kTmemCols>(smem_u32(&s_tmem_base));
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = s_tmem_base;
+  pdl_trigger();
+  if (threadIdx.x == 0) trace_mark(tr, 1);
+
+  const int G = gridDim.x;
+  const int c = blockIdx.x;
+  const int nkb = g.num_kb;
+  const int u0 = (int)((int64_t)c * total_units / G);
+  const int u1 = (int)((int64_t)(c + 1) * total_units / G);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const int n_units = u1 - u0;
+      const int pre = min(n_units, STAGES);
+      int tile = u0 / nkb, kb = u0 - tile * nkb;
+      // weights do not depend on the previous kernel: fill the ring with weight boxes before the PDL wait
+      for (int i = 0; i < pre; ++i) {
+        mbar_expect_tx(full_bar(i), L::kStageBytes);
+        tma_load_2d(base + i * L::kStageBytes, &tmap_w, full_bar(i), kb * kBK, tile * 128, kEvictFirst);
+        if (++kb == nkb) { kb = 0; ++tile; }
+      }
+      pdl_wait();
+      trace_mark(tr, 2);
+      tile = u0 / nkb, kb = u0 - tile * nkb;
+      for (int i = 0; i < pre; ++i) {
+        tma_load_2d(base + i * L::kStageBytes + kWBytes, &tmap_x, full_bar(i), kb * kBK, 0, kEvictLast);
+        if (++kb == nkb) { kb = 0; ++tile; }
+      }
+      for (int i = pre; i < n_units; ++i) {
+        const int s = i % STAGES;
+        mbar_wait(empty_bar(s), ((i / STAGES) & 1) ^ 1);
+        mbar_expect_tx(full_bar(s), L::kStageBytes);
+        const uint32_t sa = base + s * L::kStageBytes;
+        tma_load_2d(sa, &tmap_w, full_bar(s), kb * kBK, tile * 128, kEvictFirst);
+        tma_load_2d(sa + kWBytes, &tmap_x, full_bar(s), kb * kBK, 0, kEvictLast);
+        if (++kb == nkb) { kb = 0; ++tile; }
+      }
+    } else {
+      pdl_wait();
+    }
+  } else if (warp == 1) {
+    pdl_wait();
+    if (lane == 0) {
+      constexpr uint32_t idesc = MODE == kModeI8 ? make_idesc(/*s32*/ 2, /*int8*/ 1, 1, 128, BN)
+                                                 : make_idesc(/*f32*/ 1, /*e4m3*/ 0, 0, 128, BN);
+      int it = 0, seg = 0;
+      for (int u = u0; u < u1; ++seg) {
+        const int tile = u / nkb;
+        const int seg_end = min(u1, (tile + 1) * nkb);
+        const int buf = seg & 1;
+        mbar_wait(tmem_empty_bar(buf), ((seg >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * BN;
+        for (int i = u; i < seg_end; ++i, ++it) {
+          const int s = it % STAGES;
+          mbar_wait(full_bar(s), (it / STAGES) & 1);
+          if (it == 0) trace_mark(tr, 3);
+          tc_fence_after();
+          const uint32_t sa = base + s * L::kStageBytes;
+          const uint64_t da = smem_desc_k_sw128(sa);
+          const uint64_t db = smem_desc_k_sw128(sa + kWBytes);
+#pragma unroll
+          for (int k = 0; k < kBK / 32; ++k) umma<kKind>(d_tmem, da + 2 * k, db + 2 * k, idesc, (i > u) || (k != 0));
+          tc_commit(empty_bar(s));
+        }
+        tc_commit(tmem_full_bar(buf));
+        u = seg_end;
+      }
+      trace_mark(tr, 4);
+    }
+  } else if (warp >= 4) {
+    pdl_wait();
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const bool has_bias = g.bias != nullptr;
+    const bool bf = g.out_is_bf16 != 0;
+    const int m_cols = min(BN, (g.M + 15) & ~15);  // token columns that hold data, in groups of 16
+    // per-token scales of this launch -> shared memory (the inner loops below touch no global memory but their stores)
+    for (int i = threadIdx.x - 128; i < BN; i += 128) s_scale_m[i] = i < g.M ? g.scale_m[i] : 0.f;
+    epi_bar_sync();
+    uint32_t fix_phase = 0;
+    int seg = 0;
+    for (int u = u0; u < u1; ++seg) {
+      const int tile = u / nkb;
+      const int kb_begin = u - tile * nkb;
+      const int seg_end = min(u1, (tile + 1) * nkb);
+      const bool starts = kb_begin == 0;
+      const bool ends = seg_end == (tile + 1) * nkb;
+      const int buf = seg & 1;
+      mbar_wait(tmem_full_bar(buf), (seg >> 1) & 1);
+      tc_fence_after();
+      if (threadIdx.x == 128) trace_mark(tr, seg == 0 ? 5 : 7);  // 5: first segment accumulated, 7: latest one
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN;
+      if (!starts) {
+        // contribution: raw accumulators -> partials[c][col][row]; a warp store covers 128 contiguous bytes
+        uint32_t* dst = partials + (size_t)c * BN * 128 + row;
+#pragma unroll 1
+        for (int c0 = 0; c0 < m_cols; c0 += 16) {
+          uint32_t r[16];
+          tmem_ld16(taddr + c0, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) __stcg(dst + (c0 + j) * 128, r[j]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tmem_empty_bar(buf));
+        epi_bar_sync();  // orders every epilogue thread's stores before the release below (cumulativity)
+        if (threadIdx.x == 128) st_release_u32(flags + c, 1u);
+        if (threadIdx.x == 128) trace_mark(tr, 6);  // contribution published
+      } else {
+        // owner of the tile: peers are the CTAs after this one whose ranges start inside the tile
+        int n_peers = 0;
+        if (!ends) {
+          const int tile_end = (tile + 1) * nkb;
+          while (c + 1 + n_peers < G && (int)((int64_t)(c + 1 + n_peers) * total_units / G) < tile_end) ++n_peers;
+          for (int p = 0; p < n_peers; ++p)
+            while (ld_acquire_u32(flags + c + 1 + p) == 0u) {
+            }
+          if (threadIdx.x == 128) trace_mark(tr, 8);  // peers' flags seen
+          if (threadIdx.x == 128 && tr != nullptr) tr[10] = (unsigned long long)n_peers;
+        }
+        const int n = tile * 128 + row;
+        const bool n_ok = n < g.N;
+        float sn = 0.f, bias = 0.f;
+        if (n_ok) {
+          sn = g.scale_n[n];
+          if (has_bias) bias = load_bias(g.bias, n, g.out_is_bf16);
+        }
+        // This is the CTA's last segment when it has peers: every MMA has retired, so the TMA ring is free and the
+        // peers' partials are pulled into it with bulk copies (a batch = as many peers as fit) instead of
+        // latency-bound per-thread loads; the running sum of all but the last batch goes back to TMEM.
+        const uint32_t pbytes = (uint32_t)m_cols * 512u;
+        const int per_batch = max(1, (int)((uint32_t)(STAGES * L::kStageBytes) / pbytes));
+        int p0 = 0;
+        do {
+          const int nb = min(per_batch, n_peers - p0);
+          const bool last = p0 + nb >= n_peers;
+          if (nb > 0) {
+            if (threadIdx.x == 128) {
+              asm volatile("fence.proxy.async.global;\n" ::: "memory");  // peers wrote with generic-proxy stores
+              mbar_expect_tx(fix_bar, (uint32_t)nb * pbytes);
+              for (int i = 0; i < nb; ++i)
+                bulk_load_1d(base + (uint32_t)i * pbytes, partials + (size_t)(c + 1 + p0 + i) * BN * 128, pbytes, fix_bar);
+            }
+            mbar_wait(fix_bar, fix_phase);
+            fix_phase ^= 1u;
+          }
+          const uint32_t* sp = reinterpret_cast<const uint32_t*>(smem_raw + (base - smem_u32(smem_raw))) + row;
+          uint16_t* outp = reinterpret_cast<uint16_t*>(g.out) + n;
+          int32_t* accp = (MODE == kModeI8 && g.acc_out != nullptr) ? g.acc_out + n : nullptr;
+#pragma unroll 1
+          for (int c0 = 0; c0 < m_cols; c0 += 16) {
+            uint32_t r[16];
+            tmem_ld16(taddr + c0, r);
+            tmem_ld_wait();
+            for (int i = 0; i < nb; ++i) {
+              const uint32_t* src = sp + (size_t)i * (pbytes / 4) + c0 * 128;
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const uint32_t v = src[j * 128];
+                if constexpr (MODE == kModeI8) r[j] = (uint32_t)((int32_t)r[j] + (int32_t)v);
+                else r[j] = __float_as_uint(__fadd_rn(__uint_as_float(r[j]), __uint_as_float(v)));
+              }
+            }
+            if (last) {
+              finalize_store16<MODE>(r, s_scale_m + c0, sn, has_bias, bias, bf, outp + (int64_t)c0 * g.N,
+                                     accp ? accp + (int64_t)c0 * g.N : nullptr, g.N, g.M - c0, n_ok);
+            } else {
+              tmem_st16(taddr + c0, r);
+            }
+          }
+          if (!last) {
+            tmem_st_wait();
+            epi_bar_sync();  // everyone is done reading this batch before the next one overwrites it
+          }
+          p0 += nb;
+        } while (p0 < n_peers);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tmem_empty_bar(buf));
+        if (n_peers > 0) {
+          epi_bar_sync();  // every epilogue thread has consumed the peers' partials
+          if (threadIdx.x == 128)
+            for (int p = 0; p < n_peers; ++p) flags[c + 1 + p] = 0u;
+        }
+      }
+      u = seg_end;
+    }
+    if (threadIdx.x == 128) trace_mark(tr, 9);
+  } else {
+    pdl_wait();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<L::kTmemCols>(tmem_base);
+  if (threadIdx.x == 0) trace_mark(tr, 15);
+}
+
 // ---- host side -----------------------------------------------------------------------------------
 struct TmapKey {
   const void* p;
@@ -611,13 +935,70 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmA
   return launch_k(kern, grid, dim3(kGemmThreads), L::kBytes, st, SWAP ? (unsigned)g.splits : 1u, true, ta, tb, g);
 }
 
+// workspace of the stream-K decode path: [flags, kSkFlagBytes][partials: G x BN x 128 x 4 B]
+static int streamk_bn(int64_t M) { return M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256; }
+static size_t streamk_workspace_bytes(int64_t M) {
+  if (M > 256) return 0;
+  return (size_t)kSkFlagBytes + (size_t)sm_count() * streamk_bn(M) * 128 * 4;
+}
+
+template <int MODE, int BN>
+static int launch_streamk(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& g, int total_units, int ctas,
+                          void* ws, cudaStream_t st) {
+  using L = StreamK<BN>;
+  auto kern = gemm_streamk_kernel<MODE, BN>;
+  B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
+  uint32_t* flags = reinterpret_cast<uint32_t*>(ws);
+  uint32_t* partials = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(ws) + kSkFlagBytes);
+  return launch_k(kern, dim3((unsigned)ctas), dim3(kGemmThreads), L::kBytes, st, 1, true, tw, tx, g, total_units, flags,
+                  partials);
+}
+
 template <int MODE>
-static int run_gemm(GemmArgs g, const void* a, const void* b, int64_t M, int64_t N, int64_t K, cudaStream_t st) {
+static int run_gemm(GemmArgs g, const void* a, const void* b, int64_t M, int64_t N, int64_t K, cudaStream_t st,
+                    void* ws = nullptr, size_t ws_bytes = 0) {
   g.M = (int)M;
   g.N = (int)N;
   g.num_kb = (int)ceil_div(K, kBK);
+  g.trace = g_trace;
+  g.trace_slots = (int)g_trace_slots;
   CUtensorMap ta, tb;
   int rc;
+  if constexpr (MODE != kModeF8Block) {
+    static const bool streamk = getenv("B200_GEMM_STREAMK") == nullptr || getenv("B200_GEMM_STREAMK")[0] != '0';
+    // measured (profiles/r01e_gemm_decode.jsonl): below 64 tokens the epilogue is negligible and the cluster kernel's
+    // two CTAs per SM start streaming earlier; from 64 tokens up the balanced persistent kernel wins
+    static const int streamk_min_m = getenv("B200_GEMM_STREAMK_MIN_M") ? atoi(getenv("B200_GEMM_STREAMK_MIN_M")) : 33;
+    if (M <= 256 && M >= streamk_min_m && ws != nullptr && streamk) {
+      const size_t need = streamk_workspace_bytes(M);
+      if (ws_bytes < need)
+        return fail(B200_ERR_WORKSPACE, "scaled_mm: workspace of %zu bytes, %zu needed", ws_bytes, need);
+      B200_REQUIRE(((uintptr_t)ws % 16) == 0, "scaled_mm: workspace must be 16-byte aligned");
+      const int bn = streamk_bn(M);
+      const int64_t units = ceil_div(N, 128) * g.num_kb;
+      B200_REQUIRE(units < (1ll << 30), "scaled_mm: too many work units");
+      // Grid: one CTA per SM.  When there are fewer tiles than SMs, prefer P = #SM / tiles CTAs per tile with ranges
+      // aligned to tile boundaries (one segment per CTA, P - 1 peers per owner) if that still fills >= 85% of the SMs.
+      const int sms = sm_count();
+      const int tiles = (int)ceil_div(N, 128);
+      int ctas = (int)(units < sms ? units : sms);
+      if (tiles < sms) {
+        const int per_tile = sms / tiles < g.num_kb ? sms / tiles : g.num_kb;
+        if (tiles * per_tile * 100 >= sms * 85) ctas = tiles * per_tile;
+      }
+      g.splits = 1;
+      g.kb_per_split = g.num_kb;
+      if ((rc = cached_tmap(&ta, b, (uint64_t)N, (uint64_t)K, 128)) != B200_OK) return rc;
+      if ((rc = cached_tmap(&tb, a, (uint64_t)M, (uint64_t)K, (uint32_t)bn)) != B200_OK) return rc;
+      switch (bn) {
+        case 16: return launch_streamk<MODE, 16>(ta, tb, g, (int)units, ctas, ws, st);
+        case 32: return launch_streamk<MODE, 32>(ta, tb, g, (int)units, ctas, ws, st);
+        case 64: return launch_streamk<MODE, 64>(ta, tb, g, (int)units, ctas, ws, st);
+        case 128: return launch_streamk<MODE, 128>(ta, tb, g, (int)units, ctas, ws, st);
+        default: return launch_streamk<MODE, 256>(ta, tb, g, (int)units, ctas, ws, st);
+      }
+    }
+  }
   // block-scaled FP8 keeps BN fp32 accumulators per epilogue thread in registers, so its token tile stops at 128
   const int64_t swap_max_m = MODE == kModeF8Block ? 128 : 256;
   if (M <= swap_max_m) {
@@ -689,7 +1070,10 @@ using namespace b200;
 
 B200_API int b200_int8_scaled_mm_workspace_bytes(int64_t M, int64_t N, int64_t K, size_t* bytes) {
   B200_REQUIRE(bytes != nullptr, "int8_scaled_mm_workspace_bytes: null out pointer");
-  *bytes = 0;  // split-K reduces through distributed shared memory; no global workspace
+  // stream-K decode path (M <= 256): per-CTA partial slots + flags; must be zero-initialised ONCE by the caller and
+  // is self-cleaning afterwards.  One workspace serves all scaled_mm calls of a stream (calls on different streams
+  // need their own).  Prefill sizes need none.
+  *bytes = streamk_workspace_bytes(M);
   return B200_OK;
 }
 
@@ -705,11 +1089,12 @@ B200_API int b200_int8_scaled_mm(void* out, const int8_t* a, const int8_t* b, co
   GemmArgs g = {};
   g.out = out; g.scale_m = scale_a; g.scale_n = scale_b; g.bias = bias; g.acc_out = acc_out;
   g.out_is_bf16 = out_dtype == B200_BF16;
-  return run_gemm<kModeI8>(g, a, b, M, N, K, (cudaStream_t)stream);
+  return run_gemm<kModeI8>(g, a, b, M, N, K, (cudaStream_t)stream, workspace, workspace_bytes);
 }
 
 B200_API int b200_fp8_scaled_mm(void* out, const void* a, const void* b, const float* scale_a, const float* scale_b,
-                                const void* bias, int64_t M, int64_t N, int64_t K, int out_dtype, void* stream) {
+                                const void* bias, int64_t M, int64_t N, int64_t K, int out_dtype, void* workspace,
+                                size_t workspace_bytes, void* stream) {
   int rc = check_common("fp8_scaled_mm", out, a, b, M, N, K, out_dtype);
   if (rc != B200_OK) return rc;
   if (M == 0) return B200_OK;
@@ -717,7 +1102,7 @@ B200_API int b200_fp8_scaled_mm(void* out, const void* a, const void* b, const f
   GemmArgs g = {};
   g.out = out; g.scale_m = scale_a; g.scale_n = scale_b; g.bias = bias;
   g.out_is_bf16 = out_dtype == B200_BF16;
-  return run_gemm<kModeF8Chan>(g, a, b, M, N, K, (cudaStream_t)stream);
+  return run_gemm<kModeF8Chan>(g, a, b, M, N, K, (cudaStream_t)stream, workspace, workspace_bytes);
 }
 
 B200_API int b200_fp8_blockwise_scaled_mm(void* out, const void* a, const void* b, const float* scale_a,

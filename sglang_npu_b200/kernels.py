@@ -42,6 +42,13 @@ def _count(n: int = 1) -> None:
     _LAUNCHES += n
 
 
+def set_trace(buf: Optional[torch.Tensor]) -> None:
+    """Diagnostics: per-CTA phase timestamps of the GEMM kernels into `buf` (uint64/int64 [ctas, 16]); None = off."""
+    lib = _cabi.load()
+    _check(lib.b200_debug_set_trace(ptr(buf), 0 if buf is None else buf.numel() * buf.element_size()),
+           "b200_debug_set_trace")
+
+
 def _is64(t: torch.Tensor) -> int:
     if t.dtype == torch.int64:
         return 1
@@ -183,8 +190,8 @@ _INT8_WS = {}
 
 
 def _int8_workspace(device, nbytes: int) -> torch.Tensor:
-    # One self-cleaning split-K workspace per device: int8 GEMMs of one process are stream-ordered on the
-    # forward stream (as in the reference's single-threaded TP worker); allocate it before graph capture.
+    # One self-cleaning stream-K workspace (flags + per-CTA partial accumulators) per device: the scaled GEMMs of
+    # one process are stream-ordered on the forward stream (as in the reference's single-threaded TP worker).
     key = device.index
     ws = _INT8_WS.get(key)
     if ws is None or ws.numel() < nbytes:
@@ -193,12 +200,24 @@ def _int8_workspace(device, nbytes: int) -> torch.Tensor:
     return ws
 
 
+def _scaled_mm_workspace(lib, device, M: int, N: int, K: int) -> torch.Tensor:
+    need = c_size_t(0)
+    check(lib.b200_int8_scaled_mm_workspace_bytes(M, N, K, byref(need)), "b200_int8_scaled_mm_workspace_bytes")
+    # sized for the largest decode tile up front so a CUDA-graph capture never sees a re-allocation
+    return _int8_workspace(device, max(need.value, _WS_MIN_BYTES))
+
+
+_WS_MIN_BYTES = 1024 + 160 * 256 * 128 * 4
+
+
 def int8_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tensor,
                    scales_b: torch.Tensor, out_dtype: torch.dtype,
-                   bias: Optional[torch.Tensor] = None, return_acc: bool = False):
+                   bias: Optional[torch.Tensor] = None, return_acc: bool = False, cluster_splitk: bool = False):
     """sgl_kernel.int8_scaled_mm (sgl-kernel/python/sgl_kernel/gemm.py:20-29).
 
     mat_a [M,K] int8 row-major; mat_b [K,N] int8 COLUMN-major (weight.t()); scales fp32.
+    `cluster_splitk=True` passes no workspace, which selects the cluster split-K decode kernel instead of the
+    persistent stream-K one (A/B and parity of both CUDA kernels; results are bit-identical).
     """
     require_cuda(mat_a, mat_b, scales_a, scales_b)
     lib = _cabi.load()
@@ -222,12 +241,10 @@ def int8_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Ten
         bias = bias.contiguous()
     out = torch.empty((M, N), device=mat_a.device, dtype=out_dtype)
     acc = torch.empty((M, N), device=mat_a.device, dtype=torch.int32) if return_acc else None
-    need = c_size_t(0)
-    check(lib.b200_int8_scaled_mm_workspace_bytes(M, N, K, byref(need)), "b200_int8_scaled_mm_workspace_bytes")
-    ws = _int8_workspace(mat_a.device, need.value)
+    ws = None if cluster_splitk else _scaled_mm_workspace(lib, mat_a.device, M, N, K)
     check(lib.b200_int8_scaled_mm(ptr(out), ptr(mat_a), ptr(mat_b), ptr(scales_a), ptr(scales_b),
                                   ptr(bias), M, N, K, dtype_code(out_dtype), ptr(acc), ptr(ws),
-                                  ws.numel(), stream_ptr(mat_a.device)), "b200_int8_scaled_mm")
+                                  0 if ws is None else ws.numel(), stream_ptr(mat_a.device)), "b200_int8_scaled_mm")
     return (out, acc) if return_acc else out
 
 
@@ -311,8 +328,10 @@ def fp8_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tens
     out = torch.empty((M, N), device=mat_a.device, dtype=out_dtype)
     if bias is not None:
         bias = bias.to(out_dtype).contiguous()
+    ws = _scaled_mm_workspace(lib, mat_a.device, M, N, K)
     check(lib.b200_fp8_scaled_mm(ptr(out), ptr(mat_a), ptr(mat_b), ptr(scales_a), ptr(scales_b), ptr(bias),
-                                 M, N, K, dtype_code(out_dtype), stream_ptr(mat_a.device)), "b200_fp8_scaled_mm")
+                                 M, N, K, dtype_code(out_dtype), ptr(ws), ws.numel(), stream_ptr(mat_a.device)),
+          "b200_fp8_scaled_mm")
     return out
 
 

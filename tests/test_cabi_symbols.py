@@ -34,7 +34,7 @@ def test_library_exports_every_header_symbol(lib):
 
 
 def test_abi_version_and_error_channel(lib):
-    assert lib.b200_abi_version() == 1
+    assert lib.b200_abi_version() == 2
     # argument validation happens before any CUDA call, so it is testable without a GPU
     st = lib.b200_set_kv_buffer(None, None, None, None, None, 0, 4, 8, 8, 8, 8, 8, 8, 2, None)
     assert st == _cabi.B200_ERR_INVALID_ARG

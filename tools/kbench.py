@@ -89,16 +89,17 @@ def bench_decode(args):
 def bench_gemm_int8(args):
     dev = torch.device("cuda")
     shapes = [(4096, 6144), (4096, 4096), (4096, 28672), (14336, 4096)]
-    for m in ([args.m] if args.m else [1, 16, 64, 128, 256, 2048, 8192]):
+    for m in ([args.m] if args.m else [1, 16, 64, 128, 256, 512, 2048, 8192]):
         for (kk, n) in shapes:
             a = torch.randint(-127, 128, (m, kk), device=dev, dtype=torch.int8)
             copies = max(2, int(300e6 // (n * kk)) + 1)
             ws = [torch.randint(-127, 128, (n, kk), device=dev, dtype=torch.int8) for _ in range(copies)]
             sa = torch.rand(m, device=dev)
             sb = torch.rand(n, device=dev)
-            med = best = timeit_rot(lambda c: (lambda: kernels.int8_scaled_mm(a, ws[c].t(), sa, sb, torch.bfloat16)), copies)
+            med = best = timeit_rot(lambda c: (lambda: kernels.int8_scaled_mm(a, ws[c].t(), sa, sb, torch.bfloat16,
+                                                                              cluster_splitk=args.cluster)), copies)
             byts = n * kk + m * kk + m * n * 2
-            print(json.dumps(dict(kernel="int8_scaled_mm", m=m, n=n, k=kk, ms_med=round(med, 4), ms_best=round(best, 4),
+            print(json.dumps(dict(kernel="int8_scaled_mm", path="cluster" if args.cluster else "streamk", m=m, n=n, k=kk, ms_med=round(med, 4), ms_best=round(best, 4),
                                   gbs=round(byts / med / 1e6, 1), tops=round(2 * m * n * kk / med / 1e9, 1))), flush=True)
 
 
@@ -192,5 +193,6 @@ if __name__ == "__main__":
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--m", type=int, default=0)
     ap.add_argument("--ragged", action="store_true")
+    ap.add_argument("--cluster", action="store_true", help="gemm_int8: cluster split-K kernel instead of stream-K")
     args = ap.parse_args()
     {"decode": bench_decode, "gemm_int8": bench_gemm_int8, "awq": bench_awq, "peak": bench_peak, "extend": bench_extend}[args.what](args)
