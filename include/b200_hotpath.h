@@ -221,6 +221,45 @@ int b200_rope_neox_set_kv(void* q, void* k, const void* v, const float* cos_sin_
                           int64_t k_token_stride, int64_t v_token_stride, int64_t k_cache_token_stride,
                           int64_t v_cache_token_stride, int dtype, void* stream);
 
+/* ---- caller-side page-table kernels ----------------------------------------------------------
+ * Bit-exact integer kernels that replace the Triton kernels feeding the path every step:
+ *   b200_alloc_extend   alloc_extend_kernel (python/sglang/srt/mem_cache/allocator.py:276-360): for request b with
+ *       prefix p_b and length s_b, token j of the extension gets last_loc_b + 1 + j while the old partial page
+ *       lasts, then free_pages[first_new_page_b + k / P] * P + k % P; out_indices are concatenated in request
+ *       order; *ret_values = (new_pages << 32) | sum_extend.
+ *   b200_alloc_decode   alloc_decode_kernel (allocator.py:364-401): one token per request; *ret_values = new_pages.
+ *     Fusions (allocator.py:411 "TODO: fuse last_loc into the kernel"): last_loc == NULL reads it from
+ *     req_to_token[req_pool_indices[b], prefix_b - 1] (get_last_loc); write_req_to_token != 0 also stores the new
+ *     slots into req_to_token[req, prefix_b : s_b] (write_req_to_token_pool_triton).
+ *   b200_write_req_to_token_pool  write_req_to_token_pool_triton (managers/schedule_batch.py:1920-1953)
+ *   b200_get_last_loc             get_last_loc_kernel / get_last_loc_torch (schedule_batch.py:1972-2027)
+ *   b200_compute_position         compute_position_kernel (model_executor/forward_batch_info.py:886-957)
+ *   b200_create_kv_indices        create_flashinfer_kv_indices_triton (layers/attention/utils.py:11-47)
+ * `*_is_int64` flags give the element type (int32 / int64) of the index arrays next to them; free_pages,
+ * out_indices, ret_values and positions are int64, req_to_token / kv_indptr / kv_indices / extend_start_loc int32.
+ */
+int b200_alloc_extend(int64_t* out_indices, int64_t* ret_values, const void* prefix_lens, const void* seq_lens,
+                      const void* last_loc, int lens_is_int64, const int64_t* free_pages, int batch, int page_size,
+                      int32_t* req_to_token, int64_t req_to_token_stride, const void* req_pool_indices,
+                      int pool_is_int64, int write_req_to_token, void* stream);
+int b200_alloc_decode(int64_t* out_indices, int64_t* ret_values, const void* seq_lens, const void* last_loc,
+                      int lens_is_int64, const int64_t* free_pages, int batch, int page_size,
+                      int32_t* req_to_token, int64_t req_to_token_stride, const void* req_pool_indices,
+                      int pool_is_int64, int write_req_to_token, void* stream);
+int b200_write_req_to_token_pool(int32_t* req_to_token, int64_t req_to_token_stride, const void* req_pool_indices,
+                                 int pool_is_int64, const void* prefix_lens, const void* seq_lens,
+                                 const void* extend_lens, int lens_is_int64, const void* out_cache_loc,
+                                 int loc_is_int64, int batch, void* stream);
+int b200_get_last_loc(void* result, const int32_t* req_to_token, int64_t req_to_token_stride,
+                      const void* req_pool_indices, int pool_is_int64, const void* prefix_lens, int lens_is_int64,
+                      int n, void* stream);
+int b200_compute_position(int64_t* positions, int32_t* extend_start_loc, const void* extend_prefix_lens,
+                          const void* extend_seq_lens, int lens_is_int64, int batch, void* stream);
+int b200_create_kv_indices(int32_t* kv_indices, const int32_t* req_to_token, int64_t req_to_token_stride,
+                           const void* req_pool_indices, int pool_is_int64, const void* page_kernel_lens,
+                           int lens_is_int64, const int32_t* kv_indptr, const int32_t* kv_start_idx, int batch,
+                           void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -69,6 +69,12 @@ _SIGNATURES = {
     "b200_silu_and_mul_quant_int8": [_P, _P, _P, c_int64, c_int64, c_int, _P],
     "b200_rope_neox_set_kv": [_P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int64, c_int, c_int, c_int, c_int,
                               c_int64, c_int64, c_int64, c_int64, c_int64, c_int, _P],
+    "b200_alloc_extend": [_P, _P, _P, _P, _P, c_int, _P, c_int, c_int, _P, c_int64, _P, c_int, c_int, _P],
+    "b200_alloc_decode": [_P, _P, _P, _P, c_int, _P, c_int, c_int, _P, c_int64, _P, c_int, c_int, _P],
+    "b200_write_req_to_token_pool": [_P, c_int64, _P, c_int, _P, _P, _P, c_int, _P, c_int, c_int, _P],
+    "b200_get_last_loc": [_P, _P, c_int64, _P, c_int, _P, c_int, c_int, _P],
+    "b200_compute_position": [_P, _P, _P, _P, c_int, c_int, _P],
+    "b200_create_kv_indices": [_P, _P, c_int64, _P, c_int, _P, c_int, _P, _P, c_int, _P],
 }
 
 EXPORTED_SYMBOLS = sorted(list(_SIGNATURES) + ["b200_last_error"])

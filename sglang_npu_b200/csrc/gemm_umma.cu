@@ -838,6 +838,7 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
             }
             mbar_wait(fix_bar, fix_phase);
             fix_phase ^= 1u;
+            if (threadIdx.x == 128) trace_mark(tr, 11);  // peers' partials in shared memory
           }
           const uint32_t* sp = reinterpret_cast<const uint32_t*>(smem_raw + (base - smem_u32(smem_raw))) + row;
           uint16_t* outp = reinterpret_cast<uint16_t*>(g.out) + n;

@@ -493,3 +493,100 @@ def rope_neox_set_kv(positions: torch.Tensor, q: torch.Tensor, k: torch.Tensor, 
                                     is64, T, hq, hkv, head_dim, cos_sin_cache.shape[-1], q.stride(0), k.stride(0),
                                     v.stride(0), kcs, vcs, dtype_code(q.dtype), stream_ptr(q.device)),
           "b200_rope_neox_set_kv")
+
+
+# ---- caller-side page-table kernels --------------------------------------------------------------------
+def _same_int_dtype(*ts: torch.Tensor) -> int:
+    dts = {t.dtype for t in ts if t is not None}
+    if len(dts) != 1:
+        raise RuntimeError(f"index tensors must share one dtype, got {sorted(map(str, dts))}")
+    return _is64(next(t for t in ts if t is not None))
+
+
+def alloc_extend(prefix_lens: torch.Tensor, seq_lens: torch.Tensor, last_loc: Optional[torch.Tensor],
+                 free_pages: torch.Tensor, out_indices: torch.Tensor, ret_values: torch.Tensor, page_size: int,
+                 req_to_token: Optional[torch.Tensor] = None, req_pool_indices: Optional[torch.Tensor] = None,
+                 write_req_to_token: bool = False) -> None:
+    """alloc_extend_kernel (mem_cache/allocator.py:276-360).  last_loc=None reads it from req_to_token (get_last_loc
+    fused); write_req_to_token=True also stores the new slots into req_to_token[req, prefix:seq]."""
+    require_cuda(prefix_lens, seq_lens, last_loc, free_pages, out_indices, ret_values, req_to_token, req_pool_indices)
+    lib = _cabi.load()
+    assert free_pages.dtype == torch.int64 and out_indices.dtype == torch.int64 and ret_values.dtype == torch.int64
+    assert req_to_token is None or (req_to_token.dtype == torch.int32 and req_to_token.stride(1) == 1)
+    check(lib.b200_alloc_extend(ptr(out_indices), ptr(ret_values), ptr(prefix_lens), ptr(seq_lens), ptr(last_loc),
+                                _same_int_dtype(prefix_lens, seq_lens, last_loc), ptr(free_pages), seq_lens.numel(),
+                                int(page_size), ptr(req_to_token), 0 if req_to_token is None else req_to_token.stride(0),
+                                ptr(req_pool_indices), 0 if req_pool_indices is None else _is64(req_pool_indices),
+                                int(write_req_to_token), stream_ptr(seq_lens.device)), "b200_alloc_extend")
+
+
+def alloc_decode(seq_lens: torch.Tensor, last_loc: Optional[torch.Tensor], free_pages: torch.Tensor,
+                 out_indices: torch.Tensor, ret_values: torch.Tensor, page_size: int,
+                 req_to_token: Optional[torch.Tensor] = None, req_pool_indices: Optional[torch.Tensor] = None,
+                 write_req_to_token: bool = False) -> None:
+    """alloc_decode_kernel (allocator.py:364-401), same fusions as alloc_extend."""
+    require_cuda(seq_lens, last_loc, free_pages, out_indices, ret_values, req_to_token, req_pool_indices)
+    lib = _cabi.load()
+    assert free_pages.dtype == torch.int64 and out_indices.dtype == torch.int64 and ret_values.dtype == torch.int64
+    assert req_to_token is None or (req_to_token.dtype == torch.int32 and req_to_token.stride(1) == 1)
+    check(lib.b200_alloc_decode(ptr(out_indices), ptr(ret_values), ptr(seq_lens), ptr(last_loc),
+                                _same_int_dtype(seq_lens, last_loc), ptr(free_pages), seq_lens.numel(), int(page_size),
+                                ptr(req_to_token), 0 if req_to_token is None else req_to_token.stride(0),
+                                ptr(req_pool_indices), 0 if req_pool_indices is None else _is64(req_pool_indices),
+                                int(write_req_to_token), stream_ptr(seq_lens.device)), "b200_alloc_decode")
+
+
+def write_req_to_token_pool(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, prefix_lens: torch.Tensor,
+                            seq_lens: torch.Tensor, extend_lens: torch.Tensor, out_cache_loc: torch.Tensor) -> None:
+    """write_req_to_token_pool_triton (managers/schedule_batch.py:1920-1953)."""
+    require_cuda(req_to_token, req_pool_indices, prefix_lens, seq_lens, extend_lens, out_cache_loc)
+    lib = _cabi.load()
+    assert req_to_token.dtype == torch.int32 and req_to_token.stride(1) == 1
+    check(lib.b200_write_req_to_token_pool(ptr(req_to_token), req_to_token.stride(0), ptr(req_pool_indices),
+                                           _is64(req_pool_indices), ptr(prefix_lens), ptr(seq_lens), ptr(extend_lens),
+                                           _same_int_dtype(prefix_lens, seq_lens, extend_lens), ptr(out_cache_loc),
+                                           _is64(out_cache_loc), req_pool_indices.numel(),
+                                           stream_ptr(req_to_token.device)), "b200_write_req_to_token_pool")
+
+
+def get_last_loc(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, prefix_lens: torch.Tensor) -> torch.Tensor:
+    """get_last_loc (schedule_batch.py:1956-2027): result has prefix_lens' dtype."""
+    require_cuda(req_to_token, req_pool_indices, prefix_lens)
+    lib = _cabi.load()
+    assert req_to_token.dtype == torch.int32 and req_to_token.stride(1) == 1
+    result = torch.empty_like(prefix_lens)
+    check(lib.b200_get_last_loc(ptr(result), ptr(req_to_token), req_to_token.stride(0), ptr(req_pool_indices),
+                                _is64(req_pool_indices), ptr(prefix_lens), _is64(prefix_lens), prefix_lens.numel(),
+                                stream_ptr(prefix_lens.device)), "b200_get_last_loc")
+    return result
+
+
+def compute_position(extend_prefix_lens: Optional[torch.Tensor], extend_seq_lens: torch.Tensor,
+                     extend_seq_lens_sum: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    """compute_position_triton (model_executor/forward_batch_info.py:886-910): (positions int64, extend_start_loc int32)."""
+    require_cuda(extend_prefix_lens, extend_seq_lens)
+    lib = _cabi.load()
+    bs = extend_seq_lens.numel()
+    if extend_prefix_lens is not None and extend_prefix_lens.numel() != bs:
+        extend_prefix_lens = None  # the reference's has_prefix rule (:890)
+    positions = torch.empty(extend_seq_lens_sum, dtype=torch.int64, device=extend_seq_lens.device)
+    start = torch.empty(bs, dtype=torch.int32, device=extend_seq_lens.device)
+    check(lib.b200_compute_position(ptr(positions), ptr(start), ptr(extend_prefix_lens), ptr(extend_seq_lens),
+                                    _same_int_dtype(extend_prefix_lens, extend_seq_lens), bs,
+                                    stream_ptr(extend_seq_lens.device)), "b200_compute_position")
+    return positions, start
+
+
+def create_flashinfer_kv_indices(req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+                                 page_kernel_lens: torch.Tensor, kv_indptr: torch.Tensor,
+                                 kv_start_idx: Optional[torch.Tensor], kv_indices: torch.Tensor) -> None:
+    """create_flashinfer_kv_indices_triton (layers/attention/utils.py:11-47)."""
+    require_cuda(req_to_token, req_pool_indices, page_kernel_lens, kv_indptr, kv_start_idx, kv_indices)
+    lib = _cabi.load()
+    assert req_to_token.dtype == torch.int32 and req_to_token.stride(1) == 1
+    assert kv_indptr.dtype == torch.int32 and kv_indices.dtype == torch.int32
+    assert kv_start_idx is None or kv_start_idx.dtype == torch.int32
+    check(lib.b200_create_kv_indices(ptr(kv_indices), ptr(req_to_token), req_to_token.stride(0), ptr(req_pool_indices),
+                                     _is64(req_pool_indices), ptr(page_kernel_lens), _is64(page_kernel_lens),
+                                     ptr(kv_indptr), ptr(kv_start_idx), req_pool_indices.numel(),
+                                     stream_ptr(req_to_token.device)), "b200_create_kv_indices")

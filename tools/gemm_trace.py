@@ -16,7 +16,7 @@ from sglang_npu_b200 import kernels  # noqa: E402
 GHZ = 1.965
 NAMES = {
     "streamk": {1: "setup", 2: "pdl_wait", 3: "first_full", 4: "mma_issued", 5: "seg0_acc", 6: "contrib_pub",
-                7: "last_seg_acc", 8: "flags_seen", 9: "epi_done"},
+                7: "last_seg_acc", 8: "flags_seen", 11: "partials_in_smem", 9: "epi_done"},
     "cluster": {1: "setup", 2: "pdl_wait", 3: "first_full", 4: "mma_issued", 5: "acc_ready", 6: "csync1", 7: "scatter",
                 8: "csync2", 9: "epi_done"},
 }
