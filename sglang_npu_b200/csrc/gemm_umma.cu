@@ -94,17 +94,40 @@ template <int MODE>
 __device__ __forceinline__ void finalize_store16(const uint32_t (&r)[16], const float* s_scale, float sn, bool has_bias,
                                                  float bias, bool bf, uint16_t* p, int32_t* ap, int64_t N, int m_left,
                                                  bool n_ok) {
+  float sc[16];
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    const float v = finalize<MODE>(r[j], s_scale[j], sn, has_bias, bias);
-    const uint16_t hb = __half_as_ushort(__float2half_rn(v));
-    const uint16_t bb = __bfloat16_as_ushort(__float2bfloat16_rn(v));
-    if (n_ok && j < m_left) p[(int64_t)j * N] = bf ? bb : hb;
+  for (int j = 0; j < 16; j += 4) {
+    const float4 t = *reinterpret_cast<const float4*>(s_scale + j);  // s_scale + c0 is 64-byte aligned
+    sc[j] = t.x; sc[j + 1] = t.y; sc[j + 2] = t.z; sc[j + 3] = t.w;
+  }
+  uint16_t h[16];
+  if (bf) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) h[j] = __bfloat16_as_ushort(__float2bfloat16_rn(finalize<MODE>(r[j], sc[j], sn, has_bias, bias)));
+  } else {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) h[j] = __half_as_ushort(__float2half_rn(finalize<MODE>(r[j], sc[j], sn, has_bias, bias)));
+  }
+  if (!n_ok) return;
+  if (m_left >= 16) {  // full group of tokens: straight-line stores
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      *p = h[j];
+      p += N;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      if (j < m_left) *p = h[j];
+      p += N;
+    }
   }
   if (ap != nullptr) {
 #pragma unroll
-    for (int j = 0; j < 16; ++j)
-      if (n_ok && j < m_left) ap[(int64_t)j * N] = (int32_t)r[j];
+    for (int j = 0; j < 16; ++j) {
+      if (j < m_left) *ap = (int32_t)r[j];
+      ap += N;
+    }
   }
 }
 
@@ -655,7 +678,7 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
   constexpr int kWBytes = 128 * kBK;
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint32_t s_tmem_base;
-  __shared__ float s_scale_m[BN];
+  __shared__ __align__(16) float s_scale_m[BN];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar = base + L::kBarOff;
   const uint32_t fix_bar = bar + (2 * STAGES + 4) * 8;
