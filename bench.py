@@ -293,9 +293,10 @@ def main():
     def timed(*a, **kw):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        orig(*a, **kw)
+        r = orig(*a, **kw)  # stage 1 + stage 2 (the LSE merge, fused with the int8 quant of the o_proj input)
         e1.record()
         pairs.append((e0, e1))
+        return r
 
     kernels.decode_attention_fwd = timed
     import sglang_npu_b200.srt.layers.attention.b200_backend as bmod
@@ -314,7 +315,7 @@ def main():
     attn_bytes = bs * ctx * 2 * hkv_local * cfg.head_dim * 2 + bs * hq_local * cfg.head_dim * 2 * 2 + 4 * bs * (ctx // PAGE)
     peaks, peak_kind = measured_peaks()
     achieved = attn_bytes / (attn_ms * 1e-3) / 1e9
-    roofline = {"kernel": "decode_attn_kernel (+ decode_merge_kernel), one launch per layer", "bound": "hbm",
+    roofline = {"kernel": "decode_attn_kernel (+ decode_merge_quant_kernel: LSE merge fused with the int8 quant of the o_proj input), one launch pair per layer", "bound": "hbm",
                 "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                 "peak_kind": f"{peak_kind} (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)",
                 "frac_of_nominal_8TBs": achieved / 8000.0, "bytes_per_launch": attn_bytes, "ms_per_launch": attn_ms,

@@ -89,6 +89,16 @@ int b200_decode_attn(void* o, const void* q, const void* k_cache, const void* v_
                      int64_t kv_token_stride, float sm_scale, float logit_cap,
                      int kv_chunk, int max_splits, void* workspace, size_t workspace_bytes,
                      int dtype, void* stream);
+/* Same, with stage 2 fused with the per-token int8 quantisation feeding o_proj:
+ * (oq, oq_scale) = per_token_quant_int8(o) — bit-identical to b200_decode_attn followed by
+ * b200_per_token_quant_int8 on the [batch, num_q_heads * head_dim] output; o is still written. */
+int b200_decode_attn_int8(void* o, int8_t* oq, float* oq_scale, const void* q, const void* k_cache,
+                          const void* v_cache, const int32_t* req_to_token, int64_t req_to_token_stride,
+                          const void* req_pool_indices, const void* seq_lens, int index_is_int64, int batch,
+                          int num_q_heads, int num_kv_heads, int head_dim, int64_t q_token_stride,
+                          int64_t o_token_stride, int64_t kv_token_stride, float sm_scale, float logit_cap,
+                          int kv_chunk, int max_splits, void* workspace, size_t workspace_bytes, int dtype,
+                          void* stream);
 
 /* ---- extend (prefill) attention ------------------------------------------------------
  * Replaces extend_attention_fwd (triton_ops/extend_attention.py:302-440) and the
@@ -200,6 +210,13 @@ int b200_rope_neox(void* q, void* k, const float* cos_sin_cache, const int64_t* 
                    int64_t num_tokens, int num_q_heads, int num_kv_heads, int head_dim,
                    int rot_dim, int64_t q_token_stride, int64_t k_token_stride, int dtype,
                    void* stream);
+
+/* Greedy sampling (python/sglang/srt/layers/sampler.py greedy path, torch.argmax(logits, -1)): out[r] = index of
+ * the largest x[r, :V] (lowest index on ties).  Workspace: b200_argmax_workspace_bytes, zero-initialised once by
+ * the caller, self-cleaning; NULL restricts the kernel to one CTA per row. */
+int b200_argmax_workspace_bytes(int64_t rows, size_t* bytes);
+int b200_argmax(int64_t* out, const void* x, int64_t rows, int64_t V, int64_t row_stride, int dtype,
+                void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- fused steps ("fused_add_rmsnorm + emit per-token int8 quant for the following GEMM,
  * RoPE + fused KV-cache write, silu_and_mul + quant for down_proj") ---------------------------------------------

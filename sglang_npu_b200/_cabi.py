@@ -45,6 +45,9 @@ _SIGNATURES = {
     "b200_decode_attn": [_P, _P, _P, _P, _P, c_int64, _P, _P, c_int, c_int, c_int, c_int, c_int,
                          c_int64, c_int64, c_int64, c_float, c_float, c_int, c_int, _P, c_size_t,
                          c_int, _P],
+    "b200_decode_attn_int8": [_P, _P, _P, _P, _P, _P, _P, c_int64, _P, _P, c_int, c_int, c_int, c_int, c_int,
+                              c_int64, c_int64, c_int64, c_float, c_float, c_int, c_int, _P, c_size_t,
+                              c_int, _P],
     "b200_extend_attn": [_P, _P, _P, _P, _P, _P, _P, c_int64, _P, c_int, _P, _P, c_int, c_int,
                          c_int, c_int, c_int, c_int64, c_int64, c_int64, c_int64, c_int64, c_float,
                          c_float, c_int, c_int, _P],
@@ -65,6 +68,8 @@ _SIGNATURES = {
     "b200_silu_and_mul": [_P, _P, c_int64, c_int64, c_int, _P],
     "b200_rope_neox": [_P, _P, _P, _P, c_int64, c_int, c_int, c_int, c_int, c_int64, c_int64,
                        c_int, _P],
+    "b200_argmax_workspace_bytes": [c_int64, POINTER(c_size_t)],
+    "b200_argmax": [_P, _P, c_int64, c_int64, c_int64, c_int, _P, c_size_t, _P],
     "b200_rmsnorm_quant_int8": [_P, _P, _P, _P, _P, _P, c_int64, c_int64, c_float, c_int, _P],
     "b200_silu_and_mul_quant_int8": [_P, _P, _P, c_int64, c_int64, c_int, _P],
     "b200_rope_neox_set_kv": [_P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int64, c_int, c_int, c_int, c_int,

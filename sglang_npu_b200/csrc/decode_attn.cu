@@ -47,6 +47,8 @@ struct DecodeArgs {
   int kv_chunk, max_splits;
   float* part_o;    // [batch, Hq, max_splits, D]
   float* part_lse;  // [batch, Hq, max_splits]   (log2 domain)
+  int8_t* oq;       // optional fused output quant (b200_decode_attn_int8): [batch, Hq * D] int8 codes
+  float* oq_scale;  // [batch] per-token scales
 };
 
 template <int D>
@@ -394,6 +396,113 @@ __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeArgs a) {
   for (int d = 0; d < kPer; d += 2) *reinterpret_cast<uint32_t*>(dst + d) = pack2<T>(acc[d], acc[d + 1]);
 }
 
+// Stage 2 fused with the per-token int8 quantisation that feeds o_proj (b200_decode_attn_int8): one CTA per request
+// merges every q head (or picks up the bf16 row stage 1 already finalised), rounds to T exactly like
+// decode_merge_kernel, and then quantises the [Hq * D] row exactly like per_token_quant_int8_kernel (quant.cu) —
+// bit-identical to the two kernels back to back, one launch and one activation round-trip less.
+template <typename T, int D>
+__global__ void __launch_bounds__(1024) decode_merge_quant_kernel(const DecodeArgs a) {
+  extern __shared__ float row_f[];  // Hq * D
+  __shared__ float red[32];
+  pdl_trigger();
+  pdl_wait();
+  const int b = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nwarps = blockDim.x >> 5;
+  const int seq_len = (int)load_index(a.seq_lens, b, a.index_is_int64);
+  const int num_splits = (seq_len + a.kv_chunk - 1) / a.kv_chunk;
+  constexpr int kPer = D / 32;
+  float amax = 0.f;
+  for (int h = warp; h < a.num_q_heads; h += nwarps) {  // one warp per q head: every head's loads are in flight at once
+    T* dst = reinterpret_cast<T*>(a.o) + (int64_t)b * a.o_token_stride + (int64_t)h * D + lane * kPer;
+    float acc[kPer];
+    if (num_splits == 1) {
+#pragma unroll
+      for (int d = 0; d < kPer; d += 2) {
+        const float2 v = unpack2<T>(*reinterpret_cast<const uint32_t*>(dst + d));
+        acc[d] = v.x;
+        acc[d + 1] = v.y;
+      }
+    } else {
+#pragma unroll
+      for (int d = 0; d < kPer; ++d) acc[d] = 0.f;
+      if (num_splits > 1) {
+        const int64_t base = ((int64_t)b * a.num_q_heads + h) * a.max_splits;
+        float M = -INFINITY;
+        for (int s = lane; s < num_splits; s += 32) M = fmaxf(M, a.part_lse[base + s]);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, off));
+        float L = 0.f;
+        for (int s0 = 0; s0 < num_splits; s0 += 4) {  // 4 chunks' partial rows loaded before any is used
+          float pv[4][kPer];
+          float pl[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const bool ok = s0 + i < num_splits;
+            const int s = ok ? s0 + i : s0;
+            pl[i] = ok ? a.part_lse[base + s] : -INFINITY;
+            const float* src = a.part_o + (base + s) * D + lane * kPer;
+            if (kPer == 4) {
+              const float4 v = *reinterpret_cast<const float4*>(src);
+              pv[i][0] = v.x; pv[i][1] = v.y; pv[i][2] = v.z; pv[i][kPer - 1] = v.w;
+            } else {
+              const float2 v = *reinterpret_cast<const float2*>(src);
+              pv[i][0] = v.x; pv[i][1] = v.y;
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {  // same accumulation order as decode_merge_kernel (s ascending)
+            if (s0 + i < num_splits) {
+              const float w = fast_exp2(pl[i] - M);
+              L += w;
+#pragma unroll
+              for (int d = 0; d < kPer; ++d) acc[d] += pv[i][d] * w;
+            }
+          }
+        }
+        const float inv = 1.f / L;
+#pragma unroll
+        for (int d = 0; d < kPer; ++d) acc[d] *= inv;
+      }
+#pragma unroll
+      for (int d = 0; d < kPer; d += 2) {
+        const uint32_t u = pack2<T>(acc[d], acc[d + 1]);
+        *reinterpret_cast<uint32_t*>(dst + d) = u;
+        const float2 v = unpack2<T>(u);  // the T-rounded value the un-fused quant kernel would read
+        acc[d] = v.x;
+        acc[d + 1] = v.y;
+      }
+    }
+#pragma unroll
+    for (int d = 0; d < kPer; ++d) {
+      row_f[h * D + lane * kPer + d] = acc[d];
+      amax = fmaxf(amax, fabsf(acc[d]));
+    }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, off));
+  if (lane == 0) red[warp] = amax;
+  __syncthreads();
+  amax = red[0];
+  for (int i = 1; i < nwarps; ++i) amax = fmaxf(amax, red[i]);
+  amax = fmaxf(amax, 1e-10f);
+  const float inv = __fmul_rn(__frcp_rn(amax), 127.f);
+  if (threadIdx.x == 0) a.oq_scale[b] = __fdiv_rn(amax, 127.f);
+  const int H = a.num_q_heads * D;
+  int8_t* qr = a.oq + (int64_t)b * H;
+  for (int c = threadIdx.x * 8; c < H; c += (int)blockDim.x * 8) {
+    uint32_t lo = 0, hi = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int x0 = __float2int_rn(__fmul_rn(row_f[c + i], inv));
+      const int x1 = __float2int_rn(__fmul_rn(row_f[c + 4 + i], inv));
+      lo |= (uint32_t)(x0 & 0xff) << (8 * i);
+      hi |= (uint32_t)(x1 & 0xff) << (8 * i);
+    }
+    *reinterpret_cast<uint2*>(qr + c) = make_uint2(lo, hi);
+  }
+}
+
 template <typename T, int D>
 static int launch_decode(const DecodeArgs& a, cudaStream_t stream) {
   constexpr int STAGES = 3;
@@ -414,6 +523,14 @@ static int launch_decode(const DecodeArgs& a, cudaStream_t stream) {
     rc = launch_k(kern, grid, dim3(kDecThreads), smem, stream, 1, true, a);
   }
   if (rc != B200_OK) return rc;
+  if (a.oq != nullptr) {
+    const int qsmem = a.num_q_heads * D * (int)sizeof(float);
+    auto kern = decode_merge_quant_kernel<T, D>;
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, qsmem));
+    int threads = 32 * a.num_q_heads;
+    threads = threads > 1024 ? 1024 : threads < 128 ? 128 : threads;
+    return launch_k(kern, dim3(a.batch), dim3(threads), qsmem, stream, 1, true, a);
+  }
   const int warps = a.batch * a.num_q_heads;
   return launch_k(decode_merge_kernel<T, D>, dim3((warps + 3) / 4), dim3(128), 0, stream, 1, true, a);
 }
@@ -431,14 +548,14 @@ B200_API int b200_decode_attn_workspace_bytes(int batch, int num_q_heads, int he
   return B200_OK;
 }
 
-B200_API int b200_decode_attn(void* o, const void* q, const void* k_cache, const void* v_cache,
-                                const int32_t* req_to_token, int64_t req_to_token_stride,
-                                const void* req_pool_indices, const void* seq_lens,
-                                int index_is_int64, int batch, int num_q_heads, int num_kv_heads,
-                                int head_dim, int64_t q_token_stride, int64_t o_token_stride,
-                                int64_t kv_token_stride, float sm_scale, float logit_cap,
-                                int kv_chunk, int max_splits, void* workspace,
-                                size_t workspace_bytes, int dtype, void* stream) {
+static int decode_attn_impl(void* o, const void* q, const void* k_cache, const void* v_cache,
+                            const int32_t* req_to_token, int64_t req_to_token_stride,
+                            const void* req_pool_indices, const void* seq_lens,
+                            int index_is_int64, int batch, int num_q_heads, int num_kv_heads,
+                            int head_dim, int64_t q_token_stride, int64_t o_token_stride,
+                            int64_t kv_token_stride, float sm_scale, float logit_cap,
+                            int kv_chunk, int max_splits, void* workspace,
+                            size_t workspace_bytes, int dtype, int8_t* oq, float* oq_scale, void* stream) {
   using namespace b200;
   B200_REQUIRE(batch >= 0, "decode_attn: negative batch");
   if (batch == 0) return B200_OK;
@@ -474,6 +591,12 @@ B200_API int b200_decode_attn(void* o, const void* q, const void* k_cache, const
   const size_t n = (size_t)batch * num_q_heads * max_splits;
   a.part_o = reinterpret_cast<float*>(workspace);
   a.part_lse = a.part_o ? a.part_o + n * head_dim : nullptr;
+  a.oq = oq;
+  a.oq_scale = oq_scale;
+  B200_REQUIRE((oq == nullptr) == (oq_scale == nullptr), "decode_attn_int8: oq and oq_scale go together");
+  B200_REQUIRE(oq == nullptr || ((uintptr_t)oq % 8 == 0 && (num_q_heads * head_dim) % 8 == 0 &&
+                                 (size_t)num_q_heads * head_dim * 4 <= 200 * 1024),
+               "decode_attn_int8: row of %d values not supported", num_q_heads * head_dim);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == B200_BF16) {
     if (head_dim == 128) return launch_decode<__nv_bfloat16, 128>(a, st);
@@ -485,4 +608,32 @@ B200_API int b200_decode_attn(void* o, const void* q, const void* k_cache, const
     return fail(B200_ERR_UNSUPPORTED, "decode_attn: dtype %d not supported (bf16/f16 only)", dtype);
   }
   return fail(B200_ERR_UNSUPPORTED, "decode_attn: head_dim %d not supported (64, 128)", head_dim);
+}
+
+B200_API int b200_decode_attn(void* o, const void* q, const void* k_cache, const void* v_cache,
+                              const int32_t* req_to_token, int64_t req_to_token_stride,
+                              const void* req_pool_indices, const void* seq_lens,
+                              int index_is_int64, int batch, int num_q_heads, int num_kv_heads,
+                              int head_dim, int64_t q_token_stride, int64_t o_token_stride,
+                              int64_t kv_token_stride, float sm_scale, float logit_cap,
+                              int kv_chunk, int max_splits, void* workspace,
+                              size_t workspace_bytes, int dtype, void* stream) {
+  return decode_attn_impl(o, q, k_cache, v_cache, req_to_token, req_to_token_stride, req_pool_indices, seq_lens,
+                          index_is_int64, batch, num_q_heads, num_kv_heads, head_dim, q_token_stride, o_token_stride,
+                          kv_token_stride, sm_scale, logit_cap, kv_chunk, max_splits, workspace, workspace_bytes, dtype,
+                          nullptr, nullptr, stream);
+}
+
+B200_API int b200_decode_attn_int8(void* o, int8_t* oq, float* oq_scale, const void* q, const void* k_cache,
+                                   const void* v_cache, const int32_t* req_to_token, int64_t req_to_token_stride,
+                                   const void* req_pool_indices, const void* seq_lens, int index_is_int64, int batch,
+                                   int num_q_heads, int num_kv_heads, int head_dim, int64_t q_token_stride,
+                                   int64_t o_token_stride, int64_t kv_token_stride, float sm_scale, float logit_cap,
+                                   int kv_chunk, int max_splits, void* workspace, size_t workspace_bytes, int dtype,
+                                   void* stream) {
+  B200_REQUIRE(oq != nullptr && oq_scale != nullptr, "decode_attn_int8: null quant output");
+  return decode_attn_impl(o, q, k_cache, v_cache, req_to_token, req_to_token_stride, req_pool_indices, seq_lens,
+                          index_is_int64, batch, num_q_heads, num_kv_heads, head_dim, q_token_stride, o_token_stride,
+                          kv_token_stride, sm_scale, logit_cap, kv_chunk, max_splits, workspace, workspace_bytes, dtype,
+                          oq, oq_scale, stream);
 }

@@ -130,6 +130,73 @@ __global__ void __launch_bounds__(256) rope_neox_kernel(T* __restrict__ q, T* __
 
 using namespace b200;
 
+// ---- greedy sampling: row-wise argmax of the logits (sampler.py greedy path: torch.argmax(logits, -1)) -----------------
+// A row is split over `parts` CTAs (grid.y) so that 64 decode rows still cover every SM; each CTA reduces its
+// slice with 16-byte loads and publishes one 64-bit key (order-preserving float bits << 32 | ~index) with
+// atomicMax, so equal maxima resolve to the LOWEST index whatever the arrival order; the last CTA of a row
+// (counter) decodes the key into the int64 token id and resets key and counter (self-cleaning scratch).
+template <typename T>
+__global__ void __launch_bounds__(256) argmax_kernel(int64_t* __restrict__ out, const T* __restrict__ x, int64_t V,
+                                                     int64_t row_stride, unsigned long long* __restrict__ keys,
+                                                     unsigned int* __restrict__ counters) {
+  __shared__ unsigned long long s_key[8];
+  pdl_trigger();
+  pdl_wait();
+  const int64_t row = blockIdx.x;
+  const int parts = gridDim.y;
+  const int64_t per = ((V + parts - 1) / parts + 7) & ~(int64_t)7;
+  const int64_t lo = (int64_t)blockIdx.y * per;
+  const int64_t hi = lo + per < V ? lo + per : V;
+  const T* xr = x + row * row_stride;
+  float best = -INFINITY;
+  int64_t best_i = V;  // NaN-free logits assumed (as torch's fast path); V = "none seen"
+  for (int64_t c = lo + threadIdx.x * 8; c < hi; c += 256 * 8) {
+    if (c + 8 <= hi) {
+      const int4 v = ld_nc_v4(xr + c);
+      const uint32_t* u = reinterpret_cast<const uint32_t*>(&v);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 f = unpack2<T>(u[i]);
+        if (f.x > best) { best = f.x; best_i = c + 2 * i; }
+        if (f.y > best) { best = f.y; best_i = c + 2 * i + 1; }
+      }
+    } else {
+      for (int64_t j = c; j < hi; ++j) {
+        const float f = DT<T>::to_f(xr[j]);
+        if (f > best) { best = f; best_i = j; }
+      }
+    }
+  }
+  // order-preserving key: larger value wins, then smaller index
+  uint32_t fb = __float_as_uint(best);
+  fb = (fb & 0x80000000u) ? ~fb : (fb | 0x80000000u);
+  unsigned long long key = ((unsigned long long)fb << 32) | (unsigned long long)(0xFFFFFFFFu - (uint32_t)best_i);
+  if (best_i >= V) key = 0ull;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+    key = other > key ? other : key;
+  }
+  if ((threadIdx.x & 31) == 0) s_key[threadIdx.x >> 5] = key;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int w = 1; w < 8; ++w) key = s_key[w] > key ? s_key[w] : key;
+    if (parts == 1) {
+      out[row] = (int64_t)(0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull));
+    } else {
+      atomicMax(keys + row, key);
+      __threadfence();
+      if (atomicAdd(counters + row, 1u) == (unsigned)parts - 1u) {
+        __threadfence();
+        const unsigned long long k = atomicExch(keys + row, 0ull);
+        counters[row] = 0u;
+        out[row] = (int64_t)(0xFFFFFFFFu - (uint32_t)(k & 0xFFFFFFFFull));
+      }
+    }
+  }
+}
+
 B200_API int b200_rmsnorm(void* out, void* residual, const void* x, const void* weight, int64_t M, int64_t H,
                             float eps, int dtype, void* stream) {
   B200_REQUIRE(M >= 0 && H > 0, "rmsnorm: bad sizes");
@@ -189,4 +256,35 @@ B200_API int b200_rope_neox(void* q, void* k, const float* cos_sin_cache, const 
     return launch_k(rope_neox_kernel<__half>, dim3((unsigned)num_tokens), dim3(256), 0, st, 1, true, (__half*)q, (__half*)k,
                     cos_sin_cache, positions, num_q_heads, num_kv_heads, head_dim, rot_dim, q_token_stride, k_token_stride);
   return fail(B200_ERR_UNSUPPORTED, "rope_neox: dtype %d not supported", dtype);
+}
+
+B200_API int b200_argmax_workspace_bytes(int64_t rows, size_t* bytes) {
+  B200_REQUIRE(bytes != nullptr && rows >= 0, "argmax_workspace_bytes: bad arguments");
+  *bytes = (size_t)rows * 16;  // one u64 key + one u32 counter (padded) per row; zero-initialised once, self-cleaning
+  return B200_OK;
+}
+
+B200_API int b200_argmax(int64_t* out, const void* x, int64_t rows, int64_t V, int64_t row_stride, int dtype,
+                         void* workspace, size_t workspace_bytes, void* stream) {
+  B200_REQUIRE(rows >= 0 && V > 0 && V < (1ll << 32), "argmax: bad sizes");
+  if (rows == 0) return B200_OK;
+  B200_REQUIRE(out && x, "argmax: null pointer");
+  B200_REQUIRE(row_stride % 8 == 0 && ((uintptr_t)x % 16) == 0, "argmax: rows must be 16-byte aligned");
+  B200_REQUIRE(rows <= 65535 * 32768ll, "argmax: too many rows");
+  int parts = (int)((2 * (int64_t)sm_count() + rows - 1) / rows);  // ~2 CTAs per SM
+  const int64_t max_parts = ceil_div(V, 2048);
+  if (parts > max_parts) parts = (int)max_parts;
+  if (parts < 1) parts = 1;
+  if (workspace == nullptr || workspace_bytes < (size_t)rows * 16) parts = 1;
+  unsigned long long* keys = reinterpret_cast<unsigned long long*>(workspace);
+  unsigned int* counters = parts > 1 ? reinterpret_cast<unsigned int*>(keys + rows) : nullptr;
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((unsigned)rows, (unsigned)parts);
+  if (dtype == B200_BF16)
+    return launch_k(argmax_kernel<__nv_bfloat16>, grid, dim3(256), 0, st, 1, true, out, (const __nv_bfloat16*)x, V,
+                    row_stride, keys, counters);
+  if (dtype == B200_F16)
+    return launch_k(argmax_kernel<__half>, grid, dim3(256), 0, st, 1, true, out, (const __half*)x, V, row_stride, keys,
+                    counters);
+  return fail(B200_ERR_UNSUPPORTED, "argmax: dtype %d not supported (bf16/f16)", dtype);
 }

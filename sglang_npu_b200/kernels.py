@@ -17,8 +17,8 @@ from ._cabi import check as _check, dtype_code, ptr, require_cuda, stream_ptr
 
 
 _LAUNCHES = 0
-_KERNELS_PER_CALL = {"b200_decode_attn": 2, "b200_decode_attn_workspace_bytes": 0,
-                     "b200_int8_scaled_mm_workspace_bytes": 0}
+_KERNELS_PER_CALL = {"b200_decode_attn": 2, "b200_decode_attn_int8": 2, "b200_decode_attn_workspace_bytes": 0,
+                     "b200_int8_scaled_mm_workspace_bytes": 0, "b200_argmax_workspace_bytes": 0}
 
 
 def check(status: int, what: str) -> None:
@@ -99,8 +99,9 @@ def decode_attention_fwd(q: torch.Tensor, k_buffer: torch.Tensor, v_buffer: torc
                          o: torch.Tensor, req_to_token: torch.Tensor,
                          req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
                          workspace: Optional[torch.Tensor], kv_chunk: int, max_splits: int,
-                         sm_scale: float, logit_cap: float = 0.0) -> None:
-    """q [bs, Hq, D]; k/v_buffer [slots, Hkv, D]; o [bs, Hq, D] (written)."""
+                         sm_scale: float, logit_cap: float = 0.0, int8_out: bool = False):
+    """q [bs, Hq, D]; k/v_buffer [slots, Hkv, D]; o [bs, Hq, D] (written).  int8_out=True fuses the per-token int8
+    quantisation of the [bs, Hq*D] output into stage 2 and returns it as an Int8Activation (for o_proj)."""
     require_cuda(q, k_buffer, v_buffer, o, req_to_token, req_pool_indices, seq_lens)
     lib = _cabi.load()
     bs, hq, d = q.shape
@@ -111,6 +112,16 @@ def decode_attention_fwd(q: torch.Tensor, k_buffer: torch.Tensor, v_buffer: torc
     assert req_pool_indices.dtype == seq_lens.dtype
     assert req_pool_indices.is_contiguous() and seq_lens.is_contiguous()
     ws_bytes = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    if int8_out:
+        oq = torch.empty((bs, hq * d), device=q.device, dtype=torch.int8)
+        oscale = torch.empty((bs, 1), device=q.device, dtype=torch.float32)
+        check(lib.b200_decode_attn_int8(
+            ptr(o), ptr(oq), ptr(oscale), ptr(q), ptr(k_buffer), ptr(v_buffer), ptr(req_to_token),
+            req_to_token.stride(0), ptr(req_pool_indices), ptr(seq_lens), _is64(seq_lens), bs, hq, hkv, d,
+            q.stride(0), o.stride(0), k_buffer.stride(0), float(sm_scale), float(logit_cap),
+            int(kv_chunk), int(max_splits), ptr(workspace), ws_bytes, dtype_code(q.dtype),
+            stream_ptr(q.device)), "b200_decode_attn_int8")
+        return Int8Activation(oq, oscale, q.dtype)
     check(lib.b200_decode_attn(
         ptr(o), ptr(q), ptr(k_buffer), ptr(v_buffer), ptr(req_to_token), req_to_token.stride(0),
         ptr(req_pool_indices), ptr(seq_lens), _is64(seq_lens), bs, hq, hkv, d,
@@ -590,3 +601,25 @@ def create_flashinfer_kv_indices(req_to_token: torch.Tensor, req_pool_indices: t
                                      _is64(req_pool_indices), ptr(page_kernel_lens), _is64(page_kernel_lens),
                                      ptr(kv_indptr), ptr(kv_start_idx), req_pool_indices.numel(),
                                      stream_ptr(req_to_token.device)), "b200_create_kv_indices")
+
+
+# ---- greedy sampling ------------------------------------------------------------------------------------------------------
+_ARGMAX_WS = {}
+
+
+def argmax(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """torch.argmax(logits, -1) for [rows, V] bf16/fp16 logits (lowest index on ties), rows split over CTAs."""
+    require_cuda(logits, out)
+    lib = _cabi.load()
+    assert logits.dim() == 2 and logits.stride(1) == 1
+    rows, V = logits.shape
+    if out is None:
+        out = torch.empty(rows, dtype=torch.int64, device=logits.device)
+    assert out.dtype == torch.int64 and out.is_contiguous() and out.numel() == rows
+    ws = _ARGMAX_WS.get(logits.device.index)
+    if ws is None or ws.numel() < rows * 16:
+        ws = torch.zeros(max(rows, 1024) * 16, dtype=torch.uint8, device=logits.device)
+        _ARGMAX_WS[logits.device.index] = ws
+    check(lib.b200_argmax(ptr(out), ptr(logits), rows, V, logits.stride(0), dtype_code(logits.dtype), ptr(ws), ws.numel(),
+                          stream_ptr(logits.device)), "b200_argmax")
+    return out

@@ -173,7 +173,9 @@ class B200AttnBackend(AttentionBackend):
         if layer.qk_head_dim != layer.v_head_dim:
             raise NotImplementedError("B200AttnBackend: qk_head_dim != v_head_dim is out of scope")
 
-    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, int8_out: bool = False):
+        """int8_out=True returns the output already per-token int8-quantised (kernels.Int8Activation) for a W8A8-int8
+        o_proj: the quant is fused into the split-KV merge kernel."""
         self._check_layer(layer)
         q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
         o = torch.empty_like(q)
@@ -181,16 +183,16 @@ class B200AttnBackend(AttentionBackend):
             self._save_kv(layer, forward_batch, k, v)
         md = self.forward_metadata
         pool = forward_batch.token_to_kv_pool
-        kernels.decode_attention_fwd(
+        act = kernels.decode_attention_fwd(
             q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
             pool.get_key_buffer(layer.layer_id), pool.get_value_buffer(layer.layer_id),
             o.view(-1, layer.tp_q_head_num, layer.v_head_dim),
             forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
             forward_batch.seq_lens, md.workspace, md.kv_chunk, md.max_splits,
-            layer.scaling, layer.logit_cap or 0.0)
-        return o
+            layer.scaling, layer.logit_cap or 0.0, int8_out=int8_out)
+        return act if int8_out else o
 
-    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True):
+    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, int8_out: bool = False):
         self._check_layer(layer)
         q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
         o = torch.empty_like(q)
@@ -208,6 +210,9 @@ class B200AttnBackend(AttentionBackend):
             forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
             md.qo_indptr, md.prefix_lens, md.max_extend_len,
             layer.scaling, layer.logit_cap or 0.0, causal)
+        if int8_out:  # prefill is tensor-bound; the quant stays its own (bandwidth-bound) kernel there
+            xq, xs = kernels.per_token_quant_int8(o)
+            return kernels.Int8Activation(xq, xs, o.dtype)
         return o
 
     def support_triton(self):

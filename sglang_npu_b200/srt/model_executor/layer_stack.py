@@ -87,6 +87,7 @@ class DecoderLayer(nn.Module):
 
         self.fused_int8 = (type(self.qkv_proj.quant_method).__name__ == "B200W8A8Int8LinearMethod"
                            and os.environ.get("B200_FUSE_STEPS", "1") != "0")
+        self.fuse_attn_quant = os.environ.get("B200_FUSE_ATTN_QUANT", "1") != "0"  # A/B switch
         self.input_layernorm = nn.Parameter(torch.ones(cfg.hidden_size, dtype=dtype), requires_grad=False)
         self.post_attention_layernorm = nn.Parameter(torch.ones(cfg.hidden_size, dtype=dtype), requires_grad=False)
 
@@ -125,7 +126,7 @@ class DecoderLayer(nn.Module):
         kernels.rope_neox_set_kv(positions, q, k, v, self.cfg.head_dim, cos_sin_cache,
                                  pool.get_key_buffer(self.attn.layer_id), pool.get_value_buffer(self.attn.layer_id),
                                  forward_batch.out_cache_loc)
-        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=False)
+        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=False, int8_out=self.fuse_attn_quant)
         hidden_states, _ = self.o_proj(attn_out)
         act = kernels.rmsnorm_quant_int8(hidden_states, self.post_attention_layernorm, eps, residual=residual)
         gate_up, _ = self.gate_up_proj(act)

@@ -15,6 +15,7 @@ import torch
 
 from ..layers.attention.b200_backend import B200AttnBackend
 from ..mem_cache.memory_pool import MHATokenToKVPool, ReqToTokenPool
+from ... import kernels
 from .forward_batch_info import ForwardBatch, ForwardMode
 from .layer_stack import LayerStack, StackConfig, load_synthetic_weights
 
@@ -105,7 +106,7 @@ class HotPathRunner:
             torch.sub(st["seq_lens"], 1, out=st["positions"])
             hidden = self.model(st["input_ids"], st["positions"], fb)
             logits = self.model.logits(hidden)
-            torch.argmax(logits, dim=-1, out=st["next_token_ids"])  # greedy sampling
+            kernels.argmax(logits, out=st["next_token_ids"])  # greedy sampling (sampler.py: torch.argmax(logits, -1))
 
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))

@@ -237,3 +237,32 @@ def test_decode_full_size_properties(cuda_device):
     # (b) idempotence: same launch twice is bit-identical (no atomics / order dependence)
     o3 = layer(q, None, None, fb, save_kv_cache=False).view(bs, hq, d)
     assert torch.equal(o2, o3)
+
+
+@pytest.mark.parametrize("hq,hkv,d", [(32, 8, 128), (14, 2, 64), (40, 8, 128)])
+@pytest.mark.parametrize("forced_chunk", [0, 64])
+def test_decode_int8_out_equals_unfused_quant(cuda_device, hq, hkv, d, forced_chunk):
+    """Stage 2 fused with per_token_quant_int8 (b200_decode_attn_int8): same bits as the two kernels back to back,
+    for requests merged from several chunks and for requests stage 1 finalised itself (one chunk)."""
+    dev = cuda_device
+    lens = [1, 2, 15, 16, 17, 255, 256, 257, 700, 1030]
+    page, dtype = 16, torch.bfloat16
+    pb = synth.make_paged_batch(lens, page, seed=4)
+    runner, backend = harness.build_runner(dev, pb.req_to_token, pb.num_slots, page, hq, hkv, d, dtype, ctx=max(lens))
+    if forced_chunk:
+        backend.forced_chunk = forced_chunk
+    k0, v0 = synth.randn_kv(pb.num_slots, page, hkv, d, dtype, seed=14)
+    runner.token_to_kv_pool.k_buffer[0].copy_(k0)
+    runner.token_to_kv_pool.v_buffer[0].copy_(v0)
+    bs = len(lens)
+    q = torch.randn((bs, hq * d), generator=torch.Generator().manual_seed(5)).to(dtype).to(dev)
+    out_loc = torch.stack([pb.req_to_token[pb.req_pool_indices[i], lens[i] - 1] for i in range(bs)]).long()
+    fb = harness.decode_batch(runner, backend, pb.req_pool_indices, pb.seq_lens, out_loc)
+    layer = harness.make_layer(hq, hkv, d)
+    o = layer(q, None, None, fb, save_kv_cache=False)
+    act = layer(q, None, None, fb, save_kv_cache=False, int8_out=True)
+    xq, xs = kernels.per_token_quant_int8(o)
+    torch.cuda.synchronize()
+    assert isinstance(act, kernels.Int8Activation)
+    assert torch.equal(act.x_q.cpu(), xq.cpu())
+    assert torch.equal(act.x_scale.cpu().view(torch.int32), xs.cpu().view(torch.int32))

@@ -172,3 +172,27 @@ def test_int8_linear_accepts_prequantised_activation(cuda_device):
     y_ref, _ = lin(kernels.silu_and_mul(x))
     y_fused, _ = lin(kernels.silu_and_mul_quant_int8(x))
     assert torch.equal(y_ref, y_fused)
+
+
+@pytest.mark.parametrize("rows,V", [(1, 128256), (64, 128256), (7, 151936), (300, 2048), (3, 1000), (64, 16032)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_argmax_matches_torch(cuda_device, rows, V, dtype):
+    g = torch.Generator().manual_seed(rows + V)
+    x = torch.randn((rows, V), generator=g).to(dtype)
+    x[0, V - 1] = 30.0  # maximum in the ragged tail
+    if rows > 1:
+        x[1, 5] = 31.0
+        x[1, V // 2] = 31.0  # tie: the lowest index wins
+    xd = x.to(cuda_device)
+    for _ in range(2):  # second call checks the self-cleaning scratch
+        out = kernels.argmax(xd)
+    torch.cuda.synchronize()
+    ref = torch.argmax(x.float(), dim=-1)
+    if rows > 1:
+        assert int(out[1]) == 5
+        ref[1] = 5
+    assert torch.equal(out.cpu(), ref)
+    # strided rows (a [:, :V] slice of a padded matrix)
+    pad = torch.full((rows, V + 8), 100.0, dtype=dtype, device=cuda_device)
+    pad[:, :V] = xd
+    assert torch.equal(kernels.argmax(pad[:, :V]).cpu(), ref)
