@@ -345,6 +345,9 @@ def main():
             "config": {"workload": f"{MODEL} W8A8-int8 decode step ({n_layers} layers + bf16 lm_head + greedy argmax), "
                                    f"global batch {bs}, ctx {ctx}, page_size {PAGE}, bf16 KV",
                        "global_batch": bs, "seq_len": ctx, "parallelism": f"tp{tp}", "cuda_graph": True,
+                       "tp_exchange": ("none (tp1)" if tp == 1 else
+                                       "fused reduce+rmsnorm+int8-quant over NVLink peer memory (csrc/tp_comm.cu)"
+                                       if getattr(runner, "tp_comm", None) is not None else "NCCL all-reduce"),
                        "l2_policy": "inputs larger than L2: 1.07 GB of KV + 0.22 GB of weights per layer vs 126 MB L2",
                        "tok_s_per_gpu": value / world},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},

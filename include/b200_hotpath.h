@@ -277,6 +277,34 @@ int b200_create_kv_indices(int32_t* kv_indices, const int32_t* req_to_token, int
                            int lens_is_int64, const int32_t* kv_indptr, const int32_t* kv_start_idx, int batch,
                            void* stream);
 
+/* ---- tensor-parallel exchange fused with the following norm + quant --------------------------
+ * Replaces, for the row-parallel linears (o_proj, down_proj): tensor_model_parallel_all_reduce
+ * (python/sglang/srt/layers/linear.py:1303-1304, distributed/communication_op.py:11-13; custom one-shot kernel
+ * sgl-kernel/csrc/allreduce/custom_all_reduce.cuh) + fused_add_rmsnorm + per_token_quant_int8 of the next linear
+ * (the reference's partial fusion: layers/flashinfer_comm_fusion.py).  Symmetric buffers are plain device
+ * allocations shared with cudaIpc: b200_comm_malloc (zero-filled) / b200_comm_ipc_handle on the owner,
+ * b200_comm_ipc_open on the peers.
+ *
+ * b200_tp_reduce_rmsnorm_quant_int8: `partial_ptrs[r]` = rank r's [M, H] partial GEMM output (as mapped in THIS
+ * process; r == tp_rank is the local one).  This rank reduces rows [tp_rank * ceil(M/tp), ...) over all ranks in
+ * rank order (fp32, one rounding), adds them to `residual` rows (local, optional, updated in place), applies
+ * RMSNorm(weight, eps) and writes, for those rows, into EVERY rank's buffers: int8 codes + scales
+ * (xq_ptrs / xscale_ptrs, optional) and/or the normalised activation (y_ptrs, optional).  It returns (stream-
+ * ordered) when every rank's rows have landed locally.  flag_ptrs[r]: rank r's 2 * 8 * max_blocks uint32 flag
+ * words; epoch: local max_blocks uint32; both zero-initialised once.  All ranks must issue the same sequence
+ * of calls.  Arithmetic = b200_rmsnorm_quant_int8 applied to the all-reduced tensor, bit for bit.
+ */
+int b200_comm_malloc(void** dev_ptr, size_t bytes);
+int b200_comm_free(void* dev_ptr);
+int b200_comm_ipc_handle(void* dev_ptr, unsigned char* handle64);
+int b200_comm_ipc_open(const unsigned char* handle64, void** peer_ptr);
+int b200_comm_ipc_close(void* peer_ptr);
+int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, void* const* xq_ptrs,
+                                      void* const* xscale_ptrs, void* const* y_ptrs, void* const* flag_ptrs,
+                                      void* epoch, void* residual, const void* weight, int64_t M, int64_t H,
+                                      float eps, int tp_size, int tp_rank, int max_blocks, int dtype,
+                                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif

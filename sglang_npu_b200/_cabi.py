@@ -80,6 +80,13 @@ _SIGNATURES = {
     "b200_get_last_loc": [_P, _P, c_int64, _P, c_int, _P, c_int, c_int, _P],
     "b200_compute_position": [_P, _P, _P, _P, c_int, c_int, _P],
     "b200_create_kv_indices": [_P, _P, c_int64, _P, c_int, _P, c_int, _P, _P, c_int, _P],
+    "b200_comm_malloc": [POINTER(c_void_p), c_size_t],
+    "b200_comm_free": [_P],
+    "b200_comm_ipc_handle": [_P, _P],
+    "b200_comm_ipc_open": [_P, POINTER(c_void_p)],
+    "b200_comm_ipc_close": [_P],
+    "b200_tp_reduce_rmsnorm_quant_int8": [_P, _P, _P, _P, _P, _P, _P, _P, c_int64, c_int64, c_float, c_int, c_int,
+                                          c_int, c_int, _P],
 }
 
 EXPORTED_SYMBOLS = sorted(list(_SIGNATURES) + ["b200_last_error"])

@@ -1,0 +1,289 @@
+// Tensor-parallel exchange step of the row-parallel linears, fused with what follows it.
+//
+// Reference path being replaced (python/sglang/srt/): RowParallelLinear.forward -> tensor_model_parallel_all_reduce
+// (layers/linear.py:1303-1304, distributed/communication_op.py:11-13: NCCL / custom one-shot all-reduce,
+// sgl-kernel/csrc/allreduce/custom_all_reduce.cuh) followed by fused_add_rmsnorm and the per-token int8 quant of the
+// next linear; the reference's own fusion of the first two is layers/flashinfer_comm_fusion.py (allreduce + rmsnorm).
+//
+// Here it is ONE kernel over NVLink peer memory, and a two-shot one: every rank's row-parallel GEMM writes its partial
+// [M, H] output into a symmetric buffer (cudaIpc-mapped into every peer).  Rank r owns the token slice
+// [r * ceil(M / tp), ...): its CTAs (one per token row)
+//   1. wait until every peer's partial is complete (flag barrier, sys-scope release/acquire),
+//   2. read that row from all tp partial buffers with 16-byte peer loads and add them in rank order in fp32
+//      (one rounding to T: for tp = 2 this is bit-identical to NCCL's bf16 sum),
+//   3. residual += sum (kept only on the owning rank: the residual stream is token-sharded between exchanges),
+//      RMSNorm, per-token int8 quantisation — the arithmetic of rmsnorm_quant_int8_kernel (fused_steps.cu), bit for bit,
+//   4. store the int8 row + its scale (and/or the normalised T row) straight into EVERY rank's activation buffer
+//      (the all-gather half, at 1 byte per element instead of 2), then signal the peers and wait for theirs.
+// Per exchange a rank moves (tp-1)/tp * M * H * (2 + 1) bytes over NVLink instead of 2 * (tp-1)/tp * M * H * 2 for a
+// ring all-reduce of bf16, launches one kernel instead of three, and normalises M / tp rows instead of M.
+#include <cstring>
+
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kMaxTp = 8;
+constexpr int kCommThreads = 256;
+
+struct TpArgs {
+  const void* partial[kMaxTp];  // [M, H] T, one per rank (own included), rank order
+  int8_t* xq[kMaxTp];           // [M, H] int8 destination on every rank (or null)
+  float* xscale[kMaxTp];        // [M]
+  void* y[kMaxTp];              // [M, H] T destination on every rank (or null)
+  uint32_t* flags[kMaxTp];      // per rank: [2][kMaxTp][max_blocks] epochs (start, end)
+  uint32_t* epoch;              // local: [max_blocks]
+  void* residual;               // local [M, H] T or null
+  const void* weight;           // [H] T
+  int64_t M, H;
+  int tp, rank, max_blocks;
+  float eps;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ int4 ld_volatile_v4(const void* p) {
+  int4 r;
+  asm volatile("ld.volatile.global.v4.s32 {%0,%1,%2,%3}, [%4];\n" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+// Block-level barrier across ranks: thread t < tp publishes `e` into peer t's slot [phase][rank][b] and waits for
+// peer t's value in the local slot [phase][t][b].  A peer that never arrives traps after ~2 s instead of hanging.
+__device__ __forceinline__ void rank_barrier(const TpArgs& a, int phase, int b, uint32_t e) {
+  if ((int)threadIdx.x < a.tp) {
+    const int t = threadIdx.x;
+    const size_t slot = ((size_t)phase * kMaxTp) * a.max_blocks + b;
+    st_release_sys(a.flags[t] + slot + (size_t)a.rank * a.max_blocks, e);
+    const uint32_t* mine = a.flags[a.rank] + slot + (size_t)t * a.max_blocks;
+    long long spins = 0;
+    while (ld_acquire_sys(mine) != e) {
+      if (++spins > (1ll << 28)) {
+        printf("b200 tp exchange: rank %d block %d phase %d never heard from rank %d (epoch %u)\n", a.rank, b, phase, t, e);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+template <typename T>
+__device__ __forceinline__ void unpack8(const int4& v, float (&f)[8]) {
+  const uint32_t* u = reinterpret_cast<const uint32_t*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 x = unpack2<T>(u[i]);
+    f[2 * i] = x.x;
+    f[2 * i + 1] = x.y;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kCommThreads) tp_reduce_norm_quant_kernel(const TpArgs a) {
+  extern __shared__ float row_f[];  // H floats
+  __shared__ float red[8];
+  __shared__ float red2[8];
+  pdl_trigger();
+  pdl_wait();  // the local GEMM has written this rank's partial
+  const int b = blockIdx.x;
+  const int64_t rows_per = (a.M + a.tp - 1) / a.tp;
+  const uint32_t e = a.epoch[b] + 1u;
+  rank_barrier(a, 0, b, e);  // every peer's GEMM output is complete and visible
+  const int64_t H = a.H;
+  // the grid is capped (every CTA of every rank must be resident for the barriers): a CTA walks rows b, b + grid, ...
+  for (int64_t ri = b; ri < rows_per; ri += gridDim.x) {
+    const int64_t row = (int64_t)a.rank * rows_per + ri;
+    if (row >= a.M) break;
+    __syncthreads();  // row_f / red are reused across rows
+    T* rr = a.residual ? reinterpret_cast<T*>(a.residual) + row * H : nullptr;
+    float ss = 0.f;
+    for (int64_t c = threadIdx.x * 8; c < H; c += kCommThreads * 8) {
+      float s[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s[i] = 0.f;
+      for (int r = 0; r < a.tp; ++r) {  // fixed rank order: deterministic, identical on every rank
+        float f[8];
+        unpack8<T>(ld_volatile_v4(reinterpret_cast<const T*>(a.partial[r]) + row * H + c), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s[i] += f[i];
+      }
+      float f[8];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {  // the all-reduce result as a T tensor (what the un-fused path hands to the norm)
+        const float2 x = unpack2<T>(pack2<T>(s[2 * i], s[2 * i + 1]));
+        f[2 * i] = x.x;
+        f[2 * i + 1] = x.y;
+      }
+      if (rr) {
+        float r8[8];
+        unpack8<T>(*reinterpret_cast<const int4*>(rr + c), r8);
+        int4 nv;
+        uint32_t* nu = reinterpret_cast<uint32_t*>(&nv);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          f[2 * i] += r8[2 * i];
+          f[2 * i + 1] += r8[2 * i + 1];
+          nu[i] = pack2<T>(f[2 * i], f[2 * i + 1]);
+        }
+        *reinterpret_cast<int4*>(rr + c) = nv;  // residual = T(x + residual), owner rank only
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        row_f[c + i] = f[i];
+        ss += f[i] * f[i];
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    float tot = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) tot += red[i];
+    const float rstd = rsqrtf(tot / (float)H + a.eps);
+    float amax = 0.f;
+    const T* w = reinterpret_cast<const T*>(a.weight);
+    for (int64_t c = threadIdx.x * 8; c < H; c += kCommThreads * 8) {
+      float wv[8];
+      unpack8<T>(*reinterpret_cast<const int4*>(w + c), wv);
+      int4 ov;
+      uint32_t* ou = reinterpret_cast<uint32_t*>(&ov);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        ou[i] = pack2<T>(row_f[c + 2 * i] * rstd * wv[2 * i], row_f[c + 2 * i + 1] * rstd * wv[2 * i + 1]);
+        const float2 y = unpack2<T>(ou[i]);
+        row_f[c + 2 * i] = y.x;
+        row_f[c + 2 * i + 1] = y.y;
+        amax = fmaxf(amax, fmaxf(fabsf(y.x), fabsf(y.y)));
+      }
+      if (a.y[0] != nullptr) {
+        for (int r = 0; r < a.tp; ++r) *reinterpret_cast<int4*>(reinterpret_cast<T*>(a.y[r]) + row * H + c) = ov;
+      }
+    }
+    if (a.xq[0] != nullptr) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+      if ((threadIdx.x & 31) == 0) red2[threadIdx.x >> 5] = amax;
+      __syncthreads();
+      amax = red2[0];
+#pragma unroll
+      for (int i = 1; i < 8; ++i) amax = fmaxf(amax, red2[i]);
+      amax = fmaxf(amax, 1e-10f);
+      const float inv = __fmul_rn(__frcp_rn(amax), 127.f);
+      if ((int)threadIdx.x < a.tp) a.xscale[threadIdx.x][row] = __fdiv_rn(amax, 127.f);
+      for (int64_t c = threadIdx.x * 8; c < H; c += kCommThreads * 8) {
+        uint32_t lo = 0, hi = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int x0 = __float2int_rn(__fmul_rn(row_f[c + i], inv));
+          const int x1 = __float2int_rn(__fmul_rn(row_f[c + 4 + i], inv));
+          lo |= (uint32_t)(x0 & 0xff) << (8 * i);
+          hi |= (uint32_t)(x1 & 0xff) << (8 * i);
+        }
+        const uint2 q = make_uint2(lo, hi);
+        for (int r = 0; r < a.tp; ++r) *reinterpret_cast<uint2*>(a.xq[r] + row * H + c) = q;
+      }
+    }
+  }
+  __threadfence_system();  // this CTA's rows are visible on every rank before the arrival below
+  __syncthreads();
+  rank_barrier(a, 1, b, e);  // every peer has delivered its rows of block b; the grid's exit covers all blocks
+  if (threadIdx.x == 0) a.epoch[b] = e;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+B200_API int b200_comm_malloc(void** dev_ptr, size_t bytes) {
+  B200_REQUIRE(dev_ptr != nullptr && bytes > 0, "comm_malloc: bad arguments");
+  B200_CUDA_OK(cudaMalloc(dev_ptr, bytes));
+  B200_CUDA_OK(cudaMemset(*dev_ptr, 0, bytes));
+  B200_CUDA_OK(cudaDeviceSynchronize());
+  return B200_OK;
+}
+
+B200_API int b200_comm_free(void* dev_ptr) {
+  if (dev_ptr) B200_CUDA_OK(cudaFree(dev_ptr));
+  return B200_OK;
+}
+
+B200_API int b200_comm_ipc_handle(void* dev_ptr, unsigned char* handle64) {
+  B200_REQUIRE(dev_ptr && handle64, "comm_ipc_handle: null pointer");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  cudaIpcMemHandle_t h;
+  B200_CUDA_OK(cudaIpcGetMemHandle(&h, dev_ptr));
+  memcpy(handle64, &h, 64);
+  return B200_OK;
+}
+
+B200_API int b200_comm_ipc_open(const unsigned char* handle64, void** peer_ptr) {
+  B200_REQUIRE(handle64 && peer_ptr, "comm_ipc_open: null pointer");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  B200_CUDA_OK(cudaIpcOpenMemHandle(peer_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return B200_OK;
+}
+
+B200_API int b200_comm_ipc_close(void* peer_ptr) {
+  if (peer_ptr) B200_CUDA_OK(cudaIpcCloseMemHandle(peer_ptr));
+  return B200_OK;
+}
+
+B200_API int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, void* const* xq_ptrs,
+                                               void* const* xscale_ptrs, void* const* y_ptrs, void* const* flag_ptrs,
+                                               void* epoch, void* residual, const void* weight, int64_t M, int64_t H,
+                                               float eps, int tp_size, int tp_rank, int max_blocks, int dtype,
+                                               void* stream) {
+  B200_REQUIRE(tp_size >= 2 && tp_size <= kMaxTp && tp_rank >= 0 && tp_rank < tp_size, "tp exchange: bad tp %d / rank %d",
+               tp_size, tp_rank);
+  B200_REQUIRE(M >= 0 && H > 0 && H % 8 == 0 && H * 4 <= 200 * 1024, "tp exchange: bad sizes M %lld H %lld", (long long)M,
+               (long long)H);
+  if (M == 0) return B200_OK;
+  B200_REQUIRE(partial_ptrs && flag_ptrs && epoch && weight, "tp exchange: null pointer");
+  B200_REQUIRE(xq_ptrs != nullptr || y_ptrs != nullptr, "tp exchange: no output requested");
+  B200_REQUIRE((xq_ptrs == nullptr) == (xscale_ptrs == nullptr), "tp exchange: xq and xscale go together");
+  const int64_t rows_per = ceil_div(M, tp_size);
+  B200_REQUIRE(max_blocks >= 1, "tp exchange: no flag slots");
+  int64_t grid = 2 * (int64_t)sm_count();  // all CTAs co-resident on every rank (16 KiB smem, 256 threads each)
+  if (grid > max_blocks) grid = max_blocks;
+  if (grid > rows_per) grid = rows_per;
+  TpArgs a = {};
+  for (int r = 0; r < tp_size; ++r) {
+    B200_REQUIRE(partial_ptrs[r] && flag_ptrs[r], "tp exchange: null peer pointer");
+    a.partial[r] = partial_ptrs[r];
+    a.flags[r] = reinterpret_cast<uint32_t*>(flag_ptrs[r]);
+    if (xq_ptrs) {
+      B200_REQUIRE(xq_ptrs[r] && xscale_ptrs[r], "tp exchange: null peer pointer");
+      a.xq[r] = reinterpret_cast<int8_t*>(xq_ptrs[r]);
+      a.xscale[r] = reinterpret_cast<float*>(xscale_ptrs[r]);
+    }
+    if (y_ptrs) {
+      B200_REQUIRE(y_ptrs[r], "tp exchange: null peer pointer");
+      a.y[r] = y_ptrs[r];
+    }
+  }
+  a.epoch = reinterpret_cast<uint32_t*>(epoch);
+  a.residual = residual;
+  a.weight = weight;
+  a.M = M; a.H = H; a.tp = tp_size; a.rank = tp_rank; a.max_blocks = max_blocks; a.eps = eps;
+  const int smem = (int)(H * sizeof(float));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == B200_BF16) {
+    auto kern = tp_reduce_norm_quant_kernel<__nv_bfloat16>;
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    return launch_k(kern, dim3((unsigned)grid), dim3(kCommThreads), smem, st, 1, true, a);
+  }
+  if (dtype == B200_F16) {
+    auto kern = tp_reduce_norm_quant_kernel<__half>;
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    return launch_k(kern, dim3((unsigned)grid), dim3(kCommThreads), smem, st, 1, true, a);
+  }
+  return fail(B200_ERR_UNSUPPORTED, "tp exchange: dtype %d not supported (bf16/f16)", dtype);
+}

@@ -223,7 +223,8 @@ _WS_MIN_BYTES = 1024 + 160 * 256 * 128 * 4
 
 def int8_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tensor,
                    scales_b: torch.Tensor, out_dtype: torch.dtype,
-                   bias: Optional[torch.Tensor] = None, return_acc: bool = False, cluster_splitk: bool = False):
+                   bias: Optional[torch.Tensor] = None, return_acc: bool = False, cluster_splitk: bool = False,
+                   out: Optional[torch.Tensor] = None):
     """sgl_kernel.int8_scaled_mm (sgl-kernel/python/sgl_kernel/gemm.py:20-29).
 
     mat_a [M,K] int8 row-major; mat_b [K,N] int8 COLUMN-major (weight.t()); scales fp32.
@@ -250,7 +251,10 @@ def int8_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Ten
     if bias is not None:
         assert bias.numel() == N and bias.dtype == out_dtype
         bias = bias.contiguous()
-    out = torch.empty((M, N), device=mat_a.device, dtype=out_dtype)
+    if out is None:
+        out = torch.empty((M, N), device=mat_a.device, dtype=out_dtype)
+    elif out.shape != (M, N) or out.dtype != out_dtype or not out.is_contiguous():
+        raise RuntimeError("int8_scaled_mm: `out` must be a contiguous [M, N] tensor of out_dtype")
     acc = torch.empty((M, N), device=mat_a.device, dtype=torch.int32) if return_acc else None
     ws = None if cluster_splitk else _scaled_mm_workspace(lib, mat_a.device, M, N, K)
     check(lib.b200_int8_scaled_mm(ptr(out), ptr(mat_a), ptr(mat_b), ptr(scales_a), ptr(scales_b),

@@ -14,6 +14,7 @@ import torch.distributed as dist
 _TP_GROUP = None
 _TP_RANK = 0
 _TP_SIZE = 1
+_TP_COMM = None  # B200TPComm (symmetric-memory exchange fused with norm + quant) or None -> NCCL all-reduce
 
 
 def init_tensor_parallel(group=None):
@@ -28,8 +29,31 @@ def init_tensor_parallel(group=None):
 
 
 def destroy_tensor_parallel():
-    global _TP_GROUP, _TP_RANK, _TP_SIZE
-    _TP_GROUP, _TP_RANK, _TP_SIZE = None, 0, 1
+    global _TP_GROUP, _TP_RANK, _TP_SIZE, _TP_COMM
+    if _TP_COMM is not None:
+        _TP_COMM.close()
+    _TP_GROUP, _TP_RANK, _TP_SIZE, _TP_COMM = None, 0, 1, None
+
+
+def init_tp_comm(max_tokens: int, hidden: int, dtype, device):
+    """Create the fused exchange (csrc/tp_comm.cu) for this TP group; B200_TP_FUSED_EXCHANGE=0 keeps NCCL."""
+    import os
+
+    global _TP_COMM
+    if _TP_SIZE == 1 or os.environ.get("B200_TP_FUSED_EXCHANGE", "1") == "0" or not torch.cuda.is_available():
+        return None
+    from .b200_comm import B200TPComm
+
+    if _TP_COMM is not None:
+        if _TP_COMM.max_tokens >= max_tokens and _TP_COMM.hidden == hidden and _TP_COMM.dtype == dtype:
+            return _TP_COMM
+        _TP_COMM.close()
+    _TP_COMM = B200TPComm(_TP_GROUP, max_tokens, hidden, dtype, device)
+    return _TP_COMM
+
+
+def get_tp_comm():
+    return _TP_COMM
 
 
 def get_tensor_model_parallel_rank() -> int:

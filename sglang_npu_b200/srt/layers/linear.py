@@ -181,14 +181,19 @@ class RowParallelLinear(LinearBase):
         else:
             param.data.copy_(loaded_weight)
 
-    def forward(self, input_, can_fuse_mlp_allreduce: bool = False):
+    def forward(self, input_, can_fuse_mlp_allreduce: bool = False, out=None):
+        """can_fuse_mlp_allreduce (reference linear.py:1285): skip the all-reduce, the caller fuses it into the next
+        norm.  `out`: destination of the partial sums (the symmetric buffer of B200TPComm)."""
         if self.input_is_parallel:
             input_parallel = input_
         else:
             shard = self.input_size_per_partition
             input_parallel = input_.narrow(-1, self.tp_rank * shard, shard).contiguous()
         bias_ = None if (self.tp_rank > 0 or self.skip_bias_add) else self.bias
-        output_parallel = self.quant_method.apply(self, input_parallel, bias=bias_)
+        if out is not None:
+            output_parallel = self.quant_method.apply(self, input_parallel, bias=bias_, out=out)
+        else:
+            output_parallel = self.quant_method.apply(self, input_parallel, bias=bias_)
         if self.reduce_results and self.tp_size > 1 and not can_fuse_mlp_allreduce:
             output = tensor_model_parallel_all_reduce(output_parallel)
         else:

@@ -85,12 +85,14 @@ class B200W8A8Int8LinearMethod(LinearMethodBase):
             layer._b200_w_transposed = True
         layer.weight_scale = Parameter(layer.weight_scale.data, requires_grad=False)
 
-    def apply(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None):
+    def apply(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None,
+              out: Optional[torch.Tensor] = None):
+        """`out` (optional, beyond the reference signature): write the [M, N] result there — the symmetric buffer of
+        the fused TP exchange for row-parallel layers."""
         if isinstance(x, kernels.Int8Activation):  # quantised by the producer kernel (fused rmsnorm / silu-mul)
-            out = kernels.int8_scaled_mm(x.x_q, layer.weight, x.x_scale, layer.weight_scale, out_dtype=x.out_dtype,
-                                         bias=bias)
-            return out
+            return kernels.int8_scaled_mm(x.x_q, layer.weight, x.x_scale, layer.weight_scale, out_dtype=x.out_dtype,
+                                          bias=bias, out=out)
         x_q, x_scale = kernels.per_token_quant_int8(x)
-        out = kernels.int8_scaled_mm(x_q.view(-1, x_q.shape[-1]), layer.weight, x_scale, layer.weight_scale,
-                                     out_dtype=x.dtype, bias=bias)
-        return out.view(x.shape[:-1] + (out.shape[-1],))
+        res = kernels.int8_scaled_mm(x_q.view(-1, x_q.shape[-1]), layer.weight, x_scale, layer.weight_scale,
+                                     out_dtype=x.dtype, bias=bias, out=out)
+        return res.view(x.shape[:-1] + (res.shape[-1],))

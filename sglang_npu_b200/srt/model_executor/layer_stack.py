@@ -19,7 +19,7 @@ from torch import nn
 
 from ... import kernels
 from ..distributed.parallel_state import (get_tensor_model_parallel_rank, get_tensor_model_parallel_world_size,
-                                          tensor_model_parallel_all_gather)
+                                          get_tp_comm, tensor_model_parallel_all_gather)
 from ..layers.linear import MergedColumnParallelLinear, QKVParallelLinear, RowParallelLinear
 from ..layers.radix_attention import RadixAttention
 
@@ -91,7 +91,9 @@ class DecoderLayer(nn.Module):
         self.input_layernorm = nn.Parameter(torch.ones(cfg.hidden_size, dtype=dtype), requires_grad=False)
         self.post_attention_layernorm = nn.Parameter(torch.ones(cfg.hidden_size, dtype=dtype), requires_grad=False)
 
-    def forward(self, positions, hidden_states, forward_batch, residual, cos_sin_cache):
+    def forward(self, positions, hidden_states, forward_batch, residual, cos_sin_cache, comm=None):
+        if self.fused_int8 and comm is not None:
+            return self.forward_fused_int8_tp(positions, hidden_states, forward_batch, residual, cos_sin_cache, comm)
         if self.fused_int8:
             return self.forward_fused_int8(positions, hidden_states, forward_batch, residual, cos_sin_cache)
         eps = self.cfg.rms_norm_eps
@@ -135,6 +137,32 @@ class DecoderLayer(nn.Module):
 
     forward_fused_int8 = _forward_fused_int8
 
+    def forward_fused_int8_tp(self, positions, hidden_states, forward_batch, residual, cos_sin_cache, comm):
+        """TP > 1 with the fused exchange: o_proj / down_proj write their partial sums into the
+        symmetric buffer and the NEXT norm is the exchange kernel (reduce over ranks + residual + RMSNorm + int8 quant
+        + all-gather of the int8 rows).  `hidden_states` arrives un-reduced except at the first layer (residual None);
+        it leaves un-reduced, to be consumed by the next layer's input norm or the stack's final norm."""
+        eps = self.cfg.rms_norm_eps
+        M = hidden_states.shape[0]
+        if residual is None:
+            residual = hidden_states
+            act = kernels.rmsnorm_quant_int8(hidden_states, self.input_layernorm, eps)
+        else:
+            act = comm.reduce_rmsnorm_quant_int8(M, self.input_layernorm, eps, residual)
+        qkv, _ = self.qkv_proj(act)
+        q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
+        pool = forward_batch.token_to_kv_pool
+        kernels.rope_neox_set_kv(positions, q, k, v, self.cfg.head_dim, cos_sin_cache,
+                                 pool.get_key_buffer(self.attn.layer_id), pool.get_value_buffer(self.attn.layer_id),
+                                 forward_batch.out_cache_loc)
+        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=False, int8_out=self.fuse_attn_quant)
+        self.o_proj(attn_out, can_fuse_mlp_allreduce=True, out=comm.partial(M))
+        act = comm.reduce_rmsnorm_quant_int8(M, self.post_attention_layernorm, eps, residual)
+        gate_up, _ = self.gate_up_proj(act)
+        hidden_states, _ = self.down_proj(kernels.silu_and_mul_quant_int8(gate_up), can_fuse_mlp_allreduce=True,
+                                          out=comm.partial(M))
+        return hidden_states, residual
+
 
 class LayerStack(nn.Module):
     """embed -> N decoder layers -> final norm -> lm_head (vocab-parallel) -> greedy argmax."""
@@ -161,8 +189,15 @@ class LayerStack(nn.Module):
     def forward(self, input_ids, positions, forward_batch):
         hidden_states = self.embed_tokens[input_ids]
         residual = None
+        comm = get_tp_comm() if (self.tp_size > 1 and self.layers and self.layers[0].fused_int8) else None
+        if comm is not None and hidden_states.shape[0] > comm.max_tokens:
+            comm = None  # larger than the symmetric buffers: NCCL all-reduce path
         for layer in self.layers:
-            hidden_states, residual = layer(positions, hidden_states, forward_batch, residual, self.cos_sin_cache)
+            hidden_states, residual = layer(positions, hidden_states, forward_batch, residual, self.cos_sin_cache, comm)
+        if comm is not None and len(self.layers) > 0:
+            # final norm = the last exchange: every rank receives the normalised rows of all tokens
+            return comm.reduce_rmsnorm_quant_int8(hidden_states.shape[0], self.norm, self.cfg.rms_norm_eps, residual,
+                                                  quant=False, normed=True)
         kernels.fused_add_rmsnorm(hidden_states, residual, self.norm, self.cfg.rms_norm_eps)
         return hidden_states
 

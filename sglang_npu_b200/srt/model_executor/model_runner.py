@@ -36,7 +36,7 @@ class HostDecodeBatch:
 class HotPathRunner:
     def __init__(self, cfg: StackConfig, quant_config, *, max_reqs: int, max_total_tokens: int, page_size: int,
                  context_len: Optional[int] = None, dtype=torch.bfloat16, device="cuda", num_layers: Optional[int] = None,
-                 tp_size: int = 1, seed: int = 1234, weight_gain: float = 1.0):
+                 tp_size: int = 1, seed: int = 1234, weight_gain: float = 1.0, tp_comm_tokens: int = 0):
         self.device = torch.device(device)
         self.model_config = cfg
         if context_len is not None:
@@ -55,6 +55,10 @@ class HotPathRunner:
             self.model = LayerStack(cfg, quant_config, dtype, n_layers)
         load_synthetic_weights(self.model, seed=seed, device=self.device, gain=weight_gain)
         self.attn_backend = B200AttnBackend(self)
+        if tp_size > 1:
+            from ..distributed.parallel_state import init_tp_comm
+
+            self.tp_comm = init_tp_comm(max(max_reqs, tp_comm_tokens), cfg.hidden_size, dtype, self.device)
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self._static = None
 

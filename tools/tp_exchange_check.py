@@ -1,0 +1,189 @@
+"""Multi-GPU check of the fused TP exchange (csrc/tp_comm.cu); run with one process per GPU:
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
+        tools/tp_exchange_check.py
+
+1. kernel parity: reduce + residual + RMSNorm + int8 quant vs NCCL all-reduce(bf16) -> b200_rmsnorm_quant_int8
+   (bit-exact at tp = 2, where NCCL's bf16 sum is a single rounding too; tolerance at tp > 2), over several token
+   counts, repeated launches (epoch / flag reuse) and a CUDA-graph replay;
+2. layer-stack parity: logits of the TP stack with the fused exchange vs the NCCL path;
+3. timing of one exchange against NCCL all-reduce + rmsnorm_quant.
+Prints one JSON line per check from rank 0; exits non-zero on any mismatch.
+"""
+import copy
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from sglang_npu_b200 import kernels, synth  # noqa: E402
+from sglang_npu_b200.srt.distributed import parallel_state as ps  # noqa: E402
+from sglang_npu_b200.srt.distributed.b200_comm import B200TPComm  # noqa: E402
+
+
+def say(rank, **kw):
+    if rank == 0:
+        print(json.dumps(kw), flush=True)
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank)))
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    ps.init_tensor_parallel()
+    H, eps, dt = 4096, 1e-5, torch.bfloat16
+    comm = B200TPComm(dist.group.WORLD, 512, H, dt, dev)
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+    gs = torch.Generator(device=dev).manual_seed(7)  # identical on every rank
+    w = (1 + 0.1 * torch.randn(H, generator=gs, device=dev)).to(dt)
+    ok = True
+
+    def reference(partial, residual):
+        ar = partial.clone()
+        dist.all_reduce(ar)
+        res = residual.clone() if residual is not None else None
+        act, y = kernels.rmsnorm_quant_int8(ar, w, eps, residual=res, return_normed=True)
+        return act, y, res
+
+    # ---- 1. kernel parity ---------------------------------------------------------------------------------------------
+    for it, M in enumerate([1, 7, 64, 128, 300, 64, 512]):
+        part = torch.randn((M, H), generator=g, device=dev).to(dt)
+        residual = torch.randn((M, H), generator=gs, device=dev).to(dt) if it % 3 != 2 else None
+        ref_act, ref_y, ref_res = reference(part, residual)
+        comm.partial(M).copy_(part)
+        res = residual.clone() if residual is not None else None
+        act, y = comm.reduce_rmsnorm_quant_int8(M, w, eps, res, quant=True, normed=True)
+        torch.cuda.synchronize()
+        rows = comm.rows_of(M)
+        if world == 2:
+            good = (torch.equal(act.x_q, ref_act.x_q) and torch.equal(act.x_scale.view(torch.int32), ref_act.x_scale.view(torch.int32))
+                    and torch.equal(y.view(torch.int16), ref_y.view(torch.int16)))
+            if residual is not None:
+                good = good and torch.equal(res[rows].view(torch.int16), ref_res[rows].view(torch.int16))
+        else:  # NCCL rounds to bf16 at every hop of its ring / tree: compare within bf16 resolution
+            good = (y.float() - ref_y.float()).abs().max().item() <= 0.06 and \
+                (act.x_q.int() - ref_act.x_q.int()).abs().max().item() <= 2
+        flag = torch.tensor([int(good)], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok = ok and bool(flag.item())
+        say(rank, check="exchange_parity", M=M, residual=residual is not None, tp=world, bit_exact=world == 2, ok=bool(flag.item()))
+
+    # CUDA-graph replay of three chained exchanges (what the decode graph does 65 times per step)
+    M = 64
+    part = torch.randn((M, H), generator=g, device=dev).to(dt)
+    res0 = torch.randn((M, H), generator=gs, device=dev).to(dt)
+    res_g = res0.clone()
+
+    def chain():
+        for _ in range(3):
+            comm.partial(M).copy_(part)
+            comm.reduce_rmsnorm_quant_int8(M, w, eps, res_g)
+
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(side):
+        chain()
+    torch.cuda.current_stream(dev).wait_stream(side)
+    torch.cuda.synchronize()
+    res_g.copy_(res0)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        chain()
+    for _ in range(3):
+        res_g.copy_(res0)
+        graph.replay()
+    torch.cuda.synchronize()
+    xq_graph = comm._xq(M).clone()
+    ref_res = res0.clone()
+    for _ in range(3):
+        ar = part.clone()
+        dist.all_reduce(ar)
+        ref_act = kernels.rmsnorm_quant_int8(ar, w, eps, residual=ref_res)
+    torch.cuda.synchronize()
+    good = torch.equal(xq_graph, ref_act.x_q) if world == 2 else (xq_graph.int() - ref_act.x_q.int()).abs().max().item() <= 3
+    flag = torch.tensor([int(good)], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    ok = ok and bool(flag.item())
+    say(rank, check="exchange_cuda_graph_replay", ok=bool(flag.item()))
+
+    # ---- 3. timing ------------------------------------------------------------------------------------------------------
+    for M in (64 * world, 512):
+        part = torch.randn((M, H), generator=g, device=dev).to(dt)
+        res = torch.randn((M, H), generator=gs, device=dev).to(dt)
+        comm.partial(M).copy_(part)
+
+        def fused():
+            comm.reduce_rmsnorm_quant_int8(M, w, eps, res)
+
+        def nccl():
+            dist.all_reduce(part)
+            kernels.rmsnorm_quant_int8(part, w, eps, residual=res)
+
+        out = {}
+        for name, fn in (("fused_us", fused), ("nccl_us", nccl)):
+            for _ in range(5):
+                fn()
+            dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(50):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1) / 50 * 1e3], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            out[name] = round(t.item(), 2)
+        say(rank, check="exchange_timing", M=M, H=H, tp=world, **out)
+
+    # ---- 2. layer-stack parity --------------------------------------------------------------------------------------------
+    from sglang_npu_b200.srt.layers.quantization.w8a8_int8 import B200W8A8Int8Config
+    from sglang_npu_b200.srt.model_executor.layer_stack import CONFIGS
+    from sglang_npu_b200.srt.model_executor.model_runner import HotPathRunner
+
+    cfg = copy.deepcopy(CONFIGS["llama-3.1-8b"])
+    cfg.vocab_size = 4096
+    bs, page = 16, 16
+    lens = [100 + 3 * i for i in range(bs)]
+    pb = synth.make_paged_batch(lens, page, seed=3)
+    logits = {}
+    for mode in ("0", "1"):
+        os.environ["B200_TP_FUSED_EXCHANGE"] = mode
+        if mode == "0" and ps.get_tp_comm() is not None:
+            ps.get_tp_comm().close()
+            ps._TP_COMM = None
+        runner = HotPathRunner(cfg, B200W8A8Int8Config(), max_reqs=pb.req_to_token.shape[0], max_total_tokens=pb.num_slots,
+                               page_size=page, context_len=pb.req_to_token.shape[1] - 4, device=dev, num_layers=3,
+                               tp_size=world, seed=1234)
+        runner.req_to_token_pool.req_to_token.copy_(pb.req_to_token)
+        gk = torch.Generator(device=dev).manual_seed(9)
+        for buf in runner.token_to_kv_pool.k_buffer + runner.token_to_kv_pool.v_buffer:
+            buf.normal_(generator=gk)
+        ids = torch.randint(0, cfg.vocab_size, (bs,), generator=torch.Generator().manual_seed(1)).to(dev)
+        loc = torch.stack([pb.req_to_token[pb.req_pool_indices[i], lens[i] - 1] for i in range(bs)]).long().to(dev)
+        out = runner.forward_decode(ids, pb.req_pool_indices.to(dev), pb.seq_lens.to(dev), loc, seq_lens_cpu=pb.seq_lens)
+        torch.cuda.synchronize()
+        logits[mode] = out.float().clone()
+        assert (runner.tp_comm is not None) == (mode == "1")
+        del runner
+    diff = (logits["0"] - logits["1"]).abs().max().item()
+    same_tokens = bool((logits["0"].argmax(-1) == logits["1"].argmax(-1)).all())
+    good = (diff == 0.0) if world == 2 else (diff < 0.1)
+    flag = torch.tensor([int(good)], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    ok = ok and bool(flag.item())
+    say(rank, check="stack_logits_fused_vs_nccl", tp=world, max_abs_diff=diff, greedy_tokens_identical=same_tokens,
+        ok=bool(flag.item()))
+
+    torch.cuda.synchronize()
+    dist.barrier()
+    sys.stdout.flush()
+    os._exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()
