@@ -24,7 +24,7 @@
 namespace b200 {
 
 constexpr int kMaxTp = 8;
-constexpr int kCommThreads = 256;
+constexpr int kCommThreads = 512;
 
 struct TpArgs {
   const void* partial[kMaxTp];  // [M, H] T, one per rank (own included), rank order
@@ -38,6 +38,8 @@ struct TpArgs {
   int64_t M, H;
   int tp, rank, max_blocks;
   float eps;
+  unsigned long long* trace;  // diagnostics (b200_debug_set_trace) or null
+  int trace_slots;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -48,22 +50,43 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ int4 ld_volatile_v4(const void* p) {
+// Peer (and local) partial rows are read exactly once per launch, after the start barrier.  ld.volatile is the
+// load that is guaranteed not to be served from this SM's L1 (peer lines may live there across launches — an
+// ld.global.cg version read stale rows); as a volatile asm it also stays after the barrier, while consecutive
+// loads still issue back to back: all ranks' rows are in flight together, one NVLink round trip per row.
+__device__ __forceinline__ int4 ld_peer_v4(const void* p) {
   int4 r;
-  asm volatile("ld.volatile.global.v4.s32 {%0,%1,%2,%3}, [%4];\n" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  asm volatile("ld.volatile.global.v4.s32 {%0,%1,%2,%3}, [%4];\n" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
   return r;
+}
+
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
 }
 
 // Block-level barrier across ranks: thread t < tp publishes `e` into peer t's slot [phase][rank][b] and waits for
 // peer t's value in the local slot [phase][t][b].  A peer that never arrives traps after ~2 s instead of hanging.
+//   phase 0 (start): relaxed flags.  What it orders is "the peer's previous kernel (its GEMM) has completed": those
+//     writes went to the PEER's own memory and were made visible by that kernel's completion; we read them at their
+//     home through NVLink with L1-bypassing loads, so no system-scope fence (several microseconds) is needed.
+//   phase 1 (end): release / acquire.  ONE releasing thread per peer: the CTA barrier before it orders every
+//     thread's peer stores before the release (cumulativity), so the other 500 threads do not fence at all.
 __device__ __forceinline__ void rank_barrier(const TpArgs& a, int phase, int b, uint32_t e) {
+  __syncthreads();
   if ((int)threadIdx.x < a.tp) {
     const int t = threadIdx.x;
     const size_t slot = ((size_t)phase * kMaxTp) * a.max_blocks + b;
-    st_release_sys(a.flags[t] + slot + (size_t)a.rank * a.max_blocks, e);
+    uint32_t* theirs = a.flags[t] + slot + (size_t)a.rank * a.max_blocks;
     const uint32_t* mine = a.flags[a.rank] + slot + (size_t)t * a.max_blocks;
+    if (phase == 0) st_relaxed_sys(theirs, e);
+    else st_release_sys(theirs, e);
     long long spins = 0;
-    while (ld_acquire_sys(mine) != e) {
+    while ((phase == 0 ? ld_relaxed_sys(mine) : ld_acquire_sys(mine)) != e) {
       if (++spins > (1ll << 28)) {
         printf("b200 tp exchange: rank %d block %d phase %d never heard from rank %d (epoch %u)\n", a.rank, b, phase, t, e);
         __trap();
@@ -87,15 +110,24 @@ __device__ __forceinline__ void unpack8(const int4& v, float (&f)[8]) {
 template <typename T>
 __global__ void __launch_bounds__(kCommThreads) tp_reduce_norm_quant_kernel(const TpArgs a) {
   extern __shared__ float row_f[];  // H floats
-  __shared__ float red[8];
-  __shared__ float red2[8];
+  __shared__ float red[kCommThreads / 32];
+  __shared__ float red2[kCommThreads / 32];
+  constexpr int kWarps = kCommThreads / 32;
+  const int b = blockIdx.x;
+  unsigned long long* const tr = (a.trace != nullptr && b < a.trace_slots) ? a.trace + (size_t)b * 16 : nullptr;
+  if (threadIdx.x == 0) {
+    trace_mark(tr, 0);
+    trace_mark(tr, 14);
+  }
   pdl_trigger();
   pdl_wait();  // the local GEMM has written this rank's partial
-  const int b = blockIdx.x;
+  if (threadIdx.x == 0) trace_mark(tr, 1);
   const int64_t rows_per = (a.M + a.tp - 1) / a.tp;
   const uint32_t e = a.epoch[b] + 1u;
   rank_barrier(a, 0, b, e);  // every peer's GEMM output is complete and visible
+  if (threadIdx.x == 0) trace_mark(tr, 2);
   const int64_t H = a.H;
+  const int tp = a.tp;
   // the grid is capped (every CTA of every rank must be resident for the barriers): a CTA walks rows b, b + grid, ...
   for (int64_t ri = b; ri < rows_per; ri += gridDim.x) {
     const int64_t row = (int64_t)a.rank * rows_per + ri;
@@ -104,14 +136,23 @@ __global__ void __launch_bounds__(kCommThreads) tp_reduce_norm_quant_kernel(cons
     T* rr = a.residual ? reinterpret_cast<T*>(a.residual) + row * H : nullptr;
     float ss = 0.f;
     for (int64_t c = threadIdx.x * 8; c < H; c += kCommThreads * 8) {
+      int4 pv[kMaxTp];
+#pragma unroll
+      for (int r = 0; r < kMaxTp; ++r)
+        if (r < tp) pv[r] = ld_peer_v4(reinterpret_cast<const T*>(a.partial[r]) + row * H + c);
+      int4 rv = make_int4(0, 0, 0, 0);
+      if (rr) rv = *reinterpret_cast<const int4*>(rr + c);
       float s[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) s[i] = 0.f;
-      for (int r = 0; r < a.tp; ++r) {  // fixed rank order: deterministic, identical on every rank
-        float f[8];
-        unpack8<T>(ld_volatile_v4(reinterpret_cast<const T*>(a.partial[r]) + row * H + c), f);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) s[i] += f[i];
+      for (int r = 0; r < kMaxTp; ++r) {  // fixed rank order: deterministic, identical on every rank
+        if (r < tp) {
+          float f[8];
+          unpack8<T>(pv[r], f);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) s[i] += f[i];
+        }
       }
       float f[8];
 #pragma unroll
@@ -122,7 +163,7 @@ __global__ void __launch_bounds__(kCommThreads) tp_reduce_norm_quant_kernel(cons
       }
       if (rr) {
         float r8[8];
-        unpack8<T>(*reinterpret_cast<const int4*>(rr + c), r8);
+        unpack8<T>(rv, r8);
         int4 nv;
         uint32_t* nu = reinterpret_cast<uint32_t*>(&nv);
 #pragma unroll
@@ -134,15 +175,23 @@ __global__ void __launch_bounds__(kCommThreads) tp_reduce_norm_quant_kernel(cons
         *reinterpret_cast<int4*>(rr + c) = nv;  // residual = T(x + residual), owner rank only
       }
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        row_f[c + i] = f[i];
-        ss += f[i] * f[i];
-      }
+      for (int i = 0; i < 8; ++i) row_f[c + i] = f[i];
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
     __syncthreads();
+    // Sum of squares in EXACTLY the order of rmsnorm_quant_int8_kernel (256 threads, thread j runs over the 8-column
+    // groups j, j + 256, ... sequentially, then a warp tree, then 8 warp sums in order): fp32 addition is not
+    // associative and the fused exchange must give the bits of the un-fused path.
+    if (threadIdx.x < 256) {
+      for (int64_t c = threadIdx.x * 8; c < H; c += 256 * 8) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ss += row_f[c + i] * row_f[c + i];
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+      if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && ri == b) trace_mark(tr, 3);
     float tot = 0.f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) tot += red[i];
@@ -163,7 +212,7 @@ __global__ void __launch_bounds__(kCommThreads) tp_reduce_norm_quant_kernel(cons
         amax = fmaxf(amax, fmaxf(fabsf(y.x), fabsf(y.y)));
       }
       if (a.y[0] != nullptr) {
-        for (int r = 0; r < a.tp; ++r) *reinterpret_cast<int4*>(reinterpret_cast<T*>(a.y[r]) + row * H + c) = ov;
+        for (int r = 0; r < tp; ++r) *reinterpret_cast<int4*>(reinterpret_cast<T*>(a.y[r]) + row * H + c) = ov;
       }
     }
     if (a.xq[0] != nullptr) {
@@ -173,10 +222,10 @@ __global__ void __launch_bounds__(kCommThreads) tp_reduce_norm_quant_kernel(cons
       __syncthreads();
       amax = red2[0];
 #pragma unroll
-      for (int i = 1; i < 8; ++i) amax = fmaxf(amax, red2[i]);
+      for (int i = 1; i < kWarps; ++i) amax = fmaxf(amax, red2[i]);
       amax = fmaxf(amax, 1e-10f);
       const float inv = __fmul_rn(__frcp_rn(amax), 127.f);
-      if ((int)threadIdx.x < a.tp) a.xscale[threadIdx.x][row] = __fdiv_rn(amax, 127.f);
+      if ((int)threadIdx.x < tp) a.xscale[threadIdx.x][row] = __fdiv_rn(amax, 127.f);
       for (int64_t c = threadIdx.x * 8; c < H; c += kCommThreads * 8) {
         uint32_t lo = 0, hi = 0;
 #pragma unroll
@@ -187,14 +236,17 @@ __global__ void __launch_bounds__(kCommThreads) tp_reduce_norm_quant_kernel(cons
           hi |= (uint32_t)(x1 & 0xff) << (8 * i);
         }
         const uint2 q = make_uint2(lo, hi);
-        for (int r = 0; r < a.tp; ++r) *reinterpret_cast<uint2*>(a.xq[r] + row * H + c) = q;
+        for (int r = 0; r < tp; ++r) *reinterpret_cast<uint2*>(a.xq[r] + row * H + c) = q;
       }
     }
   }
-  __threadfence_system();  // this CTA's rows are visible on every rank before the arrival below
-  __syncthreads();
+  if (threadIdx.x == 0) trace_mark(tr, 4);
   rank_barrier(a, 1, b, e);  // every peer has delivered its rows of block b; the grid's exit covers all blocks
-  if (threadIdx.x == 0) a.epoch[b] = e;
+  if (threadIdx.x == 0) {
+    a.epoch[b] = e;
+    trace_mark(tr, 6);
+    trace_mark(tr, 15);
+  }
 }
 
 }  // namespace b200
@@ -251,7 +303,7 @@ B200_API int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, 
   B200_REQUIRE((xq_ptrs == nullptr) == (xscale_ptrs == nullptr), "tp exchange: xq and xscale go together");
   const int64_t rows_per = ceil_div(M, tp_size);
   B200_REQUIRE(max_blocks >= 1, "tp exchange: no flag slots");
-  int64_t grid = 2 * (int64_t)sm_count();  // all CTAs co-resident on every rank (16 KiB smem, 256 threads each)
+  int64_t grid = sm_count();  // all CTAs co-resident on every rank (one 512-thread CTA per SM)
   if (grid > max_blocks) grid = max_blocks;
   if (grid > rows_per) grid = rows_per;
   TpArgs a = {};
@@ -272,6 +324,7 @@ B200_API int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, 
   a.epoch = reinterpret_cast<uint32_t*>(epoch);
   a.residual = residual;
   a.weight = weight;
+  a.trace = g_trace; a.trace_slots = (int)g_trace_slots;
   a.M = M; a.H = H; a.tp = tp_size; a.rank = tp_rank; a.max_blocks = max_blocks; a.eps = eps;
   const int smem = (int)(H * sizeof(float));
   cudaStream_t st = (cudaStream_t)stream;

@@ -67,6 +67,13 @@ def main():
         else:  # NCCL rounds to bf16 at every hop of its ring / tree: compare within bf16 resolution
             good = (y.float() - ref_y.float()).abs().max().item() <= 0.06 and \
                 (act.x_q.int() - ref_act.x_q.int()).abs().max().item() <= 2
+        if not good:
+            print(json.dumps(dict(rank=rank, M=M, xq_bad_rows=int((act.x_q != ref_act.x_q).any(1).sum()),
+                                  scale_bad=int((act.x_scale.view(torch.int32) != ref_act.x_scale.view(torch.int32)).sum()),
+                                  y_bad_rows=int((y.view(torch.int16) != ref_y.view(torch.int16)).any(1).sum()),
+                                  y_max_diff=float((y.float() - ref_y.float()).abs().max()),
+                                  res_bad_rows=(int((res[rows].view(torch.int16) != ref_res[rows].view(torch.int16)).any(1).sum())
+                                                if residual is not None else -1))), flush=True)
         flag = torch.tensor([int(good)], device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         ok = ok and bool(flag.item())
@@ -109,6 +116,41 @@ def main():
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     ok = ok and bool(flag.item())
     say(rank, check="exchange_cuda_graph_replay", ok=bool(flag.item()))
+
+    # per-CTA phase timeline of one exchange inside a CUDA graph of 8 (GEMM-stand-in copy + exchange) pairs
+    M = 64 * world
+    part = torch.randn((M, H), generator=g, device=dev).to(dt)
+    res_t = torch.randn((M, H), generator=gs, device=dev).to(dt)
+    tbuf = torch.zeros((256, 16), dtype=torch.int64, device=dev)
+
+    def chain8():
+        for _ in range(8):
+            comm.partial(M).copy_(part)
+            comm.reduce_rmsnorm_quant_int8(M, w, eps, res_t)
+
+    kernels.set_trace(tbuf)
+    with torch.cuda.stream(side):
+        chain8()
+    torch.cuda.synchronize()
+    g8 = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g8):
+        chain8()
+    kernels.set_trace(None)
+    for _ in range(3):
+        g8.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        g8.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    t = tbuf.cpu()
+    t = t[t[:, 0] != 0]
+    names = {1: "pdl_wait", 2: "start_barrier", 3: "row_reduced", 4: "stores_issued", 6: "end_barrier"}
+    row = {n: [int(((t[:, i] - t[:, 14]).float() / 1.965).median()), int(((t[:, i] - t[:, 14]).float() / 1.965).max())]
+           for i, n in names.items()}
+    say(rank, check="exchange_trace_ns_med_max", M=M, ctas=int(t.shape[0]), graph_us_per_pair=round(e0.elapsed_time(e1) / 80 * 1e3, 2), **row)
 
     # ---- 3. timing ------------------------------------------------------------------------------------------------------
     for M in (64 * world, 512):
