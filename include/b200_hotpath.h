@@ -69,6 +69,17 @@ int b200_set_kv_buffer(void* k_cache, void* v_cache, const void* k, const void* 
                        int64_t k_cache_token_stride, int64_t v_cache_token_stride,
                        int elem_bytes, void* stream);
 
+/* FP8 (e4m3) KV cache, --kv-cache-dtype fp8_e4m3 (memory_pool.py:114-118: stored as uint8): set_kv_buffer's cast branch
+ * (memory_pool.py:385-391) fused with the scatter.  k/v are bf16 or f16 (src_dtype); when k_scale / v_scale > 0 the
+ * row is first divided by it in fp32 and rounded back to the source dtype (Tensor.div_ by a Python float on the oracle's
+ * CPU path), then cast like c10::Float8_e4m3fn(float): round-to-nearest-even, |x| > 464 or NaN -> NaN code (not
+ * saturating).  Bit-exact.  The caller's k/v are NOT modified (the reference divides them in place).  Strides in
+ * elements; cache rows are [num_kv_heads, head_dim] bytes.  Row elements must be a multiple of 16. */
+int b200_set_kv_buffer_fp8(void* k_cache, void* v_cache, const void* k, const void* v, const void* loc,
+                           int loc_is_int64, int64_t num_tokens, int64_t k_row_elems, int64_t v_row_elems,
+                           int64_t k_token_stride, int64_t v_token_stride, int64_t k_cache_token_stride,
+                           int64_t v_cache_token_stride, float k_scale, float v_scale, int src_dtype, void* stream);
+
 /* ---- decode attention -----------------------------------------------------------------
  * Replaces decode_attention_fwd (python/sglang/srt/layers/attention/triton_ops/
  * decode_attention.py:677-728; stage1 :241-401, stage2 :492-552) and the oracle's
@@ -99,6 +110,20 @@ int b200_decode_attn_int8(void* o, int8_t* oq, float* oq_scale, const void* q, c
                           int64_t o_token_stride, int64_t kv_token_stride, float sm_scale, float logit_cap,
                           int kv_chunk, int max_splits, void* workspace, size_t workspace_bytes, int dtype,
                           void* stream);
+
+/* Decode attention over an FP8 (e4m3) KV cache.  K and V are taken at their exact e4m3 values, up-cast
+ * before the dot like the reference's Triton kernel does (decode_attention.py:336 `k.to(q.dtype)`); k_scale / v_scale
+ * (1.0 = the reference Triton path, which ignores them on the read side) multiply the logits and the output, undoing
+ * set_kv_buffer's division.  q / o are `dtype` (bf16 / f16); kv_token_stride in bytes (= elements).  oq / oq_scale
+ * may be NULL (plain output) or request the fused o_proj int8 quantisation of b200_decode_attn_int8.  Halves the
+ * algorithmic bytes of the step: sum_b len_b * 2 * Hkv * D * 1. */
+int b200_decode_attn_fp8kv(void* o, int8_t* oq, float* oq_scale, const void* q, const void* k_cache,
+                           const void* v_cache, const int32_t* req_to_token, int64_t req_to_token_stride,
+                           const void* req_pool_indices, const void* seq_lens, int index_is_int64, int batch,
+                           int num_q_heads, int num_kv_heads, int head_dim, int64_t q_token_stride,
+                           int64_t o_token_stride, int64_t kv_token_stride, float sm_scale, float logit_cap,
+                           float k_scale, float v_scale, int kv_chunk, int max_splits, void* workspace,
+                           size_t workspace_bytes, int dtype, void* stream);
 
 /* ---- extend (prefill) attention ------------------------------------------------------
  * Replaces extend_attention_fwd (triton_ops/extend_attention.py:302-440) and the

@@ -26,6 +26,36 @@ def set_kv_buffer(k_cache: torch.Tensor, v_cache: torch.Tensor, loc: torch.Tenso
     v_cache[loc] = cache_v
 
 
+def set_kv_buffer_fp8(k_cache_u8: torch.Tensor, v_cache_u8: torch.Tensor, loc: torch.Tensor,
+                      cache_k: torch.Tensor, cache_v: torch.Tensor, k_scale: Optional[float] = None,
+                      v_scale: Optional[float] = None) -> None:
+    """The cast branch of MHATokenToKVPool.set_kv_buffer for an fp8_e4m3 pool (memory_pool.py:385-395): optional
+    in-place division by the scale (done on a copy here), `.to(float8_e4m3fn)`, stored through the uint8 view
+    (memory_pool.py:114-118)."""
+    ck, cv = cache_k.clone(), cache_v.clone()
+    if k_scale is not None:
+        ck.div_(k_scale)
+    if v_scale is not None:
+        cv.div_(v_scale)
+    k_cache_u8[loc] = ck.to(torch.float8_e4m3fn).view(torch.uint8)
+    v_cache_u8[loc] = cv.to(torch.float8_e4m3fn).view(torch.uint8)
+
+
+def decode_attention_fp8kv(q: torch.Tensor, k_cache_u8: torch.Tensor, v_cache_u8: torch.Tensor,
+                           req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
+                           scaling: float, k_scale: Optional[float] = None, v_scale: Optional[float] = None,
+                           compute_dtype: Optional[torch.dtype] = torch.float32) -> torch.Tensor:
+    """Decode over an fp8_e4m3 cache.  torch_native has no fp8 path (SDPA rejects mixed dtypes), so this restates the
+    reference's Triton kernel: K is up-cast to the q dtype before the dot (triton_ops/decode_attention.py:336,
+    exact for e4m3 -> bf16/f16), V likewise here (the Triton kernel instead rounds P to e4m3, :373 — a precision
+    loss this build does not copy).  k_scale / v_scale undo set_kv_buffer's division (FlashInfer-style read side);
+    None = the Triton backend's behaviour."""
+    k = k_cache_u8.view(torch.float8_e4m3fn).to(torch.float32) * (1.0 if k_scale is None else float(k_scale))
+    v = v_cache_u8.view(torch.float8_e4m3fn).to(torch.float32) * (1.0 if v_scale is None else float(v_scale))
+    return decode_attention(q, k, v, req_to_token, req_pool_indices, seq_lens, scaling,
+                            compute_dtype=compute_dtype).to(q.dtype)
+
+
 def _sdpa(q, k, v, scaling, causal, enable_gqa):
     # q [H, Lq, D], k/v [Hkv, Lk, D] — torch_native_backend.py:97-107 / :164-174
     return F.scaled_dot_product_attention(q.unsqueeze(0), k.unsqueeze(0), v.unsqueeze(0),

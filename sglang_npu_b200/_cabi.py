@@ -41,6 +41,8 @@ _SIGNATURES = {
     "b200_debug_set_trace": [_P, c_size_t],
     "b200_set_kv_buffer": [_P, _P, _P, _P, _P, c_int, c_int64, c_int64, c_int64, c_int64, c_int64,
                            c_int64, c_int64, c_int, _P],
+    "b200_set_kv_buffer_fp8": [_P, _P, _P, _P, _P, c_int, c_int64, c_int64, c_int64, c_int64, c_int64,
+                               c_int64, c_int64, c_float, c_float, c_int, _P],
     "b200_decode_attn_workspace_bytes": [c_int, c_int, c_int, c_int, POINTER(c_size_t)],
     "b200_decode_attn": [_P, _P, _P, _P, _P, c_int64, _P, _P, c_int, c_int, c_int, c_int, c_int,
                          c_int64, c_int64, c_int64, c_float, c_float, c_int, c_int, _P, c_size_t,
@@ -48,6 +50,9 @@ _SIGNATURES = {
     "b200_decode_attn_int8": [_P, _P, _P, _P, _P, _P, _P, c_int64, _P, _P, c_int, c_int, c_int, c_int, c_int,
                               c_int64, c_int64, c_int64, c_float, c_float, c_int, c_int, _P, c_size_t,
                               c_int, _P],
+    "b200_decode_attn_fp8kv": [_P, _P, _P, _P, _P, _P, _P, c_int64, _P, _P, c_int, c_int, c_int, c_int, c_int,
+                               c_int64, c_int64, c_int64, c_float, c_float, c_float, c_float, c_int, c_int, _P,
+                               c_size_t, c_int, _P],
     "b200_extend_attn": [_P, _P, _P, _P, _P, _P, _P, c_int64, _P, c_int, _P, _P, c_int, c_int,
                          c_int, c_int, c_int, c_int64, c_int64, c_int64, c_int64, c_int64, c_float,
                          c_float, c_int, c_int, _P],

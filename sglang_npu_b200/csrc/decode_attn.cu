@@ -21,6 +21,7 @@
 //    CTA writes the final output, else fp32 partial (o, lse) go to the workspace and
 //    decode_merge_kernel combines the chunks (log-sum-exp merge).
 #include "common.cuh"
+#include <type_traits>
 
 namespace b200 {
 
@@ -44,6 +45,7 @@ struct DecodeArgs {
   float scale_log2;   // sm_scale * log2(e)
   float sm_scale;
   float logit_cap;
+  float out_scale;    // fp8 KV only: v_scale, applied with the final 1/l
   int kv_chunk, max_splits;
   float* part_o;    // [batch, Hq, max_splits, D]
   float* part_lse;  // [batch, Hq, max_splits]   (log2 domain)
@@ -60,6 +62,61 @@ struct DecodeSmem {
   static constexpr int merge_bytes() { return kDecWarps * 16 * kOPad * 4 + 2 * kDecWarps * 16 * 4; }
   static constexpr int pipe_bytes(int stages) { return kDecWarps * stages * kStageBytes; }
 };
+
+// Tail of stage 1: the 4 warps' (m, l, O) sit in shared memory ([warps][16][kOPad] fp32 rows + m + l); merge them and
+// write either the final output row (one chunk per request) or the fp32 partial (o, lse) of this chunk.
+template <typename T, int D>
+__device__ __forceinline__ void combine_warps_and_store(const DecodeArgs& a, const float* sm_o, const float* sm_m,
+                                                        const float* sm_l, int n_heads, int head0, int b, int split,
+                                                        int num_splits, float out_scale) {
+  using S = DecodeSmem<D>;
+  // thread -> (row = head within block, 8 threads per row, D/8 consecutive dims each)
+  {
+    const int row = threadIdx.x >> 3;
+    const int seg = threadIdx.x & 7;
+    if (row < n_heads) {
+      float mw[kDecWarps], wgt[kDecWarps];
+      float M = -INFINITY;
+#pragma unroll
+      for (int w = 0; w < kDecWarps; ++w) {
+        mw[w] = sm_m[w * 16 + row];
+        M = fmaxf(M, mw[w]);
+      }
+      float L = 0.f;
+#pragma unroll
+      for (int w = 0; w < kDecWarps; ++w) {
+        wgt[w] = (mw[w] == -INFINITY) ? 0.f : fast_exp2(mw[w] - M);
+        L += sm_l[w * 16 + row] * wgt[w];
+      }
+      const float inv_l = out_scale / L;
+      const int head = head0 + row;
+      constexpr int kPer = D / 8;
+      float acc[kPer];
+#pragma unroll
+      for (int d = 0; d < kPer; ++d) acc[d] = 0.f;
+#pragma unroll
+      for (int w = 0; w < kDecWarps; ++w) {
+        const float* src = sm_o + (w * 16 + row) * S::kOPad + seg * kPer;
+#pragma unroll
+        for (int d = 0; d < kPer; ++d) acc[d] += src[d] * wgt[w];
+      }
+      if (num_splits == 1) {
+        T* dst = reinterpret_cast<T*>(a.o) + (int64_t)b * a.o_token_stride + (int64_t)head * D + seg * kPer;
+#pragma unroll
+        for (int d = 0; d < kPer; d += 2)
+          *reinterpret_cast<uint32_t*>(dst + d) = pack2<T>(acc[d] * inv_l, acc[d + 1] * inv_l);
+      } else {
+        const int64_t pidx = ((int64_t)b * a.num_q_heads + head) * a.max_splits + split;
+        float* dst = a.part_o + pidx * D + seg * kPer;
+#pragma unroll
+        for (int d = 0; d < kPer; d += 4)
+          *reinterpret_cast<float4*>(dst + d) =
+              make_float4(acc[d] * inv_l, acc[d + 1] * inv_l, acc[d + 2] * inv_l, acc[d + 3] * inv_l);
+        if (seg == 0) a.part_lse[pidx] = M + log2f(L);
+      }
+    }
+  }
+}
 
 // Issue the cp.async copies of one 16-token block (K and V) owned by this warp.
 template <typename T, int D>
@@ -301,52 +358,317 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_attn_kernel(const Decod
   }
   __syncthreads();
 
-  // thread -> (row = head within block, 8 threads per row, D/8 consecutive dims each)
+  combine_warps_and_store<T, D>(a, sm_o, sm_m, sm_l, n_heads, head0, b, split, num_splits, 1.f);
+}
+
+// ---- FP8 (e4m3) KV cache ---------------------------------------------------------------------------------------
+// --kv-cache-dtype fp8_e4m3 (reference memory_pool.py:114-118 stores it as uint8): the step's KV bytes
+// halve.  Semantics follow the reference's Triton decode kernel, which up-casts K to the q dtype before the dot
+// (decode_attention.py:336): K and V are taken at their exact e4m3 values; k_scale / v_scale (the factors
+// set_kv_buffer divided by, memory_pool.py:385-391) are folded into the softmax scale and the final 1/l.
+//
+// Same CTA/warp decomposition as decode_attn_kernel.  Rows are D bytes, so there is no 16-bit ldmatrix path; instead
+// the mma fragments are read straight from shared memory with 16-byte loads and converted in registers
+// (cvt.rn.f16x2.e4m3x2, exact), using the freedom to permute the reduction axis of an MMA:
+//  * S = Q K^T: thread (g, t) reads bytes [t*D/4, (t+1)*D/4) of token row g; k-step ks uses the 4 bytes at
+//    t*D/4 + 4*ks as k-slots {2t, 2t+1, 2t+8, 2t+9}.  The Q fragments are loaded with the same dim permutation.
+//  * O += P V: thread (g, t) reads D/8 consecutive bytes at g*D/8 of token rows {2t, 2t+1, 2t+8, 2t+9}; byte nt pairs
+//    up (prmt) into the B fragment of n-tile nt, i.e. accumulator column j of n-tile nt is dim j*D/8 + nt.  The
+//    permutation is undone when the accumulators are written to shared memory for the warp merge.
+// Both MMAs run in f16 (e4m3 and P are exact / finer in f16 than in bf16; a bf16 q is converted with a clamp to the
+// f16 range, exact for |q| in [2^-14, 65504]).
+template <int D>
+struct DecodeSmem8 {
+  static constexpr int kChunks = D / 16;                      // 16-byte chunks per row
+  static constexpr int kBlkBytes = kBlkTok * D;               // one K (or V) block of a warp
+  static constexpr int kStageBytes = 2 * kBlkBytes;
+  static constexpr int pipe_bytes(int stages) { return kDecWarps * stages * kStageBytes; }
+  // physical 16-byte chunk of logical chunk c in row r (bank-conflict-free for both access patterns at D = 128)
+  static __device__ __forceinline__ int swz(int c, int r) { return c ^ ((r / (8 / kChunks)) & (kChunks - 1)); }
+};
+
+template <int D>
+__device__ __forceinline__ void issue_block8(const uint8_t* __restrict__ k_cache, const uint8_t* __restrict__ v_cache,
+                                             int64_t kv_token_stride, int kv_head_off,
+                                             const int32_t* __restrict__ s_slots, int tok0, int n_tok,
+                                             uint32_t smem_k, uint32_t smem_v, int lane) {
+  using S8 = DecodeSmem8<D>;
+  constexpr int kChunks = S8::kChunks;
+  constexpr int kRowsPerIter = 32 / kChunks;
+  const int c = lane % kChunks;
+  const int r0 = lane / kChunks;
+#pragma unroll
+  for (int it = 0; it < kBlkTok / kRowsPerIter; ++it) {
+    const int r = r0 + it * kRowsPerIter;
+    const int tok = tok0 + r;
+    const bool valid = tok < n_tok;
+    const int slot = valid ? s_slots[tok] : 0;
+    const int64_t off = (int64_t)slot * kv_token_stride + kv_head_off + c * 16;
+    const uint32_t so = (uint32_t)(r * D + (S8::swz(c, r) << 4));
+    cp_async16_pred(smem_k + so, k_cache + off, valid);
+    cp_async16_pred(smem_v + so, v_cache + off, valid);
+  }
+}
+
+// two e4m3 bytes (low half of `pair` after the shift) -> f16x2, low byte in the low half
+__device__ __forceinline__ uint32_t e4m3x2_to_f16x2(uint32_t word, int hi) {
+  uint32_t d;
+  const uint16_t h = (uint16_t)(hi ? (word >> 16) : (word & 0xffffu));
+  asm("cvt.rn.f16x2.e4m3x2 %0, %1;\n" : "=r"(d) : "h"(h));
+  return d;
+}
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;\n" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+  return d;
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];\n" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];\n" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.b32 {%0,%1}, [%2];\n" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+  return v;
+}
+// 4 consecutive q values (dims d..d+3 of one head) -> two f16x2 registers
+template <typename T>
+__device__ __forceinline__ void load_q4_f16(const T* p, bool valid, uint32_t& lo, uint32_t& hi) {
+  if (!valid) { lo = hi = 0u; return; }
+  const uint2 raw = *reinterpret_cast<const uint2*>(p);
+  if constexpr (std::is_same<T, __half>::value) {
+    lo = raw.x; hi = raw.y;
+  } else {
+    const float2 a = unpack2<T>(raw.x), c = unpack2<T>(raw.y);
+    lo = pack2<__half>(fminf(fmaxf(a.x, -65504.f), 65504.f), fminf(fmaxf(a.y, -65504.f), 65504.f));
+    hi = pack2<__half>(fminf(fmaxf(c.x, -65504.f), 65504.f), fminf(fmaxf(c.y, -65504.f), 65504.f));
+  }
+}
+
+template <typename T, int D, int STAGES, bool UPPER>
+__global__ void __launch_bounds__(kDecThreads, 2) decode_attn_fp8kv_kernel(const DecodeArgs a) {
+  using S = DecodeSmem<D>;
+  using S8 = DecodeSmem8<D>;
+  using H = __half;
+  constexpr int NT = D / 8;       // n-tiles of O; also the bytes a thread reads per V row
+  constexpr int KS = D / 16;      // k-steps of S = Q K^T; also the 4-byte words a thread reads per K row
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+
+  const int split = blockIdx.x;
+  const int kvh = blockIdx.y / a.head_blocks;
+  const int hb = blockIdx.y - kvh * a.head_blocks;
+  const int b = blockIdx.z;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int g = lane >> 2;
+  const int t = lane & 3;
+
+  pdl_trigger();
+  pdl_wait();
+  const int seq_len = (int)load_index(a.seq_lens, b, a.index_is_int64);
+  const int start = split * a.kv_chunk;
+  if (start >= seq_len) return;
+  const int n_tok = min(seq_len - start, a.kv_chunk);
+  const int num_splits = (seq_len + a.kv_chunk - 1) / a.kv_chunk;
+
+  uint8_t* pipe = smem_raw;
+  int32_t* s_slots = reinterpret_cast<int32_t*>(smem_raw + S8::pipe_bytes(STAGES));
   {
-    const int row = threadIdx.x >> 3;
-    const int seg = threadIdx.x & 7;
-    if (row < n_heads) {
-      float mw[kDecWarps], wgt[kDecWarps];
-      float M = -INFINITY;
+    const int64_t req = load_index(a.req_pool_indices, b, a.index_is_int64);
+    const int32_t* row = a.req_to_token + req * a.req_to_token_stride + start;
+    for (int i = threadIdx.x; i < n_tok; i += kDecThreads) s_slots[i] = __ldg(row + i);
+  }
+  __syncthreads();
+
+  const uint8_t* k_cache = reinterpret_cast<const uint8_t*>(a.k_cache);
+  const uint8_t* v_cache = reinterpret_cast<const uint8_t*>(a.v_cache);
+  const int kv_head_off = kvh * D;
+  const uint32_t warp_pipe = smem_u32(pipe) + warp * STAGES * S8::kStageBytes;
+  const int n_blocks = (n_tok + kBlkTok - 1) / kBlkTok;
+  const int my_blocks = (n_blocks - warp + kDecWarps - 1) / kDecWarps;
+
 #pragma unroll
-      for (int w = 0; w < kDecWarps; ++w) {
-        mw[w] = sm_m[w * 16 + row];
-        M = fmaxf(M, mw[w]);
-      }
-      float L = 0.f;
+  for (int s = 0; s < STAGES - 1; ++s) {
+    if (s < my_blocks) {
+      const int tok0 = (warp + s * kDecWarps) * kBlkTok;
+      issue_block8<D>(k_cache, v_cache, a.kv_token_stride, kv_head_off, s_slots, tok0, n_tok,
+                      warp_pipe + s * S8::kStageBytes, warp_pipe + s * S8::kStageBytes + S8::kBlkBytes, lane);
+    }
+    cp_async_commit();
+  }
+
+  // Q fragments in f16 with the k-axis permutation of the header comment: k-step ks <-> dims t*D/4 + 4*ks + {0..3}
+  const int head0 = kvh * a.group + hb * 16;
+  const int n_heads = min(16, a.group - hb * 16);
+  uint32_t qf[KS][4];
+  {
+    const T* qb = reinterpret_cast<const T*>(a.q) + (int64_t)b * a.q_token_stride + (int64_t)head0 * D;
+    const bool v0 = g < n_heads;
+    const bool v1 = UPPER && (g + 8 < n_heads);
 #pragma unroll
-      for (int w = 0; w < kDecWarps; ++w) {
-        wgt[w] = (mw[w] == -INFINITY) ? 0.f : fast_exp2(mw[w] - M);
-        L += sm_l[w * 16 + row] * wgt[w];
-      }
-      const float inv_l = 1.f / L;
-      const int head = head0 + row;
-      constexpr int kPer = D / 8;
-      float acc[kPer];
-#pragma unroll
-      for (int d = 0; d < kPer; ++d) acc[d] = 0.f;
-#pragma unroll
-      for (int w = 0; w < kDecWarps; ++w) {
-        const float* src = sm_o + (w * 16 + row) * S::kOPad + seg * kPer;
-#pragma unroll
-        for (int d = 0; d < kPer; ++d) acc[d] += src[d] * wgt[w];
-      }
-      if (num_splits == 1) {
-        T* dst = reinterpret_cast<T*>(a.o) + (int64_t)b * a.o_token_stride + (int64_t)head * D + seg * kPer;
-#pragma unroll
-        for (int d = 0; d < kPer; d += 2)
-          *reinterpret_cast<uint32_t*>(dst + d) = pack2<T>(acc[d] * inv_l, acc[d + 1] * inv_l);
-      } else {
-        const int64_t pidx = ((int64_t)b * a.num_q_heads + head) * a.max_splits + split;
-        float* dst = a.part_o + pidx * D + seg * kPer;
-#pragma unroll
-        for (int d = 0; d < kPer; d += 4)
-          *reinterpret_cast<float4*>(dst + d) =
-              make_float4(acc[d] * inv_l, acc[d + 1] * inv_l, acc[d + 2] * inv_l, acc[d + 3] * inv_l);
-        if (seg == 0) a.part_lse[pidx] = M + log2f(L);
-      }
+    for (int ks = 0; ks < KS; ++ks) {
+      const int col = t * (D / 4) + 4 * ks;
+      load_q4_f16<T>(qb + g * D + col, v0, qf[ks][0], qf[ks][2]);
+      load_q4_f16<T>(qb + (g + 8) * D + col, v1, qf[ks][1], qf[ks][3]);
     }
   }
+
+  float o_acc[NT][4];
+#pragma unroll
+  for (int i = 0; i < NT; ++i) o_acc[i][0] = o_acc[i][1] = o_acc[i][2] = o_acc[i][3] = 0.f;
+  float m_run[2] = {-INFINITY, -INFINITY};
+  float l_run[2] = {0.f, 0.f};
+
+  const bool use_cap = a.logit_cap > 0.f;
+  const float cap_in = use_cap ? a.sm_scale / a.logit_cap : 0.f;
+  const float cap_out = a.logit_cap * kLog2e;
+
+  for (int i = 0; i < my_blocks; ++i) {
+    {
+      const int nb = i + STAGES - 1;
+      if (nb < my_blocks) {
+        const int st = nb % STAGES;
+        const int tok0 = (warp + nb * kDecWarps) * kBlkTok;
+        issue_block8<D>(k_cache, v_cache, a.kv_token_stride, kv_head_off, s_slots, tok0, n_tok,
+                        warp_pipe + st * S8::kStageBytes, warp_pipe + st * S8::kStageBytes + S8::kBlkBytes, lane);
+      }
+      cp_async_commit();
+    }
+    cp_async_wait<STAGES - 1>();
+    __syncwarp();
+
+    const int st = i % STAGES;
+    const uint32_t sk = warp_pipe + st * S8::kStageBytes;
+    const uint32_t sv = sk + S8::kBlkBytes;
+    const int tok0 = (warp + i * kDecWarps) * kBlkTok;
+
+    // S = Q K^T
+    float s[2][4];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+      const int r = j * 8 + g;
+      uint32_t w[KS];
+#pragma unroll
+      for (int c = 0; c < KS / 4; ++c) {
+        const uint4 v = lds128(sk + r * D + (S8::swz(t * (KS / 4) + c, r) << 4));
+        w[4 * c] = v.x; w[4 * c + 1] = v.y; w[4 * c + 2] = v.z; w[4 * c + 3] = v.w;
+      }
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks)
+        mma_16816<H>(s[j], qf[ks], e4m3x2_to_f16x2(w[ks], 0), e4m3x2_to_f16x2(w[ks], 1));
+    }
+
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float v = s[j][e];
+        if (use_cap) v = cap_out * tanh_approx(v * cap_in);
+        else v *= a.scale_log2;
+        const int tok = tok0 + j * 8 + 2 * t + (e & 1);
+        s[j][e] = tok < n_tok ? v : -INFINITY;
+      }
+    }
+
+    float alpha[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      if (h == 1 && !UPPER) { alpha[1] = 1.f; break; }
+      float mx = fmaxf(fmaxf(s[0][2 * h], s[0][2 * h + 1]), fmaxf(s[1][2 * h], s[1][2 * h + 1]));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      const float m_new = fmaxf(m_run[h], mx);
+      alpha[h] = fast_exp2(m_run[h] - m_new);
+      m_run[h] = m_new;
+      float sum = 0.f;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        s[j][2 * h] = fast_exp2(s[j][2 * h] - m_new);
+        s[j][2 * h + 1] = fast_exp2(s[j][2 * h + 1] - m_new);
+        sum += s[j][2 * h] + s[j][2 * h + 1];
+      }
+      l_run[h] = l_run[h] * alpha[h] + sum;
+    }
+    if (!UPPER) { s[0][2] = s[0][3] = s[1][2] = s[1][3] = 0.f; }
+
+    uint32_t pf[4];
+    pf[0] = pack2<H>(s[0][0], s[0][1]);
+    pf[1] = pack2<H>(s[0][2], s[0][3]);
+    pf[2] = pack2<H>(s[1][0], s[1][1]);
+    pf[3] = pack2<H>(s[1][2], s[1][3]);
+
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      o_acc[nt][0] *= alpha[0];
+      o_acc[nt][1] *= alpha[0];
+      if (UPPER) {
+        o_acc[nt][2] *= alpha[1];
+        o_acc[nt][3] *= alpha[1];
+      }
+    }
+
+    // O += P V: token rows {2t, 2t+1, 2t+8, 2t+9}, bytes [g*NT, (g+1)*NT)
+    uint32_t vw[4][NT / 4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int r = 2 * t + (q & 1) + (q >> 1) * 8;
+      if constexpr (NT == 16) {
+        const uint4 v = lds128(sv + r * D + (S8::swz(g, r) << 4));
+        vw[q][0] = v.x; vw[q][1] = v.y; vw[q][2] = v.z; vw[q][3] = v.w;
+      } else {
+        const uint2 v = lds64(sv + r * D + (S8::swz(g >> 1, r) << 4) + (g & 1) * 8);
+        vw[q][0] = v.x; vw[q][1] = v.y;
+      }
+    }
+#pragma unroll
+    for (int wi = 0; wi < NT / 4; ++wi) {
+      const uint32_t lo01 = prmt(vw[0][wi], vw[1][wi], 0x5140u), lo23 = prmt(vw[0][wi], vw[1][wi], 0x7362u);
+      const uint32_t hi01 = prmt(vw[2][wi], vw[3][wi], 0x5140u), hi23 = prmt(vw[2][wi], vw[3][wi], 0x7362u);
+      mma_16816<H>(o_acc[4 * wi + 0], pf, e4m3x2_to_f16x2(lo01, 0), e4m3x2_to_f16x2(hi01, 0));
+      mma_16816<H>(o_acc[4 * wi + 1], pf, e4m3x2_to_f16x2(lo01, 1), e4m3x2_to_f16x2(hi01, 1));
+      mma_16816<H>(o_acc[4 * wi + 2], pf, e4m3x2_to_f16x2(lo23, 0), e4m3x2_to_f16x2(hi23, 0));
+      mma_16816<H>(o_acc[4 * wi + 3], pf, e4m3x2_to_f16x2(lo23, 1), e4m3x2_to_f16x2(hi23, 1));
+    }
+    __syncwarp();
+  }
+  cp_async_wait<0>();
+
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    l_run[h] += __shfl_xor_sync(0xffffffffu, l_run[h], 1);
+    l_run[h] += __shfl_xor_sync(0xffffffffu, l_run[h], 2);
+  }
+  __syncthreads();
+  float* sm_o = reinterpret_cast<float*>(pipe);
+  float* sm_m = sm_o + kDecWarps * 16 * S::kOPad;
+  float* sm_l = sm_m + kDecWarps * 16;
+  {
+    float* wo = sm_o + warp * 16 * S::kOPad;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {  // accumulator column j of n-tile nt is dim j * NT + nt
+      wo[g * S::kOPad + (2 * t) * NT + nt] = o_acc[nt][0];
+      wo[g * S::kOPad + (2 * t + 1) * NT + nt] = o_acc[nt][1];
+      if (UPPER) {
+        wo[(g + 8) * S::kOPad + (2 * t) * NT + nt] = o_acc[nt][2];
+        wo[(g + 8) * S::kOPad + (2 * t + 1) * NT + nt] = o_acc[nt][3];
+      }
+    }
+    if (t == 0) {
+      sm_m[warp * 16 + g] = m_run[0];
+      sm_l[warp * 16 + g] = l_run[0];
+      sm_m[warp * 16 + g + 8] = UPPER ? m_run[1] : -INFINITY;
+      sm_l[warp * 16 + g + 8] = UPPER ? l_run[1] : 0.f;
+    }
+  }
+  __syncthreads();
+  combine_warps_and_store<T, D>(a, sm_o, sm_m, sm_l, n_heads, head0, b, split, num_splits, a.out_scale);
 }
 
 // Stage 2: combine the chunks of each (request, q head).  One warp per (b, h); each lane owns
@@ -503,17 +825,28 @@ __global__ void __launch_bounds__(1024) decode_merge_quant_kernel(const DecodeAr
   }
 }
 
-template <typename T, int D>
+template <typename T, int D, bool KV8>
 static int launch_decode(const DecodeArgs& a, cudaStream_t stream) {
-  constexpr int STAGES = 3;
+  // same bytes in flight per warp for both KV widths: 3 stages of 16 tokens x 2 B, 6 stages x 1 B
+  constexpr int STAGES = KV8 ? 6 : 3;
   using S = DecodeSmem<D>;
-  const int pipe = S::pipe_bytes(STAGES);
-  static_assert(S::merge_bytes() <= S::pipe_bytes(STAGES), "merge scratch must fit in the pipeline buffers");
+  constexpr int pipe = KV8 ? DecodeSmem8<D>::pipe_bytes(STAGES) : S::pipe_bytes(STAGES);
+  static_assert(S::merge_bytes() <= pipe, "merge scratch must fit in the pipeline buffers");
   const int smem = pipe + a.kv_chunk * 4;
   dim3 grid(a.max_splits, a.num_kv_heads * a.head_blocks, a.batch);
   const bool upper = a.group > 8;
   int rc;
-  if (upper) {
+  if constexpr (KV8) {
+    if (upper) {
+      auto kern = decode_attn_fp8kv_kernel<T, D, STAGES, true>;
+      B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      rc = launch_k(kern, grid, dim3(kDecThreads), smem, stream, 1, true, a);
+    } else {
+      auto kern = decode_attn_fp8kv_kernel<T, D, STAGES, false>;
+      B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      rc = launch_k(kern, grid, dim3(kDecThreads), smem, stream, 1, true, a);
+    }
+  } else if (upper) {
     auto kern = decode_attn_kernel<T, D, STAGES, true>;
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     rc = launch_k(kern, grid, dim3(kDecThreads), smem, stream, 1, true, a);
@@ -555,7 +888,8 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
                             int head_dim, int64_t q_token_stride, int64_t o_token_stride,
                             int64_t kv_token_stride, float sm_scale, float logit_cap,
                             int kv_chunk, int max_splits, void* workspace,
-                            size_t workspace_bytes, int dtype, int8_t* oq, float* oq_scale, void* stream) {
+                            size_t workspace_bytes, int dtype, int8_t* oq, float* oq_scale, void* stream,
+                            bool kv_fp8 = false, float k_scale = 1.f, float v_scale = 1.f) {
   using namespace b200;
   B200_REQUIRE(batch >= 0, "decode_attn: negative batch");
   if (batch == 0) return B200_OK;
@@ -567,8 +901,11 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
                "decode_attn: kv_chunk %d must be a multiple of 16 in [16, 4096]", kv_chunk);
   B200_REQUIRE(max_splits >= 1 && max_splits <= 65535, "decode_attn: max_splits %d", max_splits);
   B200_REQUIRE(batch <= 65535, "decode_attn: batch %d exceeds grid.z", batch);
-  B200_REQUIRE(q_token_stride % 2 == 0 && o_token_stride % 2 == 0 && kv_token_stride % 8 == 0,
+  B200_REQUIRE(q_token_stride % 2 == 0 && o_token_stride % 2 == 0 && kv_token_stride % (kv_fp8 ? 16 : 8) == 0,
                "decode_attn: strides must keep 4-byte (q/o) and 16-byte (kv) alignment");
+  B200_REQUIRE(!kv_fp8 || (q_token_stride % 4 == 0 && (uintptr_t)q % 8 == 0),
+               "decode_attn_fp8kv: q rows must be 8-byte aligned");
+  B200_REQUIRE(k_scale > 0.f && v_scale > 0.f, "decode_attn_fp8kv: k_scale / v_scale must be positive");
   B200_REQUIRE(((uintptr_t)k_cache | (uintptr_t)v_cache) % 16 == 0 && ((uintptr_t)q | (uintptr_t)o) % 4 == 0,
                "decode_attn: pointer alignment");
   size_t need = 0;
@@ -586,7 +923,9 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
   a.group = num_q_heads / num_kv_heads;
   a.head_blocks = (a.group + 15) / 16;
   a.q_token_stride = q_token_stride; a.o_token_stride = o_token_stride; a.kv_token_stride = kv_token_stride;
+  sm_scale *= k_scale;  // logits of the stored K/k_scale values, scaled back
   a.sm_scale = sm_scale; a.scale_log2 = sm_scale * kLog2e; a.logit_cap = logit_cap;
+  a.out_scale = v_scale;
   a.kv_chunk = kv_chunk; a.max_splits = max_splits;
   const size_t n = (size_t)batch * num_q_heads * max_splits;
   a.part_o = reinterpret_cast<float*>(workspace);
@@ -599,11 +938,11 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
                "decode_attn_int8: row of %d values not supported", num_q_heads * head_dim);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == B200_BF16) {
-    if (head_dim == 128) return launch_decode<__nv_bfloat16, 128>(a, st);
-    if (head_dim == 64) return launch_decode<__nv_bfloat16, 64>(a, st);
+    if (head_dim == 128) return kv_fp8 ? launch_decode<__nv_bfloat16, 128, true>(a, st) : launch_decode<__nv_bfloat16, 128, false>(a, st);
+    if (head_dim == 64) return kv_fp8 ? launch_decode<__nv_bfloat16, 64, true>(a, st) : launch_decode<__nv_bfloat16, 64, false>(a, st);
   } else if (dtype == B200_F16) {
-    if (head_dim == 128) return launch_decode<__half, 128>(a, st);
-    if (head_dim == 64) return launch_decode<__half, 64>(a, st);
+    if (head_dim == 128) return kv_fp8 ? launch_decode<__half, 128, true>(a, st) : launch_decode<__half, 128, false>(a, st);
+    if (head_dim == 64) return kv_fp8 ? launch_decode<__half, 64, true>(a, st) : launch_decode<__half, 64, false>(a, st);
   } else {
     return fail(B200_ERR_UNSUPPORTED, "decode_attn: dtype %d not supported (bf16/f16 only)", dtype);
   }
@@ -636,4 +975,17 @@ B200_API int b200_decode_attn_int8(void* o, int8_t* oq, float* oq_scale, const v
                           index_is_int64, batch, num_q_heads, num_kv_heads, head_dim, q_token_stride, o_token_stride,
                           kv_token_stride, sm_scale, logit_cap, kv_chunk, max_splits, workspace, workspace_bytes, dtype,
                           oq, oq_scale, stream);
+}
+
+B200_API int b200_decode_attn_fp8kv(void* o, int8_t* oq, float* oq_scale, const void* q, const void* k_cache,
+                                    const void* v_cache, const int32_t* req_to_token, int64_t req_to_token_stride,
+                                    const void* req_pool_indices, const void* seq_lens, int index_is_int64, int batch,
+                                    int num_q_heads, int num_kv_heads, int head_dim, int64_t q_token_stride,
+                                    int64_t o_token_stride, int64_t kv_token_stride, float sm_scale, float logit_cap,
+                                    float k_scale, float v_scale, int kv_chunk, int max_splits, void* workspace,
+                                    size_t workspace_bytes, int dtype, void* stream) {
+  return decode_attn_impl(o, q, k_cache, v_cache, req_to_token, req_to_token_stride, req_pool_indices, seq_lens,
+                          index_is_int64, batch, num_q_heads, num_kv_heads, head_dim, q_token_stride, o_token_stride,
+                          kv_token_stride, sm_scale, logit_cap, kv_chunk, max_splits, workspace, workspace_bytes, dtype,
+                          oq, oq_scale, stream, true, k_scale, v_scale);
 }

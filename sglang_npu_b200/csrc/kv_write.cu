@@ -41,6 +41,56 @@ __global__ void __launch_bounds__(256) kv_write_kernel(const KvWriteArgs a) {
   }
 }
 
+// FP8 (e4m3) KV cache: set_kv_buffer's cast branch (memory_pool.py:385-391) fused with the scatter:
+//     if scale given: x = T(float(x) / scale)     (Tensor.div_ of a bf16/f16 tensor by a Python float, fp32 math)
+//     cache[loc[t]] = float8_e4m3fn(x)            (round-to-nearest-even; |x| > 464 or NaN -> NaN, as c10's cast does,
+//                                                  not saturating)
+// Each thread converts 16 source elements (two 16-byte loads) into one 16-byte store.
+template <typename T>
+__device__ __forceinline__ uint32_t to_e4m3_torch(float x, float scale, bool has_scale) {
+  if (has_scale) x = DT<T>::to_f(DT<T>::from_f(__fdiv_rn(x, scale)));
+  uint16_t r;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(r) : "f"(0.f), "f"(x));
+  uint32_t b = r & 0xffu;
+  if (!(fabsf(x) <= 464.f)) b = 0x7fu | (__float_as_uint(x) >> 24 & 0x80u);
+  return b;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) kv_write_fp8_kernel(const KvWriteArgs a, float k_scale, float v_scale) {
+  pdl_trigger();
+  pdl_wait();
+  const bool isv = blockIdx.y != 0;
+  uint8_t* const cache = isv ? a.cache[1] : a.cache[0];
+  const uint8_t* const src = isv ? a.src[1] : a.src[0];
+  const int64_t row_bytes = isv ? a.row_bytes[1] : a.row_bytes[0];  // of the fp8 cache row
+  const int64_t src_stride = isv ? a.src_stride_bytes[1] : a.src_stride_bytes[0];
+  const int64_t cache_stride = isv ? a.cache_stride_bytes[1] : a.cache_stride_bytes[0];
+  const float scale = isv ? v_scale : k_scale;
+  const bool has_scale = scale > 0.f;
+  const int64_t chunks_per_row = row_bytes >> 4;
+  const int64_t total = a.num_tokens * chunks_per_row;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t t = i / chunks_per_row;
+    const int64_t c = i - t * chunks_per_row;
+    const int64_t slot = load_index(a.loc, t, a.loc_is_int64);
+    const int4 lo = ld_nc_v4(src + t * src_stride + (c << 5));
+    const int4 hi = ld_nc_v4(src + t * src_stride + (c << 5) + 16);
+    const uint32_t in[8] = {(uint32_t)lo.x, (uint32_t)lo.y, (uint32_t)lo.z, (uint32_t)lo.w,
+                            (uint32_t)hi.x, (uint32_t)hi.y, (uint32_t)hi.z, (uint32_t)hi.w};
+    uint32_t out[4];
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const float2 p0 = unpack2<T>(in[2 * w]), p1 = unpack2<T>(in[2 * w + 1]);
+      out[w] = to_e4m3_torch<T>(p0.x, scale, has_scale) | to_e4m3_torch<T>(p0.y, scale, has_scale) << 8 |
+               to_e4m3_torch<T>(p1.x, scale, has_scale) << 16 | to_e4m3_torch<T>(p1.y, scale, has_scale) << 24;
+    }
+    *reinterpret_cast<int4*>(cache + slot * cache_stride + (c << 4)) =
+        make_int4((int)out[0], (int)out[1], (int)out[2], (int)out[3]);
+  }
+}
+
 }  // namespace b200
 
 B200_API int b200_set_kv_buffer(void* k_cache, void* v_cache, const void* k, const void* v,
@@ -83,4 +133,46 @@ B200_API int b200_set_kv_buffer(void* k_cache, void* v_cache, const void* k, con
   const int64_t cap = (int64_t)sm_count() * 16;
   if (blocks > cap) blocks = cap;
   return launch_k(kv_write_kernel, dim3((unsigned)blocks, 2), dim3(256), 0, (cudaStream_t)stream, 1, true, a);
+}
+
+B200_API int b200_set_kv_buffer_fp8(void* k_cache, void* v_cache, const void* k, const void* v, const void* loc,
+                                    int loc_is_int64, int64_t num_tokens, int64_t k_row_elems, int64_t v_row_elems,
+                                    int64_t k_token_stride, int64_t v_token_stride, int64_t k_cache_token_stride,
+                                    int64_t v_cache_token_stride, float k_scale, float v_scale, int src_dtype,
+                                    void* stream) {
+  using namespace b200;
+  B200_REQUIRE(num_tokens >= 0, "set_kv_buffer_fp8: negative num_tokens");
+  if (num_tokens == 0) return B200_OK;
+  B200_REQUIRE(k_cache && v_cache && k && v && loc, "set_kv_buffer_fp8: null pointer");
+  B200_REQUIRE(k_row_elems % 16 == 0 && v_row_elems % 16 == 0, "set_kv_buffer_fp8: row elements must be a multiple of 16");
+  B200_REQUIRE(k_token_stride % 8 == 0 && v_token_stride % 8 == 0 && k_cache_token_stride % 16 == 0 &&
+                   v_cache_token_stride % 16 == 0,
+               "set_kv_buffer_fp8: token strides must be 16-byte multiples");
+  B200_REQUIRE(((uintptr_t)k_cache | (uintptr_t)v_cache | (uintptr_t)k | (uintptr_t)v) % 16 == 0,
+               "set_kv_buffer_fp8: pointers must be 16-byte aligned");
+  KvWriteArgs a;
+  a.cache[0] = (uint8_t*)k_cache;
+  a.cache[1] = (uint8_t*)v_cache;
+  a.src[0] = (const uint8_t*)k;
+  a.src[1] = (const uint8_t*)v;
+  a.row_bytes[0] = k_row_elems;
+  a.row_bytes[1] = v_row_elems;
+  a.src_stride_bytes[0] = k_token_stride * 2;
+  a.src_stride_bytes[1] = v_token_stride * 2;
+  a.cache_stride_bytes[0] = k_cache_token_stride;
+  a.cache_stride_bytes[1] = v_cache_token_stride;
+  a.loc = loc;
+  a.loc_is_int64 = loc_is_int64;
+  a.num_tokens = num_tokens;
+  const int64_t max_row = k_row_elems > v_row_elems ? k_row_elems : v_row_elems;
+  int64_t blocks = ceil_div(num_tokens * (max_row >> 4), 256);
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  const dim3 grid((unsigned)blocks, 2);
+  if (src_dtype == B200_BF16)
+    return launch_k(kv_write_fp8_kernel<__nv_bfloat16>, grid, dim3(256), 0, (cudaStream_t)stream, 1, true, a, k_scale,
+                    v_scale);
+  if (src_dtype == B200_F16)
+    return launch_k(kv_write_fp8_kernel<__half>, grid, dim3(256), 0, (cudaStream_t)stream, 1, true, a, k_scale, v_scale);
+  return fail(B200_ERR_UNSUPPORTED, "set_kv_buffer_fp8: source dtype %d not supported (bf16/f16)", src_dtype);
 }

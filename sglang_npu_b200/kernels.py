@@ -17,7 +17,7 @@ from ._cabi import check as _check, dtype_code, ptr, require_cuda, stream_ptr
 
 
 _LAUNCHES = 0
-_KERNELS_PER_CALL = {"b200_decode_attn": 2, "b200_decode_attn_int8": 2, "b200_decode_attn_workspace_bytes": 0,
+_KERNELS_PER_CALL = {"b200_decode_attn": 2, "b200_decode_attn_int8": 2, "b200_decode_attn_fp8kv": 2, "b200_decode_attn_workspace_bytes": 0,
                      "b200_int8_scaled_mm_workspace_bytes": 0, "b200_argmax_workspace_bytes": 0}
 
 
@@ -58,15 +58,37 @@ def _is64(t: torch.Tensor) -> int:
 
 
 # ---- KV write ------------------------------------------------------------------------------
+_FP8_STORE = (torch.float8_e4m3fn, torch.uint8)
+
+
 def set_kv_buffer(k_cache: torch.Tensor, v_cache: torch.Tensor, loc: torch.Tensor,
-                  cache_k: torch.Tensor, cache_v: torch.Tensor) -> None:
-    """k_cache[loc] = cache_k; v_cache[loc] = cache_v (memory_pool.py:369-407), one launch."""
+                  cache_k: torch.Tensor, cache_v: torch.Tensor, k_scale: Optional[float] = None,
+                  v_scale: Optional[float] = None) -> None:
+    """k_cache[loc] = cache_k; v_cache[loc] = cache_v (memory_pool.py:369-407), one launch.  When the cache is FP8
+    (float8_e4m3fn, or its uint8 store view) and cache_k/v are bf16/f16, the cast branch (:385-391: optional division
+    by k_scale / v_scale, then `.to(float8_e4m3fn)`) runs inside the same launch."""
     require_cuda(k_cache, v_cache, loc, cache_k, cache_v)
     lib = _cabi.load()
     T = loc.numel()
     if T == 0:
         return
     assert cache_k.shape[0] == T and cache_v.shape[0] == T
+    if cache_k.dtype != k_cache.dtype and k_cache.dtype in _FP8_STORE and cache_k.dtype in (torch.bfloat16, torch.float16):
+        assert cache_v.dtype == cache_k.dtype and v_cache.dtype in _FP8_STORE
+        cache_k = cache_k.reshape(T, -1)
+        cache_v = cache_v.reshape(T, -1)
+        cache_k = cache_k if cache_k.stride(-1) == 1 else cache_k.contiguous()
+        cache_v = cache_v if cache_v.stride(-1) == 1 else cache_v.contiguous()
+        loc = loc if loc.is_contiguous() else loc.contiguous()
+        kc = k_cache.view(k_cache.shape[0], -1)
+        vc = v_cache.view(v_cache.shape[0], -1)
+        assert kc.shape[1] == cache_k.shape[1] and vc.shape[1] == cache_v.shape[1]
+        check(lib.b200_set_kv_buffer_fp8(
+            ptr(kc), ptr(vc), ptr(cache_k), ptr(cache_v), ptr(loc), _is64(loc), T,
+            cache_k.shape[1], cache_v.shape[1], cache_k.stride(0), cache_v.stride(0), kc.stride(0), vc.stride(0),
+            float(k_scale) if k_scale is not None else 0.0, float(v_scale) if v_scale is not None else 0.0,
+            dtype_code(cache_k.dtype), stream_ptr(k_cache.device)), "b200_set_kv_buffer_fp8")
+        return
     assert cache_k.dtype == k_cache.dtype and cache_v.dtype == v_cache.dtype
     cache_k = cache_k.reshape(T, -1) if cache_k.dim() != 2 else cache_k
     cache_v = cache_v.reshape(T, -1) if cache_v.dim() != 2 else cache_v
@@ -99,9 +121,11 @@ def decode_attention_fwd(q: torch.Tensor, k_buffer: torch.Tensor, v_buffer: torc
                          o: torch.Tensor, req_to_token: torch.Tensor,
                          req_pool_indices: torch.Tensor, seq_lens: torch.Tensor,
                          workspace: Optional[torch.Tensor], kv_chunk: int, max_splits: int,
-                         sm_scale: float, logit_cap: float = 0.0, int8_out: bool = False):
+                         sm_scale: float, logit_cap: float = 0.0, int8_out: bool = False,
+                         k_scale: Optional[float] = None, v_scale: Optional[float] = None):
     """q [bs, Hq, D]; k/v_buffer [slots, Hkv, D]; o [bs, Hq, D] (written).  int8_out=True fuses the per-token int8
-    quantisation of the [bs, Hq*D] output into stage 2 and returns it as an Int8Activation (for o_proj)."""
+    quantisation of the [bs, Hq*D] output into stage 2 and returns it as an Int8Activation (for o_proj).  An FP8
+    (float8_e4m3fn / uint8 store view) k/v_buffer selects the FP8-KV kernel; k_scale / v_scale apply only there."""
     require_cuda(q, k_buffer, v_buffer, o, req_to_token, req_pool_indices, seq_lens)
     lib = _cabi.load()
     bs, hq, d = q.shape
@@ -112,6 +136,19 @@ def decode_attention_fwd(q: torch.Tensor, k_buffer: torch.Tensor, v_buffer: torc
     assert req_pool_indices.dtype == seq_lens.dtype
     assert req_pool_indices.is_contiguous() and seq_lens.is_contiguous()
     ws_bytes = 0 if workspace is None else workspace.numel() * workspace.element_size()
+    if k_buffer.dtype in _FP8_STORE:
+        assert v_buffer.dtype in _FP8_STORE
+        oq = torch.empty((bs, hq * d), device=q.device, dtype=torch.int8) if int8_out else None
+        oscale = torch.empty((bs, 1), device=q.device, dtype=torch.float32) if int8_out else None
+        check(lib.b200_decode_attn_fp8kv(
+            ptr(o), ptr(oq), ptr(oscale), ptr(q), ptr(k_buffer), ptr(v_buffer), ptr(req_to_token),
+            req_to_token.stride(0), ptr(req_pool_indices), ptr(seq_lens), _is64(seq_lens), bs, hq, hkv, d,
+            q.stride(0), o.stride(0), k_buffer.stride(0), float(sm_scale), float(logit_cap),
+            1.0 if k_scale is None else float(k_scale), 1.0 if v_scale is None else float(v_scale),
+            int(kv_chunk), int(max_splits), ptr(workspace), ws_bytes, dtype_code(q.dtype),
+            stream_ptr(q.device)), "b200_decode_attn_fp8kv")
+        return Int8Activation(oq, oscale, q.dtype) if int8_out else None
+    assert k_buffer.dtype == q.dtype
     if int8_out:
         oq = torch.empty((bs, hq * d), device=q.device, dtype=torch.int8)
         oscale = torch.empty((bs, 1), device=q.device, dtype=torch.float32)

@@ -165,7 +165,18 @@ class B200AttnBackend(AttentionBackend):
         if k.dtype == kb.dtype and layer.k_scale is None:
             kernels.set_kv_buffer(kb, pool.get_value_buffer(layer.layer_id), forward_batch.out_cache_loc, k, v)
         else:  # dtype conversion / scaling rules live in the pool (memory_pool.py:385-391)
-            pool.set_kv_buffer(layer, forward_batch.out_cache_loc, k, v, layer.k_scale, layer.v_scale)
+            pool.set_kv_buffer(layer, forward_batch.out_cache_loc, k, v, *self._kv_scales(layer))
+
+    @staticmethod
+    def _kv_scales(layer):
+        """(k_scale, v_scale) as Python floats or None (radix_attention.py:73-76 keeps both a tensor and a float)."""
+        ks = getattr(layer, "k_scale_float", None)
+        vs = getattr(layer, "v_scale_float", None)
+        if ks is None and layer.k_scale is not None:
+            ks = float(layer.k_scale)
+        if vs is None and layer.v_scale is not None:
+            vs = float(layer.v_scale)
+        return ks, vs
 
     def _check_layer(self, layer):
         if layer.sliding_window_size is not None and layer.sliding_window_size > -1:
@@ -189,7 +200,8 @@ class B200AttnBackend(AttentionBackend):
             o.view(-1, layer.tp_q_head_num, layer.v_head_dim),
             forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
             forward_batch.seq_lens, md.workspace, md.kv_chunk, md.max_splits,
-            layer.scaling, layer.logit_cap or 0.0, int8_out=int8_out)
+            layer.scaling, layer.logit_cap or 0.0, int8_out=int8_out,
+            **({} if pool.dtype == q.dtype else dict(zip(("k_scale", "v_scale"), self._kv_scales(layer)))))
         return act if int8_out else o
 
     def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, int8_out: bool = False):
@@ -200,6 +212,9 @@ class B200AttnBackend(AttentionBackend):
             self._save_kv(layer, forward_batch, k, v)
         md = self.forward_metadata
         pool = forward_batch.token_to_kv_pool
+        if pool.dtype != q.dtype:
+            raise NotImplementedError("B200AttnBackend: extend attention over an FP8 KV cache is not built yet "
+                                      "(decode and the KV write are)")
         causal = not (layer.is_cross_attention or getattr(layer.attn_type, "value", "") == "encoder_only")
         kernels.extend_attention_fwd(
             q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),

@@ -90,15 +90,17 @@ class MHATokenToKVPool:
                       k_scale: Optional[float] = None, v_scale: Optional[float] = None,
                       layer_id_override: Optional[int] = None):
         layer_id = layer_id_override if layer_id_override is not None else layer.layer_id
+        kb = self.k_buffer[layer_id - self.start_layer]
+        vb = self.v_buffer[layer_id - self.start_layer]
         if cache_k.dtype != self.dtype:
-            if k_scale is not None:
-                cache_k.div_(k_scale)
-            if v_scale is not None:
-                cache_v.div_(v_scale)
-            cache_k = cache_k.to(self.dtype)
-            cache_v = cache_v.to(self.dtype)
+            # the cast branch (memory_pool.py:385-391) runs inside the scatter kernel; the reference's in-place
+            # `cache_k.div_(k_scale)` side effect on the caller's tensor is not reproduced
+            if self.dtype != torch.float8_e4m3fn:
+                raise NotImplementedError(f"B200 KV pool: cast {cache_k.dtype} -> {self.dtype} is not supported "
+                                          "(bf16/f16 -> float8_e4m3fn only)")
+            kernels.set_kv_buffer(kb, vb, loc, cache_k, cache_v, k_scale, v_scale)
+            return
         if self.store_dtype != self.dtype:
             cache_k = cache_k.view(self.store_dtype)
             cache_v = cache_v.view(self.store_dtype)
-        kernels.set_kv_buffer(self.k_buffer[layer_id - self.start_layer],
-                              self.v_buffer[layer_id - self.start_layer], loc, cache_k, cache_v)
+        kernels.set_kv_buffer(kb, vb, loc, cache_k, cache_v)

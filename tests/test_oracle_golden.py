@@ -47,3 +47,17 @@ def test_fp32_oracle_close_to_reference(path):
     o = ao.decode_attention(q, rec["k_cache_after"], rec["v_cache_after"], rec["req_to_token"],
                             rec["req_pool_indices"], rec["seq_lens"], c["d"] ** -0.5, compute_dtype=torch.float32)
     assert (o.float().reshape(rec["o"].shape) - rec["o"].float()).abs().max() < 2e-2
+
+
+def test_oracle_fp8_kv_write_matches_reference_golden():
+    """oracle.set_kv_buffer_fp8 vs the reference's MHATokenToKVPool(dtype=float8_e4m3fn).set_kv_buffer, bit-exact,
+    incl. the e4m3 edge values (tests/golden/make_golden_fp8kv.py)."""
+    recs = load_golden(golden_files("kvwrite_fp8")[0])
+    assert len(recs) >= 4
+    for rec in recs:
+        kc = torch.zeros_like(rec["k_cache_after"])
+        vc = torch.zeros_like(rec["v_cache_after"])
+        ao.set_kv_buffer_fp8(kc, vc, rec["loc"], rec["k"], rec["v"], rec["k_scale"], rec["v_scale"])
+        assert torch.equal(kc, rec["k_cache_after"]) and torch.equal(vc, rec["v_cache_after"])
+        # the edge rows really exercise the NaN code and the subnormal range
+        assert (rec["k_cache_after"] == 0x7F).any() and (rec["k_cache_after"] == 0xFF).any()

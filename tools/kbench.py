@@ -70,18 +70,20 @@ def bench_decode(args):
     lens = [ctx] * bs if not args.ragged else torch.randint(ctx // 2, ctx + 1, (bs,), generator=torch.Generator().manual_seed(0)).tolist()
     pb = synth.make_paged_batch(lens, page, seed=1)
     k, v = synth.randn_kv_device(pb.num_slots, page, hkv, d, torch.bfloat16, dev)
+    if args.fp8kv:
+        k, v = k.to(torch.float8_e4m3fn), v.to(torch.float8_e4m3fn)
     q = torch.randn(bs, hq, d, device=dev).to(torch.bfloat16)
     o = torch.empty_like(q)
     r2t = pb.req_to_token.to(dev)
     rpi = pb.req_pool_indices.to(dev)
     sl = pb.seq_lens.to(dev)
-    kv_bytes = sum(lens) * 2 * hkv * d * 2
+    kv_bytes = sum(lens) * 2 * hkv * d * k.element_size()
     for chunk in ([args.chunk] if args.chunk else [0, 256, 512, 1024, 2048]):
         ch, splits = plan_decode_splits(bs, hkv, hq // hkv, max(lens), 148, chunk)
         ws = torch.empty(max(kernels.decode_attn_workspace_bytes(bs, hq, d, splits), 16), dtype=torch.uint8, device=dev)
         fn = lambda: kernels.decode_attention_fwd(q, k, v, o, r2t, rpi, sl, ws, ch, splits, d ** -0.5)
         med, best = timeit(fn)
-        print(json.dumps(dict(kernel="decode_attn", bs=bs, ctx=ctx, chunk=ch, splits=splits, ms_med=round(med, 4),
+        print(json.dumps(dict(kernel="decode_attn_fp8kv" if args.fp8kv else "decode_attn", bs=bs, ctx=ctx, chunk=ch, splits=splits, ms_med=round(med, 4),
                               ms_best=round(best, 4), gbs_med=round(kv_bytes / med / 1e6, 1),
                               frac_of_measured=round(kv_bytes / med / 1e6 / HBM, 3))), flush=True)
 
@@ -193,6 +195,7 @@ if __name__ == "__main__":
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--m", type=int, default=0)
     ap.add_argument("--ragged", action="store_true")
+    ap.add_argument("--fp8kv", action="store_true", help="decode: FP8 (e4m3) KV cache")
     ap.add_argument("--cluster", action="store_true", help="gemm_int8: cluster split-K kernel instead of stream-K")
     args = ap.parse_args()
     {"decode": bench_decode, "gemm_int8": bench_gemm_int8, "awq": bench_awq, "peak": bench_peak, "extend": bench_extend}[args.what](args)
