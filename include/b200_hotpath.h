@@ -125,6 +125,25 @@ int b200_decode_attn_fp8kv(void* o, int8_t* oq, float* oq_scale, const void* q, 
                            float k_scale, float v_scale, int kv_chunk, int max_splits, void* workspace,
                            size_t workspace_bytes, int dtype, void* stream);
 
+/* Shared-prefix (cascade) decode (the reference's building blocks are merge_state,
+ * sgl-kernel/csrc/attention/cascade.cu:20-55, and FlashInfer's cascade wrappers).  Every request of the batch starts
+ * with the same `shared_prefix_len` physical KV slots (a radix-cache hit on a common system prompt: BASELINE config 5);
+ * request 0's page-table row names them.  Result = b200_decode_attn's (same formula), computed as
+ *   1. prefix pass: all batch x Hq query rows against the shared tokens as ONE tensor-core attention problem
+ *      (tcgen05, 128 query rows per CTA), cut into segments of `seg_len` tokens (multiple of 128) for SM occupancy;
+ *      the shared KV bytes are read once per 128 requests instead of once per request;
+ *   2. the split-KV decode kernel over each request's own tokens [shared_prefix_len, seq_len);
+ *   3. one LSE merge over the segment partials and the decode partials (the decode stage-2 kernel).
+ * Requires seq_lens[b] > shared_prefix_len for every b.  Workspace: b200_decode_attn_workspace_bytes(batch, Hq, D,
+ * ceil(shared_prefix_len / seg_len) + max_splits).  oq / oq_scale as in b200_decode_attn_int8, or NULL. */
+int b200_decode_attn_shared_prefix(void* o, int8_t* oq, float* oq_scale, const void* q, const void* k_cache,
+                                   const void* v_cache, const int32_t* req_to_token, int64_t req_to_token_stride,
+                                   const void* req_pool_indices, const void* seq_lens, int index_is_int64, int batch,
+                                   int num_q_heads, int num_kv_heads, int head_dim, int64_t q_token_stride,
+                                   int64_t o_token_stride, int64_t kv_token_stride, float sm_scale, float logit_cap,
+                                   int shared_prefix_len, int seg_len, int kv_chunk, int max_splits, void* workspace,
+                                   size_t workspace_bytes, int dtype, void* stream);
+
 /* ---- extend (prefill) attention ------------------------------------------------------
  * Replaces extend_attention_fwd (triton_ops/extend_attention.py:302-440) and the
  * oracle's _run_sdpa_forward_extend (torch_native_backend.py:27-110).  Request b has

@@ -21,6 +21,7 @@
 //    CTA writes the final output, else fp32 partial (o, lse) go to the workspace and
 //    decode_merge_kernel combines the chunks (log-sum-exp merge).
 #include "common.cuh"
+#include "extend_attn.cuh"
 #include <type_traits>
 
 namespace b200 {
@@ -47,8 +48,13 @@ struct DecodeArgs {
   float logit_cap;
   float out_scale;    // fp8 KV only: v_scale, applied with the final 1/l
   int kv_chunk, max_splits;
-  float* part_o;    // [batch, Hq, max_splits, D]
-  float* part_lse;  // [batch, Hq, max_splits]   (log2 domain)
+  // shared-prefix (cascade) decode: tokens [0, kv_start) of every request were already reduced into partials
+  // 0..n_seg-1 of the workspace by the tensor-core prefix kernel (extend_attn_umma.cu, segment mode); this kernel
+  // covers tokens [kv_start, seq_len) and writes partials n_seg.. ; both are 0 for plain decode
+  int kv_start, n_seg;
+  int ws_splits;    // partial slots per (request, head) = n_seg + max_splits
+  float* part_o;    // [batch, Hq, ws_splits, D]
+  float* part_lse;  // [batch, Hq, ws_splits]   (log2 domain)
   int8_t* oq;       // optional fused output quant (b200_decode_attn_int8): [batch, Hq * D] int8 codes
   float* oq_scale;  // [batch] per-token scales
 };
@@ -106,7 +112,7 @@ __device__ __forceinline__ void combine_warps_and_store(const DecodeArgs& a, con
         for (int d = 0; d < kPer; d += 2)
           *reinterpret_cast<uint32_t*>(dst + d) = pack2<T>(acc[d] * inv_l, acc[d + 1] * inv_l);
       } else {
-        const int64_t pidx = ((int64_t)b * a.num_q_heads + head) * a.max_splits + split;
+        const int64_t pidx = ((int64_t)b * a.num_q_heads + head) * a.ws_splits + a.n_seg + split;
         float* dst = a.part_o + pidx * D + seg * kPer;
 #pragma unroll
         for (int d = 0; d < kPer; d += 4)
@@ -157,11 +163,11 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_attn_kernel(const Decod
 
   pdl_trigger();
   pdl_wait();
-  const int seq_len = (int)load_index(a.seq_lens, b, a.index_is_int64);
+  const int seq_len = (int)load_index(a.seq_lens, b, a.index_is_int64) - a.kv_start;  // tokens this kernel covers
   const int start = split * a.kv_chunk;
   if (start >= seq_len) return;
   const int n_tok = min(seq_len - start, a.kv_chunk);
-  const int num_splits = (seq_len + a.kv_chunk - 1) / a.kv_chunk;
+  const int num_splits = a.n_seg + (seq_len + a.kv_chunk - 1) / a.kv_chunk;
 
   // carve shared memory: [pipeline | slots]; the merge scratch aliases the pipeline.
   uint8_t* pipe = smem_raw;
@@ -170,7 +176,7 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_attn_kernel(const Decod
   // ---- 1. page-table slice of this chunk -> shared memory --------------------------------
   {
     const int64_t req = load_index(a.req_pool_indices, b, a.index_is_int64);
-    const int32_t* row = a.req_to_token + req * a.req_to_token_stride + start;
+    const int32_t* row = a.req_to_token + req * a.req_to_token_stride + a.kv_start + start;
     for (int i = threadIdx.x; i < n_tok; i += kDecThreads) s_slots[i] = __ldg(row + i);
   }
   __syncthreads();
@@ -451,8 +457,8 @@ __device__ __forceinline__ void load_q4_f16(const T* p, bool valid, uint32_t& lo
   }
 }
 
-template <typename T, int D, int STAGES, bool UPPER>
-__global__ void __launch_bounds__(kDecThreads, 2) decode_attn_fp8kv_kernel(const DecodeArgs a) {
+template <typename T, int D, int STAGES, bool UPPER, int MINB>
+__global__ void __launch_bounds__(kDecThreads, MINB) decode_attn_fp8kv_kernel(const DecodeArgs a) {
   using S = DecodeSmem<D>;
   using S8 = DecodeSmem8<D>;
   using H = __half;
@@ -471,17 +477,17 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_attn_fp8kv_kernel(const
 
   pdl_trigger();
   pdl_wait();
-  const int seq_len = (int)load_index(a.seq_lens, b, a.index_is_int64);
+  const int seq_len = (int)load_index(a.seq_lens, b, a.index_is_int64) - a.kv_start;  // tokens this kernel covers
   const int start = split * a.kv_chunk;
   if (start >= seq_len) return;
   const int n_tok = min(seq_len - start, a.kv_chunk);
-  const int num_splits = (seq_len + a.kv_chunk - 1) / a.kv_chunk;
+  const int num_splits = a.n_seg + (seq_len + a.kv_chunk - 1) / a.kv_chunk;
 
   uint8_t* pipe = smem_raw;
   int32_t* s_slots = reinterpret_cast<int32_t*>(smem_raw + S8::pipe_bytes(STAGES));
   {
     const int64_t req = load_index(a.req_pool_indices, b, a.index_is_int64);
-    const int32_t* row = a.req_to_token + req * a.req_to_token_stride + start;
+    const int32_t* row = a.req_to_token + req * a.req_to_token_stride + a.kv_start + start;
     for (int i = threadIdx.x; i < n_tok; i += kDecThreads) s_slots[i] = __ldg(row + i);
   }
   __syncthreads();
@@ -552,7 +558,6 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_attn_fp8kv_kernel(const
     float s[2][4];
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
       const int r = j * 8 + g;
       uint32_t w[KS];
 #pragma unroll
@@ -560,9 +565,17 @@ __global__ void __launch_bounds__(kDecThreads, 2) decode_attn_fp8kv_kernel(const
         const uint4 v = lds128(sk + r * D + (S8::swz(t * (KS / 4) + c, r) << 4));
         w[4 * c] = v.x; w[4 * c + 1] = v.y; w[4 * c + 2] = v.z; w[4 * c + 3] = v.w;
       }
+      // even / odd k-steps accumulate separately: with two warps per scheduler the dependent-HMMA chain is what the
+      // loop waits on, so keep four chains (2 n-tiles x 2) in flight instead of two
+      float s2[4] = {0.f, 0.f, 0.f, 0.f};
+      s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
 #pragma unroll
-      for (int ks = 0; ks < KS; ++ks)
+      for (int ks = 0; ks < KS; ks += 2) {
         mma_16816<H>(s[j], qf[ks], e4m3x2_to_f16x2(w[ks], 0), e4m3x2_to_f16x2(w[ks], 1));
+        mma_16816<H>(s2, qf[ks + 1], e4m3x2_to_f16x2(w[ks + 1], 0), e4m3x2_to_f16x2(w[ks + 1], 1));
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) s[j][e] += s2[e];
     }
 
 #pragma unroll
@@ -683,8 +696,8 @@ __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeArgs a) {
   if (warp_global >= a.batch * a.num_q_heads) return;
   const int b = warp_global / a.num_q_heads;
   const int h = warp_global - b * a.num_q_heads;
-  const int seq_len = (int)load_index(a.seq_lens, b, a.index_is_int64);
-  const int num_splits = (seq_len + a.kv_chunk - 1) / a.kv_chunk;
+  const int seq_len = max((int)load_index(a.seq_lens, b, a.index_is_int64) - a.kv_start, 0);
+  const int num_splits = a.n_seg + (seq_len + a.kv_chunk - 1) / a.kv_chunk;
   if (num_splits == 1) return;
   constexpr int kPer = D / 32;
   T* dst = reinterpret_cast<T*>(a.o) + (int64_t)b * a.o_token_stride + (int64_t)h * D + lane * kPer;
@@ -692,7 +705,7 @@ __global__ void __launch_bounds__(128) decode_merge_kernel(const DecodeArgs a) {
 #pragma unroll
   for (int d = 0; d < kPer; ++d) acc[d] = 0.f;
   if (num_splits > 1) {
-    const int64_t base = ((int64_t)b * a.num_q_heads + h) * a.max_splits;
+    const int64_t base = ((int64_t)b * a.num_q_heads + h) * a.ws_splits;
     float M = -INFINITY;
     for (int s = lane; s < num_splits; s += 32) M = fmaxf(M, a.part_lse[base + s]);
 #pragma unroll
@@ -731,8 +744,8 @@ __global__ void __launch_bounds__(1024) decode_merge_quant_kernel(const DecodeAr
   const int b = blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nwarps = blockDim.x >> 5;
-  const int seq_len = (int)load_index(a.seq_lens, b, a.index_is_int64);
-  const int num_splits = (seq_len + a.kv_chunk - 1) / a.kv_chunk;
+  const int seq_len = max((int)load_index(a.seq_lens, b, a.index_is_int64) - a.kv_start, 0);
+  const int num_splits = a.n_seg + (seq_len + a.kv_chunk - 1) / a.kv_chunk;
   constexpr int kPer = D / 32;
   float amax = 0.f;
   for (int h = warp; h < a.num_q_heads; h += nwarps) {  // one warp per q head: every head's loads are in flight at once
@@ -749,7 +762,7 @@ __global__ void __launch_bounds__(1024) decode_merge_quant_kernel(const DecodeAr
 #pragma unroll
       for (int d = 0; d < kPer; ++d) acc[d] = 0.f;
       if (num_splits > 1) {
-        const int64_t base = ((int64_t)b * a.num_q_heads + h) * a.max_splits;
+        const int64_t base = ((int64_t)b * a.num_q_heads + h) * a.ws_splits;
         float M = -INFINITY;
         for (int s = lane; s < num_splits; s += 32) M = fmaxf(M, a.part_lse[base + s]);
 #pragma unroll
@@ -825,27 +838,38 @@ __global__ void __launch_bounds__(1024) decode_merge_quant_kernel(const DecodeAr
   }
 }
 
+template <typename T, int D, int STAGES, int MINB>
+static int launch_decode_fp8kv_stage1(const DecodeArgs& a, cudaStream_t stream) {
+  using S = DecodeSmem<D>;
+  constexpr int pipe = DecodeSmem8<D>::pipe_bytes(STAGES);
+  static_assert(S::merge_bytes() <= pipe, "merge scratch must fit in the pipeline buffers");
+  const int smem = pipe + a.kv_chunk * 4;
+  dim3 grid(a.max_splits, a.num_kv_heads * a.head_blocks, a.batch);
+  if (a.group > 8) {
+    auto kern = decode_attn_fp8kv_kernel<T, D, STAGES, true, MINB>;
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    return launch_k(kern, grid, dim3(kDecThreads), smem, stream, 1, true, a);
+  }
+  auto kern = decode_attn_fp8kv_kernel<T, D, STAGES, false, MINB>;
+  B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  return launch_k(kern, grid, dim3(kDecThreads), smem, stream, 1, true, a);
+}
+
 template <typename T, int D, bool KV8>
 static int launch_decode(const DecodeArgs& a, cudaStream_t stream) {
-  // same bytes in flight per warp for both KV widths: 3 stages of 16 tokens x 2 B, 6 stages x 1 B
-  constexpr int STAGES = KV8 ? 6 : 3;
+  constexpr int STAGES = 3;
   using S = DecodeSmem<D>;
-  constexpr int pipe = KV8 ? DecodeSmem8<D>::pipe_bytes(STAGES) : S::pipe_bytes(STAGES);
+  constexpr int pipe = S::pipe_bytes(STAGES);
   static_assert(S::merge_bytes() <= pipe, "merge scratch must fit in the pipeline buffers");
   const int smem = pipe + a.kv_chunk * 4;
   dim3 grid(a.max_splits, a.num_kv_heads * a.head_blocks, a.batch);
   const bool upper = a.group > 8;
   int rc;
   if constexpr (KV8) {
-    if (upper) {
-      auto kern = decode_attn_fp8kv_kernel<T, D, STAGES, true>;
-      B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      rc = launch_k(kern, grid, dim3(kDecThreads), smem, stream, 1, true, a);
-    } else {
-      auto kern = decode_attn_fp8kv_kernel<T, D, STAGES, false>;
-      B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-      rc = launch_k(kern, grid, dim3(kDecThreads), smem, stream, 1, true, a);
-    }
+    // 4 stages x 3 CTAs/SM (measured 0.118 ms at cfg 2, profiles/r01g_kbench_fp8kv.jsonl) vs 6 stages x 2 CTAs/SM
+    // (0.128 ms, B200_FP8KV_OCC=2): the register-side conversions want more warps per scheduler
+    static const int occ = [] { const char* e = getenv("B200_FP8KV_OCC"); return e ? atoi(e) : 3; }();
+    rc = occ == 3 ? launch_decode_fp8kv_stage1<T, D, 4, 3>(a, stream) : launch_decode_fp8kv_stage1<T, D, 6, 2>(a, stream);
   } else if (upper) {
     auto kern = decode_attn_kernel<T, D, STAGES, true>;
     B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -889,7 +913,8 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
                             int64_t kv_token_stride, float sm_scale, float logit_cap,
                             int kv_chunk, int max_splits, void* workspace,
                             size_t workspace_bytes, int dtype, int8_t* oq, float* oq_scale, void* stream,
-                            bool kv_fp8 = false, float k_scale = 1.f, float v_scale = 1.f) {
+                            bool kv_fp8 = false, float k_scale = 1.f, float v_scale = 1.f, int shared_prefix = 0,
+                            int seg_len = 0) {
   using namespace b200;
   B200_REQUIRE(batch >= 0, "decode_attn: negative batch");
   if (batch == 0) return B200_OK;
@@ -908,9 +933,19 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
   B200_REQUIRE(k_scale > 0.f && v_scale > 0.f, "decode_attn_fp8kv: k_scale / v_scale must be positive");
   B200_REQUIRE(((uintptr_t)k_cache | (uintptr_t)v_cache) % 16 == 0 && ((uintptr_t)q | (uintptr_t)o) % 4 == 0,
                "decode_attn: pointer alignment");
+  int n_seg = 0;
+  if (shared_prefix > 0) {
+    B200_REQUIRE(!kv_fp8, "decode_attn_shared_prefix: FP8 KV is not supported by the prefix kernel");
+    B200_REQUIRE(seg_len >= 128 && seg_len % 128 == 0, "decode_attn_shared_prefix: seg_len %d must be a multiple of 128",
+                 seg_len);
+    n_seg = (shared_prefix + seg_len - 1) / seg_len;
+    B200_REQUIRE(n_seg <= 65535 && (q_token_stride * 2) % 16 == 0 && (uintptr_t)q % 16 == 0,
+                 "decode_attn_shared_prefix: %d segments / q alignment", n_seg);
+  }
+  const int ws_splits = n_seg + max_splits;
   size_t need = 0;
-  b200_decode_attn_workspace_bytes(batch, num_q_heads, head_dim, max_splits, &need);
-  if (max_splits > 1) {
+  b200_decode_attn_workspace_bytes(batch, num_q_heads, head_dim, ws_splits, &need);
+  if (ws_splits > 1) {
     if (workspace == nullptr || workspace_bytes < need)
       return fail(B200_ERR_WORKSPACE, "decode_attn: workspace %zu B < required %zu B", workspace_bytes, need);
     B200_REQUIRE((uintptr_t)workspace % 16 == 0, "decode_attn: workspace must be 16-byte aligned");
@@ -927,7 +962,8 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
   a.sm_scale = sm_scale; a.scale_log2 = sm_scale * kLog2e; a.logit_cap = logit_cap;
   a.out_scale = v_scale;
   a.kv_chunk = kv_chunk; a.max_splits = max_splits;
-  const size_t n = (size_t)batch * num_q_heads * max_splits;
+  a.kv_start = shared_prefix; a.n_seg = n_seg; a.ws_splits = ws_splits;
+  const size_t n = (size_t)batch * num_q_heads * ws_splits;
   a.part_o = reinterpret_cast<float*>(workspace);
   a.part_lse = a.part_o ? a.part_o + n * head_dim : nullptr;
   a.oq = oq;
@@ -937,6 +973,22 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
                                  (size_t)num_q_heads * head_dim * 4 <= 200 * 1024),
                "decode_attn_int8: row of %d values not supported", num_q_heads * head_dim);
   cudaStream_t st = (cudaStream_t)stream;
+  if (n_seg > 0) {
+    // prefix pass on the tensor cores: every request's q rows against the shared tokens, one segment per grid.z
+    ExtendArgs e;
+    e.o = nullptr; e.q = q; e.k_new = nullptr; e.v_new = nullptr; e.k_cache = k_cache; e.v_cache = v_cache;
+    e.req_to_token = req_to_token; e.req_to_token_stride = req_to_token_stride;
+    e.req_pool_indices = req_pool_indices; e.index_is_int64 = index_is_int64;
+    e.qo_indptr = nullptr; e.prefix_lens = nullptr;
+    e.batch = n_seg; e.num_q_heads = num_q_heads; e.num_kv_heads = num_kv_heads;
+    e.q_token_stride = q_token_stride; e.o_token_stride = o_token_stride;
+    e.knew_token_stride = 0; e.vnew_token_stride = 0; e.kv_token_stride = kv_token_stride;
+    e.scale_log2 = a.scale_log2; e.sm_scale = a.sm_scale; e.logit_cap = logit_cap; e.causal = 0;
+    e.part_o = a.part_o; e.part_lse = a.part_lse; e.part_stride = ws_splits; e.seg_len = seg_len;
+    e.seg_rows = batch; e.seg_prefix = shared_prefix;
+    const int rc = launch_extend_umma(e, batch, head_dim, dtype, st);
+    if (rc != B200_OK) return rc;
+  }
   if (dtype == B200_BF16) {
     if (head_dim == 128) return kv_fp8 ? launch_decode<__nv_bfloat16, 128, true>(a, st) : launch_decode<__nv_bfloat16, 128, false>(a, st);
     if (head_dim == 64) return kv_fp8 ? launch_decode<__nv_bfloat16, 64, true>(a, st) : launch_decode<__nv_bfloat16, 64, false>(a, st);
@@ -988,4 +1040,20 @@ B200_API int b200_decode_attn_fp8kv(void* o, int8_t* oq, float* oq_scale, const 
                           index_is_int64, batch, num_q_heads, num_kv_heads, head_dim, q_token_stride, o_token_stride,
                           kv_token_stride, sm_scale, logit_cap, kv_chunk, max_splits, workspace, workspace_bytes, dtype,
                           oq, oq_scale, stream, true, k_scale, v_scale);
+}
+
+B200_API int b200_decode_attn_shared_prefix(void* o, int8_t* oq, float* oq_scale, const void* q, const void* k_cache,
+                                            const void* v_cache, const int32_t* req_to_token,
+                                            int64_t req_to_token_stride, const void* req_pool_indices,
+                                            const void* seq_lens, int index_is_int64, int batch, int num_q_heads,
+                                            int num_kv_heads, int head_dim, int64_t q_token_stride,
+                                            int64_t o_token_stride, int64_t kv_token_stride, float sm_scale,
+                                            float logit_cap, int shared_prefix_len, int seg_len, int kv_chunk,
+                                            int max_splits, void* workspace, size_t workspace_bytes, int dtype,
+                                            void* stream) {
+  B200_REQUIRE(shared_prefix_len > 0, "decode_attn_shared_prefix: shared_prefix_len must be positive");
+  return decode_attn_impl(o, q, k_cache, v_cache, req_to_token, req_to_token_stride, req_pool_indices, seq_lens,
+                          index_is_int64, batch, num_q_heads, num_kv_heads, head_dim, q_token_stride, o_token_stride,
+                          kv_token_stride, sm_scale, logit_cap, kv_chunk, max_splits, workspace, workspace_bytes, dtype,
+                          oq, oq_scale, stream, false, 1.f, 1.f, shared_prefix_len, seg_len);
 }

@@ -25,6 +25,14 @@ struct ExtendArgs {
   int64_t q_token_stride, o_token_stride, knew_token_stride, vnew_token_stride, kv_token_stride;
   float scale_log2, sm_scale, logit_cap;
   int causal;
+  // Segment mode (shared-prefix decode, decode_attn.cu): part_o != NULL.  blockIdx.z = segment s of request 0's prefix,
+  // KV positions [s * seg_len, min(prefix, (s+1) * seg_len)) only (no new tokens, no causal mask); every segment uses
+  // the same q rows (request 0's).  Instead of o the kernel writes the normalised fp32 partial and its log2-domain
+  // LSE into the split-KV workspace of the decode merge: slot s of [row, head, part_stride].
+  float* part_o = nullptr;
+  float* part_lse = nullptr;
+  int part_stride = 0, seg_len = 0;
+  int seg_rows = 0, seg_prefix = 0;  // q rows (= decode batch) and shared-prefix length: passed by value, no device arrays
 };
 
 // tcgen05 path (extend_attn_umma.cu); returns B200_ERR_UNSUPPORTED for shapes it does not cover

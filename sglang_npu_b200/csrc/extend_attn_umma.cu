@@ -211,12 +211,18 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
 
   pdl_trigger();
   pdl_wait();
-  const int q_start = a.qo_indptr[b];
-  const int ext_len = a.qo_indptr[b + 1] - q_start;
+  const bool seg_mode = a.part_o != nullptr;
+  const int rb = seg_mode ? 0 : b;  // the request whose q rows and page-table row this CTA uses
+  const int q_start = seg_mode ? 0 : a.qo_indptr[rb];
+  const int ext_len = seg_mode ? a.seg_rows : a.qo_indptr[rb + 1] - q_start;
   const int m0 = mblk * kUxBM;
   if (m0 >= ext_len) return;  // uniform for the CTA, before any barrier / TMEM use
-  const int prefix = a.prefix_lens[b];
-  const int kv_total = prefix + ext_len;
+  // segment mode: the segment is treated as a sequence of its own (positions relative to kv_begin, page-table row
+  // pointer advanced by kv_begin) that consists of prefix tokens only
+  const int kv_begin = seg_mode ? b * a.seg_len : 0;
+  const int prefix = seg_mode ? min(a.seg_prefix - kv_begin, a.seg_len) : a.prefix_lens[b];
+  if (prefix <= 0 && seg_mode) return;
+  const int kv_total = seg_mode ? prefix : prefix + ext_len;
   const int kv_end = a.causal ? min(kv_total, prefix + m0 + kUxBM) : kv_total;
   const int n_tiles = (kv_end + kUxBN - 1) / kUxBN;
   const int group = a.num_q_heads / a.num_kv_heads;
@@ -249,8 +255,8 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
     //      2-stage ring, so K of tile j+2 is fetched as soon as Q K^T of tile j has retired ---------------------------
     const bool is_v = warp >= 2;
     const int w = warp & 1;
-    const int64_t req = load_index(a.req_pool_indices, b, a.index_is_int64);
-    const int32_t* r2t_row = a.req_to_token + req * a.req_to_token_stride;
+    const int64_t req = load_index(a.req_pool_indices, rb, a.index_is_int64);
+    const int32_t* r2t_row = a.req_to_token + req * a.req_to_token_stride + kv_begin;
     const T* cache = reinterpret_cast<const T*>(is_v ? a.v_cache : a.k_cache);
     const T* fresh = reinterpret_cast<const T*>(is_v ? a.v_new : a.k_new);
     const int64_t fresh_stride = is_v ? a.vnew_token_stride : a.knew_token_stride;
@@ -397,6 +403,24 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
     tc_fence_after();
     const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
     const bool row_ok = m0 + row < ext_len;
+    if (seg_mode) {  // fp32 partial + log2-domain LSE into the decode merge's workspace
+      const int64_t pidx = ((int64_t)(q_start + m0 + row) * a.num_q_heads + head) * a.part_stride + b;
+      float* prow = a.part_o + pidx * D;
+      if (row_ok) a.part_lse[pidx] = l_run > 0.f ? m_used + log2f(l_run) : -INFINITY;
+#pragma unroll 1
+      for (int c0 = 0; c0 < D; c0 += 16) {
+        uint32_t r[16];
+        tmem_ld16(t_lane + kOCol + c0, r);
+        tmem_ld_wait();
+        if (row_ok) {
+#pragma unroll
+          for (int i = 0; i < 16; i += 4)
+            *reinterpret_cast<float4*>(prow + c0 + i) =
+                make_float4(__uint_as_float(r[i]) * inv, __uint_as_float(r[i + 1]) * inv,
+                            __uint_as_float(r[i + 2]) * inv, __uint_as_float(r[i + 3]) * inv);
+        }
+      }
+    } else {
     T* orow = reinterpret_cast<T*>(a.o) + (int64_t)(q_start + m0 + row) * a.o_token_stride + (int64_t)head * D;
 #pragma unroll 1
     for (int c0 = 0; c0 < D; c0 += 16) {
@@ -416,6 +440,7 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
         }
       }
     }
+    }  // !seg_mode
   }
 
   tc_fence_before();
@@ -428,7 +453,7 @@ static int launch_ux(const ExtendArgs& a, int max_extend_len, cudaStream_t strea
   using L = UxSmem<D>;
   auto kern = extend_attn_umma_kernel<T, D>;
   B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
-  dim3 grid((max_extend_len + kUxBM - 1) / kUxBM, a.num_q_heads, a.batch);
+  dim3 grid((max_extend_len + kUxBM - 1) / kUxBM, a.num_q_heads, a.batch);  // segment mode: batch = segments
   return launch_k(kern, grid, dim3(kUxThreads), L::kBytes, stream, 1, true, a);
 }
 

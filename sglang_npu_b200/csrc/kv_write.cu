@@ -6,6 +6,7 @@
 // covers 512 contiguous bytes of a row, so both the gather (k/v activations) and the
 // scatter (cache rows) are fully coalesced.  blockIdx.y selects K (0) or V (1).
 #include "common.cuh"
+#include <type_traits>
 
 namespace b200 {
 
@@ -47,12 +48,19 @@ __global__ void __launch_bounds__(256) kv_write_kernel(const KvWriteArgs a) {
 //                                                  not saturating)
 // Each thread converts 16 source elements (two 16-byte loads) into one 16-byte store.
 template <typename T>
-__device__ __forceinline__ uint32_t to_e4m3_torch(float x, float scale, bool has_scale) {
-  if (has_scale) x = DT<T>::to_f(DT<T>::from_f(__fdiv_rn(x, scale)));
+__device__ __forceinline__ uint32_t to_e4m3_torch(float x, uint32_t sign, float scale, bool has_scale) {
+  // `sign` (0x80 or 0) comes from the raw 16-bit pattern: the f16 -> f32 convert drops a NaN's sign
+  if (has_scale) {
+    // NaN sign after the division, as ATen's CPU kernels leave it (pinned by tests/golden/kvwrite_fp8.pt): the
+    // vectorised fp32 -> bf16 pack writes NaN as 0xFFFF (negative); the f16 pack keeps the operand's sign.  The GPU
+    // divide would canonicalise it to +NaN.
+    if (std::is_same<T, __nv_bfloat16>::value && x != x) sign = 0x80u;
+    x = DT<T>::to_f(DT<T>::from_f(__fdiv_rn(x, scale)));
+  }
   uint16_t r;
   asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(r) : "f"(0.f), "f"(x));
   uint32_t b = r & 0xffu;
-  if (!(fabsf(x) <= 464.f)) b = 0x7fu | (__float_as_uint(x) >> 24 & 0x80u);
+  if (!(fabsf(x) <= 464.f)) b = 0x7fu | sign;
   return b;
 }
 
@@ -83,8 +91,11 @@ __global__ void __launch_bounds__(256) kv_write_fp8_kernel(const KvWriteArgs a, 
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
       const float2 p0 = unpack2<T>(in[2 * w]), p1 = unpack2<T>(in[2 * w + 1]);
-      out[w] = to_e4m3_torch<T>(p0.x, scale, has_scale) | to_e4m3_torch<T>(p0.y, scale, has_scale) << 8 |
-               to_e4m3_torch<T>(p1.x, scale, has_scale) << 16 | to_e4m3_torch<T>(p1.y, scale, has_scale) << 24;
+      const uint32_t w0 = in[2 * w], w1 = in[2 * w + 1];
+      out[w] = to_e4m3_torch<T>(p0.x, w0 >> 8 & 0x80u, scale, has_scale) |
+               to_e4m3_torch<T>(p0.y, w0 >> 24 & 0x80u, scale, has_scale) << 8 |
+               to_e4m3_torch<T>(p1.x, w1 >> 8 & 0x80u, scale, has_scale) << 16 |
+               to_e4m3_torch<T>(p1.y, w1 >> 24 & 0x80u, scale, has_scale) << 24;
     }
     *reinterpret_cast<int4*>(cache + slot * cache_stride + (c << 4)) =
         make_int4((int)out[0], (int)out[1], (int)out[2], (int)out[3]);

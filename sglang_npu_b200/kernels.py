@@ -17,7 +17,7 @@ from ._cabi import check as _check, dtype_code, ptr, require_cuda, stream_ptr
 
 
 _LAUNCHES = 0
-_KERNELS_PER_CALL = {"b200_decode_attn": 2, "b200_decode_attn_int8": 2, "b200_decode_attn_fp8kv": 2, "b200_decode_attn_workspace_bytes": 0,
+_KERNELS_PER_CALL = {"b200_decode_attn_shared_prefix": 3, "b200_decode_attn": 2, "b200_decode_attn_int8": 2, "b200_decode_attn_fp8kv": 2, "b200_decode_attn_workspace_bytes": 0,
                      "b200_int8_scaled_mm_workspace_bytes": 0, "b200_argmax_workspace_bytes": 0}
 
 
@@ -165,6 +165,45 @@ def decode_attention_fwd(q: torch.Tensor, k_buffer: torch.Tensor, v_buffer: torc
         q.stride(0), o.stride(0), k_buffer.stride(0), float(sm_scale), float(logit_cap),
         int(kv_chunk), int(max_splits), ptr(workspace), ws_bytes, dtype_code(q.dtype),
         stream_ptr(q.device)), "b200_decode_attn")
+
+
+def plan_shared_prefix_segments(shared_prefix_len: int, batch: int, num_q_heads: int, sm_count: int = 148) -> int:
+    """Segment length (multiple of 128) for the prefix pass of the shared-prefix decode: enough segments that
+    ceil(batch/128) * Hq * segments covers the SMs about twice, but not shorter than 512 tokens (4 KV tiles)."""
+    ctas_per_seg = max(1, (batch + 127) // 128) * num_q_heads
+    want = max(1, (2 * sm_count + ctas_per_seg - 1) // ctas_per_seg)
+    seg = (shared_prefix_len + want - 1) // want
+    seg = max(512, (seg + 127) // 128 * 128)
+    return seg
+
+
+def decode_attention_shared_prefix_fwd(q: torch.Tensor, k_buffer: torch.Tensor, v_buffer: torch.Tensor,
+                                       o: torch.Tensor, req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+                                       seq_lens: torch.Tensor, shared_prefix_len: int, seg_len: int,
+                                       workspace: torch.Tensor, kv_chunk: int, max_splits: int, sm_scale: float,
+                                       logit_cap: float = 0.0, int8_out: bool = False):
+    """Decode attention for a batch whose requests all start with the same `shared_prefix_len` KV slots (request 0's
+    page-table row names them); same result as decode_attention_fwd.  See b200_decode_attn_shared_prefix."""
+    require_cuda(q, k_buffer, v_buffer, o, req_to_token, req_pool_indices, seq_lens, workspace)
+    lib = _cabi.load()
+    bs, hq, d = q.shape
+    hkv = k_buffer.shape[1]
+    assert q.stride(2) == 1 and q.stride(1) == d and o.stride(2) == 1 and o.stride(1) == d
+    assert k_buffer.stride(2) == 1 and k_buffer.stride(1) == d and v_buffer.stride() == k_buffer.stride()
+    assert k_buffer.dtype == q.dtype
+    assert req_to_token.dtype == torch.int32 and req_to_token.stride(1) == 1
+    assert req_pool_indices.dtype == seq_lens.dtype
+    assert req_pool_indices.is_contiguous() and seq_lens.is_contiguous()
+    oq = torch.empty((bs, hq * d), device=q.device, dtype=torch.int8) if int8_out else None
+    oscale = torch.empty((bs, 1), device=q.device, dtype=torch.float32) if int8_out else None
+    check(lib.b200_decode_attn_shared_prefix(
+        ptr(o), ptr(oq), ptr(oscale), ptr(q), ptr(k_buffer), ptr(v_buffer), ptr(req_to_token),
+        req_to_token.stride(0), ptr(req_pool_indices), ptr(seq_lens), _is64(seq_lens), bs, hq, hkv, d,
+        q.stride(0), o.stride(0), k_buffer.stride(0), float(sm_scale), float(logit_cap), int(shared_prefix_len),
+        int(seg_len), int(kv_chunk), int(max_splits), ptr(workspace),
+        workspace.numel() * workspace.element_size(), dtype_code(q.dtype), stream_ptr(q.device)),
+        "b200_decode_attn_shared_prefix")
+    return Int8Activation(oq, oscale, q.dtype) if int8_out else None
 
 
 # ---- extend attention -------------------------------------------------------------------------

@@ -31,6 +31,8 @@ class ForwardMetadata:
     kv_chunk: int = 0
     max_splits: int = 0
     workspace: Optional[torch.Tensor] = None
+    shared_prefix_len: int = 0  # > 0: shared-prefix (cascade) decode, see forward_decode
+    seg_len: int = 0
     # extend
     qo_indptr: Optional[torch.Tensor] = None
     prefix_lens: Optional[torch.Tensor] = None
@@ -84,6 +86,7 @@ class B200AttnBackend(AttentionBackend):
             raise NotImplementedError("B200AttnBackend: v_head_dim != head_dim (MLA-style) is out of scope")
         self.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         self.forced_chunk = int(os.environ.get("B200_DECODE_KV_CHUNK", "0"))
+        self.min_shared_prefix = int(os.environ.get("B200_MIN_SHARED_PREFIX", "1024"))
         self.forward_metadata: Optional[ForwardMetadata] = None
         self._workspace: Optional[torch.Tensor] = None
         self._graph_workspace: Optional[torch.Tensor] = None
@@ -114,6 +117,23 @@ class B200AttnBackend(AttentionBackend):
                 max_len = int(forward_batch.seq_lens_cpu.max()) if bs > 0 else 1
             else:
                 max_len = self.max_context_len  # no host sync: plan for the worst case
+            # Extension over the reference's ForwardBatch: a scheduler whose radix cache matched the same prefix for
+            # every request of the batch (BASELINE config 5) sets `shared_prefix_len`; the first that many entries of
+            # every req_to_token row are then the same physical slots.  Worth the extra launch from ~1k tokens on.
+            shared = int(getattr(forward_batch, "shared_prefix_len", 0) or 0)
+            if shared and forward_batch.seq_lens_cpu is not None and bs > 0:
+                shared = min(shared, int(forward_batch.seq_lens_cpu.min()) - 1)  # every request keeps >= 1 own token
+            kv_dtype = forward_batch.token_to_kv_pool.dtype
+            if shared >= self.min_shared_prefix and bs >= 2 and kv_dtype in (torch.bfloat16, torch.float16):
+                shared = shared // 128 * 128  # whole KV tiles for the prefix pass; the remainder stays per-request
+                chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, max(max_len - shared, 1),
+                                                   self.sm_count, self.forced_chunk)
+                seg = kernels.plan_shared_prefix_segments(shared, bs, self.num_head, self.sm_count)
+                n_seg = (shared + seg - 1) // seg
+                self.forward_metadata = ForwardMetadata(
+                    kv_chunk=chunk, max_splits=splits, shared_prefix_len=shared, seg_len=seg,
+                    workspace=self._decode_workspace(bs, n_seg + splits))
+                return
             chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, max_len, self.sm_count,
                                                self.forced_chunk)
             self.forward_metadata = ForwardMetadata(kv_chunk=chunk, max_splits=splits,
@@ -194,6 +214,15 @@ class B200AttnBackend(AttentionBackend):
             self._save_kv(layer, forward_batch, k, v)
         md = self.forward_metadata
         pool = forward_batch.token_to_kv_pool
+        if md.shared_prefix_len > 0:
+            act = kernels.decode_attention_shared_prefix_fwd(
+                q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
+                pool.get_key_buffer(layer.layer_id), pool.get_value_buffer(layer.layer_id),
+                o.view(-1, layer.tp_q_head_num, layer.v_head_dim),
+                forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
+                forward_batch.seq_lens, md.shared_prefix_len, md.seg_len, md.workspace, md.kv_chunk, md.max_splits,
+                layer.scaling, layer.logit_cap or 0.0, int8_out=int8_out)
+            return act if int8_out else o
         act = kernels.decode_attention_fwd(
             q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
             pool.get_key_buffer(layer.layer_id), pool.get_value_buffer(layer.layer_id),

@@ -81,3 +81,7 @@ class ForwardBatch:
 
     spec_info: Any = None
     encoder_lens: Optional[torch.Tensor] = None
+
+    # Extension (not a reference field): number of leading tokens whose KV slots are identical for EVERY request of a
+    # decode batch (a radix-cache hit on a common prefix).  B200AttnBackend then runs the shared-prefix decode.
+    shared_prefix_len: int = 0

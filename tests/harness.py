@@ -34,14 +34,15 @@ def build_runner(device, req_to_token, num_slots, page_size, hq, hkv, d, dtype, 
     return runner, backend
 
 
-def decode_batch(runner, backend, req_pool_indices, seq_lens, out_cache_loc, with_cpu_lens=True):
+def decode_batch(runner, backend, req_pool_indices, seq_lens, out_cache_loc, with_cpu_lens=True,
+                 shared_prefix_len=0):
     dev = runner.device
     fb = ForwardBatch(forward_mode=ForwardMode.DECODE, batch_size=len(seq_lens), input_ids=None,
                       req_pool_indices=req_pool_indices.to(dev), seq_lens=seq_lens.to(dev),
                       out_cache_loc=out_cache_loc.to(dev), seq_lens_sum=int(seq_lens.sum()),
                       seq_lens_cpu=seq_lens.cpu() if with_cpu_lens else None,
                       req_to_token_pool=runner.req_to_token_pool, token_to_kv_pool=runner.token_to_kv_pool,
-                      attn_backend=backend)
+                      attn_backend=backend, shared_prefix_len=shared_prefix_len)
     backend.init_forward_metadata(fb)
     return fb
 

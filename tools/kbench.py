@@ -68,7 +68,7 @@ def bench_decode(args):
     dev = torch.device("cuda")
     bs, ctx, hq, hkv, d, page = args.bs, args.ctx, args.hq, args.hkv, args.d, args.page
     lens = [ctx] * bs if not args.ragged else torch.randint(ctx // 2, ctx + 1, (bs,), generator=torch.Generator().manual_seed(0)).tolist()
-    pb = synth.make_paged_batch(lens, page, seed=1)
+    pb = synth.make_paged_batch(lens, page, seed=1, shared_prefix=args.shared)
     k, v = synth.randn_kv_device(pb.num_slots, page, hkv, d, torch.bfloat16, dev)
     if args.fp8kv:
         k, v = k.to(torch.float8_e4m3fn), v.to(torch.float8_e4m3fn)
@@ -82,6 +82,19 @@ def bench_decode(args):
         ch, splits = plan_decode_splits(bs, hkv, hq // hkv, max(lens), 148, chunk)
         ws = torch.empty(max(kernels.decode_attn_workspace_bytes(bs, hq, d, splits), 16), dtype=torch.uint8, device=dev)
         fn = lambda: kernels.decode_attention_fwd(q, k, v, o, r2t, rpi, sl, ws, ch, splits, d ** -0.5)
+        if args.shared:  # shared-prefix (cascade) decode next to the plain kernel on the same batch
+            uch, usp = plan_decode_splits(bs, hkv, hq // hkv, max(lens) - args.shared, 148, chunk)
+            seg = kernels.plan_shared_prefix_segments(args.shared, bs, hq)
+            nseg = (args.shared + seg - 1) // seg
+            ws2 = torch.empty(kernels.decode_attn_workspace_bytes(bs, hq, d, nseg + usp), dtype=torch.uint8, device=dev)
+            fn2 = lambda: kernels.decode_attention_shared_prefix_fwd(q, k, v, o, r2t, rpi, sl, args.shared, seg, ws2,
+                                                                     uch, usp, d ** -0.5)
+            med2, best2 = timeit(fn2)
+            unique = (args.shared + sum(n - args.shared for n in lens)) * 2 * hkv * d * k.element_size()
+            print(json.dumps(dict(kernel="decode_attn_shared_prefix", bs=bs, ctx=ctx, shared=args.shared, seg_len=seg,
+                                  segments=nseg, chunk=uch, splits=usp, ms_med=round(med2, 4), ms_best=round(best2, 4),
+                                  unique_gbs=round(unique / med2 / 1e6, 1), logical_gbs=round(kv_bytes / med2 / 1e6, 1),
+                                  prefix_tflops=round(4.0 * hq * d * bs * args.shared / med2 / 1e9, 1))), flush=True)
         med, best = timeit(fn)
         print(json.dumps(dict(kernel="decode_attn_fp8kv" if args.fp8kv else "decode_attn", bs=bs, ctx=ctx, chunk=ch, splits=splits, ms_med=round(med, 4),
                               ms_best=round(best, 4), gbs_med=round(kv_bytes / med / 1e6, 1),
@@ -196,6 +209,7 @@ if __name__ == "__main__":
     ap.add_argument("--m", type=int, default=0)
     ap.add_argument("--ragged", action="store_true")
     ap.add_argument("--fp8kv", action="store_true", help="decode: FP8 (e4m3) KV cache")
+    ap.add_argument("--shared", type=int, default=0, help="decode: every request shares this many leading tokens")
     ap.add_argument("--cluster", action="store_true", help="gemm_int8: cluster split-K kernel instead of stream-K")
     args = ap.parse_args()
     {"decode": bench_decode, "gemm_int8": bench_gemm_int8, "awq": bench_awq, "peak": bench_peak, "extend": bench_extend}[args.what](args)
