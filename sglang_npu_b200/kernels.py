@@ -168,13 +168,14 @@ def decode_attention_fwd(q: torch.Tensor, k_buffer: torch.Tensor, v_buffer: torc
 
 
 def plan_shared_prefix_segments(shared_prefix_len: int, batch: int, num_q_heads: int, sm_count: int = 148) -> int:
-    """Segment length (multiple of 128) for the prefix pass of the shared-prefix decode: enough segments that
-    ceil(batch/128) * Hq * segments covers the SMs about twice, but not shorter than 512 tokens (4 KV tiles)."""
+    """Segment length (multiple of 128) for the prefix pass of the shared-prefix decode.  The pass runs one CTA per SM
+    (512 TMEM columns), ceil(batch/128) * Hq CTAs per segment: take as many segments as fit in ONE wave (cfg 5 per GPU:
+    16 CTAs x 9 segments = 144 of 148 SMs; 19 segments = 2.05 waves measured 0.140 ms vs 0.1xx), at least 512 tokens
+    each."""
     ctas_per_seg = max(1, (batch + 127) // 128) * num_q_heads
-    want = max(1, (2 * sm_count + ctas_per_seg - 1) // ctas_per_seg)
-    seg = (shared_prefix_len + want - 1) // want
-    seg = max(512, (seg + 127) // 128 * 128)
-    return seg
+    n_seg = max(1, sm_count // ctas_per_seg)
+    seg = (shared_prefix_len + n_seg - 1) // n_seg
+    return max(512, (seg + 127) // 128 * 128)
 
 
 def decode_attention_shared_prefix_fwd(q: torch.Tensor, k_buffer: torch.Tensor, v_buffer: torch.Tensor,

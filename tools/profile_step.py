@@ -35,7 +35,7 @@ torch.cuda.synchronize()
 torch.cuda.nvtx.range_push("steps")
 for _ in range(a.steps):
     logits = runner.forward_decode(ids, rpi, sl, out_loc)
-    ids = logits.argmax(-1)
+    ids = kernels.argmax(logits)
 torch.cuda.synchronize()
 torch.cuda.nvtx.range_pop()
 print("ok", ids[:4].tolist())
