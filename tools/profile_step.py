@@ -8,7 +8,7 @@ import sys
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from sglang_npu_b200 import synth  # noqa: E402
+from sglang_npu_b200 import kernels, synth  # noqa: E402
 from sglang_npu_b200.srt.layers.quantization.w8a8_int8 import B200W8A8Int8Config  # noqa: E402
 from sglang_npu_b200.srt.model_executor.layer_stack import CONFIGS  # noqa: E402
 from sglang_npu_b200.srt.model_executor.model_runner import HotPathRunner  # noqa: E402
