@@ -80,6 +80,17 @@ int b200_set_kv_buffer_fp8(void* k_cache, void* v_cache, const void* k, const vo
                            int64_t k_token_stride, int64_t v_token_stride, int64_t k_cache_token_stride,
                            int64_t v_cache_token_stride, float k_scale, float v_scale, int src_dtype, void* stream);
 
+/* FP8 KV cache, prefill side: up-cast the cached prefix of every request of an extend batch into a compact 16-bit
+ * staging pool: k_out[offsets[b] + pos, :] = T(e4m3(k_cache[req_to_token[req_pool_indices[b], pos], :]) * k_scale) for
+ * pos < prefix_lens[b] (same for v).  b200_extend_attn then reads the prefix from the staging pool (page table
+ * row b = offsets[b] + 0..prefix) and the new tokens from k_new / v_new — what the reference's Triton extend kernel
+ * does with an fp8 k_buffer and bf16 k_extend (triton_ops/extend_attention.py:302-440).  Exact for scale 1. */
+int b200_fp8_kv_gather_dequant(void* k_out, void* v_out, const void* k_cache, const void* v_cache,
+                               const int32_t* req_to_token, int64_t req_to_token_stride, const void* req_pool_indices,
+                               int index_is_int64, const int32_t* prefix_lens, const int32_t* offsets, int batch,
+                               int max_prefix_len, int64_t row_elems, int64_t cache_token_stride, float k_scale,
+                               float v_scale, int out_dtype, void* stream);
+
 /* ---- decode attention -----------------------------------------------------------------
  * Replaces decode_attention_fwd (python/sglang/srt/layers/attention/triton_ops/
  * decode_attention.py:677-728; stage1 :241-401, stage2 :492-552) and the oracle's

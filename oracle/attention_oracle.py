@@ -56,6 +56,23 @@ def decode_attention_fp8kv(q: torch.Tensor, k_cache_u8: torch.Tensor, v_cache_u8
                             compute_dtype=compute_dtype).to(q.dtype)
 
 
+def extend_attention_fp8kv(q: torch.Tensor, k_new: torch.Tensor, v_new: torch.Tensor, k_cache_u8: torch.Tensor,
+                           v_cache_u8: torch.Tensor, req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
+                           seq_lens: torch.Tensor, extend_prefix_lens: torch.Tensor, extend_seq_lens: torch.Tensor,
+                           out_cache_loc: torch.Tensor, scaling: float, k_scale: Optional[float] = None,
+                           v_scale: Optional[float] = None, causal: bool = True) -> torch.Tensor:
+    """Extend over an fp8_e4m3 cache the way the reference's Triton extend kernel sees it
+    (triton_ops/extend_attention.py:302-440): prefix keys/values are the cache's e4m3 values up-cast (times the scale),
+    the new tokens are the un-quantised activations (k_extend / v_extend).  Evaluated with the torch_native extend
+    formula in fp32 on a temporary float cache holding exactly those values."""
+    kf = k_cache_u8.view(torch.float8_e4m3fn).to(torch.float32) * (1.0 if k_scale is None else float(k_scale))
+    vf = v_cache_u8.view(torch.float8_e4m3fn).to(torch.float32) * (1.0 if v_scale is None else float(v_scale))
+    kf[out_cache_loc] = k_new.to(torch.float32)
+    vf[out_cache_loc] = v_new.to(torch.float32)
+    return extend_attention(q, kf, vf, req_to_token, req_pool_indices, seq_lens, extend_prefix_lens, extend_seq_lens,
+                            scaling, causal=causal, compute_dtype=torch.float32).to(q.dtype)
+
+
 def _sdpa(q, k, v, scaling, causal, enable_gqa):
     # q [H, Lq, D], k/v [Hkv, Lk, D] — torch_native_backend.py:97-107 / :164-174
     return F.scaled_dot_product_attention(q.unsqueeze(0), k.unsqueeze(0), v.unsqueeze(0),

@@ -43,6 +43,8 @@ _SIGNATURES = {
                            c_int64, c_int64, c_int, _P],
     "b200_set_kv_buffer_fp8": [_P, _P, _P, _P, _P, c_int, c_int64, c_int64, c_int64, c_int64, c_int64,
                                c_int64, c_int64, c_float, c_float, c_int, _P],
+    "b200_fp8_kv_gather_dequant": [_P, _P, _P, _P, _P, c_int64, _P, c_int, _P, _P, c_int, c_int, c_int64, c_int64,
+                                   c_float, c_float, c_int, _P],
     "b200_decode_attn_workspace_bytes": [c_int, c_int, c_int, c_int, POINTER(c_size_t)],
     "b200_decode_attn": [_P, _P, _P, _P, _P, c_int64, _P, _P, c_int, c_int, c_int, c_int, c_int,
                          c_int64, c_int64, c_int64, c_float, c_float, c_int, c_int, _P, c_size_t,

@@ -102,6 +102,60 @@ __global__ void __launch_bounds__(256) kv_write_fp8_kernel(const KvWriteArgs a, 
   }
 }
 
+// FP8 KV cache, prefill side: up-cast the cached prefix of every request of an extend batch into a compact bf16/f16
+// staging pool, prefix token `pos` of request b -> row offsets[b] + pos, so that the tcgen05 extend kernel (which wants
+// 16-bit K-major tiles) reads the prefix from there and the new tokens from the step's activations.  Prefill is
+// tensor-bound: the staging traffic (prefix_tokens * Hkv * D * (1 + 2 + 2) B per layer, 31 MB for a 6k prefix of
+// Llama-8B) is ~5 us of HBM time next to ~1 ms of attention math.  Each thread turns one 16-byte fp8 chunk into two
+// 16-byte stores; x * scale is rounded once to T (scale = 1: exact).
+struct KvGatherArgs {
+  uint8_t* out[2];
+  const uint8_t* cache[2];
+  const int32_t* req_to_token;
+  int64_t req_to_token_stride;
+  const void* req_pool_indices;
+  int index_is_int64;
+  const int32_t* prefix_lens;
+  const int32_t* offsets;
+  int64_t row_elems;        // Hkv * D
+  int64_t cache_stride;     // bytes (= elements) per token row of the fp8 cache
+  float scale[2];
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) kv_gather_dequant_fp8_kernel(const KvGatherArgs a) {
+  pdl_trigger();
+  pdl_wait();
+  const int b = blockIdx.z;
+  const int which = blockIdx.y;
+  const int prefix = a.prefix_lens[b];
+  const int64_t chunks_per_row = a.row_elems >> 4;
+  const int64_t total = (int64_t)prefix * chunks_per_row;
+  const int64_t req = load_index(a.req_pool_indices, b, a.index_is_int64);
+  const int32_t* row = a.req_to_token + req * a.req_to_token_stride;
+  const uint8_t* cache = a.cache[which];
+  uint8_t* out = a.out[which] + (int64_t)a.offsets[b] * a.row_elems * 2;
+  const float scale = a.scale[which];
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t pos = i / chunks_per_row;
+    const int64_t c = i - pos * chunks_per_row;
+    const int4 v = ld_nc_v4(cache + (int64_t)__ldg(row + pos) * a.cache_stride + (c << 4));
+    const uint32_t w[4] = {(uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w};
+    uint32_t r[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      uint32_t h2;
+      const uint16_t pair = (uint16_t)(w[j >> 1] >> ((j & 1) * 16));
+      asm("cvt.rn.f16x2.e4m3x2 %0, %1;\n" : "=r"(h2) : "h"(pair));
+      const float2 f = __half22float2(*reinterpret_cast<__half2*>(&h2));
+      r[j] = pack2<T>(f.x * scale, f.y * scale);
+    }
+    int4* dst = reinterpret_cast<int4*>(out + (pos * a.row_elems + (c << 4)) * 2);
+    dst[0] = make_int4((int)r[0], (int)r[1], (int)r[2], (int)r[3]);
+    dst[1] = make_int4((int)r[4], (int)r[5], (int)r[6], (int)r[7]);
+  }
+}
+
 }  // namespace b200
 
 B200_API int b200_set_kv_buffer(void* k_cache, void* v_cache, const void* k, const void* v,
@@ -186,4 +240,39 @@ B200_API int b200_set_kv_buffer_fp8(void* k_cache, void* v_cache, const void* k,
   if (src_dtype == B200_F16)
     return launch_k(kv_write_fp8_kernel<__half>, grid, dim3(256), 0, (cudaStream_t)stream, 1, true, a, k_scale, v_scale);
   return fail(B200_ERR_UNSUPPORTED, "set_kv_buffer_fp8: source dtype %d not supported (bf16/f16)", src_dtype);
+}
+
+B200_API int b200_fp8_kv_gather_dequant(void* k_out, void* v_out, const void* k_cache, const void* v_cache,
+                                        const int32_t* req_to_token, int64_t req_to_token_stride,
+                                        const void* req_pool_indices, int index_is_int64, const int32_t* prefix_lens,
+                                        const int32_t* offsets, int batch, int max_prefix_len, int64_t row_elems,
+                                        int64_t cache_token_stride, float k_scale, float v_scale, int out_dtype,
+                                        void* stream) {
+  using namespace b200;
+  B200_REQUIRE(batch >= 0 && max_prefix_len >= 0, "fp8_kv_gather_dequant: negative sizes");
+  if (batch == 0 || max_prefix_len == 0) return B200_OK;
+  B200_REQUIRE(k_out && v_out && k_cache && v_cache && req_to_token && req_pool_indices && prefix_lens && offsets,
+               "fp8_kv_gather_dequant: null pointer");
+  B200_REQUIRE(row_elems % 16 == 0 && cache_token_stride % 16 == 0, "fp8_kv_gather_dequant: rows must be 16-byte multiples");
+  B200_REQUIRE(((uintptr_t)k_out | (uintptr_t)v_out | (uintptr_t)k_cache | (uintptr_t)v_cache) % 16 == 0,
+               "fp8_kv_gather_dequant: pointers must be 16-byte aligned");
+  B200_REQUIRE(batch <= 65535, "fp8_kv_gather_dequant: batch %d exceeds grid.z", batch);
+  B200_REQUIRE(k_scale > 0.f && v_scale > 0.f, "fp8_kv_gather_dequant: scales must be positive");
+  KvGatherArgs a;
+  a.out[0] = (uint8_t*)k_out; a.out[1] = (uint8_t*)v_out;
+  a.cache[0] = (const uint8_t*)k_cache; a.cache[1] = (const uint8_t*)v_cache;
+  a.req_to_token = req_to_token; a.req_to_token_stride = req_to_token_stride;
+  a.req_pool_indices = req_pool_indices; a.index_is_int64 = index_is_int64;
+  a.prefix_lens = prefix_lens; a.offsets = offsets;
+  a.row_elems = row_elems; a.cache_stride = cache_token_stride;
+  a.scale[0] = k_scale; a.scale[1] = v_scale;
+  int64_t blocks = ceil_div((int64_t)max_prefix_len * (row_elems >> 4), 256);
+  const int64_t cap = ceil_div((int64_t)sm_count() * 8, batch);
+  if (blocks > cap) blocks = cap;
+  const dim3 grid((unsigned)blocks, 2, (unsigned)batch);
+  if (out_dtype == B200_BF16)
+    return launch_k(kv_gather_dequant_fp8_kernel<__nv_bfloat16>, grid, dim3(256), 0, (cudaStream_t)stream, 1, true, a);
+  if (out_dtype == B200_F16)
+    return launch_k(kv_gather_dequant_fp8_kernel<__half>, grid, dim3(256), 0, (cudaStream_t)stream, 1, true, a);
+  return fail(B200_ERR_UNSUPPORTED, "fp8_kv_gather_dequant: output dtype %d not supported (bf16/f16)", out_dtype);
 }

@@ -108,6 +108,28 @@ def set_kv_buffer(k_cache: torch.Tensor, v_cache: torch.Tensor, loc: torch.Tenso
         "b200_set_kv_buffer")
 
 
+def fp8_kv_gather_dequant(k_out: torch.Tensor, v_out: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                          req_to_token: torch.Tensor, req_pool_indices: torch.Tensor, prefix_lens: torch.Tensor,
+                          offsets: torch.Tensor, max_prefix_len: int, k_scale: Optional[float] = None,
+                          v_scale: Optional[float] = None) -> None:
+    """k_out[offsets[b] + pos] = up-cast of the fp8 cache row of prefix token `pos` of request b (and v likewise);
+    k_out/v_out [rows, Hkv, D] bf16/f16.  Staging for extend attention over an FP8 KV cache."""
+    require_cuda(k_out, v_out, k_cache, v_cache, req_to_token, req_pool_indices, prefix_lens, offsets)
+    lib = _cabi.load()
+    assert k_cache.dtype in _FP8_STORE and v_cache.dtype in _FP8_STORE and k_out.dtype == v_out.dtype
+    assert prefix_lens.dtype == torch.int32 and offsets.dtype == torch.int32 and req_to_token.dtype == torch.int32
+    assert k_out.is_contiguous() and v_out.is_contiguous()
+    kc = k_cache.view(k_cache.shape[0], -1)
+    vc = v_cache.view(v_cache.shape[0], -1)
+    assert kc.stride(1) == 1 and kc.stride() == vc.stride() and kc.shape[1] == k_out[0].numel()
+    check(lib.b200_fp8_kv_gather_dequant(
+        ptr(k_out), ptr(v_out), ptr(kc), ptr(vc), ptr(req_to_token), req_to_token.stride(0), ptr(req_pool_indices),
+        _is64(req_pool_indices), ptr(prefix_lens), ptr(offsets), req_pool_indices.numel(), int(max_prefix_len),
+        kc.shape[1], kc.stride(0), 1.0 if k_scale is None else float(k_scale),
+        1.0 if v_scale is None else float(v_scale), dtype_code(k_out.dtype), stream_ptr(k_out.device)),
+        "b200_fp8_kv_gather_dequant")
+
+
 # ---- decode attention -------------------------------------------------------------------------
 def decode_attn_workspace_bytes(batch: int, num_q_heads: int, head_dim: int, max_splits: int) -> int:
     lib = _cabi.load()

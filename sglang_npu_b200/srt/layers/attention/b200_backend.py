@@ -37,6 +37,11 @@ class ForwardMetadata:
     qo_indptr: Optional[torch.Tensor] = None
     prefix_lens: Optional[torch.Tensor] = None
     max_extend_len: int = 0
+    # extend over an FP8 KV cache: staging of the up-cast prefix (kernels.fp8_kv_gather_dequant)
+    stage_offsets: Optional[torch.Tensor] = None   # [bs] int32, row of prefix token 0 of request b
+    stage_table: Optional[torch.Tensor] = None     # [bs, max_prefix] int32 page table into the staging pool
+    stage_rows: int = 0
+    max_prefix_len: int = 0
 
 
 def _round_up(x: int, m: int) -> int:
@@ -91,6 +96,8 @@ class B200AttnBackend(AttentionBackend):
         self._workspace: Optional[torch.Tensor] = None
         self._graph_workspace: Optional[torch.Tensor] = None
         self._graph_max_bs = 0
+        self._stage_kv = None
+        self._stage_rows_idx = None
         max_bs = model_runner.req_to_token_pool.size
         self.qo_indptr = torch.zeros((max_bs + 1,), dtype=torch.int32, device=self.device)
 
@@ -146,10 +153,22 @@ class B200AttnBackend(AttentionBackend):
                 max_extend = max(forward_batch.extend_seq_lens_cpu) if bs > 0 else 0
             else:
                 max_extend = int(ext.max().item())  # same host sync as triton_backend.py:325
-            self.forward_metadata = ForwardMetadata(
-                qo_indptr=qo_indptr,
-                prefix_lens=forward_batch.extend_prefix_lens.to(torch.int32),
-                max_extend_len=int(max_extend))
+            prefix_lens = forward_batch.extend_prefix_lens.to(torch.int32)
+            self.forward_metadata = ForwardMetadata(qo_indptr=qo_indptr, prefix_lens=prefix_lens,
+                                                    max_extend_len=int(max_extend))
+            if forward_batch.token_to_kv_pool.dtype == torch.float8_e4m3fn:
+                md = self.forward_metadata
+                if forward_batch.extend_prefix_lens_cpu is not None:
+                    md.max_prefix_len = max(forward_batch.extend_prefix_lens_cpu) if bs > 0 else 0
+                    md.stage_rows = sum(forward_batch.extend_prefix_lens_cpu)
+                else:
+                    md.max_prefix_len = int(prefix_lens.max().item())
+                    md.stage_rows = int(prefix_lens.sum().item())
+                incl = torch.cumsum(prefix_lens, dim=0, dtype=torch.int32)
+                md.stage_offsets = incl - prefix_lens
+                md.stage_table = (md.stage_offsets.view(-1, 1)
+                                  + torch.arange(max(md.max_prefix_len, 1), dtype=torch.int32, device=self.device).view(1, -1))
+                self._stage_rows_idx = torch.arange(bs, dtype=forward_batch.req_pool_indices.dtype, device=self.device)
 
     # ---- CUDA graphs (base_attn_backend.py:22-55; cuda_graph_runner.py:283-288, :642, :773) --------
     def init_cuda_graph_state(self, max_bs: int, max_num_tokens: int):
@@ -241,10 +260,33 @@ class B200AttnBackend(AttentionBackend):
             self._save_kv(layer, forward_batch, k, v)
         md = self.forward_metadata
         pool = forward_batch.token_to_kv_pool
-        if pool.dtype != q.dtype:
-            raise NotImplementedError("B200AttnBackend: extend attention over an FP8 KV cache is not built yet "
-                                      "(decode and the KV write are)")
         causal = not (layer.is_cross_attention or getattr(layer.attn_type, "value", "") == "encoder_only")
+        if pool.dtype != q.dtype:
+            # FP8 KV cache: the cached prefix is up-cast into a 16-bit staging pool (one launch, prefill is
+            # tensor-bound so its traffic is noise) and the new tokens are read from the activations un-quantised —
+            # what the Triton extend kernel does with an fp8 k_buffer and bf16 k_extend (extend_attention.py:302-440)
+            if pool.dtype != torch.float8_e4m3fn:
+                raise NotImplementedError(f"B200AttnBackend: KV cache dtype {pool.dtype} is not supported")
+            rows = max(md.stage_rows, 1)
+            if self._stage_kv is None or self._stage_kv[0].shape[0] < rows or self._stage_kv[0].dtype != q.dtype:
+                shape = (rows, layer.tp_k_head_num, layer.qk_head_dim)
+                self._stage_kv = (torch.empty(shape, dtype=q.dtype, device=q.device),
+                                  torch.empty(shape, dtype=q.dtype, device=q.device))
+            sk, sv = self._stage_kv
+            ks, vs = self._kv_scales(layer)
+            kernels.fp8_kv_gather_dequant(sk, sv, pool.get_key_buffer(layer.layer_id),
+                                          pool.get_value_buffer(layer.layer_id),
+                                          forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
+                                          md.prefix_lens, md.stage_offsets, md.max_prefix_len, ks, vs)
+            kernels.extend_attention_fwd(
+                q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
+                k.view(-1, layer.tp_k_head_num, layer.qk_head_dim), v.view(-1, layer.tp_v_head_num, layer.v_head_dim),
+                o.view(-1, layer.tp_q_head_num, layer.v_head_dim), sk, sv, md.stage_table, self._stage_rows_idx,
+                md.qo_indptr, md.prefix_lens, md.max_extend_len, layer.scaling, layer.logit_cap or 0.0, causal)
+            if int8_out:
+                xq, xs = kernels.per_token_quant_int8(o)
+                return kernels.Int8Activation(xq, xs, o.dtype)
+            return o
         kernels.extend_attention_fwd(
             q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
             None if save_kv_cache else k.view(-1, layer.tp_k_head_num, layer.qk_head_dim),

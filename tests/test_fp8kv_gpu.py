@@ -141,15 +141,85 @@ def _decode_case_fast(device, lens, seed, forced_chunk):
     return o, ref, backend
 
 
-def test_fp8kv_extend_is_refused(cuda_device):
-    pb = synth.make_paged_batch([20, 9], 16, seed=2)
-    runner, backend = harness.build_runner(cuda_device, pb.req_to_token, pb.num_slots, 16, 8, 2, 128, FP8)
-    prefix = torch.zeros(2, dtype=torch.int32)
-    loc = torch.cat([pb.req_to_token[pb.req_pool_indices[i], : int(pb.seq_lens[i])] for i in range(2)]).long()
-    fb = harness.extend_batch(runner, backend, pb.req_pool_indices, pb.seq_lens, prefix, loc)
-    layer = harness.make_layer(8, 2, 128)
-    T = int(pb.seq_lens.sum())
-    x = torch.randn((T, 8 * 128), device=cuda_device, dtype=torch.bfloat16)
-    kv = torch.randn((T, 2 * 128), device=cuda_device, dtype=torch.bfloat16)
-    with pytest.raises(NotImplementedError):
-        layer(x, kv, kv.clone(), fb)
+def _extend_case(device, lens, prefix, hq, hkv, d, page, dtype, scales=(None, None), seed=5, causal=True):
+    pb = synth.make_paged_batch(lens, page, seed=seed)
+    runner, backend = harness.build_runner(device, pb.req_to_token, pb.num_slots, page, hq, hkv, d, FP8)
+    k0, v0 = synth.randn_kv(pb.num_slots, page, hkv, d, dtype, seed=seed + 10)
+    k0 = k0.to(FP8).view(torch.uint8)
+    v0 = v0.to(FP8).view(torch.uint8)
+    pool = runner.token_to_kv_pool
+    pool.k_buffer[0].copy_(k0)
+    pool.v_buffer[0].copy_(v0)
+    bs = len(lens)
+    prefix_t = torch.tensor(prefix, dtype=torch.int32)
+    ext = pb.seq_lens.to(torch.int32) - prefix_t
+    T = int(ext.sum())
+    g = torch.Generator().manual_seed(seed + 20)
+    q = torch.randn((T, hq * d), generator=g).to(dtype)
+    k = torch.randn((T, hkv * d), generator=g).to(dtype)
+    v = torch.randn((T, hkv * d), generator=g).to(dtype)
+    out_loc = torch.cat([pb.req_to_token[pb.req_pool_indices[i], prefix[i]: lens[i]] for i in range(bs)]).long()
+    fb = harness.extend_batch(runner, backend, pb.req_pool_indices, pb.seq_lens, prefix_t, out_loc)
+    layer = harness.make_layer(hq, hkv, d)
+    layer.k_scale_float, layer.v_scale_float = scales
+    if scales[0] is not None:
+        layer.k_scale, layer.v_scale = torch.tensor(scales[0]), torch.tensor(scales[1])
+    if not causal:
+        from sglang_npu_b200.srt.layers.radix_attention import AttentionType
+        layer.attn_type = AttentionType.ENCODER_ONLY
+    o = layer(q.to(device), k.to(device), v.to(device), fb)
+    torch.cuda.synchronize()
+    ref = ao.extend_attention_fp8kv(q.view(T, hq, d), k.view(T, hkv, d), v.view(T, hkv, d), k0, v0, pb.req_to_token,
+                                    pb.req_pool_indices, pb.seq_lens, prefix_t, ext, out_loc, d ** -0.5, *scales,
+                                    causal=causal)
+    # the step's KV rows were written quantised, bit-exact
+    ao.set_kv_buffer_fp8(k0, v0, out_loc, k.view(T, hkv, d), v.view(T, hkv, d), *scales)
+    assert torch.equal(pool.k_buffer[0].cpu(), k0) and torch.equal(pool.v_buffer[0].cpu(), v0)
+    return o.view(T, hq, d), ref
+
+
+@pytest.mark.parametrize("hq,hkv,d", [(32, 8, 128), (14, 2, 64)])
+@pytest.mark.parametrize("page", [1, 16])
+def test_fp8kv_extend_prefix_and_ragged(cuda_device, hq, hkv, d, page):
+    lens = [70, 33, 16, 300, 129, 1]
+    prefix = [32, 0, 15, 128, 1, 0]
+    o, ref = _extend_case(cuda_device, lens, prefix, hq, hkv, d, page, torch.bfloat16)
+    assert_close_path(o, ref, f"fp8kv extend hq{hq} hkv{hkv} d{d} page{page}")
+
+
+def test_fp8kv_extend_scales_f16_and_no_prefix(cuda_device):
+    o, ref = _extend_case(cuda_device, [200, 257], [64, 129], 16, 4, 128, 16, torch.float16, scales=(0.5, 2.0))
+    assert_close_path(o, ref, "fp8kv extend f16 scales")
+    o, ref = _extend_case(cuda_device, [40, 9], [0, 0], 8, 2, 128, 16, torch.bfloat16)
+    assert_close_path(o, ref, "fp8kv extend, no cached prefix at all")
+
+
+def test_fp8kv_chunked_prefill_cfg3_like(cuda_device):
+    """A 2048-token chunk on top of a 1536-token cached prefix (config 3's chunked prefill with prefix reuse, scaled
+    down), fp8 cache."""
+    o, ref = _extend_case(cuda_device, [3584], [1536], 32, 8, 128, 16, torch.bfloat16)
+    assert_close_path(o, ref, "fp8kv chunked prefill")
+
+
+def test_fp8_kv_gather_dequant_exact(cuda_device):
+    g = torch.Generator().manual_seed(3)
+    hkv, d, page = 2, 128, 16
+    lens = [50, 17, 0, 33]
+    pb = synth.make_paged_batch([max(n, 1) for n in lens], page, seed=9)
+    cache = torch.randint(0, 256, (pb.num_slots + page, hkv, d), generator=g, dtype=torch.int32).to(torch.uint8)
+    cache[(cache & 0x7F) == 0x7F] = 0x3C  # no NaN codes
+    vcache = cache.flip(0).contiguous()
+    prefix = torch.tensor(lens, dtype=torch.int32)
+    offs = (torch.cumsum(prefix, 0) - prefix).to(torch.int32)
+    dev = cuda_device
+    ko = torch.zeros((int(prefix.sum()), hkv, d), dtype=torch.bfloat16, device=dev)
+    vo = torch.zeros_like(ko)
+    kernels.fp8_kv_gather_dequant(ko, vo, cache.to(dev), vcache.to(dev), pb.req_to_token.to(dev),
+                                  pb.req_pool_indices.to(dev), prefix.to(dev), offs.to(dev), max(lens))
+    torch.cuda.synchronize()
+    for b, n in enumerate(lens):
+        toks = pb.req_to_token[pb.req_pool_indices[b], :n].long()
+        exp_k = cache[toks].view(FP8).to(torch.bfloat16)
+        exp_v = vcache[toks].view(FP8).to(torch.bfloat16)
+        assert torch.equal(ko[int(offs[b]): int(offs[b]) + n].cpu().view(torch.int16), exp_k.view(torch.int16))
+        assert torch.equal(vo[int(offs[b]): int(offs[b]) + n].cpu().view(torch.int16), exp_v.view(torch.int16))
