@@ -181,6 +181,8 @@ def main():
     ap.add_argument("--ctx", type=int, default=CTX)
     ap.add_argument("--layers", type=int, default=0, help="debug only: fewer layers (marks the line invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kv-dtype", default="bf16", choices=["bf16", "fp8"],
+                    help="fp8 = --kv-cache-dtype fp8_e4m3 variant (NOT the BASELINE config: the line is marked as a variant)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -228,11 +230,19 @@ def main():
 
     pb = synth.make_paged_batch([ctx] * bs, PAGE, seed=1, width=ctx + 4, max_reqs=bs + 3)
     runner = HotPathRunner(cfg, B200W8A8Int8Config(), max_reqs=pb.req_to_token.shape[0], max_total_tokens=pb.num_slots,
-                           page_size=PAGE, context_len=ctx, device=dev, num_layers=n_layers, tp_size=tp, seed=1234)
+                           page_size=PAGE, context_len=ctx, device=dev, num_layers=n_layers, tp_size=tp, seed=1234,
+                           kv_cache_dtype=torch.float8_e4m3fn if args.kv_dtype == "fp8" else None)
+    kv_bytes = 1 if args.kv_dtype == "fp8" else 2
     runner.req_to_token_pool.req_to_token.copy_(pb.req_to_token)
     g = torch.Generator(device=dev).manual_seed(7)
     for buf in runner.token_to_kv_pool.k_buffer + runner.token_to_kv_pool.v_buffer:
-        buf.normal_(generator=g)  # KV of the 4k-token contexts, N(0,1) like the reference tests
+        if kv_bytes == 2:
+            buf.normal_(generator=g)  # KV of the 4k-token contexts, N(0,1) like the reference tests
+        else:  # the same distribution, stored as e4m3 bytes (a random finite e4m3 pattern per N(0,1) draw)
+            for lo in range(0, buf.shape[0], 1 << 16):
+                part = buf[lo: lo + (1 << 16)]
+                part.copy_(torch.empty(part.shape, dtype=torch.bfloat16, device=dev).normal_(generator=g)
+                           .to(torch.float8_e4m3fn).view(torch.uint8))
 
     out_loc = torch.stack([pb.req_to_token[pb.req_pool_indices[i], ctx - 1] for i in range(bs)]).long()
     host = HostDecodeBatch(input_ids=torch.randint(0, cfg.vocab_size, (bs,), dtype=torch.int64).pin_memory(),
@@ -312,16 +322,16 @@ def main():
     hkv_local = cfg.get_num_kv_heads(tp)
     hq_local = cfg.num_attention_heads // tp
     # algorithmic bytes per launch: KV + q/o + page ids
-    attn_bytes = bs * ctx * 2 * hkv_local * cfg.head_dim * 2 + bs * hq_local * cfg.head_dim * 2 * 2 + 4 * bs * (ctx // PAGE)
+    attn_bytes = bs * ctx * 2 * hkv_local * cfg.head_dim * kv_bytes + bs * hq_local * cfg.head_dim * 2 * 2 + 4 * bs * (ctx // PAGE)
     peaks, peak_kind = measured_peaks()
     achieved = attn_bytes / (attn_ms * 1e-3) / 1e9
-    roofline = {"kernel": "decode_attn_kernel (+ decode_merge_quant_kernel: LSE merge fused with the int8 quant of the o_proj input), one launch pair per layer", "bound": "hbm",
+    roofline = {"kernel": ("decode_attn_fp8kv_kernel" if kv_bytes == 1 else "decode_attn_kernel") + " (+ decode_merge_quant_kernel: LSE merge fused with the int8 quant of the o_proj input), one launch pair per layer", "bound": "hbm",
                 "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                 "peak_kind": f"{peak_kind} (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)",
                 "frac_of_nominal_8TBs": achieved / 8000.0, "bytes_per_launch": attn_bytes, "ms_per_launch": attn_ms,
                 "share_of_step": attn_ms * n_layers / ms_per_step, "traffic": None}
     traffic_file = os.path.join(ROOT, "profiles", "decode_attn_traffic.json")
-    if os.path.exists(traffic_file):
+    if os.path.exists(traffic_file) and kv_bytes == 2:
         try:
             roofline["traffic"] = json.load(open(traffic_file)).get("dram_bytes_per_launch")
         except Exception:
@@ -343,7 +353,7 @@ def main():
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8",
             "data": "synthetic",
             "config": {"workload": f"{MODEL} W8A8-int8 decode step ({n_layers} layers + bf16 lm_head + greedy argmax), "
-                                   f"global batch {bs}, ctx {ctx}, page_size {PAGE}, bf16 KV",
+                                   f"global batch {bs}, ctx {ctx}, page_size {PAGE}, {'bf16' if kv_bytes == 2 else 'fp8_e4m3'} KV",
                        "global_batch": bs, "seq_len": ctx, "parallelism": f"tp{tp}", "cuda_graph": True,
                        "tp_exchange": ("none (tp1)" if tp == 1 else
                                        "fused reduce+rmsnorm+int8-quant over NVLink peer memory (csrc/tp_comm.cu)"
@@ -355,6 +365,8 @@ def main():
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline}
     if args.layers:
         line["invalid"] = f"debug run with {n_layers} layers"
+    if kv_bytes == 1:
+        line["variant"] = "fp8_e4m3 KV cache: not the BASELINE configuration (bf16 KV), reported next to it"
     print(json.dumps(line), flush=True)
     _finish(world, dev)
     return 0

@@ -78,7 +78,22 @@ class OracleStack:
             q, k, v = qkv.split([L["q_size"], L["kv_size"], L["kv_size"]], dim=-1)
             q, k = qo.rope_neox(positions, q, k, d, self.cos_sin)
             T = q.shape[0]
-            ao.set_kv_buffer(k_caches[i], v_caches[i], out_cache_loc, k.reshape(T, hkv, d), v.reshape(T, hkv, d))
+            kn, vn = k.reshape(T, hkv, d), v.reshape(T, hkv, d)
+            if k_caches[i].dtype == torch.uint8:  # --kv-cache-dtype fp8_e4m3 (stored as uint8, memory_pool.py:114-118)
+                if prefix_lens is None:
+                    ao.set_kv_buffer_fp8(k_caches[i], v_caches[i], out_cache_loc, kn, vn)
+                    o = ao.decode_attention_fp8kv(q.reshape(T, hq, d), k_caches[i], v_caches[i], req_to_token,
+                                                  req_pool_indices, seq_lens, d ** -0.5)
+                else:
+                    ext = (seq_lens - prefix_lens).to(torch.int32)
+                    o = ao.extend_attention_fp8kv(q.reshape(T, hq, d), kn, vn, k_caches[i], v_caches[i], req_to_token,
+                                                  req_pool_indices, seq_lens, prefix_lens, ext, out_cache_loc, d ** -0.5)
+                    ao.set_kv_buffer_fp8(k_caches[i], v_caches[i], out_cache_loc, kn, vn)
+                h = L["o"](o.reshape(T, hq * d))
+                h, residual = qo.rmsnorm(h, L["ln2"], eps, residual)
+                h = L["down"](qo.silu_and_mul(L["gate_up"](h)))
+                continue
+            ao.set_kv_buffer(k_caches[i], v_caches[i], out_cache_loc, kn, vn)
             if prefix_lens is None:
                 o = ao.decode_attention(q.reshape(T, hq, d), k_caches[i], v_caches[i], req_to_token, req_pool_indices,
                                         seq_lens, d ** -0.5)

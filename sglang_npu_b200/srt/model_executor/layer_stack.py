@@ -125,10 +125,12 @@ class DecoderLayer(nn.Module):
         qkv, _ = self.qkv_proj(act)
         q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
         pool = forward_batch.token_to_kv_pool
+        cast_kv = pool.dtype != q.dtype  # FP8 KV cache: rope only here, the backend's cast-and-scatter writes the cache
         kernels.rope_neox_set_kv(positions, q, k, v, self.cfg.head_dim, cos_sin_cache,
-                                 pool.get_key_buffer(self.attn.layer_id), pool.get_value_buffer(self.attn.layer_id),
-                                 forward_batch.out_cache_loc)
-        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=False, int8_out=self.fuse_attn_quant)
+                                 None if cast_kv else pool.get_key_buffer(self.attn.layer_id),
+                                 None if cast_kv else pool.get_value_buffer(self.attn.layer_id),
+                                 None if cast_kv else forward_batch.out_cache_loc)
+        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=cast_kv, int8_out=self.fuse_attn_quant)
         hidden_states, _ = self.o_proj(attn_out)
         act = kernels.rmsnorm_quant_int8(hidden_states, self.post_attention_layernorm, eps, residual=residual)
         gate_up, _ = self.gate_up_proj(act)
@@ -152,10 +154,12 @@ class DecoderLayer(nn.Module):
         qkv, _ = self.qkv_proj(act)
         q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
         pool = forward_batch.token_to_kv_pool
+        cast_kv = pool.dtype != q.dtype  # FP8 KV cache: rope only here, the backend's cast-and-scatter writes the cache
         kernels.rope_neox_set_kv(positions, q, k, v, self.cfg.head_dim, cos_sin_cache,
-                                 pool.get_key_buffer(self.attn.layer_id), pool.get_value_buffer(self.attn.layer_id),
-                                 forward_batch.out_cache_loc)
-        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=False, int8_out=self.fuse_attn_quant)
+                                 None if cast_kv else pool.get_key_buffer(self.attn.layer_id),
+                                 None if cast_kv else pool.get_value_buffer(self.attn.layer_id),
+                                 None if cast_kv else forward_batch.out_cache_loc)
+        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=cast_kv, int8_out=self.fuse_attn_quant)
         self.o_proj(attn_out, can_fuse_mlp_allreduce=True, out=comm.partial(M))
         act = comm.reduce_rmsnorm_quant_int8(M, self.post_attention_layernorm, eps, residual)
         gate_up, _ = self.gate_up_proj(act)

@@ -36,7 +36,8 @@ class HostDecodeBatch:
 class HotPathRunner:
     def __init__(self, cfg: StackConfig, quant_config, *, max_reqs: int, max_total_tokens: int, page_size: int,
                  context_len: Optional[int] = None, dtype=torch.bfloat16, device="cuda", num_layers: Optional[int] = None,
-                 tp_size: int = 1, seed: int = 1234, weight_gain: float = 1.0, tp_comm_tokens: int = 0):
+                 tp_size: int = 1, seed: int = 1234, weight_gain: float = 1.0, tp_comm_tokens: int = 0,
+                 kv_cache_dtype: Optional[torch.dtype] = None):
         self.device = torch.device(device)
         self.model_config = cfg
         if context_len is not None:
@@ -49,7 +50,8 @@ class HotPathRunner:
         self.gpu_id = self.device.index or 0
         n_layers = num_layers if num_layers is not None else cfg.num_layers
         self.req_to_token_pool = ReqToTokenPool(max_reqs, cfg.context_len + 4, str(self.device))
-        self.token_to_kv_pool = MHATokenToKVPool(max_total_tokens, page_size, dtype, cfg.get_num_kv_heads(tp_size),
+        self.token_to_kv_pool = MHATokenToKVPool(max_total_tokens, page_size, kv_cache_dtype or dtype,  # --kv-cache-dtype
+                                                 cfg.get_num_kv_heads(tp_size),
                                                  cfg.head_dim, n_layers, str(self.device))
         with torch.device(self.device):
             self.model = LayerStack(cfg, quant_config, dtype, n_layers)

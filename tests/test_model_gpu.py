@@ -29,7 +29,7 @@ MARGIN = 0.15
 
 
 def _run(dev, model, quant, bs, max_prompt, page, layers, steps, vocab=4096, dtype=torch.bfloat16, gain=1.0, graph=False,
-         cos_tol=0.999, match_tol=0.85):
+         cos_tol=0.999, match_tol=0.85, kv_dtype=None):
     cfg = copy.deepcopy(CONFIGS[model])
     cfg.vocab_size = vocab
     g = torch.Generator().manual_seed(11)
@@ -38,7 +38,7 @@ def _run(dev, model, quant, bs, max_prompt, page, layers, steps, vocab=4096, dty
     qc = get_quantization_config(quant).from_config(QCFG)
     runner = HotPathRunner(cfg, qc, max_reqs=pb.req_to_token.shape[0], max_total_tokens=pb.num_slots, page_size=page,
                            context_len=pb.req_to_token.shape[1] - 4, device=dev, num_layers=layers, weight_gain=gain,
-                           dtype=dtype)
+                           dtype=dtype, kv_cache_dtype=kv_dtype)
     runner.req_to_token_pool.req_to_token.copy_(pb.req_to_token)
     oracle = OracleStack(runner.model)
     kc = [torch.zeros_like(b, device="cpu") for b in runner.token_to_kv_pool.k_buffer]
@@ -121,3 +121,10 @@ def test_llama8b_shape_block_fp8(cuda_device):
 def test_qwen32b_shape_awq_fp16(cuda_device):
     """configs[3] arithmetic: AWQ-int4 linears (fp16 activations, awq.py:111-112)."""
     _run(cuda_device, "qwen2.5-32b", "b200_awq", bs=3, max_prompt=100, page=16, layers=1, steps=2, dtype=torch.float16)
+
+
+def test_llama8b_shape_int8_fp8_kv_cache(cuda_device):
+    """configs[1] layer shapes with --kv-cache-dtype fp8_e4m3: prefill writes the cache through the cast-and-scatter
+    kernel, decode reads it with the fp8-KV kernel; the oracle stack quantises / up-casts the same way."""
+    _run(cuda_device, "llama-3.1-8b", "b200_w8a8_int8", bs=5, max_prompt=200, page=16, layers=2, steps=3,
+         kv_dtype=torch.float8_e4m3fn)
