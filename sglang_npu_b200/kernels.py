@@ -7,6 +7,7 @@ are enqueued on the current CUDA stream.  No fallbacks: non-CUDA tensors raise.
 """
 from __future__ import annotations
 
+import os
 from ctypes import byref, c_size_t
 from typing import Optional, Tuple
 
@@ -189,13 +190,17 @@ def decode_attention_fwd(q: torch.Tensor, k_buffer: torch.Tensor, v_buffer: torc
         stream_ptr(q.device)), "b200_decode_attn")
 
 
-def plan_shared_prefix_segments(shared_prefix_len: int, batch: int, num_q_heads: int, sm_count: int = 148) -> int:
+def plan_shared_prefix_segments(shared_prefix_len: int, batch: int, num_q_heads: int, sm_count: int = 148,
+                                sm_fraction: Optional[float] = None) -> int:
     """Segment length (multiple of 128) for the prefix pass of the shared-prefix decode.  The pass runs one CTA per SM
-    (512 TMEM columns), ceil(batch/128) * Hq CTAs per segment: take as many segments as fit in ONE wave (cfg 5 per GPU:
-    16 CTAs x 9 segments = 144 of 148 SMs; 19 segments = 2.05 waves measured 0.140 ms vs 0.1xx), at least 512 tokens
-    each."""
+    (512 TMEM columns, 198 KB smem), ceil(batch/128) * Hq CTAs per segment: take as many segments as fit in ONE wave
+    (2.05 waves measured 0.140 ms vs 0.122 ms for one), at least 512 tokens each.  Leaving SMs free for the forked
+    per-request pass does not pay (cfg 5 per GPU: sm_fraction 0.5 / 0.65 / 0.8 / 1.0 -> 0.160 / 0.131 / 0.125 /
+    0.117 ms): that pass needs every SM to saturate HBM, so the two passes' SM-time simply adds up."""
+    if sm_fraction is None:
+        sm_fraction = float(os.environ.get("B200_PREFIX_SM_FRACTION", "1.0"))
     ctas_per_seg = max(1, (batch + 127) // 128) * num_q_heads
-    n_seg = max(1, sm_count // ctas_per_seg)
+    n_seg = max(1, int(sm_count * sm_fraction) // ctas_per_seg)
     seg = (shared_prefix_len + n_seg - 1) // n_seg
     return max(512, (seg + 127) // 128 * 128)
 
