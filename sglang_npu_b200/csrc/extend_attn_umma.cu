@@ -18,7 +18,9 @@
 // Warp roles: 0-1 K gather, 2-3 V gather (16-byte cp.async of 256-byte cache rows through req_to_token — any
 // page_size — placed directly in the UMMA swizzle; independent 2-stage rings, page ids fetched a tile ahead),
 // 4 = MMA issuer (one lane) + TMEM allocator, 8-11 softmax / correction / epilogue (TMEM lane quarter = warp % 4).
-// mbarriers: k_full/k_empty and v_full/v_empty per stage, s_full per S buffer, p_full, pv_done.
+// mbarriers: k_full/k_empty and v_full/v_empty per stage, s_full per S buffer, p_full, pv_done per P buffer.
+// P is double-buffered in shared memory: the softmax of tile j+1 runs while P V of tile j is still on the tensor core;
+// only the (rare) lazy rescale of O waits for the previous P V.
 #include <type_traits>
 
 #include "extend_attn.cuh"
@@ -44,7 +46,8 @@ struct UxSmem {
   static constexpr int kK = kTile;                           // 2 stages
   static constexpr int kV = kK + 2 * kTile;                  // 2 stages
   static constexpr int kP = kV + 2 * kTile;                  // [128 x 128] bf16
-  static constexpr int kBar = kP + kUxBM * kUxBN * 2;
+  static constexpr int kPTile = kUxBM * kUxBN * 2;            // two P buffers: softmax of tile j+1 does not wait for P V of tile j
+  static constexpr int kBar = kP + 2 * kPTile;
   static constexpr int kBytes = kBar + 16 * 8 + 1024;
 };
 
@@ -149,12 +152,14 @@ __device__ __forceinline__ float ux_row_max(uint32_t t_s, const SoftmaxCtx& cx, 
 // p = exp2(t - m) for the row's 128 scores, written as T into the K-major SWIZZLE_128B P tile; returns sum(p)
 template <typename T, int MODE>
 __device__ __forceinline__ void ux_exp_store32(const uint32_t (&r)[32], const SoftmaxCtx& cx, int pos0, float m_use, float& sum,
-                                               uint32_t sp, int row, int c0, int half_bytes) {
+                                               float& amax, uint32_t sp, int row, int c0, int half_bytes) {
   float p[32];
 #pragma unroll
   for (int i = 0; i < 32; ++i) {
     const float v = ux_score<MODE>(__uint_as_float(r[i]), cx, pos0 + i);
-    p[i] = fast_exp2(MODE == 2 ? v - m_use : fmaf(v, cx.scale_log2, -m_use));  // masked: fma(-inf, +scale, .) = -inf -> 0
+    const float arg = MODE == 2 ? v - m_use : fmaf(v, cx.scale_log2, -m_use);  // masked: fma(-inf, +scale, .) = -inf -> 0
+    amax = fmaxf(amax, arg);
+    p[i] = fast_exp2(arg);
     sum += p[i];
   }
 #pragma unroll
@@ -166,20 +171,23 @@ __device__ __forceinline__ void ux_exp_store32(const uint32_t (&r)[32], const So
   }
 }
 
+// amax: largest exponent argument (score - m_use) seen in the row — how far the tile's max lies above the max the
+// row is normalised to (the optimistic single-pass softmax below needs it to decide whether to redo the tile)
 template <typename T, int MODE>
 __device__ __forceinline__ float ux_row_exp(uint32_t t_s, const SoftmaxCtx& cx, int kv0, float m_use, uint32_t sp, int row,
-                                            int half_bytes) {
+                                            int half_bytes, float& amax) {
   float sum = 0.f;
+  amax = -INFINITY;
   uint32_t ra[32], rb[32];
   tmem_ld32(t_s, ra);
   tmem_ld_wait();
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
     tmem_ld32(t_s + 64 * h + 32, rb);
-    ux_exp_store32<T, MODE>(ra, cx, kv0 + 64 * h, m_use, sum, sp, row, 64 * h, half_bytes);
+    ux_exp_store32<T, MODE>(ra, cx, kv0 + 64 * h, m_use, sum, amax, sp, row, 64 * h, half_bytes);
     tmem_ld_wait();
     if (h == 0) tmem_ld32(t_s + 64, ra);
-    ux_exp_store32<T, MODE>(rb, cx, kv0 + 64 * h + 32, m_use, sum, sp, row, 64 * h + 32, half_bytes);
+    ux_exp_store32<T, MODE>(rb, cx, kv0 + 64 * h + 32, m_use, sum, amax, sp, row, 64 * h + 32, half_bytes);
     if (h == 0) tmem_ld_wait();
   }
   return sum;
@@ -200,8 +208,10 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
   auto v_full = [&](int s) { return bar + (4 + s) * 8; };
   auto v_empty = [&](int s) { return bar + (6 + s) * 8; };
   auto s_full = [&](int b) { return bar + (8 + b) * 8; };
-  const uint32_t p_full = bar + 10 * 8;
-  const uint32_t pv_done = bar + 11 * 8;
+  // per P buffer, like pv_done: with one barrier the softmax warps (up to two tiles ahead of the MMA warp when a V tile is
+  // late) could complete two phases before the MMA warp tests the first — the parity wait would then never succeed
+  auto p_full = [&](int j) { return bar + ((j & 1) ? 13 : 10) * 8; };
+  auto pv_done = [&](int j) { return bar + (11 + (j & 1)) * 8; };  // P V of tile j commits to barrier j & 1, phase j >> 1
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -237,8 +247,10 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
         mbar_init(v_empty(s), 1);
         mbar_init(s_full(s), 1);
       }
-      mbar_init(p_full, 4);  // one arrive per softmax warp
-      mbar_init(pv_done, 1);
+      mbar_init(p_full(0), 4);  // one arrive per softmax warp
+      mbar_init(p_full(1), 4);
+      mbar_init(pv_done(0), 1);
+      mbar_init(pv_done(1), 1);
       fence_barrier_init();
     }
     __syncwarp();
@@ -325,9 +337,9 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
       for (int j = 0; j < n_tiles; ++j) {
         if (j + 1 < n_tiles) issue_qk(j + 1);
         mbar_wait(v_full(j & 1), (j >> 1) & 1);
-        mbar_wait(p_full, j & 1);
+        mbar_wait(p_full(j), (j >> 1) & 1);
         tc_fence_after();
-        const uint32_t sp = base + L::kP;
+        const uint32_t sp = base + L::kP + (j & 1) * L::kPTile;
         const uint32_t sv = base + L::kV + (j & 1) * L::kTile;
 #pragma unroll
         for (int kk = 0; kk < kUxBN / 16; ++kk) {
@@ -337,7 +349,7 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
           umma<kKindF16>(tmem_base + kOCol, da, db, idesc_o, (j | kk) != 0);
         }
         tc_commit(v_empty(j & 1));
-        tc_commit(pv_done);
+        tc_commit(pv_done(j));
       }
     }
   } else if (warp >= 8) {
@@ -347,7 +359,6 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
     const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
     const int lim = a.causal ? prefix + m0 + row : kv_total - 1;  // last KV position this row may see
     const bool use_cap = a.logit_cap > 0.f;
-    const uint32_t sp = base + L::kP;
     float m_used = -INFINITY;  // the max (log2 domain) the row's P and O are currently normalised to
     float l_run = 0.f;
     const SoftmaxCtx cx{a.scale_log2, use_cap ? a.sm_scale / a.logit_cap : 0.f, a.logit_cap * kLog2eExt, lim, kv_end};
@@ -361,18 +372,34 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
       mbar_wait(s_full(j & 1), (j >> 1) & 1);
       tc_fence_after();
 
-      float mx;
-      if (mode == 0) mx = ux_row_max<0>(t_s, cx, kv0);
-      else if (mode == 1) mx = ux_row_max<1>(t_s, cx, kv0);
-      else mx = ux_row_max<2>(t_s, cx, kv0);
-      const float m_new = fmaxf(m_used, mx);
-      if (j == 0) {
-        m_used = m_new;
-      } else {
-        mbar_wait(pv_done, (j - 1) & 1);  // P V of the previous tile has retired: P smem and O are ours again
+      const uint32_t sp = base + L::kP + (j & 1) * L::kPTile;
+      if (j >= 2) {  // P V of tile j-2 has retired: this P buffer is free again
+        mbar_wait(pv_done(j), ((j >> 1) - 1) & 1);
         tc_fence_after();
-        const bool grow = m_new > m_used + kRescaleThreshold;
+      }
+      auto row_exp = [&](float m_use, float& amax) {
+        if (mode == 0) return ux_row_exp<T, 0>(t_s, cx, kv0, m_use, sp, row, L::kHalf, amax);
+        if (mode == 1) return ux_row_exp<T, 1>(t_s, cx, kv0, m_use, sp, row, L::kHalf, amax);
+        return ux_row_exp<T, 2>(t_s, cx, kv0, m_use, sp, row, L::kHalf, amax);
+      };
+      float l_add, amax;
+      if (j == 0) {  // first tile: exact row max, then the exponentials
+        if (mode == 0) m_used = ux_row_max<0>(t_s, cx, kv0);
+        else if (mode == 1) m_used = ux_row_max<1>(t_s, cx, kv0);
+        else m_used = ux_row_max<2>(t_s, cx, kv0);
+        l_add = row_exp((m_used == -INFINITY) ? 0.f : m_used, amax);
+      } else {
+        // Optimistic single pass: exponentials against the max the row is already normalised to, tracking how far the
+        // tile's own max lies above it.  Within the lazy-rescale threshold (2^8 of headroom in P and l) the stale max
+        // simply stays in use — no separate max pass over S, half the TMEM reads.  Beyond it (rare after the first
+        // tiles) the warp rescales O and l in TMEM and redoes the tile against the new max.
+        const float m_use = (m_used == -INFINITY) ? 0.f : m_used;
+        l_add = row_exp(m_use, amax);
+        const bool grow = (m_used == -INFINITY) ? (amax > -INFINITY) : (amax > kRescaleThreshold);
         if (__any_sync(0xffffffffu, grow)) {
+          mbar_wait(pv_done(j - 1), ((j - 1) >> 1) & 1);  // O is touched only here: P V of the previous tile must be done
+          tc_fence_after();
+          const float m_new = m_use + amax;
           const float alpha = grow ? fast_exp2(m_used - m_new) : 1.f;
           if (grow) m_used = m_new;
           l_run *= alpha;
@@ -386,20 +413,18 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
             tmem_st16(t_lane + kOCol + c0, r);
           }
           tmem_st_wait();
+          l_add = row_exp((m_used == -INFINITY) ? 0.f : m_used, amax);  // rows that did not grow rewrite the same P
         }
       }
-      const float m_use = (m_used == -INFINITY) ? 0.f : m_used;
-      if (mode == 0) l_run += ux_row_exp<T, 0>(t_s, cx, kv0, m_use, sp, row, L::kHalf);
-      else if (mode == 1) l_run += ux_row_exp<T, 1>(t_s, cx, kv0, m_use, sp, row, L::kHalf);
-      else l_run += ux_row_exp<T, 2>(t_s, cx, kv0, m_use, sp, row, L::kHalf);
+      l_run += l_add;
       fence_proxy_async();  // P (generic-proxy stores) -> visible to the MMA's async-proxy reads
       tc_fence_before();    // orders this thread's TMEM loads / stores before the MMA warp's next tcgen05 ops
       __syncwarp();
-      if (lane == 0) mbar_arrive(p_full);
+      if (lane == 0) mbar_arrive(p_full(j));
     }
 
     // ---- epilogue: O / l -> global ----------------------------------------------------------------------------------
-    mbar_wait(pv_done, (n_tiles - 1) & 1);
+    mbar_wait(pv_done(n_tiles - 1), ((n_tiles - 1) >> 1) & 1);
     tc_fence_after();
     const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
     const bool row_ok = m0 + row < ext_len;
