@@ -57,3 +57,46 @@ def test_rmsnorm_silu_rope_shapes():
     x = torch.randn(3, 16)
     assert qo.rmsnorm(x, torch.ones(16), 1e-6).shape == x.shape
     assert qo.silu_and_mul(x).shape == (3, 8)
+
+
+# ---- FP8 KV cache / shared-prefix host logic (no GPU) ------------------------------------------------------------------
+def test_fp8_kv_oracles_are_consistent_with_the_16bit_oracles():
+    """decode / extend over an e4m3 cache == the 16-bit oracles run on the up-cast cache (the up-cast is exact)."""
+    import torch
+    from oracle import attention_oracle as ao
+    from sglang_npu_b200 import synth
+
+    hq, hkv, d, page = 8, 2, 64, 16
+    lens = [40, 17, 33]
+    pb = synth.make_paged_batch(lens, page, seed=4)
+    k0, v0 = synth.randn_kv(pb.num_slots, page, hkv, d, torch.bfloat16, seed=5)
+    k8 = k0.to(torch.float8_e4m3fn).view(torch.uint8)
+    v8 = v0.to(torch.float8_e4m3fn).view(torch.uint8)
+    g = torch.Generator().manual_seed(6)
+    q = torch.randn((3, hq, d), generator=g).to(torch.bfloat16)
+    o8 = ao.decode_attention_fp8kv(q, k8, v8, pb.req_to_token, pb.req_pool_indices, pb.seq_lens, d ** -0.5, 0.5, 2.0)
+    kf = k8.view(torch.float8_e4m3fn).float() * 0.5
+    vf = v8.view(torch.float8_e4m3fn).float() * 2.0
+    o16 = ao.decode_attention(q, kf, vf, pb.req_to_token, pb.req_pool_indices, pb.seq_lens, d ** -0.5,
+                              compute_dtype=torch.float32)
+    assert torch.equal(o8.view(torch.int16), o16.to(torch.bfloat16).view(torch.int16))
+    # the KV write of values that are already e4m3-representable is the identity
+    loc = torch.arange(page, page + 5)
+    kc, vc = torch.zeros_like(k8), torch.zeros_like(v8)
+    rows_k = k8[loc].view(torch.float8_e4m3fn).to(torch.bfloat16)
+    ao.set_kv_buffer_fp8(kc, vc, loc, rows_k, rows_k)
+    assert torch.equal(kc[loc], k8[loc])
+
+
+def test_shared_prefix_segment_planner():
+    from sglang_npu_b200.kernels import plan_shared_prefix_segments as plan
+
+    # cfg 5 per GPU: 2 row blocks x 8 heads = 16 CTAs per segment -> 9 segments fill one wave of 148 SMs
+    seg = plan(30720, 256, 8, sm_count=148, sm_fraction=1.0)
+    assert seg % 128 == 0 and (30720 + seg - 1) // seg == 9
+    # never shorter than 512 tokens, always a multiple of 128, one segment when a segment already fills the chip
+    assert plan(1024, 4, 2, sm_count=148, sm_fraction=1.0) == 512
+    assert plan(5000, 64, 32 * 8, sm_count=148, sm_fraction=1.0) == 5120
+    for p in (129, 1000, 4097, 30720):
+        s = plan(p, 64, 32, sm_count=148, sm_fraction=1.0)
+        assert s % 128 == 0 and s >= 512
