@@ -49,23 +49,27 @@ def _round_up(x: int, m: int) -> int:
 
 
 def plan_decode_splits(batch: int, num_kv_heads: int, group: int, max_len: int, sm_count: int,
-                       forced_chunk: int = 0):
+                       forced_chunk: int = 0, max_chunk: int = 2048):
     """Pick (kv_chunk, max_splits) for the split-KV decode kernel.
 
-    One CTA handles one (request, KV head, <=16 q heads, chunk); aim for ~8 waves of the
+    One CTA handles one (request, KV head, <=16 q heads, chunk); aim for ~3 waves of the
     2 x SM-count resident CTAs, with chunks of 256..2048 tokens (multiples of 16), and
     make the chunks of the longest request even.  Pure host arithmetic (graph-safe).
+    Fewer, longer chunks win once the chip is covered a few times: every chunk costs a pipeline
+    fill and an fp32 partial that stage 2 reads back (cfg 2, measured: 5 chunks of 832 tokens
+    8.374 ms/step, 2 chunks of 2048 8.311 ms/step; kernel alone 0.1915 vs 0.1874 ms).
+    max_chunk: the FP8-KV kernel (3 CTAs/SM, half the bytes per token) is best at 1024 (0.118 vs 0.128 ms at 2048).
     """
     max_len = max(int(max_len), 1)
     if forced_chunk > 0:
         chunk = _round_up(forced_chunk, 16)
     else:
         units = max(batch * num_kv_heads * ((group + 15) // 16), 1)
-        target = sm_count * _NUM_RESIDENT_CTAS_PER_SM * 8
+        target = sm_count * _NUM_RESIDENT_CTAS_PER_SM * 3
         chunk = _round_up(max(max_len * units // target, 1), 64)
-        chunk = min(max(chunk, 256), 2048)
+        chunk = min(max(chunk, 256), max_chunk)
         splits = (max_len + chunk - 1) // chunk
-        chunk = min(_round_up((max_len + splits - 1) // splits, 16), 2048)
+        chunk = min(_round_up((max_len + splits - 1) // splits, 16), max_chunk)
     chunk = max(16, min(chunk, 4096))
     return chunk, (max_len + chunk - 1) // chunk
 
@@ -92,6 +96,7 @@ class B200AttnBackend(AttentionBackend):
         self.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         self.forced_chunk = int(os.environ.get("B200_DECODE_KV_CHUNK", "0"))
         self.min_shared_prefix = int(os.environ.get("B200_MIN_SHARED_PREFIX", "1024"))
+        self._max_chunk = 1024 if model_runner.token_to_kv_pool.dtype == torch.float8_e4m3fn else 2048
         self.forward_metadata: Optional[ForwardMetadata] = None
         self._workspace: Optional[torch.Tensor] = None
         self._graph_workspace: Optional[torch.Tensor] = None
@@ -134,7 +139,7 @@ class B200AttnBackend(AttentionBackend):
             if shared >= self.min_shared_prefix and bs >= 2 and kv_dtype in (torch.bfloat16, torch.float16):
                 shared = shared // 128 * 128  # whole KV tiles for the prefix pass; the remainder stays per-request
                 chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, max(max_len - shared, 1),
-                                                   self.sm_count, self.forced_chunk)
+                                                   self.sm_count, self.forced_chunk, self._max_chunk)
                 seg = kernels.plan_shared_prefix_segments(shared, bs, self.num_head, self.sm_count)
                 n_seg = (shared + seg - 1) // seg
                 self.forward_metadata = ForwardMetadata(
@@ -142,7 +147,7 @@ class B200AttnBackend(AttentionBackend):
                     workspace=self._decode_workspace(bs, n_seg + splits))
                 return
             chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, max_len, self.sm_count,
-                                               self.forced_chunk)
+                                               self.forced_chunk, self._max_chunk)
             self.forward_metadata = ForwardMetadata(kv_chunk=chunk, max_splits=splits,
                                                     workspace=self._decode_workspace(bs, splits))
         else:
@@ -175,7 +180,7 @@ class B200AttnBackend(AttentionBackend):
         self._graph_max_bs = max_bs
         group = self.num_head // self.num_kv_head
         _, splits = plan_decode_splits(1, self.num_kv_head, group, self.max_context_len, self.sm_count,
-                                       self.forced_chunk)
+                                       self.forced_chunk, self._max_chunk)
         self._decode_workspace(max_bs, max(splits, 2), graph=True)
 
     def init_forward_metadata_capture_cuda_graph(self, bs: int, num_tokens: int, req_pool_indices, seq_lens,
@@ -184,7 +189,7 @@ class B200AttnBackend(AttentionBackend):
             raise NotImplementedError("B200AttnBackend: CUDA graphs are captured for DECODE only")
         group = self.num_head // self.num_kv_head
         chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, self.max_context_len, self.sm_count,
-                                           self.forced_chunk)
+                                           self.forced_chunk, self._max_chunk)
         self.forward_metadata = ForwardMetadata(kv_chunk=chunk, max_splits=splits,
                                                 workspace=self._decode_workspace(bs, splits, graph=True))
 
