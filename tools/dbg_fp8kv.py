@@ -7,8 +7,6 @@ from tests.util import golden_files, load_golden
 
 dev = torch.device("cuda")
 for ri, rec in enumerate(load_golden(golden_files("kvwrite_fp8")[0])):
-    for name, scale in (("k", rec["k_scale"]), ("v", rec["v_scale"])):
-        pass
     kc = torch.zeros_like(rec["k_cache_after"], device=dev)
     vc = torch.zeros_like(kc)
     kernels.set_kv_buffer(kc, vc, rec["loc"].to(dev), rec["k"].to(dev), rec["v"].to(dev), rec["k_scale"], rec["v_scale"])
