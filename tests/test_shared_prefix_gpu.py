@@ -93,3 +93,41 @@ def test_short_or_absent_prefix_takes_plain_path(cuda_device):
     out_loc = torch.zeros(2, dtype=torch.int64)
     harness.decode_batch(runner, backend, pb.req_pool_indices, pb.seq_lens, out_loc, shared_prefix_len=64)
     assert backend.forward_metadata.shared_prefix_len == 0  # below B200_MIN_SHARED_PREFIX
+
+
+def test_shared_prefix_decode_is_cuda_graph_capturable(cuda_device):
+    """The fork/join of the prefix pass onto the side stream is plain event record/wait: capture + replay must
+    reproduce the eager result bit for bit."""
+    dev = cuda_device
+    hq, hkv, d, page, shared = 8, 2, 128, 16, 512
+    lens = [600, 700, 513, 1025]
+    bs = len(lens)
+    pb = synth.make_paged_batch(lens, page, seed=7, shared_prefix=shared)
+    k, v = synth.randn_kv_device(pb.num_slots, page, hkv, d, torch.bfloat16, dev, seed=8)
+    q = torch.randn(bs, hq, d, device=dev).to(torch.bfloat16)
+    r2t, rpi, sl = pb.req_to_token.to(dev), pb.req_pool_indices.to(dev), pb.seq_lens.to(dev)
+    seg = kernels.plan_shared_prefix_segments(shared, bs, hq)
+    nseg = (shared + seg - 1) // seg
+    chunk, splits = 256, 3
+    ws = torch.empty(kernels.decode_attn_workspace_bytes(bs, hq, d, nseg + splits), dtype=torch.uint8, device=dev)
+    o_eager, o_graph = torch.empty_like(q), torch.empty_like(q)
+
+    def run(o):
+        kernels.decode_attention_shared_prefix_fwd(q, k, v, o, r2t, rpi, sl, shared, seg, ws, chunk, splits, d ** -0.5)
+
+    run(o_eager)
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(side):
+        run(o_graph)
+    torch.cuda.current_stream(dev).wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        run(o_graph)
+    o_graph.zero_()
+    for _ in range(3):
+        g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(o_graph.view(torch.int16), o_eager.view(torch.int16))
