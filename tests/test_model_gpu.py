@@ -128,3 +128,9 @@ def test_llama8b_shape_int8_fp8_kv_cache(cuda_device):
     kernel, decode reads it with the fp8-KV kernel; the oracle stack quantises / up-casts the same way."""
     _run(cuda_device, "llama-3.1-8b", "b200_w8a8_int8", bs=5, max_prompt=200, page=16, layers=2, steps=3,
          kv_dtype=torch.float8_e4m3fn)
+
+
+def test_llama8b_shape_int8_fp8_kv_cache_with_cuda_graph(cuda_device):
+    """Same, decode through the captured CUDA graph (the cast-and-scatter KV write and the fp8-KV decode inside it)."""
+    _run(cuda_device, "llama-3.1-8b", "b200_w8a8_int8", bs=4, max_prompt=120, page=16, layers=2, steps=3, graph=True,
+         kv_dtype=torch.float8_e4m3fn)
