@@ -100,3 +100,18 @@ def test_shared_prefix_segment_planner():
     for p in (129, 1000, 4097, 30720):
         s = plan(p, 64, 32, sm_count=148, sm_fraction=1.0)
         assert s % 128 == 0 and s >= 512
+
+
+def test_decode_split_planner_invariants():
+    from sglang_npu_b200.srt.layers.attention.b200_backend import plan_decode_splits as plan
+
+    for bs in (1, 7, 64, 256, 512):
+        for hkv, group in ((8, 4), (1, 8), (2, 7), (4, 20)):
+            for max_len in (1, 15, 300, 2048, 4096, 32768, 131072):
+                for cap in (2048, 1024):
+                    chunk, splits = plan(bs, hkv, group, max_len, 148, 0, cap)
+                    assert chunk % 16 == 0 and 16 <= chunk <= cap
+                    assert splits * chunk >= max_len and (splits - 1) * chunk < max_len
+    assert plan(64, 8, 4, 4096, 148) == (2048, 2)          # BASELINE config 2
+    assert plan(64, 8, 4, 4096, 148, 0, 1024) == (1024, 4)  # ... with an FP8 KV cache
+    assert plan(64, 8, 4, 4096, 148, forced_chunk=48) == (48, 86)
