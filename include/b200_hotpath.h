@@ -348,6 +348,8 @@ int b200_create_kv_indices(int32_t* kv_indices, const int32_t* req_to_token, int
  * ordered) when every rank's rows have landed locally.  flag_ptrs[r]: rank r's 2 * 8 * max_blocks uint32 flag
  * words; epoch: local max_blocks uint32; both zero-initialised once.  All ranks must issue the same sequence
  * of calls.  Arithmetic = b200_rmsnorm_quant_int8 applied to the all-reduced tensor, bit for bit.
+ * err_flag: one local zero-initialised uint32; a peer that does not reach a barrier within B200_TP_TIMEOUT_MS
+ * (default 20000) makes the kernel record the failure there and finish (no __trap): see b200_comm_check.
  */
 int b200_comm_malloc(void** dev_ptr, size_t bytes);
 int b200_comm_free(void* dev_ptr);
@@ -358,7 +360,11 @@ int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, void* con
                                       void* const* xscale_ptrs, void* const* y_ptrs, void* const* flag_ptrs,
                                       void* epoch, void* residual, const void* weight, int64_t M, int64_t H,
                                       float eps, int tp_size, int tp_rank, int max_blocks, int dtype,
-                                      void* stream);
+                                      void* err_flag, void* stream);
+/* Synchronises `stream`, then reports (B200_ERR_CUDA + message) a barrier timeout recorded in `err_flag` by an
+ * exchange kernel of this rank; B200_OK when every exchange so far met its peers.  The reference's analogue is the
+ * NCCL watchdog error surfaced on the next synchronising call. */
+int b200_comm_check(const void* err_flag, void* stream);
 
 #ifdef __cplusplus
 }

@@ -96,7 +96,8 @@ _SIGNATURES = {
     "b200_comm_ipc_open": [_P, POINTER(c_void_p)],
     "b200_comm_ipc_close": [_P],
     "b200_tp_reduce_rmsnorm_quant_int8": [_P, _P, _P, _P, _P, _P, _P, _P, c_int64, c_int64, c_float, c_int, c_int,
-                                          c_int, c_int, _P],
+                                          c_int, c_int, _P, _P],
+    "b200_comm_check": [_P, _P],
 }
 
 EXPORTED_SYMBOLS = sorted(list(_SIGNATURES) + ["b200_last_error"])

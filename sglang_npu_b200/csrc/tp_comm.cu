@@ -17,6 +17,7 @@
 //      (the all-gather half, at 1 byte per element instead of 2), then signal the peers and wait for theirs.
 // Per exchange a rank moves (tp-1)/tp * M * H * (2 + 1) bytes over NVLink instead of 2 * (tp-1)/tp * M * H * 2 for a
 // ring all-reduce of bf16, launches one kernel instead of three, and normalises M / tp rows instead of M.
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -38,6 +39,9 @@ struct TpArgs {
   int64_t M, H;
   int tp, rank, max_blocks;
   float eps;
+  uint32_t* err;                  // local: first barrier failure of this rank (0 = none), read by b200_comm_check
+  unsigned long long timeout_ns;  // how long a barrier waits for a peer before giving up (%globaltimer)
+  int relaxed_start;              // A/B switch: start barrier with relaxed flags (the round-1 protocol)
   unsigned long long* trace;  // diagnostics (b200_debug_set_trace) or null
   int trace_slots;
 };
@@ -69,13 +73,24 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
   return v;
 }
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
+  return t;
+}
+
 // Block-level barrier across ranks: thread t < tp publishes `e` into peer t's slot [phase][rank][b] and waits for
-// peer t's value in the local slot [phase][t][b].  A peer that never arrives traps after ~2 s instead of hanging.
-//   phase 0 (start): relaxed flags.  What it orders is "the peer's previous kernel (its GEMM) has completed": those
-//     writes went to the PEER's own memory and were made visible by that kernel's completion; we read them at their
-//     home through NVLink with L1-bypassing loads, so no system-scope fence (several microseconds) is needed.
-//   phase 1 (end): release / acquire.  ONE releasing thread per peer: the CTA barrier before it orders every
-//     thread's peer stores before the release (cumulativity), so the other 500 threads do not fence at all.
+// peer t's value in the local slot [phase][t][b].
+//   Both phases are a PTX release / acquire pair at system scope.  ONE releasing thread per peer: the CTA barrier
+//   before it orders every thread's earlier accesses before the release (cumulativity), so the other ~500 threads do
+//   not fence.  At the start barrier what is released is this rank's GEMM output (made visible to this thread by the
+//   kernel boundary / griddepcontrol.wait); the acquiring side then reads the peer rows with L1-bypassing loads.
+//   (`relaxed_start` keeps the round-1 protocol — relaxed start flags, relying on completed-kernel writes being visible
+//   at their home L2 — for A/B timing only: B200_TP_RELAXED_START=1.)
+//   A peer that does not arrive within `timeout_ns` (wall clock, %globaltimer; default 20 s — host skew, a lazy module
+//   load or a GC pause on a peer are legitimate reasons to be late) does NOT kill the context: the first failure is
+//   recorded in `err` (b200_comm_check reports it on the host), the wait is abandoned and the kernel completes with
+//   whatever data it has, so the process can tear down in an orderly way like it would after an NCCL timeout.
 __device__ __forceinline__ void rank_barrier(const TpArgs& a, int phase, int b, uint32_t e) {
   __syncthreads();
   if ((int)threadIdx.x < a.tp) {
@@ -83,13 +98,20 @@ __device__ __forceinline__ void rank_barrier(const TpArgs& a, int phase, int b, 
     const size_t slot = ((size_t)phase * kMaxTp) * a.max_blocks + b;
     uint32_t* theirs = a.flags[t] + slot + (size_t)a.rank * a.max_blocks;
     const uint32_t* mine = a.flags[a.rank] + slot + (size_t)t * a.max_blocks;
-    if (phase == 0) st_relaxed_sys(theirs, e);
+    const bool relaxed = phase == 0 && a.relaxed_start != 0;
+    if (relaxed) st_relaxed_sys(theirs, e);
     else st_release_sys(theirs, e);
-    long long spins = 0;
-    while ((phase == 0 ? ld_relaxed_sys(mine) : ld_acquire_sys(mine)) != e) {
-      if (++spins > (1ll << 28)) {
-        printf("b200 tp exchange: rank %d block %d phase %d never heard from rank %d (epoch %u)\n", a.rank, b, phase, t, e);
-        __trap();
+    unsigned long long t0 = 0;
+    uint32_t spins = 0;
+    while ((relaxed ? ld_relaxed_sys(mine) : ld_acquire_sys(mine)) != e) {
+      if ((++spins & 0x3ffu) == 0) {  // look at the clock every 1024 polls
+        const unsigned long long now = globaltimer_ns();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > a.timeout_ns) {
+          // code: 1 | phase << 1 | peer << 4 | block << 8  (first failure wins)
+          atomicCAS(a.err, 0u, 1u | ((uint32_t)phase << 1) | ((uint32_t)t << 4) | ((uint32_t)b << 8));
+          break;
+        }
       }
     }
   }
@@ -288,17 +310,29 @@ B200_API int b200_comm_ipc_close(void* peer_ptr) {
   return B200_OK;
 }
 
+B200_API int b200_comm_check(const void* err_flag, void* stream) {
+  // Synchronises `stream` and reports a barrier timeout recorded by an exchange kernel of this rank.
+  B200_REQUIRE(err_flag != nullptr, "comm_check: null pointer");
+  uint32_t code = 0;
+  B200_CUDA_OK(cudaMemcpyAsync(&code, err_flag, sizeof(code), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  B200_CUDA_OK(cudaStreamSynchronize((cudaStream_t)stream));
+  if (code != 0)
+    return fail(B200_ERR_CUDA, "tp exchange: %s barrier of block %u timed out waiting for rank %u (B200_TP_TIMEOUT_MS)",
+                ((code >> 1) & 1u) ? "end" : "start", code >> 8, (code >> 4) & 0xfu);
+  return B200_OK;
+}
+
 B200_API int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, void* const* xq_ptrs,
                                                void* const* xscale_ptrs, void* const* y_ptrs, void* const* flag_ptrs,
                                                void* epoch, void* residual, const void* weight, int64_t M, int64_t H,
                                                float eps, int tp_size, int tp_rank, int max_blocks, int dtype,
-                                               void* stream) {
+                                               void* err_flag, void* stream) {
   B200_REQUIRE(tp_size >= 2 && tp_size <= kMaxTp && tp_rank >= 0 && tp_rank < tp_size, "tp exchange: bad tp %d / rank %d",
                tp_size, tp_rank);
   B200_REQUIRE(M >= 0 && H > 0 && H % 8 == 0 && H * 4 <= 200 * 1024, "tp exchange: bad sizes M %lld H %lld", (long long)M,
                (long long)H);
   if (M == 0) return B200_OK;
-  B200_REQUIRE(partial_ptrs && flag_ptrs && epoch && weight, "tp exchange: null pointer");
+  B200_REQUIRE(partial_ptrs && flag_ptrs && epoch && weight && err_flag, "tp exchange: null pointer");
   B200_REQUIRE(xq_ptrs != nullptr || y_ptrs != nullptr, "tp exchange: no output requested");
   B200_REQUIRE((xq_ptrs == nullptr) == (xscale_ptrs == nullptr), "tp exchange: xq and xscale go together");
   const int64_t rows_per = ceil_div(M, tp_size);
@@ -325,6 +359,12 @@ B200_API int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, 
   a.residual = residual;
   a.weight = weight;
   a.trace = g_trace; a.trace_slots = (int)g_trace_slots;
+  a.err = reinterpret_cast<uint32_t*>(err_flag);
+  static const unsigned long long timeout_ms =
+      getenv("B200_TP_TIMEOUT_MS") ? strtoull(getenv("B200_TP_TIMEOUT_MS"), nullptr, 10) : 20000ull;
+  static const int relaxed_start = getenv("B200_TP_RELAXED_START") && getenv("B200_TP_RELAXED_START")[0] == '1';
+  a.timeout_ns = timeout_ms * 1000000ull;
+  a.relaxed_start = relaxed_start;
   a.M = M; a.H = H; a.tp = tp_size; a.rank = tp_rank; a.max_blocks = max_blocks; a.eps = eps;
   const int smem = (int)(H * sizeof(float));
   cudaStream_t st = (cudaStream_t)stream;

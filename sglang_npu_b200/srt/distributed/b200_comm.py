@@ -12,6 +12,7 @@ One `B200TPComm` per TP rank.  It owns ONE device allocation, mapped into every 
     y        [max_tokens, hidden]  act dtype   <- same, for the un-quantised consumer (final norm -> lm_head)
     flags    [2, 8, max_blocks]    uint32      <- start / end epochs written by the peers
     epoch    [max_blocks]          uint32      <- local launch counter per CTA
+    err      [1]                   uint32      <- first barrier timeout of this rank (0 = none), see check()
 
 `reduce_rmsnorm_quant_int8` launches csrc/tp_comm.cu: a two-shot exchange (reduce-scatter by token slice over peer
 loads, all-gather of the int8 result over peer stores) with the residual add, RMSNorm and int8 quant in between.
@@ -56,7 +57,7 @@ class B200TPComm:
         off, o = {}, 0
         for name, nbytes in (("partial", max_tokens * hidden * es), ("xq", max_tokens * hidden),
                              ("xscale", max_tokens * 4), ("y", max_tokens * hidden * es),
-                             ("flags", 2 * 8 * MAX_BLOCKS * 4), ("epoch", MAX_BLOCKS * 4)):
+                             ("flags", 2 * 8 * MAX_BLOCKS * 4), ("epoch", MAX_BLOCKS * 4), ("err", 256)):
             off[name] = o
             o += _align(nbytes)
         self._off, self.nbytes = off, o
@@ -122,19 +123,33 @@ class B200TPComm:
         kernels.check(lib.b200_tp_reduce_rmsnorm_quant_int8(
             pa["partial"], pa["xq"] if quant else None, pa["xscale"] if quant else None, pa["y"] if normed else None,
             pa["flags"], self._base + self._off["epoch"], ptr(residual), ptr(weight), M, self.hidden, float(eps), self.tp,
-            self.rank, MAX_BLOCKS, dtype_code(self.dtype), stream_ptr(self.device)), "b200_tp_reduce_rmsnorm_quant_int8")
+            self.rank, MAX_BLOCKS, dtype_code(self.dtype), self._base + self._off["err"], stream_ptr(self.device)),
+            "b200_tp_reduce_rmsnorm_quant_int8")
         act = kernels.Int8Activation(self._xq(M), self._xscale(M), self.dtype) if quant else None
         if quant and normed:
             return act, self._y(M)
         return act if quant else self._y(M)
 
-    def close(self):
+    def check(self) -> None:
+        """Synchronise the current stream and raise if an exchange kernel of this rank gave up waiting for a peer
+        (B200_TP_TIMEOUT_MS).  Call it where the reference would surface an NCCL timeout: after a step, before results
+        are trusted."""
         lib = _cabi.load()
+        check(lib.b200_comm_check(self._base + self._off["err"], stream_ptr(self.device)), "b200_comm_check")
+
+    def close(self):
+        """Orderly teardown: drain this rank's stream, meet the peers (nobody may still be loading from / storing to
+        a mapping that is about to go away), then unmap the peers and free the local allocation."""
+        lib = _cabi.load()
+        if not self._base:
+            return
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+        torch.cuda.synchronize(self.device)
         for r, b in enumerate(self._peer_base):
             if r != self.rank and b:
                 lib.b200_comm_ipc_close(b)
-        if self._base:
-            torch.cuda.synchronize(self.device)
-            lib.b200_comm_free(self._base)
-            self._base = 0
         self._peer_base = []
+        dist.barrier(group=self.group)  # every peer has dropped its mapping of this allocation
+        lib.b200_comm_free(self._base)
+        self._base = 0
