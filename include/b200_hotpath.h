@@ -221,7 +221,9 @@ int b200_int8_scaled_mm(void* out, const int8_t* a, const int8_t* b, const float
  * b200_fp8_blockwise_scaled_mm replaces fp8_blockwise_scaled_mm (sgl-kernel/csrc/gemm/
  * fp8_blockwise_gemm_kernel.cu:345-423): out[m,n] = sum_kb (sum_{k in kb} a[m,k] b[n,k])
  * * sa[m,kb] * sb[n/128,kb]; a [M,K] e4m3 row-major, b N rows of K contiguous e4m3;
- * K % 128 == 0, N % 128 == 0 (fp8_utils.py:190-197).
+ * K % 128 == 0, N % 128 == 0 (fp8_utils.py:190-197).  `workspace`: the self-cleaning stream-K
+ * workspace of b200_int8_scaled_mm_workspace_bytes(M, ...) (shared with the other scaled GEMMs of the
+ * stream); with a null workspace decode sizes take the cluster split-K kernel instead.
  */
 int b200_per_token_group_quant_fp8(void* xq, float* scales, const void* x, int64_t M, int64_t K,
                                    int64_t x_row_stride, int group_size, float eps,
@@ -233,7 +235,7 @@ int b200_fp8_blockwise_scaled_mm(void* out, const void* a, const void* b, const 
                                  int64_t sa_row_stride, int64_t sa_col_stride,
                                  const float* scale_b, int64_t sb_row_stride, int64_t sb_col_stride,
                                  const void* bias, int64_t M, int64_t N, int64_t K, int out_dtype,
-                                 void* stream);
+                                 void* workspace, size_t workspace_bytes, void* stream);
 /* per-token x per-channel FP8 (sgl-kernel/csrc/gemm/fp8_gemm_kernel.cu:1110-1145). */
 int b200_fp8_scaled_mm(void* out, const void* a, const void* b, const float* scale_a,
                        const float* scale_b, const void* bias, int64_t M, int64_t N, int64_t K,

@@ -70,7 +70,7 @@ _SIGNATURES = {
                                        c_int64, c_int64, c_int, _P],
     "b200_per_token_quant_fp8": [_P, _P, _P, c_int64, c_int64, c_int64, c_int, _P],
     "b200_fp8_blockwise_scaled_mm": [_P, _P, _P, _P, c_int64, c_int64, _P, c_int64, c_int64, _P,
-                                     c_int64, c_int64, c_int64, c_int, _P],
+                                     c_int64, c_int64, c_int64, c_int, _P, c_size_t, _P],
     "b200_fp8_scaled_mm": [_P, _P, _P, _P, _P, _P, c_int64, c_int64, c_int64, c_int, _P, c_size_t, _P],
     "b200_awq_dequantize": [_P, _P, _P, _P, c_int64, c_int64, c_int, c_int, _P],
     "b200_awq_gemm": [_P, _P, _P, _P, _P, _P, c_int64, c_int64, c_int64, c_int, c_int, _P],

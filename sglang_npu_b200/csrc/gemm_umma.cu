@@ -24,38 +24,11 @@
 #include <cstdlib>
 #include <unordered_map>
 
-#include "sm100.cuh"
+#include "gemm_common.cuh"
 
 namespace b200 {
 
 using namespace sm100;
-
-enum GemmMode { kModeI8 = 0, kModeF8Chan = 1, kModeF8Block = 2 };
-
-struct GemmArgs {
-  void* out;             // [M, N] bf16/f16
-  const float* scale_m;  // per token: [M] (I8 / F8Chan) or [M, K/128] with strides (F8Block)
-  const float* scale_n;  // per channel: [N] or [N/128, K/128] with strides (F8Block)
-  const void* bias;      // [N] out dtype or null
-  int32_t* acc_out;      // [M, N] raw int32 accumulators (I8 only) or null
-  int M, N;
-  int num_kb;        // K blocks of 128 bytes (ceil)
-  int kb_per_split;  // K blocks per cluster rank
-  int splits;        // cluster size along z (1, 2, 4, 8)
-  int out_is_bf16;
-  int64_t sm_rs, sm_cs;  // scale_m[m * sm_rs + kb * sm_cs]          (F8Block)
-  int64_t sn_rs, sn_cs;  // scale_n[(n / 128) * sn_rs + kb * sn_cs]   (F8Block)
-  unsigned long long* trace;  // diagnostics (b200_debug_set_trace) or null
-  int trace_slots;
-};
-
-__device__ __forceinline__ unsigned long long* trace_slot(const GemmArgs& g) {
-  const int cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
-  return (g.trace != nullptr && cta < g.trace_slots) ? g.trace + (size_t)cta * 16 : nullptr;
-}
-
-constexpr int kGemmThreads = 256;
-constexpr int kBK = 128;  // bytes of K per pipeline stage = one 128B swizzle row
 
 template <int BN, int STAGES>
 struct GemmSmemLayout {
@@ -75,16 +48,6 @@ __device__ __forceinline__ float finalize(uint32_t bits, float sm, float sn, boo
   else if constexpr (MODE == kModeF8Chan) v = __fmul_rn(__fmul_rn(__uint_as_float(bits), sm), sn);
   else v = __uint_as_float(bits);
   return has_bias ? __fadd_rn(v, bias) : v;
-}
-
-__device__ __forceinline__ float load_bias(const void* bias, int n, int is_bf16) {
-  return is_bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(bias)[n])
-                 : __half2float(reinterpret_cast<const __half*>(bias)[n]);
-}
-
-__device__ __forceinline__ void store_out(void* out, int64_t idx, float v, int is_bf16) {
-  if (is_bf16) reinterpret_cast<__nv_bfloat16*>(out)[idx] = __float2bfloat16_rn(v);
-  else reinterpret_cast<__half*>(out)[idx] = __float2half_rn(v);
 }
 
 // 16 consecutive token columns of one output channel: scales (+bias), one rounding to the output dtype, 2-byte
@@ -655,18 +618,6 @@ struct StreamK {
   static constexpr int kBytes = kBarOff + (2 * kStages + 5) * 8 + 1024;
   static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
 };
-constexpr int kSkFlagBytes = 1024;  // up to 256 CTAs
-
-__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.gpu.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;\n" ::: "memory"); }
-
 template <int MODE, int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
@@ -986,6 +937,8 @@ static int run_gemm(GemmArgs g, const void* a, const void* b, int64_t M, int64_t
   g.num_kb = (int)ceil_div(K, kBK);
   g.trace = g_trace;
   g.trace_slots = (int)g_trace_slots;
+  static const int debug = getenv("B200_GEMM_DEBUG") ? atoi(getenv("B200_GEMM_DEBUG")) : 0;
+  g.debug = debug;
   CUtensorMap ta, tb;
   int rc;
   if constexpr (MODE != kModeF8Block) {
@@ -1020,6 +973,27 @@ static int run_gemm(GemmArgs g, const void* a, const void* b, int64_t M, int64_t
         case 64: return launch_streamk<MODE, 64>(ta, tb, g, (int)units, ctas, ws, st);
         case 128: return launch_streamk<MODE, 128>(ta, tb, g, (int)units, ctas, ws, st);
         default: return launch_streamk<MODE, 256>(ta, tb, g, (int)units, ctas, ws, st);
+      }
+    }
+  }
+  if constexpr (MODE == kModeF8Block) {
+    // gemm_fp8_block.cu: stream-K weight streaming with per-K-block promotion (M <= 128, needs the workspace) and the
+    // persistent 128x256 prefill kernel; B200_FP8_BLOCK_LEGACY=1 keeps the round-1 kernels below for A/B runs
+    static const bool legacy = getenv("B200_FP8_BLOCK_LEGACY") != nullptr && getenv("B200_FP8_BLOCK_LEGACY")[0] == '1';
+    if (!legacy) {
+      if (M <= 128 && ws != nullptr) {
+        const size_t need = streamk_workspace_bytes(M);
+        if (ws_bytes < need)
+          return fail(B200_ERR_WORKSPACE, "fp8_blockwise_scaled_mm: workspace of %zu bytes, %zu needed", ws_bytes, need);
+        B200_REQUIRE(((uintptr_t)ws % 16) == 0, "fp8_blockwise_scaled_mm: workspace must be 16-byte aligned");
+        g.splits = 1;
+        g.kb_per_split = g.num_kb;
+        return launch_block_fp8_streamk(g, a, b, M, N, K, ws, st);
+      }
+      if (M > 128 && N >= 256) {
+        g.splits = 1;
+        g.kb_per_split = g.num_kb;
+        return launch_block_fp8_prefill(g, a, b, M, N, K, st);
       }
     }
   }
@@ -1132,7 +1106,8 @@ B200_API int b200_fp8_scaled_mm(void* out, const void* a, const void* b, const f
 B200_API int b200_fp8_blockwise_scaled_mm(void* out, const void* a, const void* b, const float* scale_a,
                                           int64_t sa_row_stride, int64_t sa_col_stride, const float* scale_b,
                                           int64_t sb_row_stride, int64_t sb_col_stride, const void* bias, int64_t M,
-                                          int64_t N, int64_t K, int out_dtype, void* stream) {
+                                          int64_t N, int64_t K, int out_dtype, void* workspace, size_t workspace_bytes,
+                                          void* stream) {
   int rc = check_common("fp8_blockwise_scaled_mm", out, a, b, M, N, K, out_dtype);
   if (rc != B200_OK) return rc;
   if (M == 0) return B200_OK;
@@ -1144,5 +1119,5 @@ B200_API int b200_fp8_blockwise_scaled_mm(void* out, const void* a, const void* 
   g.out = out; g.scale_m = scale_a; g.scale_n = scale_b; g.bias = bias;
   g.sm_rs = sa_row_stride; g.sm_cs = sa_col_stride; g.sn_rs = sb_row_stride; g.sn_cs = sb_col_stride;
   g.out_is_bf16 = out_dtype == B200_BF16;
-  return run_gemm<kModeF8Block>(g, a, b, M, N, K, (cudaStream_t)stream);
+  return run_gemm<kModeF8Block>(g, a, b, M, N, K, (cudaStream_t)stream, workspace, workspace_bytes);
 }

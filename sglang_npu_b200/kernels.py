@@ -407,7 +407,7 @@ def sgl_per_token_quant_fp8(x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor
 
 def fp8_blockwise_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tensor,
                             scales_b: torch.Tensor, out_dtype: torch.dtype,
-                            bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+                            bias: Optional[torch.Tensor] = None, cluster_splitk: bool = False) -> torch.Tensor:
     """sgl_kernel.fp8_blockwise_scaled_mm (gemm.py:32-42): mat_a [M,K] e4m3 row-major, mat_b [K,N]
     e4m3 column-major (weight.T), scales_a [M, K/128], scales_b [K/128, N/128] (weight_scale.T)."""
     require_cuda(mat_a, mat_b, scales_a, scales_b)
@@ -424,11 +424,15 @@ def fp8_blockwise_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: 
     out = torch.empty((M, N), device=mat_a.device, dtype=out_dtype)
     if bias is not None:
         bias = bias.to(out_dtype).contiguous()
+    # `cluster_splitk=True` passes no workspace: decode sizes then take the cluster split-K kernel instead of the
+    # stream-K one (A/B and parity of both CUDA kernels)
+    ws = None if cluster_splitk else _scaled_mm_workspace(lib, mat_a.device, M, N, K)
     # kernel wants scale_b indexed [n_block, k_block]
     check(lib.b200_fp8_blockwise_scaled_mm(
         ptr(out), ptr(mat_a), ptr(mat_b), ptr(scales_a), scales_a.stride(0), scales_a.stride(1),
         ptr(scales_b), scales_b.stride(1), scales_b.stride(0), ptr(bias), M, N, K,
-        dtype_code(out_dtype), stream_ptr(mat_a.device)), "b200_fp8_blockwise_scaled_mm")
+        dtype_code(out_dtype), ptr(ws), 0 if ws is None else ws.numel(), stream_ptr(mat_a.device)),
+        "b200_fp8_blockwise_scaled_mm")
     return out
 
 

@@ -17,13 +17,16 @@ GHZ = 1.965
 NAMES = {
     "streamk": {1: "setup", 2: "pdl_wait", 3: "first_full", 4: "mma_issued", 5: "seg0_acc", 6: "contrib_pub",
                 7: "last_seg_acc", 8: "flags_seen", 11: "partials_in_smem", 9: "epi_done"},
+    "block": {1: "setup", 2: "pdl_wait", 12: "scales_ready", 3: "first_full", 4: "mma_issued", 5: "unit0_acc",
+              6: "contrib_pub", 7: "last_unit_acc", 8: "flags_seen", 9: "epi_done"},
     "cluster": {1: "setup", 2: "pdl_wait", 3: "first_full", 4: "mma_issued", 5: "acc_ready", 6: "csync1", 7: "scatter",
                 8: "csync2", 9: "epi_done"},
 }
 
 
 def main():
-    ms = [int(x) for x in sys.argv[1:]] or [16, 64]
+    ms = [int(x) for x in sys.argv[1:] if x.isdigit()] or [16, 64]
+    fp8_block = "block" in sys.argv
     dev = torch.device("cuda")
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
     for m in ms:
@@ -31,8 +34,15 @@ def main():
             a = torch.randint(-127, 128, (m, k), device=dev, dtype=torch.int8)
             w = torch.randint(-127, 128, (n, k), device=dev, dtype=torch.int8)
             sa, sb = torch.rand(m, device=dev), torch.rand(n, device=dev)
-            for path in ("streamk", "cluster"):
+            if fp8_block:
+                a8 = ((torch.rand(m, k, device=dev) - 0.5) * 2 * 448).to(torch.float8_e4m3fn)
+                w8 = ((torch.rand(n, k, device=dev) - 0.5) * 2 * 448).to(torch.float8_e4m3fn)
+                sa8 = torch.rand(m, k // 128, device=dev) * 1e-3
+                sb8 = torch.rand(k // 128, n // 128, device=dev) * 1e-3
+            for path in (("streamk", "block") if fp8_block else ("streamk", "cluster")):
                 fn = lambda: kernels.int8_scaled_mm(a, w.t(), sa, sb, torch.bfloat16, cluster_splitk=(path == "cluster"))
+                if path == "block":
+                    fn = lambda: kernels.fp8_blockwise_scaled_mm(a8, w8.t(), sa8, sb8, torch.bfloat16)
                 fn()
                 torch.cuda.synchronize()
                 buf = torch.zeros((1024, 16), dtype=torch.int64, device=dev)
@@ -55,7 +65,7 @@ def main():
                     if ok.any():
                         d = (col[ok] - t[ok, 14]).float() / GHZ
                         row[name] = [int(d.median()), int(d.max())]
-                if path == "streamk":
+                if path == "streamk" and not fp8_block:
                     row["peers_max"] = int(t[:, 10].max())
                 print(json.dumps(row), flush=True)
 

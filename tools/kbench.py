@@ -118,6 +118,46 @@ def bench_gemm_int8(args):
                                   gbs=round(byts / med / 1e6, 1), tops=round(2 * m * n * kk / med / 1e9, 1))), flush=True)
 
 
+def bench_gemm_fp8(args):
+    """Block-scaled (--block, default) or per-channel (--chan) FP8 GEMM at the Llama-8B shapes, next to cuBLASLt fp8
+    (torch._scaled_mm, per-tensor scales: the library ceiling; blockwise scaling when this torch/cuBLASLt offers it)."""
+    dev = torch.device("cuda")
+    shapes = [(4096, 6144), (4096, 4096), (4096, 28672), (14336, 4096)]
+    one = torch.ones((), device=dev)
+    for m in ([args.m] if args.m else [64, 128, 2048, 8192]):
+        for (kk, n) in shapes:
+            a = ((torch.rand(m, kk, device=dev) - 0.5) * 2 * 448).to(torch.float8_e4m3fn)
+            copies = max(2, int(300e6 // (n * kk)) + 1) if m <= 256 else 1
+            ws = [((torch.rand(n, kk, device=dev) - 0.5) * 2 * 448).to(torch.float8_e4m3fn) for _ in range(copies)]
+            byts = n * kk + m * kk + m * n * 2
+            row = dict(kernel="fp8_blockwise_scaled_mm" if not args.chan else "fp8_scaled_mm", m=m, n=n, k=kk)
+            if args.chan:
+                sa, sb = torch.rand(m, device=dev) * 1e-3, torch.rand(n, device=dev) * 1e-3
+                t = timeit_rot(lambda c: (lambda: kernels.fp8_scaled_mm(a, ws[c].t(), sa, sb, torch.bfloat16)), copies)
+            else:
+                sa = torch.rand(m, kk // 128, device=dev) * 1e-3
+                sb = torch.rand(kk // 128, n // 128, device=dev) * 1e-3
+                t = timeit_rot(lambda c: (lambda: kernels.fp8_blockwise_scaled_mm(a, ws[c].t(), sa, sb, torch.bfloat16)), copies)
+            row.update(ms=round(t, 4), gbs=round(byts / t / 1e6, 1), frac_hbm=round(byts / t / 1e6 / HBM, 3),
+                       tflops=round(2 * m * n * kk / t / 1e9, 1))
+            try:
+                t2 = timeit_rot(lambda c: (lambda: torch._scaled_mm(a, ws[c].t(), one, one, out_dtype=torch.bfloat16)), copies)
+                row["cublaslt_fp8_tensorwise_ms"] = round(t2, 4)
+                row["cublaslt_fp8_tensorwise_tflops"] = round(2 * m * n * kk / t2 / 1e9, 1)
+                row["vs_cublaslt"] = round(t2 / t, 3)
+            except Exception as e:  # noqa: BLE001
+                row["cublaslt_err"] = str(e)[:80]
+            if not args.chan:
+                try:  # blockwise 1x128 x 128x128 scaling inside cuBLASLt, where supported
+                    sa_c = sa.t().contiguous().t()
+                    sb_c = sb.t().contiguous()
+                    t3 = timeit_rot(lambda c: (lambda: torch._scaled_mm(a, ws[c].t(), sa_c, sb_c.t(), out_dtype=torch.bfloat16)), copies)
+                    row["cublaslt_fp8_blockwise_ms"] = round(t3, 4)
+                except Exception as e:  # noqa: BLE001
+                    row["cublaslt_blockwise_err"] = str(e)[:60]
+            print(json.dumps(row), flush=True)
+
+
 def bench_awq(args):
     """cfg 4 (Qwen2.5-32B) per-GPU shapes: decode M = 128, prefill M = 2048."""
     dev = torch.device("cuda")
@@ -211,5 +251,7 @@ if __name__ == "__main__":
     ap.add_argument("--fp8kv", action="store_true", help="decode: FP8 (e4m3) KV cache")
     ap.add_argument("--shared", type=int, default=0, help="decode: every request shares this many leading tokens")
     ap.add_argument("--cluster", action="store_true", help="gemm_int8: cluster split-K kernel instead of stream-K")
+    ap.add_argument("--chan", action="store_true", help="gemm_fp8: per-channel scales (fp8_scaled_mm) instead of block scales")
     args = ap.parse_args()
-    {"decode": bench_decode, "gemm_int8": bench_gemm_int8, "awq": bench_awq, "peak": bench_peak, "extend": bench_extend}[args.what](args)
+    {"decode": bench_decode, "gemm_int8": bench_gemm_int8, "awq": bench_awq, "peak": bench_peak, "extend": bench_extend,
+     "gemm_fp8": bench_gemm_fp8}[args.what](args)
