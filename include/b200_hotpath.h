@@ -274,6 +274,23 @@ int b200_rope_neox(void* q, void* k, const float* cos_sin_cache, const int64_t* 
 int b200_argmax_workspace_bytes(int64_t rows, size_t* bytes);
 int b200_argmax(int64_t* out, const void* x, int64_t rows, int64_t V, int64_t row_stride, int dtype,
                 void* workspace, size_t workspace_bytes, void* stream);
+/* Vocab-parallel greedy sampling (replaces the all-gather of the full logits, logits_processor.py:430-500, before
+ * sampler.py's argmax): b200_argmax_key stores, per row, a non-negative int64 key = (order-preserving value bits,
+ * ~(index_offset + local index)); the TP ranks combine keys with ONE max all-reduce of 8 bytes per row
+ * (b200_allreduce / torch.distributed) and b200_argmax_key_decode turns the winning key into the token id
+ * (equal maxima resolve to the lowest global index, like torch.argmax over the gathered logits). */
+int b200_argmax_key(int64_t* key_out, const void* x, int64_t rows, int64_t V, int64_t row_stride, int dtype,
+                    int64_t index_offset, void* workspace, size_t workspace_bytes, void* stream);
+int b200_argmax_key_decode(int64_t* out, const int64_t* keys, int64_t rows, void* stream);
+/* hidden[t, :] = table[ids[t], :] (VocabParallelEmbedding.forward, python/sglang/srt/layers/vocab_parallel_embedding.py,
+ * replicated table) and, optionally, positions[t] = seq_lens[t] - 1 (forward_batch_info.py:960-962) in the same launch. */
+int b200_embedding(void* out, const void* table, const int64_t* ids, int64_t T, int64_t H, int64_t vocab, int dtype,
+                   int64_t* positions, const int64_t* seq_lens, void* stream);
+/* out[M, N] = a[M, K] . b[N, K]^T (+ bias): un-quantised bf16 / f16 weight-streaming GEMM for decode-size M (<= 256) —
+ * the lm_head / logits GEMM (logits_processor.py:470-500 `torch.matmul(hidden, lm_head.weight.T)`), tcgen05 kind::f16
+ * through the stream-K kernel; `workspace` as for b200_int8_scaled_mm. */
+int b200_dense_gemm_nt(void* out, const void* a, const void* b, const void* bias, int64_t M, int64_t N, int64_t K,
+                       int dtype, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---- fused steps ("fused_add_rmsnorm + emit per-token int8 quant for the following GEMM,
  * RoPE + fused KV-cache write, silu_and_mul + quant for down_proj") ---------------------------------------------

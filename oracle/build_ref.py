@@ -3,7 +3,7 @@ hot path, compiled from the sources where they lie under /root/reference (never 
 
     python oracle/build_ref.py        ->  oracle/_ref/libsgl_cpu_ref.so
 
-Sources: sgl-kernel/csrc/cpu/{gemm.cpp, gemm_int8.cpp, decode.cpp, extend.cpp} (+ their headers
+Sources: sgl-kernel/csrc/cpu/{gemm.cpp, gemm_int8.cpp, gemm_fp8.cpp, decode.cpp, extend.cpp} (+ their headers
 common.h / gemm.h / vec.h) and the registration shim oracle/ref_register.cpp.  Plain g++ commands — the
 reference's own CMake build is not run (it needs libnuma and builds every op).  The kernels need
 AVX512F + AVX512-BF16 + AMX-BF16 (sgl-kernel/csrc/cpu/vec.h:3-5); both the build container and the GPU
@@ -20,7 +20,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 OUT_DIR = os.path.join(HERE, "_ref")
 LIB = os.path.join(OUT_DIR, "libsgl_cpu_ref.so")
 REF_CPU = "/root/reference/sgl-kernel/csrc/cpu"
-SOURCES = ["gemm.cpp", "gemm_int8.cpp", "decode.cpp", "extend.cpp"]
+SOURCES = ["gemm.cpp", "gemm_int8.cpp", "gemm_fp8.cpp", "decode.cpp", "extend.cpp"]
 ISA = ["-mavx512f", "-mavx512bw", "-mavx512vl", "-mavx512dq", "-mavx512vnni", "-mavx512bf16", "-mavx512fp16",
        "-mamx-tile", "-mamx-bf16", "-mamx-int8", "-mfma", "-mf16c", "-mavx2"]
 

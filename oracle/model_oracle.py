@@ -61,14 +61,20 @@ class OracleStack:
         self.cos_sin = _cpu(stack.cos_sin_cache)
 
     def forward(self, input_ids, positions, k_caches, v_caches, req_to_token, req_pool_indices, seq_lens,
-                out_cache_loc, prefix_lens=None):
-        """Decode when prefix_lens is None, else extend.  k/v_caches: per-layer CPU pools (updated in place)."""
+                out_cache_loc, prefix_lens=None, record=None):
+        """Decode when prefix_lens is None, else extend.  k/v_caches: per-layer CPU pools (updated in place).
+        record: optional list that receives, per layer, (hidden_in, residual_in, hidden_out, residual_out) — the
+        teacher-forcing points of the per-layer parity test."""
         cfg = self.cfg
         eps = cfg.rms_norm_eps
         h = self.embed[input_ids]
         residual = None
         hq, hkv, d = cfg.num_attention_heads, cfg.num_kv_heads, cfg.head_dim
         for i, L in enumerate(self.layers):
+            if record is not None:
+                if i > 0:
+                    record[-1] += (h.clone(), residual.clone())
+                record.append((h.clone(), None if residual is None else residual.clone()))
             if residual is None:
                 residual = h
                 h = qo.rmsnorm(h, L["ln1"], eps)
@@ -105,6 +111,8 @@ class OracleStack:
             h, residual = qo.rmsnorm(h, L["ln2"], eps, residual)
             gu = L["gate_up"](h)
             h = L["down"](qo.silu_and_mul(gu))
+        if record is not None and self.layers:
+            record[-1] += (h.clone(), residual.clone())
         h, _ = qo.rmsnorm(h, self.norm, eps, residual)
         return h
 

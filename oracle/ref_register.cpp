@@ -1,7 +1,7 @@
 // TEST INFRASTRUCTURE — op registration shim for the reference's own CPU kernels.
 //
 // The kernels themselves are compiled straight from /root/reference/sgl-kernel/csrc/cpu/
-// {gemm,gemm_int8,decode,extend}.cpp (see oracle/build_ref.py; nothing is copied into this repo).
+// {gemm,gemm_int8,gemm_fp8,decode,extend}.cpp (see oracle/build_ref.py; nothing is copied into this repo).
 // This file only declares their entry points (signatures as in the reference's
 // torch_extension_cpu.cpp:65-133) and registers them under the `b200_ref` torch library so the
 // tests / the CPU-baseline leg of bench.py can call torch.ops.b200_ref.*.
@@ -10,6 +10,7 @@
 
 #include <optional>
 #include <tuple>
+#include <vector>
 
 void decode_attention_cpu(at::Tensor& query, at::Tensor& k_cache, at::Tensor& v_cache, at::Tensor& output,
                           at::Tensor& key, at::Tensor& value, at::Tensor& loc, at::Tensor& attn_logits,
@@ -26,7 +27,15 @@ at::Tensor int8_scaled_mm_cpu(at::Tensor& mat1, at::Tensor& mat2, at::Tensor& sc
 at::Tensor int8_scaled_mm_with_quant(at::Tensor& mat1, at::Tensor& mat2, at::Tensor& scales2,
                                      const std::optional<at::Tensor>& bias, at::ScalarType out_dtype, bool is_vnni);
 
+// block-scaled FP8 linear of the CPU backend (W8A16: bf16 activations, e4m3 weights; gemm_fp8.cpp:468-548)
+at::Tensor fp8_scaled_mm_cpu(at::Tensor& mat1, at::Tensor& mat2, at::Tensor& scales2, std::vector<int64_t> block_size,
+                             const std::optional<at::Tensor>& bias, at::ScalarType out_dtype, bool is_vnni);
+
 TORCH_LIBRARY_FRAGMENT(b200_ref, m) {
+  m.def(
+      "fp8_scaled_mm_cpu(Tensor mat1, Tensor mat2, Tensor scales2, int[] block_size, Tensor? bias, ScalarType "
+      "out_dtype, bool is_vnni) -> Tensor");
+  m.impl("fp8_scaled_mm_cpu", c10::kCPU, &fp8_scaled_mm_cpu);
   m.def(
       "decode_attention_cpu(Tensor query, Tensor k_cache, Tensor v_cache, Tensor output, Tensor key, Tensor value, "
       "Tensor loc, Tensor attn_logits, Tensor req_to_token, Tensor req_pool_indices, Tensor seq_lens, float sm_scale, "

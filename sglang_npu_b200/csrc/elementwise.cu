@@ -135,10 +135,27 @@ using namespace b200;
 // slice with 16-byte loads and publishes one 64-bit key (order-preserving float bits << 32 | ~index) with
 // atomicMax, so equal maxima resolve to the LOWEST index whatever the arrival order; the last CTA of a row
 // (counter) decodes the key into the int64 token id and resets key and counter (self-cleaning scratch).
+// key_out != nullptr (vocab-parallel greedy sampling): instead of the token id the row's key is stored with the index
+// made global (index_offset = first vocabulary row of this TP rank) and one float bit dropped so that it is a
+// NON-NEGATIVE int64 — ranks then combine their keys with one 8-byte-per-row max all-reduce and decode the winner
+// with argmax_key_decode_kernel.  The dropped bit is always zero for bf16 / f16 logits widened to fp32.
+__device__ __forceinline__ long long signed_safe_key(unsigned long long key, uint32_t index_offset) {
+  const uint32_t idx = 0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull) + index_offset;
+  return (long long)(((key >> 33) << 32) | (unsigned long long)(0xFFFFFFFFu - idx));
+}
+
+__global__ void argmax_key_decode_kernel(int64_t* __restrict__ out, const long long* __restrict__ keys, int64_t rows) {
+  pdl_trigger();
+  pdl_wait();
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < rows) out[i] = (int64_t)(0xFFFFFFFFu - (uint32_t)((unsigned long long)keys[i] & 0xFFFFFFFFull));
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) argmax_kernel(int64_t* __restrict__ out, const T* __restrict__ x, int64_t V,
                                                      int64_t row_stride, unsigned long long* __restrict__ keys,
-                                                     unsigned int* __restrict__ counters) {
+                                                     unsigned int* __restrict__ counters, long long* __restrict__ key_out,
+                                                     uint32_t index_offset) {
   __shared__ unsigned long long s_key[8];
   pdl_trigger();
   pdl_wait();
@@ -183,7 +200,8 @@ __global__ void __launch_bounds__(256) argmax_kernel(int64_t* __restrict__ out, 
 #pragma unroll
     for (int w = 1; w < 8; ++w) key = s_key[w] > key ? s_key[w] : key;
     if (parts == 1) {
-      out[row] = (int64_t)(0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull));
+      if (key_out != nullptr) key_out[row] = signed_safe_key(key, index_offset);
+      else out[row] = (int64_t)(0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull));
     } else {
       atomicMax(keys + row, key);
       __threadfence();
@@ -191,7 +209,8 @@ __global__ void __launch_bounds__(256) argmax_kernel(int64_t* __restrict__ out, 
         __threadfence();
         const unsigned long long k = atomicExch(keys + row, 0ull);
         counters[row] = 0u;
-        out[row] = (int64_t)(0xFFFFFFFFu - (uint32_t)(k & 0xFFFFFFFFull));
+        if (key_out != nullptr) key_out[row] = signed_safe_key(k, index_offset);
+        else out[row] = (int64_t)(0xFFFFFFFFu - (uint32_t)(k & 0xFFFFFFFFull));
       }
     }
   }
@@ -264,11 +283,11 @@ B200_API int b200_argmax_workspace_bytes(int64_t rows, size_t* bytes) {
   return B200_OK;
 }
 
-B200_API int b200_argmax(int64_t* out, const void* x, int64_t rows, int64_t V, int64_t row_stride, int dtype,
-                         void* workspace, size_t workspace_bytes, void* stream) {
+static int run_argmax(int64_t* out, long long* key_out, uint32_t index_offset, const void* x, int64_t rows, int64_t V,
+                      int64_t row_stride, int dtype, void* workspace, size_t workspace_bytes, void* stream) {
   B200_REQUIRE(rows >= 0 && V > 0 && V < (1ll << 32), "argmax: bad sizes");
   if (rows == 0) return B200_OK;
-  B200_REQUIRE(out && x, "argmax: null pointer");
+  B200_REQUIRE((out || key_out) && x, "argmax: null pointer");
   B200_REQUIRE(row_stride % 8 == 0 && ((uintptr_t)x % 16) == 0, "argmax: rows must be 16-byte aligned");
   B200_REQUIRE(rows <= 65535 * 32768ll, "argmax: too many rows");
   int parts = (int)((2 * (int64_t)sm_count() + rows - 1) / rows);  // ~2 CTAs per SM
@@ -282,9 +301,59 @@ B200_API int b200_argmax(int64_t* out, const void* x, int64_t rows, int64_t V, i
   dim3 grid((unsigned)rows, (unsigned)parts);
   if (dtype == B200_BF16)
     return launch_k(argmax_kernel<__nv_bfloat16>, grid, dim3(256), 0, st, 1, true, out, (const __nv_bfloat16*)x, V,
-                    row_stride, keys, counters);
+                    row_stride, keys, counters, key_out, index_offset);
   if (dtype == B200_F16)
     return launch_k(argmax_kernel<__half>, grid, dim3(256), 0, st, 1, true, out, (const __half*)x, V, row_stride, keys,
-                    counters);
+                    counters, key_out, index_offset);
   return fail(B200_ERR_UNSUPPORTED, "argmax: dtype %d not supported (bf16/f16)", dtype);
+}
+
+B200_API int b200_argmax(int64_t* out, const void* x, int64_t rows, int64_t V, int64_t row_stride, int dtype,
+                         void* workspace, size_t workspace_bytes, void* stream) {
+  return run_argmax(out, nullptr, 0u, x, rows, V, row_stride, dtype, workspace, workspace_bytes, stream);
+}
+
+B200_API int b200_argmax_key(int64_t* key_out, const void* x, int64_t rows, int64_t V, int64_t row_stride, int dtype,
+                             int64_t index_offset, void* workspace, size_t workspace_bytes, void* stream) {
+  B200_REQUIRE(index_offset >= 0 && index_offset + V < (1ll << 32), "argmax_key: index offset out of range");
+  return run_argmax(nullptr, reinterpret_cast<long long*>(key_out), (uint32_t)index_offset, x, rows, V, row_stride, dtype,
+                    workspace, workspace_bytes, stream);
+}
+
+B200_API int b200_argmax_key_decode(int64_t* out, const int64_t* keys, int64_t rows, void* stream) {
+  B200_REQUIRE(rows >= 0, "argmax_key_decode: bad sizes");
+  if (rows == 0) return B200_OK;
+  B200_REQUIRE(out && keys, "argmax_key_decode: null pointer");
+  return launch_k(argmax_key_decode_kernel, dim3((unsigned)ceil_div(rows, 128)), dim3(128), 0, (cudaStream_t)stream, 1, true,
+                  out, reinterpret_cast<const long long*>(keys), rows);
+}
+
+// ---- decode prologue: token embedding gather (+ positions = seq_lens - 1) -------------------------------------------------
+// hidden[t, :] = table[ids[t], :] (VocabParallelEmbedding.forward with a replicated table, vocab_parallel_embedding.py) and,
+// when seq_lens is given, positions[t] = seq_lens[t] - 1 (forward_batch_info.py:960-962) — one launch in place of an
+// indexing kernel and a subtraction.
+__global__ void __launch_bounds__(128) embedding_kernel(uint8_t* __restrict__ out, const uint8_t* __restrict__ table,
+                                                        const int64_t* __restrict__ ids, int64_t row_bytes, int64_t vocab,
+                                                        int64_t* __restrict__ positions, const int64_t* __restrict__ seq_lens) {
+  pdl_trigger();
+  pdl_wait();
+  const int64_t t = blockIdx.x;
+  int64_t id = ids[t];
+  if (id < 0 || id >= vocab) id = 0;  // out-of-range ids read row 0 instead of faulting (padded graph slots)
+  const int4* src = reinterpret_cast<const int4*>(table + id * row_bytes);
+  int4* dst = reinterpret_cast<int4*>(out + t * row_bytes);
+  for (int64_t i = threadIdx.x; i < row_bytes / 16; i += blockDim.x) dst[i] = ld_nc_v4(src + i);
+  if (positions != nullptr && threadIdx.x == 0) positions[t] = seq_lens[t] - 1;
+}
+
+B200_API int b200_embedding(void* out, const void* table, const int64_t* ids, int64_t T, int64_t H, int64_t vocab, int dtype,
+                            int64_t* positions, const int64_t* seq_lens, void* stream) {
+  B200_REQUIRE(T >= 0 && H > 0 && vocab > 0, "embedding: bad sizes");
+  if (T == 0) return B200_OK;
+  B200_REQUIRE(out && table && ids, "embedding: null pointer");
+  B200_REQUIRE((positions == nullptr) == (seq_lens == nullptr), "embedding: positions and seq_lens go together");
+  if (dtype != B200_BF16 && dtype != B200_F16) return fail(B200_ERR_UNSUPPORTED, "embedding: dtype %d not supported", dtype);
+  B200_REQUIRE((H * 2) % 16 == 0 && ((uintptr_t)out % 16) == 0 && ((uintptr_t)table % 16) == 0, "embedding: rows must be 16-byte multiples");
+  return launch_k(embedding_kernel, dim3((unsigned)T), dim3(128), 0, (cudaStream_t)stream, 1, true, (uint8_t*)out,
+                  (const uint8_t*)table, ids, H * 2, vocab, positions, seq_lens);
 }

@@ -7,7 +7,7 @@ namespace b200 {
 
 using namespace sm100;
 
-enum GemmMode { kModeI8 = 0, kModeF8Chan = 1, kModeF8Block = 2 };
+enum GemmMode { kModeI8 = 0, kModeF8Chan = 1, kModeF8Block = 2, kModeBF16 = 3, kModeF16 = 4 };  // 3/4: un-scaled 16-bit operands
 
 struct GemmArgs {
   void* out;             // [M, N] bf16/f16

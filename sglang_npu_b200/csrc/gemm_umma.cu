@@ -46,7 +46,7 @@ __device__ __forceinline__ float finalize(uint32_t bits, float sm, float sn, boo
   float v;
   if constexpr (MODE == kModeI8) v = __fmul_rn(__fmul_rn(sm, (float)(int32_t)bits), sn);  // (As * C) * Bs
   else if constexpr (MODE == kModeF8Chan) v = __fmul_rn(__fmul_rn(__uint_as_float(bits), sm), sn);
-  else v = __uint_as_float(bits);
+  else v = __uint_as_float(bits);  // block-FP8 (already promoted) and the un-scaled 16-bit modes
   return has_bias ? __fadd_rn(v, bias) : v;
 }
 
@@ -625,7 +625,8 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
                     uint32_t* __restrict__ partials) {
   using L = StreamK<BN>;
   constexpr int STAGES = L::kStages;
-  constexpr int kKind = MODE == kModeI8 ? kKindI8 : kKindF8;
+  constexpr bool kDense16 = MODE == kModeBF16 || MODE == kModeF16;  // un-scaled bf16 / f16 operands (lm_head)
+  constexpr int kKind = MODE == kModeI8 ? kKindI8 : kDense16 ? kKindF16 : kKindF8;
   constexpr int kWBytes = 128 * kBK;
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint32_t s_tmem_base;
@@ -708,8 +709,11 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
   } else if (warp == 1) {
     pdl_wait();
     if (lane == 0) {
-      constexpr uint32_t idesc = MODE == kModeI8 ? make_idesc(/*s32*/ 2, /*int8*/ 1, 1, 128, BN)
-                                                 : make_idesc(/*f32*/ 1, /*e4m3*/ 0, 0, 128, BN);
+      // kind::f16 operand formats: 0 = f16, 1 = bf16; a 128-byte K block is 64 16-bit elements = 4 UMMAs of K = 16
+      constexpr uint32_t idesc = MODE == kModeI8     ? make_idesc(/*s32*/ 2, /*int8*/ 1, 1, 128, BN)
+                                 : MODE == kModeBF16 ? make_idesc(/*f32*/ 1, /*bf16*/ 1, 1, 128, BN)
+                                 : MODE == kModeF16  ? make_idesc(/*f32*/ 1, /*f16*/ 0, 0, 128, BN)
+                                                     : make_idesc(/*f32*/ 1, /*e4m3*/ 0, 0, 128, BN);
       int it = 0, seg = 0;
       for (int u = u0; u < u1; ++seg) {
         const int tile = u / nkb;
@@ -743,7 +747,7 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
     const bool bf = g.out_is_bf16 != 0;
     const int m_cols = min(BN, (g.M + 15) & ~15);  // token columns that hold data, in groups of 16
     // per-token scales of this launch -> shared memory (the inner loops below touch no global memory but their stores)
-    for (int i = threadIdx.x - 128; i < BN; i += 128) s_scale_m[i] = i < g.M ? g.scale_m[i] : 0.f;
+    for (int i = threadIdx.x - 128; i < BN; i += 128) s_scale_m[i] = (!kDense16 && i < g.M) ? g.scale_m[i] : 0.f;
     epi_bar_sync();
     uint32_t fix_phase = 0;
     int seg = 0;
@@ -791,7 +795,7 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
         const bool n_ok = n < g.N;
         float sn = 0.f, bias = 0.f;
         if (n_ok) {
-          sn = g.scale_n[n];
+          if constexpr (!kDense16) sn = g.scale_n[n];
           if (has_bias) bias = load_bias(g.bias, n, g.out_is_bf16);
         }
         // This is the CTA's last segment when it has peers: every MMA has retired, so the TMA ring is free and the
@@ -1049,6 +1053,44 @@ static int run_gemm(GemmArgs g, const void* a, const void* b, int64_t M, int64_t
   return launch_gemm<MODE, 128, 4, false>(ta, tb, g, grid, st);
 }
 
+// Un-scaled bf16 / f16 weight-streaming GEMM for decode-size M (lm_head): the stream-K kernel with kind::f16 MMAs.
+template <int MODE>
+static int run_dense16(GemmArgs g, const void* a, const void* b, int64_t M, int64_t N, int64_t K, cudaStream_t st, void* ws,
+                       size_t ws_bytes) {
+  g.M = (int)M;
+  g.N = (int)N;
+  g.num_kb = (int)ceil_div(K * 2, kBK);
+  g.trace = g_trace;
+  g.trace_slots = (int)g_trace_slots;
+  g.splits = 1;
+  g.kb_per_split = g.num_kb;
+  const size_t need = streamk_workspace_bytes(M);
+  if (ws == nullptr || ws_bytes < need)
+    return fail(B200_ERR_WORKSPACE, "dense_gemm_nt: workspace of %zu bytes, %zu needed", ws_bytes, need);
+  B200_REQUIRE(((uintptr_t)ws % 16) == 0, "dense_gemm_nt: workspace must be 16-byte aligned");
+  const int bn = streamk_bn(M);
+  const int tiles = (int)ceil_div(N, 128);
+  const int64_t units = (int64_t)tiles * g.num_kb;
+  B200_REQUIRE(units < (1ll << 30), "dense_gemm_nt: too many work units");
+  const int sms = sm_count();
+  int ctas = (int)(units < sms ? units : sms);
+  if (tiles < sms) {
+    const int per_tile = sms / tiles < g.num_kb ? sms / tiles : g.num_kb;
+    if (tiles * per_tile * 100 >= sms * 85) ctas = tiles * per_tile;
+  }
+  CUtensorMap tw, tx;
+  int rc;
+  if ((rc = cached_tmap(&tw, b, (uint64_t)N, (uint64_t)K * 2, 128)) != B200_OK) return rc;
+  if ((rc = cached_tmap(&tx, a, (uint64_t)M, (uint64_t)K * 2, (uint32_t)bn)) != B200_OK) return rc;
+  switch (bn) {
+    case 16: return launch_streamk<MODE, 16>(tw, tx, g, (int)units, ctas, ws, st);
+    case 32: return launch_streamk<MODE, 32>(tw, tx, g, (int)units, ctas, ws, st);
+    case 64: return launch_streamk<MODE, 64>(tw, tx, g, (int)units, ctas, ws, st);
+    case 128: return launch_streamk<MODE, 128>(tw, tx, g, (int)units, ctas, ws, st);
+    default: return launch_streamk<MODE, 256>(tw, tx, g, (int)units, ctas, ws, st);
+  }
+}
+
 static int check_common(const char* what, const void* out, const void* a, const void* b, int64_t M, int64_t N,
                         int64_t K, int out_dtype) {
   B200_REQUIRE(M >= 0 && N > 0 && K > 0, "%s: bad sizes", what);
@@ -1120,4 +1162,21 @@ B200_API int b200_fp8_blockwise_scaled_mm(void* out, const void* a, const void* 
   g.sm_rs = sa_row_stride; g.sm_cs = sa_col_stride; g.sn_rs = sb_row_stride; g.sn_cs = sb_col_stride;
   g.out_is_bf16 = out_dtype == B200_BF16;
   return run_gemm<kModeF8Block>(g, a, b, M, N, K, (cudaStream_t)stream, workspace, workspace_bytes);
+}
+
+B200_API int b200_dense_gemm_nt(void* out, const void* a, const void* b, const void* bias, int64_t M, int64_t N, int64_t K,
+                                int dtype, void* workspace, size_t workspace_bytes, void* stream) {
+  // out[M, N] = a[M, K] . b[N, K]^T (+ bias), bf16 or f16 operands and output, fp32 accumulation in TMEM.
+  // Decode-size M only (<= 256): the lm_head / logits GEMM of a decode step or of the last tokens of a prefill chunk.
+  int rc = check_common("dense_gemm_nt", out, a, b, M, N, K, dtype);
+  if (rc != B200_OK) return rc;
+  if (M == 0) return B200_OK;
+  B200_REQUIRE(K % 8 == 0, "dense_gemm_nt: K %lld must be a multiple of 8 (16-byte rows)", (long long)K);
+  if (M > 256) return fail(B200_ERR_UNSUPPORTED, "dense_gemm_nt: M %lld > 256 (weight-streaming sizes only)", (long long)M);
+  GemmArgs g = {};
+  g.out = out; g.bias = bias;
+  g.out_is_bf16 = dtype == B200_BF16;
+  if (dtype == B200_BF16)
+    return run_dense16<kModeBF16>(g, a, b, M, N, K, (cudaStream_t)stream, workspace, workspace_bytes);
+  return run_dense16<kModeF16>(g, a, b, M, N, K, (cudaStream_t)stream, workspace, workspace_bytes);
 }

@@ -367,6 +367,36 @@ def int8_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Ten
     return (out, acc) if return_acc else out
 
 
+def _out_buffer(out: Optional[torch.Tensor], M: int, N: int, dtype: torch.dtype, device, what: str) -> torch.Tensor:
+    """`out=` of the GEMM wrappers: the symmetric buffer of the fused TP exchange for row-parallel layers."""
+    if out is None:
+        return torch.empty((M, N), device=device, dtype=dtype)
+    if tuple(out.shape) != (M, N) or out.dtype != dtype or not out.is_contiguous():
+        raise RuntimeError(f"{what}: `out` must be a contiguous [M, N] tensor of the output dtype")
+    return out
+
+
+def dense_gemm_nt(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None,
+                  out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """a [M, K] @ b [N, K]^T (+ bias) for bf16 / f16, decode-size M (<= 256): the lm_head GEMM
+    (logits_processor.py:470-500) on the weight-streaming tcgen05 kernel instead of a library call."""
+    require_cuda(a, b, bias)
+    lib = _cabi.load()
+    if a.dim() != 2 or b.dim() != 2 or a.shape[1] != b.shape[1] or a.dtype != b.dtype:
+        raise RuntimeError("dense_gemm_nt: a [M, K] and b [N, K] of one dtype expected")
+    if a.stride(1) != 1 or a.stride(0) != a.shape[1] or b.stride(1) != 1 or b.stride(0) != b.shape[1]:
+        raise RuntimeError("dense_gemm_nt: operands must be row-major contiguous")
+    M, K = a.shape
+    N = b.shape[0]
+    out = _out_buffer(out, M, N, a.dtype, a.device, "dense_gemm_nt")
+    if bias is not None:
+        bias = bias.to(a.dtype).contiguous()
+    ws = _scaled_mm_workspace(lib, a.device, M, N, K)
+    check(lib.b200_dense_gemm_nt(ptr(out), ptr(a), ptr(b), ptr(bias), M, N, K, dtype_code(a.dtype), ptr(ws), ws.numel(),
+                                 stream_ptr(a.device)), "b200_dense_gemm_nt")
+    return out
+
+
 # ---- fp8 ---------------------------------------------------------------------------------------------
 def sgl_per_token_group_quant_fp8(x: torch.Tensor, group_size: int = 128, eps: float = 1e-10,
                                   column_major_scales: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
@@ -407,7 +437,8 @@ def sgl_per_token_quant_fp8(x: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor
 
 def fp8_blockwise_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tensor,
                             scales_b: torch.Tensor, out_dtype: torch.dtype,
-                            bias: Optional[torch.Tensor] = None, cluster_splitk: bool = False) -> torch.Tensor:
+                            bias: Optional[torch.Tensor] = None, cluster_splitk: bool = False,
+                            out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """sgl_kernel.fp8_blockwise_scaled_mm (gemm.py:32-42): mat_a [M,K] e4m3 row-major, mat_b [K,N]
     e4m3 column-major (weight.T), scales_a [M, K/128], scales_b [K/128, N/128] (weight_scale.T)."""
     require_cuda(mat_a, mat_b, scales_a, scales_b)
@@ -421,7 +452,7 @@ def fp8_blockwise_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: 
     if scales_a.shape != (M, K // 128) or scales_b.shape != (K // 128, N // 128):
         raise RuntimeError("fp8_blockwise_scaled_mm: scale shapes must be [M,K/128] and [K/128,N/128]")
     assert scales_a.dtype == torch.float32 and scales_b.dtype == torch.float32
-    out = torch.empty((M, N), device=mat_a.device, dtype=out_dtype)
+    out = _out_buffer(out, M, N, out_dtype, mat_a.device, "fp8_blockwise_scaled_mm")
     if bias is not None:
         bias = bias.to(out_dtype).contiguous()
     # `cluster_splitk=True` passes no workspace: decode sizes then take the cluster split-K kernel instead of the
@@ -438,7 +469,7 @@ def fp8_blockwise_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: 
 
 def fp8_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tensor,
                   scales_b: torch.Tensor, out_dtype: torch.dtype,
-                  bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+                  bias: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """sgl_kernel.fp8_scaled_mm: per-token x per-channel scaled e4m3 GEMM."""
     require_cuda(mat_a, mat_b, scales_a, scales_b)
     lib = _cabi.load()
@@ -448,7 +479,7 @@ def fp8_scaled_mm(mat_a: torch.Tensor, mat_b: torch.Tensor, scales_a: torch.Tens
         raise RuntimeError("fp8_scaled_mm: mat_b must be [K,N] column-major")
     scales_a = scales_a.to(torch.float32).contiguous()
     scales_b = scales_b.to(torch.float32).contiguous()
-    out = torch.empty((M, N), device=mat_a.device, dtype=out_dtype)
+    out = _out_buffer(out, M, N, out_dtype, mat_a.device, "fp8_scaled_mm")
     if bias is not None:
         bias = bias.to(out_dtype).contiguous()
     ws = _scaled_mm_workspace(lib, mat_a.device, M, N, K)
@@ -475,7 +506,7 @@ def awq_dequantize(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Te
 
 
 def awq_gemm(x: torch.Tensor, qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor,
-             bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+             bias: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Fused dequant + matmul: x [M,K] @ W(qweight, scales, qzeros) [K,N] (+bias) (awq.py:401-418)."""
     require_cuda(x, qweight, scales, qzeros)
     lib = _cabi.load()
@@ -485,7 +516,7 @@ def awq_gemm(x: torch.Tensor, qweight: torch.Tensor, scales: torch.Tensor, qzero
     x2 = x.reshape(-1, K).contiguous()
     M = x2.shape[0]
     assert x.dtype == scales.dtype
-    out = torch.empty((M, N), device=x.device, dtype=x.dtype)
+    out = _out_buffer(out, M, N, x.dtype, x.device, "awq_gemm")
     if bias is not None:
         bias = bias.to(x.dtype).contiguous()
     check(lib.b200_awq_gemm(ptr(out), ptr(x2), ptr(qweight), ptr(scales), ptr(qzeros), ptr(bias), M, N, K, G,
@@ -734,4 +765,49 @@ def argmax(logits: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Te
         _ARGMAX_WS[logits.device.index] = ws
     check(lib.b200_argmax(ptr(out), ptr(logits), rows, V, logits.stride(0), dtype_code(logits.dtype), ptr(ws), ws.numel(),
                           stream_ptr(logits.device)), "b200_argmax")
+    return out
+
+
+def argmax_key(logits: torch.Tensor, index_offset: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Per-row int64 key (value bits, ~global index) of this rank's [rows, V_local] logits slice: max-combine the
+    keys over the TP ranks, then `argmax_key_decode`.  Vocab-parallel replacement of all-gather + argmax."""
+    require_cuda(logits, out)
+    lib = _cabi.load()
+    assert logits.dim() == 2 and logits.stride(1) == 1
+    rows, V = logits.shape
+    if out is None:
+        out = torch.empty(rows, dtype=torch.int64, device=logits.device)
+    assert out.dtype == torch.int64 and out.is_contiguous() and out.numel() == rows
+    ws = _ARGMAX_WS.get(logits.device.index)
+    if ws is None or ws.numel() < rows * 16:
+        ws = torch.zeros(max(rows, 1024) * 16, dtype=torch.uint8, device=logits.device)
+        _ARGMAX_WS[logits.device.index] = ws
+    check(lib.b200_argmax_key(ptr(out), ptr(logits), rows, V, logits.stride(0), dtype_code(logits.dtype), int(index_offset),
+                              ptr(ws), ws.numel(), stream_ptr(logits.device)), "b200_argmax_key")
+    return out
+
+
+def argmax_key_decode(keys: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    require_cuda(keys, out)
+    lib = _cabi.load()
+    assert keys.dtype == torch.int64 and keys.is_contiguous()
+    if out is None:
+        out = torch.empty_like(keys)
+    check(lib.b200_argmax_key_decode(ptr(out), ptr(keys), keys.numel(), stream_ptr(keys.device)), "b200_argmax_key_decode")
+    return out
+
+
+def embedding(ids: torch.Tensor, table: torch.Tensor, seq_lens: Optional[torch.Tensor] = None,
+              positions: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """table[ids] (one launch); with seq_lens + positions also writes positions = seq_lens - 1 (decode prologue)."""
+    require_cuda(ids, table, seq_lens, positions, out)
+    lib = _cabi.load()
+    assert ids.dtype == torch.int64 and ids.is_contiguous() and table.is_contiguous() and table.dim() == 2
+    T, (V, H) = ids.numel(), table.shape
+    if out is None:
+        out = torch.empty((T, H), dtype=table.dtype, device=table.device)
+    if seq_lens is not None:
+        assert seq_lens.dtype == torch.int64 and positions.dtype == torch.int64 and positions.numel() == T
+    check(lib.b200_embedding(ptr(out), ptr(table), ptr(ids), T, H, V, dtype_code(table.dtype), ptr(positions), ptr(seq_lens),
+                             stream_ptr(table.device)), "b200_embedding")
     return out

@@ -130,6 +130,11 @@ class B200TPComm:
             return act, self._y(M)
         return act if quant else self._y(M)
 
+    def reduce_rmsnorm(self, M: int, weight: torch.Tensor, eps: float, residual: Optional[torch.Tensor]) -> torch.Tensor:
+        """The exchange for linear methods that quantise their own input (FP8, AWQ) or none at all: all-reduce of the
+        partial sums + residual add + RMSNorm, every rank receiving the normalised [M, hidden] rows."""
+        return self.reduce_rmsnorm_quant_int8(M, weight, eps, residual, quant=False, normed=True)
+
     def check(self) -> None:
         """Synchronise the current stream and raise if an exchange kernel of this rank gave up waiting for a peer
         (B200_TP_TIMEOUT_MS).  Call it where the reference would surface an NCCL timeout: after a step, before results

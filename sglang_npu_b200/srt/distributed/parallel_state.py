@@ -72,6 +72,14 @@ def tensor_model_parallel_all_reduce(x: torch.Tensor) -> torch.Tensor:
     return x
 
 
+def tensor_model_parallel_all_reduce_max(x: torch.Tensor) -> torch.Tensor:
+    """In-place max over the TP group (the 8-byte-per-row key exchange of the vocab-parallel greedy sampler)."""
+    if _TP_SIZE == 1:
+        return x
+    dist.all_reduce(x, op=dist.ReduceOp.MAX, group=_TP_GROUP)
+    return x
+
+
 def tensor_model_parallel_all_gather(x: torch.Tensor, dim: int = -1) -> torch.Tensor:
     if _TP_SIZE == 1:
         return x

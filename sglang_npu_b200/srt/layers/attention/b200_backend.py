@@ -49,7 +49,7 @@ def _round_up(x: int, m: int) -> int:
 
 
 def plan_decode_splits(batch: int, num_kv_heads: int, group: int, max_len: int, sm_count: int,
-                       forced_chunk: int = 0, max_chunk: int = 2048):
+                       forced_chunk: int = 0, max_chunk: int = 2048, exact: bool = True):
     """Pick (kv_chunk, max_splits) for the split-KV decode kernel.
 
     One CTA handles one (request, KV head, <=16 q heads, chunk); aim for ~3 waves of the
@@ -58,6 +58,9 @@ def plan_decode_splits(batch: int, num_kv_heads: int, group: int, max_len: int, 
     Fewer, longer chunks win once the chip is covered a few times: every chunk costs a pipeline
     fill and an fp32 partial that stage 2 reads back (cfg 2, measured: 5 chunks of 832 tokens
     8.374 ms/step, 2 chunks of 2048 8.311 ms/step; kernel alone 0.1915 vs 0.1874 ms).
+    exact=False: `max_len` is a worst-case bound, not the batch's longest request (graph capture / no host lengths) —
+    evening the chunks against it would mis-size them for the requests that actually run (a 4k batch planned under a
+    4k+32 bound got 3 x 1376 instead of 2 x 2048: +8 % kernel time).
     max_chunk: the FP8-KV kernel (3 CTAs/SM, half the bytes per token) is best at 1024 (0.118 vs 0.128 ms at 2048).
     """
     max_len = max(int(max_len), 1)
@@ -72,8 +75,11 @@ def plan_decode_splits(batch: int, num_kv_heads: int, group: int, max_len: int, 
             # (bs 256 x 2048 tokens x 1 KV head: 1 chunk 0.064 ms, 4 chunks 0.071 ms, 8 chunks 0.075 ms)
             chunk = max_chunk
         chunk = min(max(chunk, 256), max_chunk)
-        splits = (max_len + chunk - 1) // chunk
-        chunk = min(_round_up((max_len + splits - 1) // splits, 16), max_chunk)
+        if exact:  # max_len is the longest request of THIS batch: make its chunks even
+            splits = (max_len + chunk - 1) // chunk
+            chunk = min(_round_up((max_len + splits - 1) // splits, 16), max_chunk)
+        else:      # max_len is only a bound (CUDA-graph capture): keep whole tiles; splits past a request's end exit at once
+            chunk = _round_up(chunk, 128)
     chunk = max(16, min(chunk, 4096))
     return chunk, (max_len + chunk - 1) // chunk
 
@@ -102,6 +108,8 @@ class B200AttnBackend(AttentionBackend):
         self.min_shared_prefix = int(os.environ.get("B200_MIN_SHARED_PREFIX", "1024"))
         self._max_chunk = 1024 if model_runner.token_to_kv_pool.dtype == torch.float8_e4m3fn else 2048
         self.forward_metadata: Optional[ForwardMetadata] = None
+        self.capture_shared_prefix_len = 0
+        self._kv_dtype = model_runner.token_to_kv_pool.dtype
         self._workspace: Optional[torch.Tensor] = None
         self._graph_workspace: Optional[torch.Tensor] = None
         self._graph_max_bs = 0
@@ -111,6 +119,9 @@ class B200AttnBackend(AttentionBackend):
         self.qo_indptr = torch.zeros((max_bs + 1,), dtype=torch.int32, device=self.device)
 
     # ---- metadata -------------------------------------------------------------------------
+    def _shared_prefix_supported(self) -> bool:
+        return self._kv_dtype in (torch.bfloat16, torch.float16)
+
     def _decode_workspace(self, bs: int, max_splits: int, graph: bool = False) -> Optional[torch.Tensor]:
         if max_splits <= 1:
             return None
@@ -129,7 +140,8 @@ class B200AttnBackend(AttentionBackend):
         bs = forward_batch.batch_size
         group = self.num_head // self.num_kv_head
         if mode.is_decode_or_idle():
-            if forward_batch.seq_lens_cpu is not None:
+            exact = forward_batch.seq_lens_cpu is not None
+            if exact:
                 max_len = int(forward_batch.seq_lens_cpu.max()) if bs > 0 else 1
             else:
                 max_len = self.max_context_len  # no host sync: plan for the worst case
@@ -139,11 +151,10 @@ class B200AttnBackend(AttentionBackend):
             shared = int(getattr(forward_batch, "shared_prefix_len", 0) or 0)
             if shared and forward_batch.seq_lens_cpu is not None and bs > 0:
                 shared = min(shared, int(forward_batch.seq_lens_cpu.min()) - 1)  # every request keeps >= 1 own token
-            kv_dtype = forward_batch.token_to_kv_pool.dtype
-            if shared >= self.min_shared_prefix and bs >= 2 and kv_dtype in (torch.bfloat16, torch.float16):
+            if shared >= self.min_shared_prefix and bs >= 2 and self._shared_prefix_supported():
                 shared = shared // 128 * 128  # whole KV tiles for the prefix pass; the remainder stays per-request
                 chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, max(max_len - shared, 1),
-                                                   self.sm_count, self.forced_chunk, self._max_chunk)
+                                                   self.sm_count, self.forced_chunk, self._max_chunk, exact)
                 seg = kernels.plan_shared_prefix_segments(shared, bs, self.num_head, self.sm_count)
                 n_seg = (shared + seg - 1) // seg
                 self.forward_metadata = ForwardMetadata(
@@ -151,7 +162,7 @@ class B200AttnBackend(AttentionBackend):
                     workspace=self._decode_workspace(bs, n_seg + splits))
                 return
             chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, max_len, self.sm_count,
-                                               self.forced_chunk, self._max_chunk)
+                                               self.forced_chunk, self._max_chunk, exact)
             self.forward_metadata = ForwardMetadata(kv_chunk=chunk, max_splits=splits,
                                                     workspace=self._decode_workspace(bs, splits))
         else:
@@ -184,7 +195,7 @@ class B200AttnBackend(AttentionBackend):
         self._graph_max_bs = max_bs
         group = self.num_head // self.num_kv_head
         _, splits = plan_decode_splits(1, self.num_kv_head, group, self.max_context_len, self.sm_count,
-                                       self.forced_chunk, self._max_chunk)
+                                       self.forced_chunk, self._max_chunk, exact=False)
         self._decode_workspace(max_bs, max(splits, 2), graph=True)
 
     def init_forward_metadata_capture_cuda_graph(self, bs: int, num_tokens: int, req_pool_indices, seq_lens,
@@ -192,8 +203,19 @@ class B200AttnBackend(AttentionBackend):
         if not forward_mode.is_decode_or_idle():
             raise NotImplementedError("B200AttnBackend: CUDA graphs are captured for DECODE only")
         group = self.num_head // self.num_kv_head
+        # Extension: `capture_shared_prefix_len` (set by the graph runner before capture) captures the shared-prefix
+        # decode for a batch whose radix-matched common prefix has that many tokens; 16-bit and e4m3 KV caches alike.
+        shared = int(self.capture_shared_prefix_len or 0) // 128 * 128
+        if shared >= self.min_shared_prefix and bs >= 2 and self._shared_prefix_supported():
+            chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, max(self.max_context_len - shared, 1),
+                                               self.sm_count, self.forced_chunk, self._max_chunk, exact=False)
+            seg = kernels.plan_shared_prefix_segments(shared, bs, self.num_head, self.sm_count)
+            n_seg = (shared + seg - 1) // seg
+            self.forward_metadata = ForwardMetadata(kv_chunk=chunk, max_splits=splits, shared_prefix_len=shared, seg_len=seg,
+                                                    workspace=self._decode_workspace(bs, n_seg + splits, graph=True))
+            return
         chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, self.max_context_len, self.sm_count,
-                                           self.forced_chunk, self._max_chunk)
+                                           self.forced_chunk, self._max_chunk, exact=False)
         self.forward_metadata = ForwardMetadata(kv_chunk=chunk, max_splits=splits,
                                                 workspace=self._decode_workspace(bs, splits, graph=True))
 
@@ -232,7 +254,8 @@ class B200AttnBackend(AttentionBackend):
         if layer.qk_head_dim != layer.v_head_dim:
             raise NotImplementedError("B200AttnBackend: qk_head_dim != v_head_dim is out of scope")
 
-    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, int8_out: bool = False):
+    def forward_decode(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, int8_out: bool = False,
+                       kv_in_cache: bool = False):
         """int8_out=True returns the output already per-token int8-quantised (kernels.Int8Activation) for a W8A8-int8
         o_proj: the quant is fused into the split-KV merge kernel."""
         self._check_layer(layer)
@@ -261,7 +284,11 @@ class B200AttnBackend(AttentionBackend):
             **({} if pool.dtype == q.dtype else dict(zip(("k_scale", "v_scale"), self._kv_scales(layer)))))
         return act if int8_out else o
 
-    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, int8_out: bool = False):
+    def forward_extend(self, q, k, v, layer, forward_batch, save_kv_cache: bool = True, int8_out: bool = False,
+                       kv_in_cache: bool = False):
+        """kv_in_cache=True (with save_kv_cache=False): the caller has ALREADY written this chunk's K/V into the pool
+        (the fused rope + KV-write launch), so the kernel reads new and cached tokens alike through the page table — the
+        same path as after its own write — instead of gathering the new tokens from the strided qkv activations."""
         self._check_layer(layer)
         q = q.reshape(-1, layer.tp_q_head_num * layer.qk_head_dim)
         o = torch.empty_like(q)
@@ -298,8 +325,8 @@ class B200AttnBackend(AttentionBackend):
             return o
         kernels.extend_attention_fwd(
             q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
-            None if save_kv_cache else k.view(-1, layer.tp_k_head_num, layer.qk_head_dim),
-            None if save_kv_cache else v.view(-1, layer.tp_v_head_num, layer.v_head_dim),
+            None if (save_kv_cache or kv_in_cache) else k.view(-1, layer.tp_k_head_num, layer.qk_head_dim),
+            None if (save_kv_cache or kv_in_cache) else v.view(-1, layer.tp_v_head_num, layer.v_head_dim),
             o.view(-1, layer.tp_q_head_num, layer.v_head_dim),
             pool.get_key_buffer(layer.layer_id), pool.get_value_buffer(layer.layer_id),
             forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,

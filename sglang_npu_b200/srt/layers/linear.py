@@ -26,12 +26,19 @@ class UnquantizedLinearMethod(LinearMethodBase):
 
     def create_weights(self, layer, input_size_per_partition, output_partition_sizes, input_size, output_size,
                        params_dtype, **extra):
-        weight = Parameter(torch.empty(sum(output_partition_sizes), input_size_per_partition, dtype=params_dtype),
-                           requires_grad=False)
+        # a TP-aware parameter (reference linear.py:181-194 registers input_dim=1 / output_dim=0 on the plain weight),
+        # so layers that fall back to this method (quant ignore lists, quant_config=None) shard through the same loaders
+        from .parameter import ModelWeightParameter
+
+        weight = ModelWeightParameter(torch.empty(sum(output_partition_sizes), input_size_per_partition, dtype=params_dtype),
+                                      weight_loader=extra.get("weight_loader"), input_dim=1, output_dim=0)
         layer.register_parameter("weight", weight)
 
-    def apply(self, layer, x, bias=None):
-        return torch.nn.functional.linear(x, layer.weight, bias)
+    def apply(self, layer, x, bias=None, out=None):
+        if out is not None and bias is None:
+            return torch.matmul(x, layer.weight.t(), out=out.view(*x.shape[:-1], layer.weight.shape[0]))
+        res = torch.nn.functional.linear(x, layer.weight, bias)
+        return res if out is None else out.copy_(res.view(out.shape))
 
 
 class LinearBase(nn.Module):

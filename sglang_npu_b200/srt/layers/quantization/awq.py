@@ -110,7 +110,9 @@ class B200AWQLinearMethod(LinearMethodBase):
         layer.qzeros = Parameter(layer.qzeros.data, requires_grad=False)
         layer.scales = Parameter(layer.scales.data, requires_grad=False)
 
-    def apply(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def apply(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None,
+              out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """`out` (optional, beyond the reference signature): destination of the [M, N] result (fused TP exchange)."""
         out_shape = x.shape[:-1] + (layer.qweight.shape[-1] * self.quant_config.pack_factor,)
-        out = kernels.awq_gemm(x.reshape(-1, x.shape[-1]), layer.qweight, layer.scales, layer.qzeros, bias)
-        return out.reshape(out_shape)
+        res = kernels.awq_gemm(x.reshape(-1, x.shape[-1]), layer.qweight, layer.scales, layer.qzeros, bias, out=out)
+        return res.reshape(out_shape)

@@ -116,12 +116,15 @@ class B200Fp8LinearMethod(LinearMethodBase):
         layer.weight = Parameter(layer.weight.data, requires_grad=False)
         layer.weight_scale_inv = Parameter(layer.weight_scale_inv.data, requires_grad=False)
 
-    def apply(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def apply(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None,
+              out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """`out` (optional, beyond the reference signature): destination of the [M, N] result — the symmetric buffer
+        of the fused TP exchange for row-parallel layers."""
         input_2d = x.view(-1, x.shape[-1])
         q_input, x_scale = kernels.sgl_per_token_group_quant_fp8(input_2d, self.quant_config.weight_block_size[1])
-        out = kernels.fp8_blockwise_scaled_mm(q_input, layer.weight.t(), x_scale, layer.weight_scale_inv.t(),
-                                              out_dtype=x.dtype, bias=bias)
-        return out.view(*x.shape[:-1], layer.weight.shape[0])
+        res = kernels.fp8_blockwise_scaled_mm(q_input, layer.weight.t(), x_scale, layer.weight_scale_inv.t(),
+                                              out_dtype=x.dtype, bias=bias, out=out)
+        return res.view(*x.shape[:-1], layer.weight.shape[0])
 
 
 class B200W8A8Fp8Config(QuantizationConfig):
@@ -181,8 +184,8 @@ class B200W8A8Fp8LinearMethod(LinearMethodBase):
             layer._b200_w_transposed = True
         layer.weight_scale = Parameter(layer.weight_scale.data, requires_grad=False)
 
-    def apply(self, layer, x, bias=None):
+    def apply(self, layer, x, bias=None, out=None):
         x2 = x.view(-1, x.shape[-1])
         x_q, x_s = kernels.sgl_per_token_quant_fp8(x2)
-        out = kernels.fp8_scaled_mm(x_q, layer.weight, x_s, layer.weight_scale, out_dtype=x.dtype, bias=bias)
-        return out.view(*x.shape[:-1], out.shape[-1])
+        res = kernels.fp8_scaled_mm(x_q, layer.weight, x_s, layer.weight_scale, out_dtype=x.dtype, bias=bias, out=out)
+        return res.view(*x.shape[:-1], res.shape[-1])

@@ -111,7 +111,9 @@ class PagedTokenToKVPoolAllocator:
 
     def alloc_decode_fused(self, req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
                            seq_lens: torch.Tensor) -> Optional[torch.Tensor]:
-        if not self._ensure_pages(seq_lens - 1, seq_lens):
+        # a decode step needs at most one new page per request: skip the device-side estimate (and its host sync)
+        # whenever the free list covers that bound
+        if seq_lens.numel() > len(self.free_pages) and not self._ensure_pages(seq_lens - 1, seq_lens):
             return None
         out_indices = torch.empty((seq_lens.numel(),), dtype=torch.int64, device=self.device)
         kernels.alloc_decode(seq_lens, None, self.free_pages, out_indices, self.ret_values, self.page_size,

@@ -19,7 +19,8 @@ from torch import nn
 
 from ... import kernels
 from ..distributed.parallel_state import (get_tensor_model_parallel_rank, get_tensor_model_parallel_world_size,
-                                          get_tp_comm, tensor_model_parallel_all_gather)
+                                          get_tp_comm, tensor_model_parallel_all_gather,
+                                          tensor_model_parallel_all_reduce_max)
 from ..layers.linear import MergedColumnParallelLinear, QKVParallelLinear, RowParallelLinear
 from ..layers.radix_attention import RadixAttention
 
@@ -39,6 +40,7 @@ class StackConfig:
     qkv_bias: bool = False
     context_len: int = 4096
     is_encoder_decoder: bool = False
+    tie_word_embeddings: bool = False  # lm_head shares the embedding matrix (HF config of Qwen2.5-0.5B; qwen2.py:419-421)
 
     def get_num_kv_heads(self, tp: int) -> int:
         return max(1, self.num_kv_heads // tp)
@@ -46,7 +48,8 @@ class StackConfig:
 
 # shapes from the reference's own benchmark table (sgl-kernel/benchmark/bench_int8_gemm.py:15-58) + HF configs
 CONFIGS = {
-    "qwen2.5-0.5b": StackConfig("qwen2.5-0.5b", 896, 24, 14, 2, 64, 4864, 151936, 1e6, 1e-6, True),
+    "qwen2.5-0.5b": StackConfig("qwen2.5-0.5b", 896, 24, 14, 2, 64, 4864, 151936, 1e6, 1e-6, True,
+                                tie_word_embeddings=True),
     "llama-3.1-8b": StackConfig("llama-3.1-8b", 4096, 32, 32, 8, 128, 14336, 128256, 5e5, 1e-5, False),
     "qwen2.5-32b": StackConfig("qwen2.5-32b", 5120, 64, 40, 8, 128, 27648, 152064, 1e6, 1e-6, True),
     "llama-3.1-70b": StackConfig("llama-3.1-70b", 8192, 80, 64, 8, 128, 28672, 128256, 5e5, 1e-5, False),
@@ -96,6 +99,8 @@ class DecoderLayer(nn.Module):
             return self.forward_fused_int8_tp(positions, hidden_states, forward_batch, residual, cos_sin_cache, comm)
         if self.fused_int8:
             return self.forward_fused_int8(positions, hidden_states, forward_batch, residual, cos_sin_cache)
+        if comm is not None:
+            return self.forward_fused_tp(positions, hidden_states, forward_batch, residual, cos_sin_cache, comm)
         eps = self.cfg.rms_norm_eps
         if residual is None:
             residual = hidden_states
@@ -104,8 +109,13 @@ class DecoderLayer(nn.Module):
             kernels.fused_add_rmsnorm(hidden_states, residual, self.input_layernorm, eps)
         qkv, _ = self.qkv_proj(hidden_states)
         q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
-        kernels.apply_rope_neox_inplace(positions, q, k, self.cfg.head_dim, cos_sin_cache)
-        attn_out = self.attn(q, k, v, forward_batch)
+        pool = forward_batch.token_to_kv_pool
+        cast_kv = pool.dtype != q.dtype  # FP8 KV cache: rope only here, the backend's cast-and-scatter writes the cache
+        kernels.rope_neox_set_kv(positions, q, k, v, self.cfg.head_dim, cos_sin_cache,
+                                 None if cast_kv else pool.get_key_buffer(self.attn.layer_id),
+                                 None if cast_kv else pool.get_value_buffer(self.attn.layer_id),
+                                 None if cast_kv else forward_batch.out_cache_loc)
+        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=cast_kv, kv_in_cache=not cast_kv)
         hidden_states, _ = self.o_proj(attn_out)
         kernels.fused_add_rmsnorm(hidden_states, residual, self.post_attention_layernorm, eps)
         gate_up, _ = self.gate_up_proj(hidden_states)
@@ -130,7 +140,8 @@ class DecoderLayer(nn.Module):
                                  None if cast_kv else pool.get_key_buffer(self.attn.layer_id),
                                  None if cast_kv else pool.get_value_buffer(self.attn.layer_id),
                                  None if cast_kv else forward_batch.out_cache_loc)
-        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=cast_kv, int8_out=self.fuse_attn_quant)
+        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=cast_kv, int8_out=self.fuse_attn_quant,
+                             kv_in_cache=not cast_kv)
         hidden_states, _ = self.o_proj(attn_out)
         act = kernels.rmsnorm_quant_int8(hidden_states, self.post_attention_layernorm, eps, residual=residual)
         gate_up, _ = self.gate_up_proj(act)
@@ -159,12 +170,41 @@ class DecoderLayer(nn.Module):
                                  None if cast_kv else pool.get_key_buffer(self.attn.layer_id),
                                  None if cast_kv else pool.get_value_buffer(self.attn.layer_id),
                                  None if cast_kv else forward_batch.out_cache_loc)
-        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=cast_kv, int8_out=self.fuse_attn_quant)
+        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=cast_kv, int8_out=self.fuse_attn_quant,
+                             kv_in_cache=not cast_kv)
         self.o_proj(attn_out, can_fuse_mlp_allreduce=True, out=comm.partial(M))
         act = comm.reduce_rmsnorm_quant_int8(M, self.post_attention_layernorm, eps, residual)
         gate_up, _ = self.gate_up_proj(act)
         hidden_states, _ = self.down_proj(kernels.silu_and_mul_quant_int8(gate_up), can_fuse_mlp_allreduce=True,
                                           out=comm.partial(M))
+        return hidden_states, residual
+
+
+    def forward_fused_tp(self, positions, hidden_states, forward_batch, residual, cos_sin_cache, comm):
+        """TP > 1, FP8 / AWQ / un-quantised linears, with the fused exchange: the same protocol as
+        forward_fused_int8_tp, but the exchange kernel hands every rank the normalised rows in the activation dtype
+        (the reference's allreduce + rmsnorm fusion, layers/flashinfer_comm_fusion.py) and the linear method quantises
+        them itself.  Replaces dist.all_reduce + fused_add_rmsnorm per row-parallel linear."""
+        eps = self.cfg.rms_norm_eps
+        M = hidden_states.shape[0]
+        if residual is None:
+            residual = hidden_states
+            act = kernels.rmsnorm(hidden_states, self.input_layernorm, eps)
+        else:
+            act = comm.reduce_rmsnorm(M, self.input_layernorm, eps, residual)
+        qkv, _ = self.qkv_proj(act)
+        q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
+        pool = forward_batch.token_to_kv_pool
+        cast_kv = pool.dtype != q.dtype
+        kernels.rope_neox_set_kv(positions, q, k, v, self.cfg.head_dim, cos_sin_cache,
+                                 None if cast_kv else pool.get_key_buffer(self.attn.layer_id),
+                                 None if cast_kv else pool.get_value_buffer(self.attn.layer_id),
+                                 None if cast_kv else forward_batch.out_cache_loc)
+        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=cast_kv, kv_in_cache=not cast_kv)
+        self.o_proj(attn_out, can_fuse_mlp_allreduce=True, out=comm.partial(M))
+        act = comm.reduce_rmsnorm(M, self.post_attention_layernorm, eps, residual)
+        gate_up, _ = self.gate_up_proj(act)
+        hidden_states, _ = self.down_proj(kernels.silu_and_mul(gate_up), can_fuse_mlp_allreduce=True, out=comm.partial(M))
         return hidden_states, residual
 
 
@@ -190,27 +230,51 @@ class LayerStack(nn.Module):
                              compute_cos_sin_cache(cfg.head_dim, max_positions or cfg.context_len + 8, cfg.rope_theta),
                              persistent=False)
 
-    def forward(self, input_ids, positions, forward_batch):
-        hidden_states = self.embed_tokens[input_ids]
+    def forward(self, input_ids, positions, forward_batch, seq_lens_for_positions=None):
+        """`seq_lens_for_positions` (decode): the embedding launch also writes positions = seq_lens - 1
+        (forward_batch_info.py:960-962) into `positions`."""
+        hidden_states = kernels.embedding(input_ids, self.embed_tokens, seq_lens_for_positions,
+                                          positions if seq_lens_for_positions is not None else None)
         residual = None
-        comm = get_tp_comm() if (self.tp_size > 1 and self.layers and self.layers[0].fused_int8) else None
+        comm = get_tp_comm() if (self.tp_size > 1 and len(self.layers) > 0) else None
         if comm is not None and hidden_states.shape[0] > comm.max_tokens:
             comm = None  # larger than the symmetric buffers: NCCL all-reduce path
         for layer in self.layers:
             hidden_states, residual = layer(positions, hidden_states, forward_batch, residual, self.cos_sin_cache, comm)
         if comm is not None and len(self.layers) > 0:
             # final norm = the last exchange: every rank receives the normalised rows of all tokens
-            return comm.reduce_rmsnorm_quant_int8(hidden_states.shape[0], self.norm, self.cfg.rms_norm_eps, residual,
-                                                  quant=False, normed=True)
+            return comm.reduce_rmsnorm(hidden_states.shape[0], self.norm, self.cfg.rms_norm_eps, residual)
         kernels.fused_add_rmsnorm(hidden_states, residual, self.norm, self.cfg.rms_norm_eps)
         return hidden_states
 
+    def local_logits(self, hidden_states):
+        """This rank's [M, vocab_per_rank] slice of the logits (logits_processor.py:470-500).  Decode-size M runs the
+        repo's own weight-streaming tcgen05 GEMM; a larger M (every position of a prefill chunk — not something the
+        greedy path asks for) is a plain library GEMM."""
+        if hidden_states.shape[0] <= 256:
+            return kernels.dense_gemm_nt(hidden_states.contiguous(), self.lm_head)
+        return torch.matmul(hidden_states, self.lm_head.t())
+
     def logits(self, hidden_states):
-        """lm_head is a plain bf16 library GEMM (cuBLAS via torch), vocab-parallel + all-gather."""
-        local = torch.matmul(hidden_states, self.lm_head.t())
+        """Full logits: vocab-parallel lm_head + all-gather (what a non-greedy sampler needs)."""
+        local = self.local_logits(hidden_states)
         if self.tp_size > 1:
             local = tensor_model_parallel_all_gather(local, dim=-1)
         return local[..., : self.cfg.vocab_size]
+
+    def greedy(self, hidden_states, out=None, key_buf=None):
+        """Greedy next-token ids (sampler.py: argmax over the logits).  At TP > 1 the logits are never gathered: each
+        rank reduces its vocabulary slice to one 8-byte (value, global index) key per row and the ranks max-combine
+        the keys — 8 B/row on the wire instead of 2 * vocab B/row."""
+        local = self.local_logits(hidden_states)
+        if self.tp_size == 1:
+            return kernels.argmax(local[:, : self.cfg.vocab_size], out=out)
+        rank = get_tensor_model_parallel_rank()
+        valid = max(0, min(self.vocab_per_rank, self.cfg.vocab_size - rank * self.vocab_per_rank))
+        assert valid > 0, "vocab-parallel argmax: a rank without vocabulary rows"
+        keys = kernels.argmax_key(local[:, :valid], rank * self.vocab_per_rank, out=key_buf)
+        tensor_model_parallel_all_reduce_max(keys)
+        return kernels.argmax_key_decode(keys, out=out)
 
 
 # ---- seeded synthetic weights through the layers' own loaders ----------------------------------------
@@ -246,10 +310,7 @@ def load_synthetic_weights(stack: LayerStack, seed: int = 1234, device="cuda", g
                     lin.weight_loader(p, t, sid) if sid is not None else lin.weight_loader(p, t)
             elif method == "UnquantizedLinearMethod":
                 w = _gen((n, in_size), gen, device, "dense", in_size, gain).to(dt)
-                if sid is not None:
-                    _load_plain_merged(lin, w, sid)
-                else:
-                    lin.weight_loader(lin.weight, w)
+                lin.weight_loader(lin.weight, w, sid) if sid is not None else lin.weight_loader(lin.weight, w)
             else:
                 from ..layers.quantization import synthetic  # fp8 / awq generators live with their methods
 
@@ -286,19 +347,9 @@ def load_synthetic_weights(stack: LayerStack, seed: int = 1234, device="cuda", g
             lo, hi = max(r, rows0), min(r + n, rows0 + rows)
             if lo < hi:
                 p.data[lo - rows0: hi - rows0].copy_(blk[lo - r: hi - r].to(dt))
-
-
-def _load_plain_merged(lin, w, sid):
-    """Unquantised merged/QKV weight: shard one logical sub-matrix into the fused [N_local, K] weight."""
-    from ..layers.linear import QKVParallelLinear
-
-    if isinstance(lin, QKVParallelLinear):
-        q_sz, kv_sz = lin.num_heads * lin.head_size, lin.num_kv_heads * lin.head_size
-        off = {"q": 0, "k": q_sz, "v": q_sz + kv_sz}[sid]
-        size = q_sz if sid == "q" else kv_sz
-        rank = lin.tp_rank if sid == "q" else lin.tp_rank // lin.num_kv_head_replicas
-    else:
-        size = lin.output_sizes[sid] // lin.tp_size
-        off = sum(lin.output_sizes[:sid]) // lin.tp_size
-        rank = lin.tp_rank
-    lin.weight.data[off: off + size].copy_(w[rank * size: (rank + 1) * size])
+    if cfg.tie_word_embeddings:  # this rank's vocabulary slice of the embedding matrix (rows past the vocabulary: zero)
+        lo = rank * stack.vocab_per_rank
+        hi = min(lo + stack.vocab_per_rank, cfg.vocab_size)
+        stack.lm_head.data.zero_()
+        if hi > lo:
+            stack.lm_head.data[: hi - lo].copy_(stack.embed_tokens.data[lo:hi])

@@ -33,6 +33,23 @@ class HostDecodeBatch:
                    (self.input_ids, self.req_pool_indices, self.seq_lens, self.out_cache_loc))
 
 
+@dataclass
+class HostExtendBatch:
+    """One chunked-prefill step as the scheduler hands it over (pinned host memory), schedule_batch.py:1180-1302:
+    `input_ids` / `out_cache_loc` / `positions` hold the NEW tokens of every request back to back."""
+    input_ids: torch.Tensor         # [T] int64
+    req_pool_indices: torch.Tensor  # [bs] int64
+    seq_lens: torch.Tensor          # [bs] int64 (prefix + new)
+    prefix_lens: torch.Tensor       # [bs] int64 (radix-cache hit / earlier chunks)
+    out_cache_loc: torch.Tensor     # [T] int64
+    positions: torch.Tensor         # [T] int64
+
+    def nbytes(self) -> int:
+        return sum(t.numel() * t.element_size() for t in
+                   (self.input_ids, self.req_pool_indices, self.seq_lens, self.prefix_lens, self.out_cache_loc,
+                    self.positions))
+
+
 class HotPathRunner:
     def __init__(self, cfg: StackConfig, quant_config, *, max_reqs: int, max_total_tokens: int, page_size: int,
                  context_len: Optional[int] = None, dtype=torch.bfloat16, device="cuda", num_layers: Optional[int] = None,
@@ -71,28 +88,53 @@ class HotPathRunner:
                             seq_lens_sum=0, seq_lens_cpu=seq_lens_cpu, req_to_token_pool=self.req_to_token_pool,
                             token_to_kv_pool=self.token_to_kv_pool, attn_backend=self.attn_backend, **extend)
 
-    def forward_decode(self, input_ids, req_pool_indices, seq_lens, out_cache_loc, seq_lens_cpu=None):
-        fb = self._make_batch(ForwardMode.DECODE, input_ids, req_pool_indices, seq_lens, out_cache_loc, seq_lens_cpu)
+    def forward_decode(self, input_ids, req_pool_indices, seq_lens, out_cache_loc, seq_lens_cpu=None,
+                       shared_prefix_len: int = 0):
+        fb = self._make_batch(ForwardMode.DECODE, input_ids, req_pool_indices, seq_lens, out_cache_loc, seq_lens_cpu,
+                              shared_prefix_len=shared_prefix_len)
         fb.positions = seq_lens - 1  # forward_batch_info.py:960-962
         self.attn_backend.init_forward_metadata(fb)
         hidden = self.model(input_ids, fb.positions, fb)
         return self.model.logits(hidden)
 
     def forward_extend(self, input_ids, req_pool_indices, seq_lens, prefix_lens, out_cache_loc, positions,
-                       seq_lens_cpu=None, extend_seq_lens_cpu=None):
+                       seq_lens_cpu=None, extend_seq_lens_cpu=None, extend_prefix_lens_cpu=None, greedy=False):
+        """`greedy=True` returns the sampled next-token id of every request instead of its last-token logits."""
         ext = (seq_lens - prefix_lens.to(seq_lens.dtype)).to(torch.int32)
         fb = self._make_batch(ForwardMode.EXTEND, input_ids, req_pool_indices, seq_lens, out_cache_loc, seq_lens_cpu,
                               extend_num_tokens=int(input_ids.numel()), extend_seq_lens=ext,
-                              extend_prefix_lens=prefix_lens.to(torch.int32), extend_seq_lens_cpu=extend_seq_lens_cpu)
+                              extend_prefix_lens=prefix_lens.to(torch.int32), extend_seq_lens_cpu=extend_seq_lens_cpu,
+                              extend_prefix_lens_cpu=extend_prefix_lens_cpu)
         fb.positions = positions
         self.attn_backend.init_forward_metadata(fb)
         hidden = self.model(input_ids, positions, fb)
         last = torch.cumsum(ext, 0).long() - 1  # logits of the last token of every request
+        if greedy:
+            return self.model.greedy(hidden[last])
         return self.model.logits(hidden[last])
 
-    # ---- decode CUDA graph at a fixed batch size -------------------------------------------------------
-    def capture_decode_graph(self, bs: int):
+    def prefill_step(self, host_batch: "HostExtendBatch") -> torch.Tensor:
+        """The public end-to-end call of one chunked-prefill step: pinned host index tensors in -> pinned host
+        next-token ids out (synchronous).  Eager launches (the reference captures CUDA graphs for decode only)."""
         dev = self.device
+        d = {k: getattr(host_batch, k).to(dev, non_blocking=True) for k in
+             ("input_ids", "req_pool_indices", "seq_lens", "prefix_lens", "out_cache_loc", "positions")}
+        ext = (host_batch.seq_lens - host_batch.prefix_lens).tolist()
+        ids = self.forward_extend(d["input_ids"], d["req_pool_indices"], d["seq_lens"], d["prefix_lens"], d["out_cache_loc"],
+                                  d["positions"], seq_lens_cpu=host_batch.seq_lens, extend_seq_lens_cpu=ext,
+                                  extend_prefix_lens_cpu=host_batch.prefix_lens.tolist(), greedy=True)
+        if getattr(self, "_host_prefill_out", None) is None or self._host_prefill_out.numel() != ids.numel():
+            self._host_prefill_out = torch.zeros(ids.numel(), dtype=torch.int64).pin_memory()
+        self._host_prefill_out.copy_(ids, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        return self._host_prefill_out
+
+    # ---- decode CUDA graph at a fixed batch size -------------------------------------------------------
+    def capture_decode_graph(self, bs: int, shared_prefix_len: int = 0):
+        """`shared_prefix_len` > 0: every request of the batches this graph will replay shares its first that many
+        tokens (one radix-cache node): the shared-prefix decode is captured."""
+        dev = self.device
+        self.attn_backend.capture_shared_prefix_len = shared_prefix_len
         st = dict(
             input_ids=torch.zeros(bs, dtype=torch.int64, device=dev),
             req_pool_indices=torch.zeros(bs, dtype=torch.int64, device=dev),
@@ -100,6 +142,7 @@ class HotPathRunner:
             out_cache_loc=torch.zeros(bs, dtype=torch.int64, device=dev),
             positions=torch.zeros(bs, dtype=torch.int64, device=dev),
             next_token_ids=torch.zeros(bs, dtype=torch.int64, device=dev),
+            keys=torch.zeros(bs, dtype=torch.int64, device=dev),
         )
         self.attn_backend.init_cuda_graph_state(bs, bs)
         fb = self._make_batch(ForwardMode.DECODE, st["input_ids"], st["req_pool_indices"], st["seq_lens"],
@@ -109,10 +152,10 @@ class HotPathRunner:
         def run_once():
             self.attn_backend.init_forward_metadata_capture_cuda_graph(bs, bs, st["req_pool_indices"], st["seq_lens"],
                                                                       None, ForwardMode.DECODE, None)
-            torch.sub(st["seq_lens"], 1, out=st["positions"])
-            hidden = self.model(st["input_ids"], st["positions"], fb)
-            logits = self.model.logits(hidden)
-            kernels.argmax(logits, out=st["next_token_ids"])  # greedy sampling (sampler.py: torch.argmax(logits, -1))
+            # embedding gather + positions = seq_lens - 1 in one launch; lm_head on the weight-streaming GEMM; greedy
+            # sampling (sampler.py: torch.argmax(logits, -1)) vocab-parallel at TP > 1 (8 bytes per row on the wire)
+            hidden = self.model(st["input_ids"], st["positions"], fb, seq_lens_for_positions=st["seq_lens"])
+            self.model.greedy(hidden, out=st["next_token_ids"], key_buf=st["keys"])
 
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
@@ -140,6 +183,30 @@ class HotPathRunner:
                                                                   seq_lens_cpu)
         self.graph.replay()
         return st["next_token_ids"]
+
+    # ---- a decode loop with the caller-side page-table kernels in it ---------------------------------------------------
+    def attach_allocator(self, allocator) -> None:
+        """`PagedTokenToKVPoolAllocator` whose free pages feed `decode_loop_step`."""
+        self.allocator = allocator
+
+    def decode_loop_step(self, host_batch: HostDecodeBatch) -> torch.Tensor:
+        """One step of a real decode loop (schedule_batch.py:1519-1588 prepare_for_decode + the forward): the scheduler
+        hands over pinned-host input_ids / req_pool_indices / seq_lens (already advanced to include the token being
+        decoded); the KV slot of that token is allocated ON THE DEVICE by the fused get_last_loc + alloc_decode +
+        write_req_to_token_pool launch (csrc/page_table.cu), then the captured graph runs and the sampled ids come back
+        to pinned host memory.  host_batch.out_cache_loc is not read."""
+        st = self._static
+        st["input_ids"].copy_(host_batch.input_ids, non_blocking=True)
+        st["req_pool_indices"].copy_(host_batch.req_pool_indices, non_blocking=True)
+        st["seq_lens"].copy_(host_batch.seq_lens, non_blocking=True)
+        loc = self.allocator.alloc_decode_fused(self.req_to_token_pool.req_to_token, st["req_pool_indices"], st["seq_lens"])
+        if loc is None:
+            raise RuntimeError("decode_loop_step: out of KV pages")
+        st["out_cache_loc"].copy_(loc, non_blocking=True)
+        self.graph.replay()
+        self._host_out.copy_(st["next_token_ids"], non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return self._host_out
 
     def decode_step(self, host_batch: HostDecodeBatch) -> torch.Tensor:
         """The public end-to-end call: pinned host indices in -> pinned host next-token ids out (synchronous)."""

@@ -196,3 +196,80 @@ def test_argmax_matches_torch(cuda_device, rows, V, dtype):
     pad = torch.full((rows, V + 8), 100.0, dtype=dtype, device=cuda_device)
     pad[:, :V] = xd
     assert torch.equal(kernels.argmax(pad[:, :V]).cpu(), ref)
+
+
+# ---- decode prologue / epilogue pieces of SURVEY §8f #4: embedding gather, lm_head GEMM, vocab-parallel greedy ----------
+@pytest.mark.parametrize("M,N,K", [(1, 1024, 512), (5, 4096, 896), (64, 16032, 4096), (200, 2056, 1024), (256, 1000, 5120)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_dense_gemm_nt_lm_head(cuda_device, M, N, K, dtype):
+    """logits = hidden @ lm_head.T (logits_processor.py:470-500) on the weight-streaming tcgen05 kernel vs an fp32
+    matmul of the same 16-bit operands; ragged N (not a multiple of the 128-row tile) and K (not of the 64-element
+    TMA box) included.  Tolerance: one rounding of the fp32 sum to the output dtype."""
+    g = torch.Generator().manual_seed(M * 7 + N)
+    a = (torch.randn(M, K, generator=g) * 0.5).to(dtype)
+    b = (torch.randn(N, K, generator=g) / math.sqrt(K)).to(dtype)
+    ref = a.float() @ b.float().t()
+    out = kernels.dense_gemm_nt(a.to(cuda_device), b.to(cuda_device))
+    assert out.dtype == dtype and tuple(out.shape) == (M, N)
+    ulp = 2.0 ** -8 if dtype == torch.bfloat16 else 2.0 ** -11
+    tol = ref.abs() * ulp + 1e-3
+    assert ((out.cpu().float() - ref).abs() <= tol).all(), (out.cpu().float() - ref).abs().max()
+    assert_close_path(out, ref, "dense_gemm_nt")
+
+
+def test_dense_gemm_nt_bias_and_bounds(cuda_device):
+    g = torch.Generator().manual_seed(3)
+    a = torch.randn(8, 256, generator=g).bfloat16()
+    b = (torch.randn(384, 256, generator=g) / 16).bfloat16()
+    bias = torch.randn(384, generator=g).bfloat16()
+    out = kernels.dense_gemm_nt(a.to(cuda_device), b.to(cuda_device), bias=bias.to(cuda_device))
+    assert_close_path(out, a.float() @ b.float().t() + bias.float(), "dense_gemm_nt + bias")
+    with pytest.raises(RuntimeError, match="M 300 > 256"):
+        kernels.dense_gemm_nt(torch.zeros(300, 256, dtype=torch.bfloat16, device=cuda_device), b.to(cuda_device))
+
+
+@pytest.mark.parametrize("T,V,H", [(1, 100, 64), (64, 128256, 4096), (13, 5000, 896)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_embedding_gather_and_positions(cuda_device, T, V, H, dtype):
+    """hidden = table[ids] bit-exact (a copy), positions = seq_lens - 1 in the same launch (forward_batch_info.py:960-962)."""
+    g = torch.Generator(device=cuda_device).manual_seed(T)
+    table = torch.randn(V, H, generator=g, device=cuda_device).to(dtype)
+    ids = torch.randint(0, V, (T,), generator=g, device=cuda_device)
+    ids[0] = V - 1
+    seq = torch.randint(1, 4096, (T,), generator=g, device=cuda_device)
+    pos = torch.full((T,), -7, dtype=torch.int64, device=cuda_device)
+    out = kernels.embedding(ids, table, seq, pos)
+    assert torch.equal(out, table[ids]) and torch.equal(pos, seq - 1)
+    assert torch.equal(kernels.embedding(ids, table), table[ids])  # without the positions half
+
+
+@pytest.mark.parametrize("tp", [2, 8])
+@pytest.mark.parametrize("rows,V", [(1, 1000), (64, 128256), (7, 152064)])
+def test_vocab_parallel_argmax_keys(cuda_device, rows, V, tp):
+    """Per-rank keys max-combined == torch.argmax over the gathered logits (what logits_processor.py + sampler.py do),
+    including exact ties across and inside ranks (lowest global index wins) and a ragged last rank."""
+    g = torch.Generator(device=cuda_device).manual_seed(rows + tp)
+    logits = torch.randn(rows, V, generator=g, device=cuda_device).bfloat16()
+    if rows > 1:
+        logits[1, V - 1] = 50.0     # the maximum on the last rank's last column
+        logits[0, 5] = 60.0         # a tie between rank 0 ...
+        logits[0, V - 3] = 60.0     # ... and the last rank
+    per = (V + tp - 1) // tp // 8 * 8 + 8
+    keys = None
+    for r in range(tp):
+        lo, hi = min(r * per, V), min((r + 1) * per, V)
+        if hi <= lo:
+            continue
+        local = logits[:, lo:hi]
+        assert local.stride(0) == V
+        if (local.data_ptr() % 16) != 0:  # the kernel reads 16-byte vectors: a TP rank's slice is its own allocation
+            local = local.contiguous()
+        k = kernels.argmax_key(local, lo)
+        assert (k >= 0).all()
+        keys = k if keys is None else torch.maximum(keys, k)
+    out = kernels.argmax_key_decode(keys)
+    # expected: first index of the maximum (bf16 values are exact in fp32)
+    exp = torch.argmax(logits.float(), dim=-1)
+    mx = logits.float().amax(dim=-1, keepdim=True)
+    first = torch.where(logits.float() == mx, torch.arange(V, device=cuda_device).expand(rows, V), V).amin(dim=-1)
+    assert torch.equal(out, first), (out, first, exp)

@@ -112,6 +112,10 @@ def test_decode_split_planner_invariants():
                     chunk, splits = plan(bs, hkv, group, max_len, 148, 0, cap)
                     assert chunk % 16 == 0 and 16 <= chunk <= cap
                     assert splits * chunk >= max_len and (splits - 1) * chunk < max_len
+                    chunk, splits = plan(bs, hkv, group, max_len, 148, 0, cap, exact=False)
+                    assert chunk % 128 == 0 and 128 <= chunk <= cap and splits * chunk >= max_len
     assert plan(64, 8, 4, 4096, 148) == (2048, 2)          # BASELINE config 2
     assert plan(64, 8, 4, 4096, 148, 0, 1024) == (1024, 4)  # ... with an FP8 KV cache
     assert plan(64, 8, 4, 4096, 148, forced_chunk=48) == (48, 86)
+    # a captured graph planned under a bound a few decode steps past 4k keeps the 2048-token chunks of the 4k batch
+    assert plan(64, 8, 4, 4096 + 32, 148, exact=False) == (2048, 3)

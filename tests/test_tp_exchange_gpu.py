@@ -32,3 +32,64 @@ def test_fused_exchange_matches_nccl_path(cuda_device):
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     checks = [l for l in lines if "ok" in l]
     assert len(checks) >= 9 and all(l["ok"] for l in checks), checks
+
+
+@pytest.mark.parametrize("tp,M", [(2, 64), (2, 7), (4, 64), (8, 100)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_exchange_kernel_loopback_all_ranks_on_one_gpu(cuda_device, tp, M, dtype):
+    """The exchange kernel itself on a single-GPU box: all `tp` ranks live in THIS process, each with its own buffer
+    set and stream on the same device, and the kernels meet through the same flag protocol they use over NVLink
+    (the pointer tables simply hold local addresses).  Checked against the un-fused chain: fp32 rank-order sum of the
+    partials -> fused_add_rmsnorm -> per-token int8 quant (bit-exact), for the int8 output (W8A8-int8 consumers) and
+    the normalised 16-bit output (FP8 / AWQ consumers).  A rank that never gets scheduled next to its peers makes the
+    barrier time out (B200_TP_TIMEOUT_MS) and the test fail — it cannot hang the box."""
+    import ctypes
+
+    from sglang_npu_b200 import _cabi, kernels
+    from sglang_npu_b200._cabi import dtype_code
+
+    os.environ.setdefault("B200_TP_TIMEOUT_MS", "4000")
+    lib = _cabi.load()
+    dev = cuda_device
+    H, eps, max_blocks = 4096, 1e-5, 64
+    g = torch.Generator(device=dev).manual_seed(tp * 100 + M)
+    w = (1 + 0.1 * torch.randn(H, generator=g, device=dev)).to(dtype)
+    partial = [torch.randn(M, H, generator=g, device=dev).to(dtype) for _ in range(tp)]
+    residual0 = torch.randn(M, H, generator=g, device=dev).to(dtype)
+    xq = [torch.zeros(M, H, dtype=torch.int8, device=dev) for _ in range(tp)]
+    xs = [torch.zeros(M, dtype=torch.float32, device=dev) for _ in range(tp)]
+    y = [torch.zeros(M, H, dtype=dtype, device=dev) for _ in range(tp)]
+    flags = [torch.zeros(2 * 8 * max_blocks, dtype=torch.int32, device=dev) for _ in range(tp)]
+    epoch = [torch.zeros(max_blocks, dtype=torch.int32, device=dev) for _ in range(tp)]
+    err = [torch.zeros(64, dtype=torch.int32, device=dev) for _ in range(tp)]
+    residual = [residual0.clone() for _ in range(tp)]
+    arr = lambda ts: (ctypes.c_void_p * tp)(*[t.data_ptr() for t in ts])  # noqa: E731
+    streams = [torch.cuda.Stream(device=dev) for _ in range(tp)]
+    torch.cuda.synchronize(dev)
+    for rep in range(2):  # twice: epochs / flags are reused across launches
+        for r in range(tp):
+            rc = lib.b200_tp_reduce_rmsnorm_quant_int8(arr(partial), arr(xq), arr(xs), arr(y), arr(flags), epoch[r].data_ptr(),
+                                                       residual[r].data_ptr(), w.data_ptr(), M, H, eps, tp, r, max_blocks,
+                                                       dtype_code(dtype), err[r].data_ptr(), streams[r].cuda_stream)
+            kernels.check(rc, "b200_tp_reduce_rmsnorm_quant_int8")
+        torch.cuda.synchronize(dev)
+        for r in range(tp):
+            assert int(err[r][0]) == 0, f"rank {r}: barrier timed out (code {int(err[r][0]):#x})"
+        # the un-fused chain on the same inputs
+        tot = torch.zeros(M, H, dtype=torch.float32, device=dev)
+        for p in partial:
+            tot += p.float()
+        ar = tot.to(dtype)
+        per = (M + tp - 1) // tp
+        for r in range(tp):
+            rows = slice(min(M, r * per), min(M, (r + 1) * per))
+            if rows.start == rows.stop:
+                continue
+            res_ref = (residual0 if rep == 0 else res_after)[rows].clone()  # noqa: F821
+            act, yn = kernels.rmsnorm_quant_int8(ar[rows].clone(), w, eps, residual=res_ref, return_normed=True)
+            for dst in range(tp):  # every rank received rank r's rows
+                assert torch.equal(xq[dst][rows], act.x_q), f"int8 rows of rank {r} differ on rank {dst}"
+                assert torch.equal(xs[dst][rows].view(torch.int32), act.x_scale.view(-1).view(torch.int32))
+                assert torch.equal(y[dst][rows].view(torch.int16), yn.view(torch.int16))
+            assert torch.equal(residual[r][rows].view(torch.int16), res_ref.view(torch.int16)), "owner's residual rows"
+        res_after = torch.cat([residual[r][min(M, r * per): min(M, (r + 1) * per)] for r in range(tp)])

@@ -149,8 +149,23 @@ def test_kv_head_replication_when_tp_exceeds_kv_heads():
     assert lin.num_heads == 2 and lin.num_kv_heads == 1 and lin.num_kv_head_replicas == 2
     full_k = torch.arange(2 * 64 * 256, dtype=torch.float32).view(128, 256).bfloat16()
     lin.weight.data.zero_()
-    from sglang_npu_b200.srt.model_executor.layer_stack import _load_plain_merged
-
-    _load_plain_merged(lin, full_k, "k")
+    lin.weight_loader(lin.weight, full_k, "k")  # the layer's own loader on the un-quantised fallback parameter
     assert torch.equal(lin.weight.data[128:192], full_k[64:128])  # rank 3 -> kv head 3 // 2 = 1
     assert CONFIGS["llama-3.1-70b"].get_num_kv_heads(8) == 1 and CONFIGS["qwen2.5-32b"].get_num_kv_heads(2) == 4
+
+
+def test_unquantized_fallback_layers_shard_through_their_own_loaders():
+    """Layers on the un-quantised fallback (quant ignore lists, quant_config=None) load at tp > 1 through the layer's
+    own weight_loader: row-parallel narrows the input dim, merged-column shards each logical sub-matrix
+    (reference linear.py:181-194 registers input_dim=1 / output_dim=0 on the plain weight)."""
+    from sglang_npu_b200.srt.layers.linear import MergedColumnParallelLinear, RowParallelLinear
+
+    full = torch.arange(32 * 64, dtype=torch.float32).view(32, 64).bfloat16()
+    row = RowParallelLinear(64, 32, bias=False, params_dtype=torch.bfloat16, tp_rank=1, tp_size=2)
+    row.weight_loader(row.weight, full)
+    assert torch.equal(row.weight.data, full[:, 32:64])
+    merged = MergedColumnParallelLinear(64, [32, 32], bias=False, params_dtype=torch.bfloat16, tp_rank=1, tp_size=2)
+    merged.weight.data.zero_()
+    merged.weight_loader(merged.weight, full, 0)
+    merged.weight_loader(merged.weight, full + 1, 1)
+    assert torch.equal(merged.weight.data[:16], full[16:32]) and torch.equal(merged.weight.data[16:], (full + 1)[16:32])

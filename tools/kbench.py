@@ -80,6 +80,7 @@ def bench_decode(args):
     kv_bytes = sum(lens) * 2 * hkv * d * k.element_size()
     for chunk in ([args.chunk] if args.chunk else [0, 256, 512, 1024, 2048]):
         ch, splits = plan_decode_splits(bs, hkv, hq // hkv, max(lens), 148, chunk)
+        splits += args.extra_splits  # a graph captured under a longer context bound: trailing splits exit at once
         ws = torch.empty(max(kernels.decode_attn_workspace_bytes(bs, hq, d, splits), 16), dtype=torch.uint8, device=dev)
         fn = lambda: kernels.decode_attention_fwd(q, k, v, o, r2t, rpi, sl, ws, ch, splits, d ** -0.5)
         if args.shared:  # shared-prefix (cascade) decode next to the plain kernel on the same batch
@@ -248,6 +249,8 @@ if __name__ == "__main__":
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--m", type=int, default=0)
     ap.add_argument("--ragged", action="store_true")
+    ap.add_argument("--extra-splits", type=int, default=0, dest="extra_splits",
+                    help="decode: over-provision the split grid (a graph captured under a longer context bound)")
     ap.add_argument("--fp8kv", action="store_true", help="decode: FP8 (e4m3) KV cache")
     ap.add_argument("--shared", type=int, default=0, help="decode: every request shares this many leading tokens")
     ap.add_argument("--cluster", action="store_true", help="gemm_int8: cluster split-K kernel instead of stream-K")

@@ -198,49 +198,59 @@ def main():
             out[name] = round(t.item(), 2)
         say(rank, check="exchange_timing", M=M, H=H, tp=world, **out)
 
-    # ---- 2. layer-stack parity --------------------------------------------------------------------------------------------
-    from sglang_npu_b200.srt.layers.quantization.w8a8_int8 import B200W8A8Int8Config
+    # ---- 2. layer-stack parity: every linear method, fused exchange vs NCCL all-reduce; vocab-parallel greedy -----------
+    from sglang_npu_b200.srt.layers.quantization import get_quantization_config
     from sglang_npu_b200.srt.model_executor.layer_stack import CONFIGS
     from sglang_npu_b200.srt.model_executor.model_runner import HotPathRunner
 
-    cfg = copy.deepcopy(CONFIGS["llama-3.1-8b"])
-    cfg.vocab_size = 4096
-    bs, page = 16, 16
-    lens = [100 + 3 * i for i in range(bs)]
-    pb = synth.make_paged_batch(lens, page, seed=3)
-    logits = {}
-    for mode in ("0", "1"):
-        os.environ["B200_TP_FUSED_EXCHANGE"] = mode
-        if mode == "0" and ps.get_tp_comm() is not None:
-            ps.get_tp_comm().close()
-            ps._TP_COMM = None
-        runner = HotPathRunner(cfg, B200W8A8Int8Config(), max_reqs=pb.req_to_token.shape[0], max_total_tokens=pb.num_slots,
-                               page_size=page, context_len=pb.req_to_token.shape[1] - 4, device=dev, num_layers=3,
-                               tp_size=world, seed=1234)
-        runner.req_to_token_pool.req_to_token.copy_(pb.req_to_token)
-        gk = torch.Generator(device=dev).manual_seed(9)
-        for buf in runner.token_to_kv_pool.k_buffer + runner.token_to_kv_pool.v_buffer:
-            buf.normal_(generator=gk)
-        ids = torch.randint(0, cfg.vocab_size, (bs,), generator=torch.Generator().manual_seed(1)).to(dev)
-        loc = torch.stack([pb.req_to_token[pb.req_pool_indices[i], lens[i] - 1] for i in range(bs)]).long().to(dev)
-        out = runner.forward_decode(ids, pb.req_pool_indices.to(dev), pb.seq_lens.to(dev), loc, seq_lens_cpu=pb.seq_lens)
-        torch.cuda.synchronize()
-        logits[mode] = out.float().clone()
-        assert (runner.tp_comm is not None) == (mode == "1")
-        del runner
-    diff = (logits["0"] - logits["1"]).abs().max().item()
-    same_tokens = bool((logits["0"].argmax(-1) == logits["1"].argmax(-1)).all())
-    cos = torch.nn.functional.cosine_similarity(logits["0"].flatten(), logits["1"].flatten(), dim=0).item()
-    # tp > 2: the two paths round the exchanged sums differently (NCCL per hop, the fused kernel once)
-    top2 = logits["0"].topk(2, dim=-1).values
-    sure = (top2[:, 0] - top2[:, 1]) > 2 * diff  # rows whose greedy token cannot flip within the observed difference
-    sure_same = bool((logits["0"].argmax(-1)[sure] == logits["1"].argmax(-1)[sure]).all())
-    good = (diff == 0.0) if world == 2 else (cos > 0.999 and sure_same)
-    flag = torch.tensor([int(good)], device=dev)
-    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-    ok = ok and bool(flag.item())
-    say(rank, check="stack_logits_fused_vs_nccl", tp=world, max_abs_diff=diff, cosine=cos if world > 2 else 1.0, greedy_tokens_identical=same_tokens, rows_with_margin=int(sure.sum()), identical_on_those=sure_same,
-        ok=bool(flag.item()))
+    qcfg = {"weight_block_size": [128, 128], "activation_scheme": "dynamic", "quant_method": "fp8", "bits": 4,
+            "group_size": 128, "zero_point": True, "w_bit": 4, "q_group_size": 128}
+    for quant, model, adt in (("b200_w8a8_int8", "llama-3.1-8b", torch.bfloat16), ("b200_fp8", "llama-3.1-8b", torch.bfloat16),
+                              ("b200_awq", "qwen2.5-32b", torch.float16)):
+        cfg = copy.deepcopy(CONFIGS[model])
+        cfg.vocab_size = 4096
+        bs, page = 16, 16
+        lens = [100 + 3 * i for i in range(bs)]
+        pb = synth.make_paged_batch(lens, page, seed=3)
+        logits, greedy = {}, {}
+        for mode in ("0", "1"):
+            os.environ["B200_TP_FUSED_EXCHANGE"] = mode
+            if mode == "0" and ps.get_tp_comm() is not None:
+                ps.get_tp_comm().close()
+                ps._TP_COMM = None
+            runner = HotPathRunner(cfg, get_quantization_config(quant).from_config(qcfg), max_reqs=pb.req_to_token.shape[0],
+                                   max_total_tokens=pb.num_slots, page_size=page, context_len=pb.req_to_token.shape[1] - 4,
+                                   device=dev, num_layers=3, tp_size=world, seed=1234, dtype=adt)
+            runner.req_to_token_pool.req_to_token.copy_(pb.req_to_token)
+            gk = torch.Generator(device=dev).manual_seed(9)
+            for buf in runner.token_to_kv_pool.k_buffer + runner.token_to_kv_pool.v_buffer:
+                buf.normal_(generator=gk)
+            ids = torch.randint(0, cfg.vocab_size, (bs,), generator=torch.Generator().manual_seed(1)).to(dev)
+            loc = torch.stack([pb.req_to_token[pb.req_pool_indices[i], lens[i] - 1] for i in range(bs)]).long().to(dev)
+            out = runner.forward_decode(ids, pb.req_pool_indices.to(dev), pb.seq_lens.to(dev), loc, seq_lens_cpu=pb.seq_lens)
+            torch.cuda.synchronize()
+            logits[mode] = out.float().clone()
+            if mode == "1":  # the captured decode graph samples through the vocab-parallel argmax (no logits gather)
+                runner.capture_decode_graph(bs)
+                greedy = runner.replay_decode(ids, pb.req_pool_indices.to(dev), pb.seq_lens.to(dev), loc).clone()
+                torch.cuda.synchronize()
+            assert (runner.tp_comm is not None) == (mode == "1")
+            del runner
+        diff = (logits["0"] - logits["1"]).abs().max().item()
+        same_tokens = bool((logits["0"].argmax(-1) == logits["1"].argmax(-1)).all())
+        cos = torch.nn.functional.cosine_similarity(logits["0"].flatten(), logits["1"].flatten(), dim=0).item()
+        # tp > 2: the two paths round the exchanged sums differently (NCCL per hop, the fused kernel once)
+        top2 = logits["0"].topk(2, dim=-1).values
+        sure = (top2[:, 0] - top2[:, 1]) > 2 * diff  # rows whose greedy token cannot flip within the observed difference
+        sure_same = bool((logits["0"].argmax(-1)[sure] == logits["1"].argmax(-1)[sure]).all())
+        vp_same = bool((greedy == logits["1"].argmax(-1)).all())  # same path, gathered-logits argmax vs key exchange
+        good = ((diff == 0.0) if world == 2 else (cos > 0.999 and sure_same)) and vp_same
+        flag = torch.tensor([int(good)], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok = ok and bool(flag.item())
+        say(rank, check="stack_logits_fused_vs_nccl", quant=quant, tp=world, max_abs_diff=diff, cosine=cos if world > 2 else 1.0,
+            greedy_tokens_identical=same_tokens, rows_with_margin=int(sure.sum()), identical_on_those=sure_same,
+            vocab_parallel_argmax_equals_gathered_argmax=vp_same, ok=bool(flag.item()))
 
     torch.cuda.synchronize()
     dist.barrier()
