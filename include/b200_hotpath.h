@@ -246,14 +246,26 @@ int b200_fp8_scaled_mm(void* out, const void* a, const void* b, const float* sca
  * W[k, 8c+i] = (nib(qweight[k,c], ORDER[i]) - nib(qzeros[k/g,c], ORDER[i])) * scales[k/g, 8c+i],
  * ORDER = [0,4,1,5,2,6,3,7], computed in the scale dtype (sub then mul).
  * b200_awq_gemm fuses that dequantisation into out = x @ W (+bias)
- * (python/sglang/srt/layers/quantization/awq.py:401-418) without materialising W.
+ * (python/sglang/srt/layers/quantization/awq.py:401-418) without materialising W.  It reads the weights in a
+ * streaming layout produced ONCE by b200_awq_repack (the process_weights_after_loading hook, awq.py:396-399):
+ *   qweight_t [ceil(N/256) * ceil(K/128)][256][16] int32 — per (256-channel tile, 128-k block) a 16 KB unit whose rows
+ *             are channels and whose words hold 8 consecutive k of that channel in the AWQ nibble order (16-byte chunks
+ *             XOR-swizzled with (row >> 1) & 3, zero padding past N and K): the caller allocates
+ *             ceil(N/256) * ceil(K/128) * 16384 bytes;
+ *   sz        [K/g, N] uint32 — {scale (low 16 bits), magic + zero point (high 16 bits)}.
+ * The dequantised values are bit-identical to b200_awq_dequantize's.  `workspace` (b200_awq_gemm_workspace_bytes,
+ * 256-byte aligned, zero-initialised ONCE and then owned by the AWQ GEMMs of one stream: it carries a launch epoch
+ * across calls) holds the stream-K state: publish flags and partial accumulators of tiles shared between CTAs.
  */
 int b200_awq_dequantize(void* w_out, const int32_t* qweight, const void* scales,
                         const int32_t* qzeros, int64_t K, int64_t N, int group_size,
                         int dtype, void* stream);
-int b200_awq_gemm(void* out, const void* x, const int32_t* qweight, const void* scales,
-                  const int32_t* qzeros, const void* bias, int64_t M, int64_t N, int64_t K,
-                  int group_size, int dtype, void* stream);
+int b200_awq_repack(int32_t* qweight_t, uint32_t* sz, const int32_t* qweight, const void* scales,
+                    const int32_t* qzeros, int64_t K, int64_t N, int group_size, int dtype, void* stream);
+int b200_awq_gemm_workspace_bytes(size_t* bytes);
+int b200_awq_gemm(void* out, const void* x, const int32_t* qweight_t, const uint32_t* sz, const void* bias,
+                  int64_t M, int64_t N, int64_t K, int group_size, int dtype, void* workspace,
+                  size_t workspace_bytes, void* stream);
 
 /* ---- elementwise steps either side of the path -----------------------------
  * fused_add_rmsnorm (sgl-kernel/csrc/elementwise/fused_add_rms_norm_kernel.cu), silu_and_mul
@@ -380,6 +392,14 @@ int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, void* con
                                       void* epoch, void* residual, const void* weight, int64_t M, int64_t H,
                                       float eps, int tp_size, int tp_rank, int max_blocks, int dtype,
                                       void* err_flag, void* stream);
+/* Test entry: all `tp_size` ranks of ONE exchange in a single cooperative launch on one device (blockIdx.y = rank; the
+ * pointer tables hold local addresses; epoch / residual / err are per rank).  `args_scratch`: >= tp_size * 512 bytes of
+ * device memory.  Lets a single-GPU box execute the exchange kernel's protocol and arithmetic. */
+int b200_tp_exchange_loopback(const void* const* partial_ptrs, void* const* xq_ptrs, void* const* xscale_ptrs,
+                              void* const* y_ptrs, void* const* flag_ptrs, void* const* epoch_ptrs,
+                              void* const* residual_ptrs, const void* weight, int64_t M, int64_t H, float eps,
+                              int tp_size, int max_blocks, int dtype, void* const* err_ptrs, void* args_scratch,
+                              size_t args_scratch_bytes, void* stream);
 /* Synchronises `stream`, then reports (B200_ERR_CUDA + message) a barrier timeout recorded in `err_flag` by an
  * exchange kernel of this rank; B200_OK when every exchange so far met its peers.  The reference's analogue is the
  * NCCL watchdog error surfaced on the next synchronising call. */

@@ -73,7 +73,9 @@ _SIGNATURES = {
                                      c_int64, c_int64, c_int64, c_int, _P, c_size_t, _P],
     "b200_fp8_scaled_mm": [_P, _P, _P, _P, _P, _P, c_int64, c_int64, c_int64, c_int, _P, c_size_t, _P],
     "b200_awq_dequantize": [_P, _P, _P, _P, c_int64, c_int64, c_int, c_int, _P],
-    "b200_awq_gemm": [_P, _P, _P, _P, _P, _P, c_int64, c_int64, c_int64, c_int, c_int, _P],
+    "b200_awq_repack": [_P, _P, _P, _P, _P, c_int64, c_int64, c_int, c_int, _P],
+    "b200_awq_gemm_workspace_bytes": [POINTER(c_size_t)],
+    "b200_awq_gemm": [_P, _P, _P, _P, _P, c_int64, c_int64, c_int64, c_int, c_int, _P, c_size_t, _P],
     "b200_rmsnorm": [_P, _P, _P, _P, c_int64, c_int64, c_float, c_int, _P],
     "b200_silu_and_mul": [_P, _P, c_int64, c_int64, c_int, _P],
     "b200_rope_neox": [_P, _P, _P, _P, c_int64, c_int, c_int, c_int, c_int, c_int64, c_int64,
@@ -101,6 +103,8 @@ _SIGNATURES = {
     "b200_comm_ipc_close": [_P],
     "b200_tp_reduce_rmsnorm_quant_int8": [_P, _P, _P, _P, _P, _P, _P, _P, c_int64, c_int64, c_float, c_int, c_int,
                                           c_int, c_int, _P, _P],
+    "b200_tp_exchange_loopback": [_P, _P, _P, _P, _P, _P, _P, _P, c_int64, c_int64, c_float, c_int, c_int, c_int, _P, _P,
+                                  c_size_t, _P],
     "b200_comm_check": [_P, _P],
 }
 

@@ -14,22 +14,10 @@
 // (fp16 0x6400 = 1024, bf16 0x4300 = 128) turns it into {magic + q} and the zero point is removed with a
 // single packed subtract of {magic + z}.
 //
-// Fused GEMM (`awq_gemm_kernel`), weight-streaming at 0.5 B/weight, one orientation for decode and prefill:
-//   D[n, m] (TMEM, 128 channels x BN tokens) += W^T[n, k] * x[m, k]^T   per 64-wide K block
-//   * raw packed words: TMA (64-byte swizzle) into a RAW-deep ring — 4 KB per K block per CTA, evict-first;
-//   * the group's scales / zero points of the tile ride in the same ring as 1-D bulk copies (no global-latency
-//     stall in the dequant loop);
-//   * 4 dequant groups x 2 warps own alternate K blocks (block i -> group i % 4), so four blocks are being
-//     dequantised concurrently; each turns its block into the fp16 A operand in shared memory, MN-major
-//     SWIZZLE_128B atoms (64 channels x 8 k), one 16-byte store per packed word, bank-conflict free;
-//   * tokens x[m, k]: TMA, K-major SWIZZLE_128B (B operand), evict-last;
-//   * one thread issues tcgen05.mma kind::f16 (M=128, N=BN, K=16) with fp32 accumulators in TMEM;
-//   * split-K over a thread-block cluster (1,1,S): partial accumulators are reduce-scattered through
-//     distributed shared memory and summed in rank order (deterministic, no workspace);
-//   * epilogue: (+bias) -> fp16/bf16 -> out[m, n].
+// The fused GEMM is described at awq_streamk_kernel below.
 #include <cstdlib>
 
-#include "sm100.cuh"
+#include "gemm_common.cuh"
 
 namespace b200 {
 
@@ -57,10 +45,12 @@ __device__ __forceinline__ uint32_t mul2(uint32_t a, uint32_t b) {
   T2 r = __hmul2(*reinterpret_cast<T2*>(&a), *reinterpret_cast<T2*>(&b));
   return *reinterpret_cast<uint32_t*>(&r);
 }
-// {magic + nibble p, magic + nibble p+4} as a packed pair
+// {magic + nibble p, magic + nibble p+4} as a packed pair: one shift and ONE lop3 ((a & b) | c, LUT 0xEA)
 template <typename T>
 __device__ __forceinline__ uint32_t nib_pair(uint32_t word, int p) {
-  return ((word >> (4 * p)) & 0x000f000fu) | AwqMagic<T>::kOr;
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0xEA;\n" : "=r"(r) : "r"(word >> (4 * p)), "r"(0x000f000fu), "r"(AwqMagic<T>::kOr));
+  return r;
 }
 // 8 dequantised weights (output columns 8c .. 8c+7) of one packed word
 template <typename T>
@@ -93,32 +83,110 @@ __global__ void __launch_bounds__(256) awq_dequant_kernel(T* __restrict__ out, c
   *reinterpret_cast<uint4*>(out + idx * 8) = dequant_word<T>(q, zm, s);
 }
 
-// ---- fused GEMM ----------------------------------------------------------------------------------------------
-struct AwqArgs {
-  void* out;              // [M, N]
-  const void* scales;     // [K/g, N]
-  const uint32_t* qzeros; // [K/g, N/8]
-  const void* bias;       // [N] or null
-  int M, N, K, group_size;
-  int num_kb, kb_per_split, splits;
-  int cl;  // CTAs along n that share (multicast) the token tile: cluster dims (cl, 1, splits)
+// ---- checkpoint layout -> streaming layout (process_weights_after_loading) ------------------------------------------
+// qweight [K, N/8] (8 channels of one k per word) -> words that hold 8 consecutive k of ONE channel, in the same nibble
+// order (k offset e sits in nibble ORDER[e] = (e >> 1) + 4 * (e & 1), so `nib_pair(word, p)` is the pair (k = 2p, 2p + 1)
+// — one 32-bit TMEM cell of the MMA's A operand), stored UNIT-MAJOR: qweight_t [ceil(N/256) * ceil(K/128)][256][16] holds,
+// per (256-channel tile, 128-k block), the exact 16 KB shared-memory image the GEMM wants (rows = channels, 64 B = 128 k
+// per row, 16-byte chunks swizzled for conflict-free 16-byte reads; zero padding past N and K).  The stream-K ranges are
+// contiguous in (tile, k block) order, so every CTA reads ONE contiguous byte range of the weights with 16 KB bulk copies;  scales [K/g, N] + qzeros [K/g, N/8] -> sz [K/g, N]
+// uint32 = {scale (low half), magic + zero point (high half)}: one coalesced 4-byte load per (channel, group).
+__device__ __forceinline__ int awq_order(int e) { return (e >> 1) + 4 * (e & 1); }
+
+__global__ void __launch_bounds__(256) awq_repack_weight_kernel(uint32_t* __restrict__ qweight_t,
+                                                                const uint32_t* __restrict__ qweight, int64_t K, int64_t N,
+                                                                int64_t num_kb) {
+  const int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;  // one output word: (channel n, word j of its k run)
+  const int64_t k8 = K / 8;
+  if (idx >= N * k8) return;
+  const int64_t n = idx / k8, j = idx - n * k8;
+  const int sh = 4 * awq_order((int)(n & 7));
+  uint32_t word = 0;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const uint32_t q = (qweight[(j * 8 + e) * (N / 8) + (n >> 3)] >> sh) & 0xFu;
+    word |= q << (4 * awq_order(e));
+  }
+  // unit-major image: unit (tile, kb) = 256 channels x 16 words, the 16-byte chunk index XOR-ed with (row >> 1) & 3
+  const int64_t tile = n >> 8, kb = j >> 4;
+  const int row = (int)(n & 255), jw = (int)(j & 15);
+  const int chunk = (jw >> 2) ^ ((row >> 1) & 3);
+  qweight_t[((tile * num_kb + kb) * 256 + row) * 16 + chunk * 4 + (jw & 3)] = word;
+}
+
+__global__ void __launch_bounds__(256) awq_repack_sz_kernel(uint32_t* __restrict__ sz, const uint16_t* __restrict__ scales,
+                                                            const uint32_t* __restrict__ qzeros, int64_t groups, int64_t N,
+                                                            uint32_t magic16) {
+  const int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;  // (group, n)
+  if (idx >= groups * N) return;
+  const int64_t gi = idx / N, n = idx - gi * N;
+  const uint32_t z = (qzeros[gi * (N / 8) + (n >> 3)] >> (4 * awq_order((int)(n & 7)))) & 0xFu;
+  sz[idx] = (uint32_t)scales[idx] | ((magic16 | z) << 16);  // 1024 + z (f16) / 128 + z (bf16): exact
+}
+
+// ---- fused dequant + GEMM: persistent stream-K weight streaming with the A operand in tensor memory ----------------------
+// D[channel, token] (TMEM, fp32) += W^T[channel, k] * x[token, k]^T, weights on MMA-M, tokens on MMA-N (<= 128 per launch).
+//   * work unit = 256 channels x 128 k: 16 KB of packed words — one contiguous bulk copy of the unit-major image that
+//     awq_repack lays out (a [256 rows x 64 B] box of a row-major matrix touched half a cache line per row) — and two x chunks
+//     [BN tokens x 64 k] (128-byte-swizzled K-major boxes).  One x chunk feeds TWO M=128 MMAs (two channel groups), which
+//     halves the L2 -> SM token traffic per weight byte (at 128 tokens an x tile is 4x the bytes of a 128-channel box);
+//   * the packed words and the x chunks ride SEPARATE rings: the words — the only bytes that come from HBM — get a deep
+//     ring (8-10 units = 128-160 KB in flight per SM, freed as soon as the dequant warps hold them in registers), the x
+//     chunks — L2 hits — a shallow one.  (One ring of [words | x] stages kept only 64 KB of HBM loads in flight: 2.7 TB/s
+//     with the compute switched off.)
+//   * CTA c of a one-CTA-per-SM grid streams the contiguous unit range [c*U/G, (c+1)*U/G) (tile-major, K inner) — every
+//     SM pulls the same number of weight bytes whatever N and K are; ranges are cut into segments at tile boundaries;
+//   * 8 dequant warps: warp -> (channel group c = 0/1, TMEM lane quadrant q), thread -> ONE channel.  A thread reads its
+//     channel's 16 words (64 B, conflict-free through the swizzle), turns every word into four {k, k+1} cells with the
+//     magic-exponent trick (shift, lop3, one packed subtract of {magic + z}, one packed multiply by {s, s} — the same
+//     arithmetic as awq_dequant_kernel, so the weights are bit-identical to the reference's fp16 dequantisation) and
+//     stores them with tcgen05.st into a ring of four 64-column TMEM buffers: the dequantised matrix NEVER passes
+//     through shared memory (the round-1 kernel paid 16 KB of st.shared + 16 KB of tensor-core reads per 4 KB of weights);
+//   * one thread issues tcgen05.mma kind::f16 with A from TMEM, B = x chunk from shared memory;
+//   * the dequant warps double as the epilogue of their (group, quadrant).  A segment that covers a whole tile goes
+//     (+bias) -> fp16/bf16 -> out[m, n] straight from TMEM.  A partial segment PUBLISHES its raw fp32 accumulators to the
+//     workspace and moves on; when a CTA has streamed all its units it helps finish the (at most two) tiles it shares:
+//     the P CTAs of a tile each sum 1/P of its token columns over all P partials in CTA order (bit-deterministic) — a
+//     reduce-scatter, so no CTA ingests more than one tile's worth of partials however finely K was split.
+constexpr int kSkThreads = 384;  // warp 0 TMA (packed words), 1 MMA, 2 TMEM alloc, 3 TMA (x chunks), 4-11 dequant + epilogue
+constexpr int kUnitK = 128;
+constexpr int kUnitN = 256;
+constexpr int kARing = 4;     // A buffers of 64 TMEM columns (128 channels x 128 k): two units in flight
+constexpr int kACol0 = 256;   // A ring = TMEM columns [256, 512); accumulators below
+constexpr int kAwqStateBytes = 256;  // workspace header: [0] launch epoch, [1] CTAs done
+
+struct AwqSkArgs {
+  void* out;           // [M, N]
+  const uint8_t* qweight_t;  // unit-major packed words: 16 KB per (256-channel tile, 128-k block)
+  const uint32_t* sz;  // [K/g, N] {scale, magic + zero}
+  const void* bias;    // [N] or null
+  int M, N, K, group_size, num_groups;
+  int group_shift;  // log2(group_size) when it is a power of two, else -1 (then group_size % 128 == 0)
+  int num_kb, total_units;
+  int debug;  // B200_AWQ_DEBUG bit mask — timing experiments only, results are wrong when set: 1 no dequant math,
+              // 2 no tcgen05.st, 4 no MMA
+  unsigned long long* trace;  // diagnostics (b200_debug_set_trace): CTA 0 stamps 16 clocks per unit, or null
+  int trace_units;
+  uint32_t* state;     // [0] epoch of the last completed launch, [1] CTAs of this launch that are done
+  uint32_t* flags;     // [2 * G] epoch-valued: slot 0 = a CTA's leading partial tile, slot 1 = its trailing one
+  uint32_t* partials;  // [2 * G][2 groups][BN cols][128 rows] fp32
 };
 
-template <int BN, int STAGES, int RAW>
-struct AwqSmem {
-  static constexpr int kA = 128 * kAwqBK * 2;  // dequantised weights, MN-major: atom (k_atom * 2 + n_atom) * 1024
-  static constexpr int kB = BN * 128;          // tokens, K-major
-  static constexpr int kStage = kA + kB;
-  static constexpr int kRawStage = kAwqBK * 64;  // 64 k rows x 16 packed words
-  static constexpr int kRawOff = STAGES * kStage;
-  // per raw stage: up to kAwqMaxGps groups x (128 scales (256 B) + 16 zero-point words (64 B))
-  static constexpr int kConstStage = kAwqMaxGps * 320;
-  static constexpr int kConstOff = kRawOff + RAW * kRawStage;
-  static constexpr int kBarOff = kConstOff + RAW * kConstStage;
-  static constexpr int kNumBars = 2 * STAGES + 2 * RAW + 1;
+template <int BN>
+struct AwqSk {
+  static constexpr int kW = kUnitN * (kUnitK / 2);  // packed words of a unit
+  static constexpr int kXC = BN * 128;              // x chunk: BN tokens x 64 k
+  static constexpr int kSX = 6;  // three units of x chunks in flight (a deeper ring does not help: at 128 tokens the kernel
+                                 // is bound by shared-memory bandwidth — see the measurements in DESIGN.md)
+  static constexpr int kSWmax = (208 * 1024 - kSX * kXC) / kW;
+  static constexpr int kSW = kSWmax > 10 ? 10 : kSWmax;
+  static constexpr int kAccBufs = 4 * BN <= kACol0 ? 2 : 1;  // a buffer = two channel groups x BN token columns
+  static constexpr int kWOff = kSX * kXC;
+  static constexpr int kBarOff = kWOff + kSW * kW;
+  static constexpr int kNumBars = 2 * kSW + 2 * kSX + 2 * kARing + 4;
   static constexpr int kBytes = kBarOff + kNumBars * 8 + 1024;
-  static_assert(BN * 128 * 4 <= STAGES * kStage, "split-K receive buffer must fit in the operand stages");
-  static_assert(kBytes <= 232448, "exceeds the 227 KB shared-memory limit");
+  static_assert(2 * BN * kAccBufs <= kACol0, "accumulators overlap the A ring");
+  static_assert(kXC % 1024 == 0 && kBytes <= 232448, "shared-memory layout");
 };
 
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
@@ -126,329 +194,419 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];\n" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
   return v;
 }
-__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
-  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+__device__ __forceinline__ void dq_bar_sync() { asm volatile("bar.sync 2, 256;\n" ::: "memory"); }
+
+// tcgen05.mma with the A operand in tensor memory (M rows on the 128 lanes, K packed two 16-bit elements per column)
+__device__ __forceinline__ void umma_ts_f16(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, bool accumulate) {
+  const uint32_t acc = accumulate ? 1u : 0u;
+  asm volatile(
+      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n}\n" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(acc)
+      : "memory");
 }
 
-template <typename T, int BN, int STAGES, int RAW>
-__global__ void __launch_bounds__(kAwqThreads, (AwqSmem<BN, STAGES, RAW>::kBytes <= 113 * 1024) ? 2 : 1)
-awq_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x, const AwqArgs g) {
-  using L = AwqSmem<BN, STAGES, RAW>;
-  constexpr int kTmemCols = BN < 32 ? 32 : BN;
+// first unit of CTA c's range, and the CTA whose range holds unit u (ranges are [c*U/G, (c+1)*U/G))
+__device__ __forceinline__ int sk_first_unit(int c, int U, int G) { return (int)((int64_t)c * U / G); }
+__device__ __forceinline__ int sk_owner_of(int u, int U, int G) {
+  int c = (int)(((int64_t)u * G) / U);
+  while (c + 1 < G && sk_first_unit(c + 1, U, G) <= u) ++c;
+  while (c > 0 && sk_first_unit(c, U, G) > u) --c;
+  return c;
+}
+
+__device__ __forceinline__ void awq_stamp(const AwqSkArgs& g, int unit_idx, int k) {
+  if (g.trace != nullptr && blockIdx.x == 0 && unit_idx < g.trace_units) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%clock64;\n" : "=l"(t));
+    g.trace[(size_t)unit_idx * 16 + k] = t;
+  }
+}
+
+template <typename T, int BN>
+__global__ void __launch_bounds__(kSkThreads, 1)
+awq_streamk_kernel(const __grid_constant__ CUtensorMap tmap_x, const AwqSkArgs g) {
+  using L = AwqSk<BN>;
+  constexpr int SW = L::kSW;
+  constexpr int SX = L::kSX;
+  constexpr int NACC = L::kAccBufs;
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint32_t s_tmem_base;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar = base + L::kBarOff;
-  auto op_full = [&](int s) { return bar + s * 8; };
-  auto op_empty = [&](int s) { return bar + (STAGES + s) * 8; };
-  auto raw_full = [&](int s) { return bar + (2 * STAGES + s) * 8; };
-  auto raw_empty = [&](int s) { return bar + (2 * STAGES + RAW + s) * 8; };
-  const uint32_t tmem_full = bar + (2 * STAGES + 2 * RAW) * 8;
-
+  auto w_full = [&](int s) { return bar + s * 8; };
+  auto w_empty = [&](int s) { return bar + (SW + s) * 8; };
+  auto x_full = [&](int t) { return bar + (2 * SW + t) * 8; };
+  auto x_empty = [&](int t) { return bar + (2 * SW + SX + t) * 8; };
+  auto a_full = [&](int r) { return bar + (2 * SW + 2 * SX + r) * 8; };
+  auto a_empty = [&](int r) { return bar + (2 * SW + 2 * SX + kARing + r) * 8; };
+  auto d_full = [&](int b) { return bar + (2 * SW + 2 * SX + 2 * kARing + b) * 8; };
+  auto d_empty = [&](int b) { return bar + (2 * SW + 2 * SX + 2 * kARing + 2 + b) * 8; };
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  if (warp == 0 && lane == 0) {
-    prefetch_tmap(&tmap_w);
-    prefetch_tmap(&tmap_x);
-  }
+  if (warp == 3 && lane == 0) prefetch_tmap(&tmap_x);
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < STAGES; ++s) {
-      mbar_init(op_full(s), 1 + 2);  // x TMA (expect_tx arrive) + the two warps of the owning dequant group
-      mbar_init(op_empty(s), g.cl);  // one tcgen05.commit per CTA sharing the token tile
+    for (int s = 0; s < SW; ++s) {
+      mbar_init(w_full(s), 1);
+      mbar_init(w_empty(s), 8);  // the eight dequant warps
     }
-    for (int s = 0; s < RAW; ++s) {
-      mbar_init(raw_full(s), 1);
-      mbar_init(raw_empty(s), 2);
+    for (int t = 0; t < SX; ++t) {
+      mbar_init(x_full(t), 1);
+      mbar_init(x_empty(t), 1);
     }
-    mbar_init(tmem_full, 1);
+    for (int r = 0; r < kARing; ++r) {
+      mbar_init(a_full(r), 4);  // the four warps (lane quadrants) of the owning channel group
+      mbar_init(a_empty(r), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(d_full(b), 1);
+      mbar_init(d_empty(b), 8);
+    }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc<kTmemCols>(smem_u32(&s_tmem_base));
-  if (warp >= 4) {  // scales / zero points of channels past N (partial last tile) stay zero
-    uint32_t* cz = reinterpret_cast<uint32_t*>(smem_raw + (base - smem_u32(smem_raw)) + L::kConstOff);
-    for (int i = threadIdx.x - 128; i < RAW * L::kConstStage / 4; i += kAwqDqThreads) cz[i] = 0u;
-    fence_proxy_async();
-  }
+  if (warp == 2) tmem_alloc<512>(smem_u32(&s_tmem_base));
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = s_tmem_base;
-  const int CL = g.cl;
-  if (CL * g.splits > 1) cluster_sync();  // peers' barriers are initialised before anything is multicast to them
-  const int cx = (int)blockIdx.x % CL;                                        // position among the tile sharers
-  const uint16_t mc_mask = (uint16_t)(((1u << CL) - 1u) << (CL * blockIdx.z));  // cluster ranks cx' + CL * z
+  pdl_trigger();
 
-  const int n0 = blockIdx.x * 128;   // first output channel of this CTA
-  const int m0 = blockIdx.y * BN;    // first token
-  const int rank = (int)blockIdx.z;  // cluster dims (1,1,splits), gridDim.z == splits
-  const int S = g.splits;
-  const int kb0 = rank * g.kb_per_split;
-  const int nkb = min(g.kb_per_split, g.num_kb - kb0);
-
-  // quantisation groups per K block (1 when group_size >= 64, else 64 / group_size) and valid channels of the tile
-  const int gps = g.group_size >= kAwqBK ? 1 : kAwqBK / g.group_size;
-  const int nv = max(0, min(128, g.N - n0));  // 0 for a surplus CTA that only feeds the multicast
-  const int num_groups = g.K / g.group_size;
+  const int G = gridDim.x;
+  const int U = g.total_units;
+  const int cta = blockIdx.x;
+  const int nkb = g.num_kb;
+  const int u0 = sk_first_unit(cta, U, G);
+  const int u1 = sk_first_unit(cta + 1, U, G);
 
   if (warp == 0) {
+    // ---- packed words: independent of the previous kernel, so the ring fills before the PDL wait --------------------
     if (lane == 0) {
-      const uint8_t* scales_b = reinterpret_cast<const uint8_t*>(g.scales);
-      const uint8_t* zeros_b = reinterpret_cast<const uint8_t*>(g.qzeros);
-      for (int i = 0; i < nkb; ++i) {
-        const int rs = i % RAW;
-        mbar_wait(raw_empty(rs), ((i / RAW) & 1) ^ 1);
-        const int k0 = (kb0 + i) * kAwqBK;
-        const int grp0 = k0 / g.group_size;
-        const int ng = nv > 0 ? min(gps, num_groups - grp0) : 0;  // groups of this block that exist (K tail)
-        mbar_expect_tx(raw_full(rs), L::kRawStage + ng * (nv * 2 + nv / 2));
-        tma_load_2d(base + L::kRawOff + rs * L::kRawStage, &tmap_w, raw_full(rs), n0 / 2 /* bytes: n0/8 words */, k0,
-                    kEvictFirst);
-        for (int gi = 0; gi < ng; ++gi) {
-          const uint32_t dst = base + L::kConstOff + rs * L::kConstStage + gi * 320;
-          bulk_load_1d(dst, scales_b + ((int64_t)(grp0 + gi) * g.N + n0) * 2, nv * 2, raw_full(rs));
-          bulk_load_1d(dst + 256, zeros_b + ((int64_t)(grp0 + gi) * g.N + n0) / 2, nv / 2, raw_full(rs));
-        }
+      for (int i = 0; i < u1 - u0; ++i) {
+        const int s = i % SW;
+        mbar_wait(w_empty(s), ((i / SW) & 1) ^ 1);
+        awq_stamp(g, i, 13);
+        mbar_expect_tx(w_full(s), L::kW);
+        bulk_load_1d_hint(base + L::kWOff + s * L::kW, g.qweight_t + (size_t)(u0 + i) * L::kW, L::kW, w_full(s), kEvictFirst);
       }
     }
+    pdl_wait();
   } else if (warp == 3) {
+    // ---- x chunks (64 k each, two per unit): written by the previous kernel --------------------------------------------
+    pdl_wait();
     if (lane == 0) {
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % STAGES;
-        mbar_wait(op_empty(s), ((i / STAGES) & 1) ^ 1);
-        mbar_expect_tx(op_full(s), L::kB);
-        if (CL == 1) {
-          tma_load_2d(base + s * L::kStage + L::kA, &tmap_x, op_full(s), (kb0 + i) * kAwqBK * 2, m0, kEvictLast);
-        } else {  // this CTA fetches rows [cx, cx+1) * BN/CL of the tile and multicasts them to all sharers
-          const int rows = BN / CL;
-          tma_load_2d_mc(base + s * L::kStage + L::kA + cx * rows * 128, &tmap_x, op_full(s), (kb0 + i) * kAwqBK * 2,
-                         m0 + cx * rows, mc_mask, kEvictLast);
+      int kb = u0 % nkb;
+      for (int i = 0; i < u1 - u0; ++i) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int j = 2 * i + h;
+          const int t = j % SX;
+          mbar_wait(x_empty(t), ((j / SX) & 1) ^ 1);
+          awq_stamp(g, i, 14 + h);
+          mbar_expect_tx(x_full(t), L::kXC);
+          tma_load_2d(base + t * L::kXC, &tmap_x, x_full(t), kb * kUnitK * 2 + h * 128, 0, kEvictLast);
         }
+        if (++kb == nkb) kb = 0;
       }
     }
   } else if (warp == 1) {
+    pdl_wait();
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(/*f32*/ 1, AwqMagic<T>::kFmt, AwqMagic<T>::kFmt, 128, BN, /*A MN-major*/ 1, 0);
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % STAGES;
-        mbar_wait(op_full(s), (i / STAGES) & 1);
+      constexpr uint32_t idesc = make_idesc(/*f32*/ 1, AwqMagic<T>::kFmt, AwqMagic<T>::kFmt, 128, BN);
+      int it = 0, seg = 0;
+      for (int u = u0; u < u1; ++seg) {
+        const int tile = u / nkb;
+        const int seg_end = min(u1, (tile + 1) * nkb);
+        const int buf = seg % NACC;
+        mbar_wait(d_empty(buf), ((seg / NACC) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t sa = base + s * L::kStage;
-        const uint64_t da = smem_desc_mn_sw128(sa, /*LBO: next 64 channels*/ 1024, /*SBO: next 8 k*/ 2048);
-        const uint64_t db = smem_desc_k_sw128(sa + L::kA);
+        for (int i = u; i < seg_end; ++i, ++it) {
+          const int r0 = 2 * (it & 1);
 #pragma unroll
-        for (int k = 0; k < kAwqBK / 16; ++k)  // UMMA K = 16 elements: A advances 2 k-atoms (4096 B), B 32 bytes
-          umma<kKindF16>(tmem_base, da + 256 * k, db + 2 * k, idesc, (i | k) != 0);
-        if (CL == 1) tc_commit(op_empty(s));
-        else tc_commit_mc(op_empty(s), mc_mask);  // the stage is free once EVERY sharer's MMAs have read it
+          for (int h = 0; h < 2; ++h) {
+            const int j = 2 * it + h;
+            const int t = j % SX;
+            mbar_wait(x_full(t), (j / SX) & 1);
+            awq_stamp(g, it, h == 0 ? 8 : 11);
+            const uint64_t db = smem_desc_k_sw128(base + t * L::kXC);
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+              if (h == 0) {
+                mbar_wait(a_full(r0 + c), (it >> 1) & 1);
+                awq_stamp(g, it, 9 + c);
+              }
+              tc_fence_after();
+              const uint32_t d_tmem = tmem_base + buf * (2 * BN) + c * BN;
+              const uint32_t a_tmem = tmem_base + kACol0 + (r0 + c) * 64 + h * 32;
+#pragma unroll
+              for (int k = 0; k < 4; ++k)  // UMMA K = 16: 8 TMEM columns of A, 32 bytes of the 128-byte-swizzled x row
+                if (!(g.debug & 4)) umma_ts_f16(d_tmem, a_tmem + 8 * k, db + 2 * k, idesc, (i > u) || (h | k) != 0);
+            }
+            tc_commit(x_empty(t));
+          }
+          tc_commit(a_empty(r0));
+          tc_commit(a_empty(r0 + 1));
+          awq_stamp(g, it, 12);
+        }
+        tc_commit(d_full(buf));
+        u = seg_end;
       }
-      tc_commit(tmem_full);
     }
   } else if (warp >= 4) {
-    // ---- dequant producers: group = (warp - 4) / 2 owns K blocks i % 4 == group; within a group the two
-    //      warps take alternate 8-row k-atoms; lane -> (row of the atom, 4 consecutive packed words) ------------
-    const int dw = warp - 4;
-    const int grp_id = dw >> 1;
-    const int wsub = dw & 1;
-    const int r = lane & 7;
-    const int quad = lane >> 3;
-    const int c_base = (quad & 1) * 4;
-    for (int i = grp_id; i < nkb; i += kAwqGroups) {
-      const int rs = i % RAW;
-      const int s = i % STAGES;
-      mbar_wait(raw_full(rs), (i / RAW) & 1);
-      const uint32_t raw_base = base + L::kRawOff + rs * L::kRawStage;
-      const uint32_t const_base = base + L::kConstOff + rs * L::kConstStage;
-      uint4 q[4];
+    const int c = (warp - 4) >> 2;   // channel group of the unit
+    const int q = warp & 3;          // TMEM lane quadrant this warp may touch
+    const int row = c * 128 + q * 32 + lane;  // channel inside the 256-channel unit
+    const uint32_t sw = (uint32_t)((row >> 1) & 3);
+    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+    const int g_size = g.group_size;
+    const int last_group = g.num_groups - 1;
+    const bool has_bias = g.bias != nullptr;
+    const int m_cols = min(BN, (g.M + 15) & ~15);
+    T* out = reinterpret_cast<T*>(g.out);
+    constexpr size_t kSlot = (size_t)2 * BN * 128;  // words per partial slot
+
+    // {scale, magic + zero} of the (channel, group)s a unit touches: four 32-k chunks; no division in the unit loop
+    auto load_sz = [&](int tile, int kb, uint32_t (&dst)[4]) {
+      const int n = tile * kUnitN + row;
+      const int k0 = kb * kUnitK;
+      const int gi0 = g.group_shift >= 0 ? 0 : min(k0 / g_size, last_group);  // group_size % 128 == 0: one group per unit
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        // raw tile: row (64 B), 16-byte chunk = quad, 64-byte swizzle: chunk ^= (row >> 1) & 3
-        const int krow = (wsub + 2 * j) * 8 + r;
-        q[j] = lds128(raw_base + (uint32_t)(krow * 64 + ((quad ^ ((krow >> 1) & 3)) << 4)));
+        const int gi = g.group_shift >= 0 ? min((k0 + j * 32) >> g.group_shift, last_group) : gi0;
+        dst[j] = n < g.N ? __ldg(g.sz + (int64_t)gi * g.N + n) : 0u;
       }
-      uint32_t zm[4][4];
-      uint4 sc[4];
-      int cur_slot = -1;
-      mbar_wait(op_empty(s), ((i / STAGES) & 1) ^ 1);
-      const uint32_t a_stage = base + s * L::kStage;
+    };
+    uint32_t sz_nxt[4] = {0u, 0u, 0u, 0u};
+    int nx_tile = u0 / nkb, nx_kb = u0 - nx_tile * nkb;  // the unit whose constants are being prefetched
+    if (u0 < u1) load_sz(nx_tile, nx_kb, sz_nxt);
+
+    int it = 0, seg = 0;
+    uint32_t epoch = 0;
+    int pend0 = -1, pend1 = -1;  // tiles this CTA shares with others: its leading partial (slot 0), its trailing one (slot 1)
+    for (int u = u0; u < u1; ++seg) {
+      const int tile = u / nkb;
+      const int kb_begin = u - tile * nkb;
+      const int seg_end = min(u1, (tile + 1) * nkb);
+      const bool starts = kb_begin == 0;
+      const bool ends = seg_end == (tile + 1) * nkb;
+      const int buf = seg % NACC;
+      // ---- dequantise the segment's units into the TMEM A ring --------------------------------------------------------
+      for (int i = u; i < seg_end; ++i, ++it) {
+        uint32_t sz_cur[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int katom = wsub + 2 * j;
-        const int slot = gps == 1 ? 0 : (katom * 8 * gps) >> 6;
-        if (slot != cur_slot) {
-          cur_slot = slot;
-          const uint32_t cb = const_base + slot * 320;
-          const uint4 z = lds128(cb + 256 + quad * 16);
-          const uint32_t zw[4] = {z.x, z.y, z.z, z.w};
+        for (int j = 0; j < 4; ++j) sz_cur[j] = sz_nxt[j];
+        if (++nx_kb == nkb) { nx_kb = 0; ++nx_tile; }
+        if (i + 1 < u1) load_sz(nx_tile, nx_kb, sz_nxt);
+        const int s = it % SW;
+        const int r = 2 * (it & 1) + c;
+        mbar_wait(w_full(s), (it / SW) & 1);
+        if (q == 0 && lane == 0) awq_stamp(g, it, 4 * c + 0);
+        const uint32_t raw_row = base + L::kWOff + s * L::kW + (uint32_t)row * 64u;
+        uint4 w[4];
 #pragma unroll
-          for (int w = 0; w < 4; ++w) {
-            sc[w] = lds128(cb + quad * 64 + w * 16);
+        for (int j = 0; j < 4; ++j) w[j] = lds128(raw_row + ((((uint32_t)j) ^ sw) << 4));
+        mbar_wait(a_empty(r), ((it >> 1) & 1) ^ 1);
+        if (q == 0 && lane == 0) awq_stamp(g, it, 4 * c + 1);
+        tc_fence_after();
+        const uint32_t a_addr = lane_base + kACol0 + r * 64;
 #pragma unroll
-            for (int p = 0; p < 4; ++p) zm[w][p] = nib_pair<T>(zw[w], p);
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t s2 = __byte_perm(sz_cur[j], sz_cur[j], 0x1010);
+          const uint32_t zm = __byte_perm(sz_cur[j], sz_cur[j], 0x3232);
+          const uint32_t ww[4] = {w[j].x, w[j].y, w[j].z, w[j].w};
+          uint32_t cells[16];
+#pragma unroll
+          for (int t = 0; t < 4; ++t)
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+              cells[t * 4 + p] = (g.debug & 1) ? ww[t] + p : mul2<T>(sub2<T>(nib_pair<T>(ww[t], p), zm), s2);
+          if (!(g.debug & 2)) tmem_st16(a_addr + j * 16, cells);
+          if (j == 3) {  // the unit's words are in registers (consumed above): hand the ring slot back to the TMA warp
+            __syncwarp();
+            if (lane == 0) mbar_arrive(w_empty(s));
           }
         }
-        // A operand: atom = katom * 2 + (quad >> 1); row r; chunk c = (quad & 1) * 4 + w, swizzled by r
-        const uint32_t sa = a_stage + (uint32_t)(((katom * 2 + (quad >> 1)) << 10) + (r << 7));
-        sts128(sa + (((c_base + 0) ^ r) << 4), dequant_word<T>(q[j].x, zm[0], sc[0]));
-        sts128(sa + (((c_base + 1) ^ r) << 4), dequant_word<T>(q[j].y, zm[1], sc[1]));
-        sts128(sa + (((c_base + 2) ^ r) << 4), dequant_word<T>(q[j].z, zm[2], sc[2]));
-        sts128(sa + (((c_base + 3) ^ r) << 4), dequant_word<T>(q[j].w, zm[3], sc[3]));
+        if (q == 0 && lane == 0) awq_stamp(g, it, 4 * c + 2);
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(a_full(r));
+        if (q == 0 && lane == 0) awq_stamp(g, it, 4 * c + 3);
       }
-      fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
+      // ---- epilogue of the segment: this warp drains its (group, quadrant) of the accumulator -------------------------
+      if (epoch == 0) {  // the first global write of this thread comes after the previous kernel has completed
+        pdl_wait();
+        epoch = ld_acquire_u32(g.state) + 1u;
+      }
+      mbar_wait(d_full(buf), (seg / NACC) & 1);
+      tc_fence_after();
+      const uint32_t taddr = lane_base + buf * (2 * BN) + c * BN;
+      const int n = tile * kUnitN + row;
+      const bool n_ok = n < g.N;
+      if (starts && ends) {
+        float bias = 0.f;
+        if (n_ok && has_bias) bias = DT<T>::to_f(reinterpret_cast<const T*>(g.bias)[n]);
+#pragma unroll 1
+        for (int c0 = 0; c0 < m_cols; c0 += 16) {
+          uint32_t r16[16];
+          tmem_ld16(taddr + c0, r16);
+          tmem_ld_wait();
+          if (n_ok) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int m = c0 + j;
+              if (m < g.M) {
+                const float v = __uint_as_float(r16[j]);
+                out[(int64_t)m * g.N + n] = DT<T>::from_f(has_bias ? v + bias : v);
+              }
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(d_empty(buf));
+      } else {
+        // publish: raw fp32 accumulators -> partials[2 * cta + slot][group][col][128 rows]; a warp store covers 128 bytes
+        const int slot = starts ? 1 : 0;
+        if (slot) pend1 = tile; else pend0 = tile;
+        uint32_t* dst = g.partials + (size_t)(2 * cta + slot) * kSlot + (size_t)c * BN * 128 + q * 32 + lane;
+#pragma unroll 1
+        for (int c0 = 0; c0 < m_cols; c0 += 16) {
+          uint32_t r16[16];
+          tmem_ld16(taddr + c0, r16);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) __stcg(dst + (c0 + j) * 128, r16[j]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(d_empty(buf));
+        dq_bar_sync();  // orders every epilogue thread's stores before the release below (cumulativity)
+        if (threadIdx.x == 128) st_release_u32(g.flags + 2 * cta + slot, epoch);
+      }
+      u = seg_end;
+    }
+    if (epoch == 0) {
+      pdl_wait();
+      epoch = ld_acquire_u32(g.state) + 1u;
+    }
+    // ---- shared tiles: reduce this CTA's share of the token columns over all contributors, in CTA order ---------------
+#pragma unroll 1
+    for (int slot = 0; slot < 2; ++slot) {
+      const int tile = slot ? pend1 : pend0;
+      if (tile < 0) continue;
+      const int t_begin = tile * nkb, t_end = t_begin + nkb;
+      const int c_lo = sk_owner_of(t_begin, U, G);
+      const int c_hi = sk_owner_of(t_end - 1, U, G);
+      const int P = c_hi - c_lo + 1;
+      const int me = cta - c_lo;
+      // contributor p used slot 1 iff the tile starts inside (or at the start of) its range: only the first one can
+      for (int p = lane; p < P; p += 32) {
+        const uint32_t* f = g.flags + 2 * (c_lo + p) + (p == 0 ? 1 : 0);
+        while (ld_acquire_u32(f) != epoch) {
+        }
+      }
       __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(op_full(s));
-        mbar_arrive(raw_empty(rs));
-      }
-    }
-    mbar_wait(tmem_full, 0);
-    tc_fence_after();
-  }
-
-  // ---- epilogue: warps 4-7 take token columns [0, BN/2), warps 8-11 [BN/2, BN) (BN >= 32) ----------------------
-  constexpr int kHalves = BN >= 32 ? 2 : 1;
-  constexpr int kColsPerHalf = BN / kHalves;
-  const int q4 = warp & 3;
-  const int row = q4 * 32 + lane;  // accumulator row (TMEM lane) = output channel n0 + row
-  const int half = warp >= 8 ? 1 : 0;
-  const bool epi = warp >= 4 && half < kHalves;
-  const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16);
-  const int n = n0 + row;
-  const bool n_ok = n < g.N;
-  const bool has_bias = g.bias != nullptr;
-  float bias = 0.f;
-  if (epi && n_ok && has_bias) bias = DT<T>::to_f(reinterpret_cast<const T*>(g.bias)[n]);
-  T* out = reinterpret_cast<T*>(g.out);
-
-  if (S > 1) {
-    __syncwarp();
-    cluster_sync();  // every CTA of the cluster has retired its MMAs: operand stages are free to reuse
-    const int C = BN / S;  // token columns owned by each rank
-    const int logC = 31 - __clz(C);
-    if (epi) {
-      const uint32_t my_slot = base + (uint32_t)(rank * C * 128 + row) * 4;  // receive buffer [src rank][col][row]
-      uint32_t dst[8];
-#pragma unroll
-      for (int d = 0; d < 8; ++d) dst[d] = d < S ? mapa(my_slot, cx + CL * d) : 0;
+      const int col0 = (int)((int64_t)me * m_cols / P), col1 = (int)((int64_t)(me + 1) * m_cols / P);
+      const int n = tile * kUnitN + row;
+      const bool n_ok = n < g.N;
+      float bias = 0.f;
+      if (n_ok && has_bias) bias = DT<T>::to_f(reinterpret_cast<const T*>(g.bias)[n]);
+      const uint32_t* src0 = g.partials + (size_t)(2 * c_lo + 1) * kSlot + (size_t)c * BN * 128 + q * 32 + lane;
+      const uint32_t* srcp = g.partials + (size_t)(2 * (c_lo + 1)) * kSlot + (size_t)c * BN * 128 + q * 32 + lane;
 #pragma unroll 1
-      for (int c0 = half * kColsPerHalf; c0 < (half + 1) * kColsPerHalf; c0 += 16) {
-        if (m0 + c0 >= g.M) break;
-        uint32_t v[16];
-        tmem_ld16(taddr + c0, v);
-        tmem_ld_wait();
+      for (int col = col0; col < col1; col += 4) {
+        float acc[4];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int col = c0 + j;
-          if (m0 + col < g.M) {
-            const int d = col >> logC;
-            const int w = col & (C - 1);
-            uint32_t a = dst[0];
+        for (int j = 0; j < 4; ++j) acc[j] = col + j < col1 ? __uint_as_float(__ldcg(src0 + (col + j) * 128)) : 0.f;
+        for (int p = 1; p < P; ++p) {
+          const uint32_t* sp = srcp + (size_t)(p - 1) * 2 * kSlot;
 #pragma unroll
-            for (int dd = 1; dd < 8; ++dd)
-              if (dd == d) a = dst[dd];
-            st_cluster_u32(a + (uint32_t)(w * 128) * 4, v[j]);
+          for (int j = 0; j < 4; ++j)
+            if (col + j < col1) acc[j] = __fadd_rn(acc[j], __uint_as_float(__ldcg(sp + (col + j) * 128)));
+        }
+        if (n_ok) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int m = col + j;
+            if (m < col1 && m < g.M) out[(int64_t)m * g.N + n] = DT<T>::from_f(has_bias ? acc[j] + bias : acc[j]);
           }
         }
       }
     }
-    __syncwarp();
-    cluster_sync();  // all partials have landed
-    if (epi) {
-      const float* recv = reinterpret_cast<const float*>(smem_raw + (base - smem_u32(smem_raw)));
-      for (int w = half; w < C; w += kHalves) {
-        const int m = m0 + rank * C + w;
-        if (m >= g.M) break;
-        float t = 0.f;
-        for (int src = 0; src < S; ++src) t += recv[(src * C + w) * 128 + row];
-        if (n_ok) out[(int64_t)m * g.N + n] = DT<T>::from_f(has_bias ? t + bias : t);
+    // ---- launch epoch: the last CTA to finish publishes it (flags of this launch can never match a later one) ----------
+    dq_bar_sync();
+    if (threadIdx.x == 128) {
+      __threadfence();
+      if (atomicAdd(g.state + 1, 1u) == (uint32_t)G - 1u) {
+        g.state[1] = 0u;
+        st_release_u32(g.state, epoch);
       }
     }
-  } else if (epi) {
-#pragma unroll 1
-    for (int c0 = half * kColsPerHalf; c0 < (half + 1) * kColsPerHalf; c0 += 16) {
-      if (m0 + c0 >= g.M) break;  // warp-uniform
-      uint32_t v[16];
-      tmem_ld16(taddr + c0, v);
-      tmem_ld_wait();
-      if (n_ok) {
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int m = m0 + c0 + j;
-          if (m < g.M) {
-            const float t = __uint_as_float(v[j]);
-            out[(int64_t)m * g.N + n] = DT<T>::from_f(has_bias ? t + bias : t);
-          }
-        }
-      }
-    }
+  } else {
+    pdl_wait();
   }
-
   tc_fence_before();
   __syncthreads();
-  if (CL > 1) cluster_sync();  // no CTA exits while a sharer may still signal its barriers
-  if (warp == 2) tmem_dealloc<kTmemCols>(tmem_base);
+  if (warp == 2) tmem_dealloc<512>(tmem_base);
 }
 
-template <typename T, int BN, int STAGES, int RAW>
-static int launch_awq(const CUtensorMap& tw, const CUtensorMap& tx, const AwqArgs& g, dim3 grid, cudaStream_t st) {
-  using L = AwqSmem<BN, STAGES, RAW>;
-  auto kern = awq_gemm_kernel<T, BN, STAGES, RAW>;
+template <typename T, int BN>
+static int launch_awq_sk(const CUtensorMap& tx, const AwqSkArgs& g, int ctas, cudaStream_t st) {
+  using L = AwqSk<BN>;
+  auto kern = awq_streamk_kernel<T, BN>;
   B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = grid;
-  cfg.blockDim = dim3(kAwqThreads);
-  cfg.dynamicSmemBytes = L::kBytes;
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = g.cl;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = g.splits;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tw, tx, g));
-  return B200_OK;
+  return launch_k(kern, dim3((unsigned)ctas), dim3(kSkThreads), L::kBytes, st, 1, true, tx, g);
 }
+
+// workspace: [state 256 B][flags 2 * #SM words, padded to 4 KB][partials 2 * #SM slots of 2 x 128 x 128 fp32]
+static size_t awq_flag_bytes() { return ((size_t)2 * sm_count() * 4 + 4095) / 4096 * 4096; }
+static size_t awq_workspace_bytes() { return kAwqStateBytes + awq_flag_bytes() + (size_t)2 * sm_count() * 2 * 128 * 128 * 4; }
 
 template <typename T>
-static int run_awq_gemm(AwqArgs g, const void* x, const void* qweight, cudaStream_t st) {
-  const int64_t M = g.M, N = g.N, K = g.K;
-  g.num_kb = (int)ceil_div(K, kAwqBK);
-  const int bn = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256;
-  const int tiles = (int)ceil_div(N, 128);
-  const int mtiles = (int)ceil_div(M, bn);
-  int s = 1;
-  if (mtiles == 1)  // weight streaming: split K over a cluster until every SM has a CTA
-    while (s < 8 && tiles * s < sm_count() && g.num_kb / (s * 2) >= 4 && bn / (s * 2) >= 1) s *= 2;
-  g.splits = s;
-  g.kb_per_split = (int)ceil_div(g.num_kb, g.splits);
-  while (g.splits > 1 && (int64_t)(g.splits - 1) * g.kb_per_split >= g.num_kb) {
-    g.splits /= 2;
-    g.kb_per_split = (int)ceil_div(g.num_kb, g.splits);
-  }
-  // token-tile sharing: the tile is BN * 128 B per K block against 4 KB of packed weights, so at BN >= 64 the L2 ->
-  // SM traffic is dominated by tokens; cl CTAs along n fetch 1/cl of it each and multicast (cl * splits <= 8)
-  // Measured on B200 (profiles/awq_r01.md): sharing does not pay at these sizes — the kernel is bound by the
-  // packed-word stream, not by L2 -> SM token traffic — so it stays off unless B200_AWQ_CLUSTER_N asks for it.
-  static const int cl_env = [] { const char* e = getenv("B200_AWQ_CLUSTER_N"); return e ? atoi(e) : 1; }();
-  g.cl = (cl_env == 2 || cl_env == 4) && bn >= 64 ? cl_env : 1;
-  while (g.cl > 1 && (g.cl * g.splits > 8 || tiles < g.cl)) g.cl /= 2;
-  const int tiles_padded = (int)ceil_div(tiles, g.cl) * g.cl;  // surplus CTAs only feed the multicast
-  CUtensorMap tw, tx;
+static int run_awq_gemm(AwqSkArgs g, const void* x, const void* qweight_t, int64_t M, void* ws, size_t ws_bytes,
+                        cudaStream_t st) {
+  const size_t need = awq_workspace_bytes();
+  if (ws == nullptr || ws_bytes < need) return fail(B200_ERR_WORKSPACE, "awq_gemm: workspace of %zu bytes, %zu needed", ws_bytes, need);
+  B200_REQUIRE(((uintptr_t)ws % 256) == 0, "awq_gemm: workspace must be 256-byte aligned");
+  const int64_t N = g.N, K = g.K;
+  g.num_kb = (int)ceil_div(K, kUnitK);
+  const int tiles = (int)ceil_div(N, kUnitN);
+  const int64_t units = (int64_t)tiles * g.num_kb;
+  B200_REQUIRE(units < (1ll << 30), "awq_gemm: too many work units");
+  g.total_units = (int)units;
+  static const int dbg = getenv("B200_AWQ_DEBUG") ? atoi(getenv("B200_AWQ_DEBUG")) : 0;
+  g.debug = dbg;
+  g.trace = g_trace;
+  g.trace_units = (int)g_trace_slots;
+  uint8_t* wsb = reinterpret_cast<uint8_t*>(ws);
+  g.state = reinterpret_cast<uint32_t*>(wsb);
+  g.flags = reinterpret_cast<uint32_t*>(wsb + kAwqStateBytes);
+  g.partials = reinterpret_cast<uint32_t*>(wsb + kAwqStateBytes + awq_flag_bytes());
+  const int sms = sm_count();
+  const int ctas = (int)(units < sms ? units : sms);
+  CUtensorMap tx;
   int rc;
-  // packed weights [K rows, N/2 bytes]: box 64 rows x 64 bytes (16 words = 128 channels), 64-byte swizzle
-  if ((rc = cached_tmap(&tw, qweight, (uint64_t)K, (uint64_t)(N / 2), kAwqBK, 64, 64)) != B200_OK) return rc;
-  if ((rc = cached_tmap(&tx, x, (uint64_t)M, (uint64_t)(K * 2), (uint32_t)(bn / g.cl))) != B200_OK) return rc;
-  dim3 grid(tiles_padded, mtiles, g.splits);
-  switch (bn) {
-    // operand stages >= dequant groups + 1 (one being consumed by the MMA); the raw ring holds the bytes in flight
-    // BN <= 64: two CTAs per SM (<= 113 KB each) so one CTA's prologue / epilogue hides under the other's stream
-    case 16: return launch_awq<T, 16, 3, 8>(tw, tx, g, grid, st);
-    case 32: return launch_awq<T, 32, 3, 8>(tw, tx, g, grid, st);
-    case 64: return launch_awq<T, 64, 3, 8>(tw, tx, g, grid, st);
-    case 128: return launch_awq<T, 128, 4, 16>(tw, tx, g, grid, st);
-    default: return launch_awq<T, 256, 4, 4>(tw, tx, g, grid, st);
+  g.qweight_t = reinterpret_cast<const uint8_t*>(qweight_t);
+  uint8_t* outp = reinterpret_cast<uint8_t*>(g.out);
+  const uint8_t* xp = reinterpret_cast<const uint8_t*>(x);
+  // more than 128 tokens: one pass over the packed weights per 128-token chunk (at 128 tokens per pass the fp16 tensor
+  // pipe, not the weight stream, is already the bound: 512 flop per weight byte)
+  for (int64_t m0 = 0; m0 < M; m0 += 128) {
+    const int64_t mc = M - m0 < 128 ? M - m0 : 128;
+    g.M = (int)mc;
+    g.out = outp + m0 * N * 2;
+    const int bn = mc <= 16 ? 16 : mc <= 32 ? 32 : mc <= 64 ? 64 : 128;
+    if ((rc = cached_tmap(&tx, xp + m0 * K * 2, (uint64_t)mc, (uint64_t)(K * 2), (uint32_t)bn)) != B200_OK) return rc;
+    switch (bn) {
+      case 16: rc = launch_awq_sk<T, 16>(tx, g, ctas, st); break;
+      case 32: rc = launch_awq_sk<T, 32>(tx, g, ctas, st); break;
+      case 64: rc = launch_awq_sk<T, 64>(tx, g, ctas, st); break;
+      default: rc = launch_awq_sk<T, 128>(tx, g, ctas, st); break;
+    }
+    if (rc != B200_OK) return rc;
   }
+  return B200_OK;
 }
 
 }  // namespace b200
@@ -479,26 +637,56 @@ B200_API int b200_awq_dequantize(void* w_out, const int32_t* qweight, const void
   return B200_OK;
 }
 
-B200_API int b200_awq_gemm(void* out, const void* x, const int32_t* qweight, const void* scales, const int32_t* qzeros,
-                           const void* bias, int64_t M, int64_t N, int64_t K, int group_size, int dtype, void* stream) {
+B200_API int b200_awq_repack(int32_t* qweight_t, uint32_t* sz, const int32_t* qweight, const void* scales,
+                             const int32_t* qzeros, int64_t K, int64_t N, int group_size, int dtype, void* stream) {
+  // one-time layout change for the streaming GEMM (process_weights_after_loading): see awq_repack_*_kernel
+  B200_REQUIRE(K > 0 && N > 0 && N % 8 == 0 && K % 8 == 0, "awq_repack: K %lld and N %lld must be multiples of 8",
+               (long long)K, (long long)N);
+  B200_REQUIRE(qweight_t && sz && qweight && scales && qzeros, "awq_repack: null pointer");
+  B200_REQUIRE(group_size > 0 && K % group_size == 0, "awq_repack: K %lld is not a multiple of group_size %d", (long long)K,
+               group_size);
+  if (dtype != B200_F16 && dtype != B200_BF16) return fail(B200_ERR_UNSUPPORTED, "awq_repack: dtype %d not supported", dtype);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t words = N * (K / 8), cells = (K / group_size) * N;
+  const int64_t num_kb = ceil_div(K, 128);
+  B200_CUDA_OK(cudaMemsetAsync(qweight_t, 0, (size_t)(ceil_div(N, 256) * num_kb) * 16384, st));  // padding past N and K
+  awq_repack_weight_kernel<<<(unsigned)ceil_div(words, 256), 256, 0, st>>>((uint32_t*)qweight_t, (const uint32_t*)qweight, K, N,
+                                                                           num_kb);
+  B200_LAUNCH_OK();
+  awq_repack_sz_kernel<<<(unsigned)ceil_div(cells, 256), 256, 0, st>>>(sz, (const uint16_t*)scales, (const uint32_t*)qzeros,
+                                                                       K / group_size, N, dtype == B200_F16 ? 0x6400u : 0x4300u);
+  B200_LAUNCH_OK();
+  return B200_OK;
+}
+
+B200_API int b200_awq_gemm_workspace_bytes(size_t* bytes) {
+  B200_REQUIRE(bytes != nullptr, "awq_gemm_workspace_bytes: null pointer");
+  *bytes = awq_workspace_bytes();
+  return B200_OK;
+}
+
+B200_API int b200_awq_gemm(void* out, const void* x, const int32_t* qweight_t, const uint32_t* sz, const void* bias, int64_t M,
+                           int64_t N, int64_t K, int group_size, int dtype, void* workspace, size_t workspace_bytes,
+                           void* stream) {
   B200_REQUIRE(M >= 0 && N > 0 && K > 0, "awq_gemm: bad sizes");
   if (M == 0) return B200_OK;
-  B200_REQUIRE(out && x && qweight && scales && qzeros, "awq_gemm: null pointer");
-  // same shape rules as AWQLinearMethod.create_weights (awq.py:339-352): K % group == 0, N % pack_factor == 0;
-  // the TMA row pitch additionally needs N % 32 == 0 (16-byte rows of packed words) and K % 8 == 0
+  B200_REQUIRE(out && x && qweight_t && sz, "awq_gemm: null pointer");
+  // shape rules of AWQLinearMethod.create_weights (awq.py:339-352): K % group == 0, N % pack_factor == 0; the TMA row
+  // pitches additionally need K % 32 == 0 (16-byte rows of packed words)
   B200_REQUIRE(group_size > 0 && K % group_size == 0, "awq_gemm: K %lld is not a multiple of group_size %d", (long long)K,
                group_size);
-  if (group_size < 32 || (group_size < kAwqBK ? kAwqBK % group_size != 0 : group_size % kAwqBK != 0))
-    return fail(B200_ERR_UNSUPPORTED, "awq_gemm: group_size %d not supported (32, or a multiple of 64)", group_size);
-  B200_REQUIRE(N % 32 == 0, "awq_gemm: N %lld must be a multiple of 32", (long long)N);
-  B200_REQUIRE(K % 8 == 0, "awq_gemm: K %lld must be a multiple of 8", (long long)K);
-  B200_REQUIRE(((uintptr_t)out % 2) == 0 && ((uintptr_t)scales % 16) == 0, "awq_gemm: pointer alignment");
+  if (!(group_size == 32 || group_size == 64 || group_size % 128 == 0))
+    return fail(B200_ERR_UNSUPPORTED, "awq_gemm: group_size %d not supported (32, 64 or a multiple of 128)", group_size);
+  B200_REQUIRE(N % 8 == 0, "awq_gemm: N %lld must be a multiple of 8", (long long)N);
+  B200_REQUIRE(K % 32 == 0, "awq_gemm: K %lld must be a multiple of 32", (long long)K);
+  B200_REQUIRE(((uintptr_t)out % 2) == 0 && ((uintptr_t)x % 16) == 0 && ((uintptr_t)qweight_t % 16) == 0, "awq_gemm: pointer alignment");
   B200_REQUIRE(M < (1ll << 30) && N < (1ll << 30) && K < (1ll << 30), "awq_gemm: sizes exceed 32-bit tile math");
-  AwqArgs g = {};
-  g.out = out; g.scales = scales; g.qzeros = (const uint32_t*)qzeros; g.bias = bias;
-  g.M = (int)M; g.N = (int)N; g.K = (int)K; g.group_size = group_size;
+  AwqSkArgs g = {};
+  g.out = out; g.sz = sz; g.bias = bias;
+  g.N = (int)N; g.K = (int)K; g.group_size = group_size; g.num_groups = (int)(K / group_size);
+  g.group_shift = (group_size & (group_size - 1)) == 0 ? 31 - __builtin_clz((unsigned)group_size) : -1;
   cudaStream_t st = (cudaStream_t)stream;
-  if (dtype == B200_F16) return run_awq_gemm<__half>(g, x, qweight, st);
-  if (dtype == B200_BF16) return run_awq_gemm<__nv_bfloat16>(g, x, qweight, st);
+  if (dtype == B200_F16) return run_awq_gemm<__half>(g, x, qweight_t, M, workspace, workspace_bytes, st);
+  if (dtype == B200_BF16) return run_awq_gemm<__nv_bfloat16>(g, x, qweight_t, M, workspace, workspace_bytes, st);
   return fail(B200_ERR_UNSUPPORTED, "awq_gemm: dtype %d not supported (f16/bf16)", dtype);
 }

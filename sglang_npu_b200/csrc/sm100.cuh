@@ -80,6 +80,16 @@ __device__ __forceinline__ void bulk_load_1d(uint32_t smem_dst, const void* gsrc
                : "memory");
 }
 
+// same, with an L2 eviction-priority hint (kEvictFirst for bytes that are streamed once)
+__device__ __forceinline__ void bulk_load_1d_hint(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t bar,
+                                                  uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;\n" ::"r"(
+          smem_dst),
+      "l"(gsrc), "r"(bytes), "r"(bar), "l"(policy)
+      : "memory");
+}
+
 // ---- tcgen05 / TMEM ------------------------------------------------------------------------
 template <int COLS>
 __device__ __forceinline__ void tmem_alloc(uint32_t smem_result_addr) {

@@ -130,10 +130,7 @@ __device__ __forceinline__ void unpack8(const int4& v, float (&f)[8]) {
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kCommThreads) tp_reduce_norm_quant_kernel(const TpArgs a) {
-  extern __shared__ float row_f[];  // H floats
-  __shared__ float red[kCommThreads / 32];
-  __shared__ float red2[kCommThreads / 32];
+__device__ __forceinline__ void tp_reduce_norm_quant_body(const TpArgs& a, float* row_f, float* red, float* red2) {
   constexpr int kWarps = kCommThreads / 32;
   const int b = blockIdx.x;
   unsigned long long* const tr = (a.trace != nullptr && b < a.trace_slots) ? a.trace + (size_t)b * 16 : nullptr;
@@ -271,6 +268,29 @@ __global__ void __launch_bounds__(kCommThreads) tp_reduce_norm_quant_kernel(cons
   }
 }
 
+template <typename T>
+__global__ void __launch_bounds__(kCommThreads) tp_reduce_norm_quant_kernel(const TpArgs a) {
+  extern __shared__ float row_f[];  // H floats
+  __shared__ float red[kCommThreads / 32];
+  __shared__ float red2[kCommThreads / 32];
+  tp_reduce_norm_quant_body<T>(a, row_f, red, red2);
+}
+
+// Single-GPU emulation for the test suite: ALL ranks of the exchange in ONE cooperative launch, blockIdx.y = rank, every
+// rank with its own argument block and buffer set on the same device.  Ranks wait on one another through the same flag
+// protocol as over NVLink; the cooperative launch guarantees that all of them are resident (separate launches that spin
+// on one another are not guaranteed to run together on one GPU).
+template <typename T>
+__global__ void __launch_bounds__(kCommThreads) tp_reduce_norm_quant_loopback_kernel(const TpArgs* __restrict__ rank_args) {
+  extern __shared__ float row_f[];
+  __shared__ float red[kCommThreads / 32];
+  __shared__ float red2[kCommThreads / 32];
+  __shared__ TpArgs a;
+  if (threadIdx.x == 0) a = rank_args[blockIdx.y];
+  __syncthreads();
+  tp_reduce_norm_quant_body<T>(a, row_f, red, red2);
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -322,25 +342,23 @@ B200_API int b200_comm_check(const void* err_flag, void* stream) {
   return B200_OK;
 }
 
-B200_API int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, void* const* xq_ptrs,
-                                               void* const* xscale_ptrs, void* const* y_ptrs, void* const* flag_ptrs,
-                                               void* epoch, void* residual, const void* weight, int64_t M, int64_t H,
-                                               float eps, int tp_size, int tp_rank, int max_blocks, int dtype,
-                                               void* err_flag, void* stream) {
+static int build_tp_args(TpArgs& a, int64_t& grid, const void* const* partial_ptrs, void* const* xq_ptrs,
+                         void* const* xscale_ptrs, void* const* y_ptrs, void* const* flag_ptrs, void* epoch, void* residual,
+                         const void* weight, int64_t M, int64_t H, float eps, int tp_size, int tp_rank, int max_blocks,
+                         void* err_flag) {
   B200_REQUIRE(tp_size >= 2 && tp_size <= kMaxTp && tp_rank >= 0 && tp_rank < tp_size, "tp exchange: bad tp %d / rank %d",
                tp_size, tp_rank);
-  B200_REQUIRE(M >= 0 && H > 0 && H % 8 == 0 && H * 4 <= 200 * 1024, "tp exchange: bad sizes M %lld H %lld", (long long)M,
+  B200_REQUIRE(M > 0 && H > 0 && H % 8 == 0 && H * 4 <= 200 * 1024, "tp exchange: bad sizes M %lld H %lld", (long long)M,
                (long long)H);
-  if (M == 0) return B200_OK;
   B200_REQUIRE(partial_ptrs && flag_ptrs && epoch && weight && err_flag, "tp exchange: null pointer");
   B200_REQUIRE(xq_ptrs != nullptr || y_ptrs != nullptr, "tp exchange: no output requested");
   B200_REQUIRE((xq_ptrs == nullptr) == (xscale_ptrs == nullptr), "tp exchange: xq and xscale go together");
   const int64_t rows_per = ceil_div(M, tp_size);
   B200_REQUIRE(max_blocks >= 1, "tp exchange: no flag slots");
-  int64_t grid = sm_count();  // all CTAs co-resident on every rank (one 512-thread CTA per SM)
+  grid = sm_count();  // all CTAs co-resident on every rank (one 512-thread CTA per SM)
   if (grid > max_blocks) grid = max_blocks;
   if (grid > rows_per) grid = rows_per;
-  TpArgs a = {};
+  a = TpArgs{};
   for (int r = 0; r < tp_size; ++r) {
     B200_REQUIRE(partial_ptrs[r] && flag_ptrs[r], "tp exchange: null peer pointer");
     a.partial[r] = partial_ptrs[r];
@@ -366,6 +384,20 @@ B200_API int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, 
   a.timeout_ns = timeout_ms * 1000000ull;
   a.relaxed_start = relaxed_start;
   a.M = M; a.H = H; a.tp = tp_size; a.rank = tp_rank; a.max_blocks = max_blocks; a.eps = eps;
+  return B200_OK;
+}
+
+B200_API int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, void* const* xq_ptrs,
+                                               void* const* xscale_ptrs, void* const* y_ptrs, void* const* flag_ptrs,
+                                               void* epoch, void* residual, const void* weight, int64_t M, int64_t H,
+                                               float eps, int tp_size, int tp_rank, int max_blocks, int dtype,
+                                               void* err_flag, void* stream) {
+  if (M == 0) return B200_OK;
+  TpArgs a;
+  int64_t grid = 0;
+  int rc = build_tp_args(a, grid, partial_ptrs, xq_ptrs, xscale_ptrs, y_ptrs, flag_ptrs, epoch, residual, weight, M, H, eps,
+                         tp_size, tp_rank, max_blocks, err_flag);
+  if (rc != B200_OK) return rc;
   const int smem = (int)(H * sizeof(float));
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == B200_BF16) {
@@ -379,4 +411,39 @@ B200_API int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, 
     return launch_k(kern, dim3((unsigned)grid), dim3(kCommThreads), smem, st, 1, true, a);
   }
   return fail(B200_ERR_UNSUPPORTED, "tp exchange: dtype %d not supported (bf16/f16)", dtype);
+}
+
+B200_API int b200_tp_exchange_loopback(const void* const* partial_ptrs, void* const* xq_ptrs, void* const* xscale_ptrs,
+                                       void* const* y_ptrs, void* const* flag_ptrs, void* const* epoch_ptrs,
+                                       void* const* residual_ptrs, const void* weight, int64_t M, int64_t H, float eps,
+                                       int tp_size, int max_blocks, int dtype, void* const* err_ptrs, void* args_scratch,
+                                       size_t args_scratch_bytes, void* stream) {
+  // Test entry: every rank of one exchange in a single cooperative launch on ONE device (see the loopback kernel).
+  // args_scratch: device memory for tp_size argument blocks (b200_tp_exchange_loopback needs tp_size * 512 bytes).
+  if (M == 0) return B200_OK;
+  B200_REQUIRE(epoch_ptrs && err_ptrs && args_scratch, "tp loopback: null pointer");
+  B200_REQUIRE(args_scratch_bytes >= (size_t)tp_size * sizeof(TpArgs), "tp loopback: argument scratch of %zu bytes, %zu needed",
+               args_scratch_bytes, (size_t)tp_size * sizeof(TpArgs));
+  TpArgs host_args[kMaxTp];
+  int64_t grid = 0;
+  for (int r = 0; r < tp_size; ++r) {
+    int rc = build_tp_args(host_args[r], grid, partial_ptrs, xq_ptrs, xscale_ptrs, y_ptrs, flag_ptrs, epoch_ptrs[r],
+                           residual_ptrs ? residual_ptrs[r] : nullptr, weight, M, H, eps, tp_size, r, max_blocks, err_ptrs[r]);
+    if (rc != B200_OK) return rc;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  B200_CUDA_OK(cudaMemcpyAsync(args_scratch, host_args, (size_t)tp_size * sizeof(TpArgs), cudaMemcpyHostToDevice, st));
+  const int smem = (int)(H * sizeof(float));
+  const void* kern = dtype == B200_BF16 ? (const void*)tp_reduce_norm_quant_loopback_kernel<__nv_bfloat16>
+                     : dtype == B200_F16 ? (const void*)tp_reduce_norm_quant_loopback_kernel<__half> : nullptr;
+  if (kern == nullptr) return fail(B200_ERR_UNSUPPORTED, "tp loopback: dtype %d not supported (bf16/f16)", dtype);
+  B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  int per_sm = 0;
+  B200_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kCommThreads, smem));
+  B200_REQUIRE(grid * tp_size <= (int64_t)per_sm * sm_count(), "tp loopback: %lld CTAs cannot be co-resident",
+               (long long)(grid * tp_size));
+  const TpArgs* dev_args = reinterpret_cast<const TpArgs*>(args_scratch);
+  void* params[] = {(void*)&dev_args};
+  B200_CUDA_OK(cudaLaunchCooperativeKernel(kern, dim3((unsigned)grid, (unsigned)tp_size), dim3(kCommThreads), params, smem, st));
+  return B200_OK;
 }

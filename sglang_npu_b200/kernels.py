@@ -505,23 +505,67 @@ def awq_dequantize(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Te
     return out
 
 
-def awq_gemm(x: torch.Tensor, qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor,
-             bias: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """Fused dequant + matmul: x [M,K] @ W(qweight, scales, qzeros) [K,N] (+bias) (awq.py:401-418)."""
-    require_cuda(x, qweight, scales, qzeros)
+_AWQ_WS = {}
+
+
+def _awq_workspace(lib, device) -> torch.Tensor:
+    """Stream-K state of the fused AWQ GEMM (launch epoch, publish flags, partial accumulators), one zero-initialised
+    buffer per device; the AWQ GEMMs of a process are stream-ordered on the forward stream."""
+    ws = _AWQ_WS.get(device.index)
+    if ws is None:
+        need = c_size_t(0)
+        check(lib.b200_awq_gemm_workspace_bytes(byref(need)), "b200_awq_gemm_workspace_bytes")
+        ws = torch.zeros(need.value, device=device, dtype=torch.uint8)
+        _AWQ_WS[device.index] = ws
+    return ws
+
+
+def awq_repack(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Checkpoint layout (qweight [K, N/8], scales [K/g, N], qzeros [K/g, N/8]) -> the streaming layout of the fused GEMM:
+    (qweight_t [units, 256, 16] int32 — one 16 KB image per (256-channel tile, 128-k block) — and sz [K/g, N] int32 =
+    {scale, magic + zero}).  One-time, at process_weights_after_loading."""
+    require_cuda(qweight, scales, qzeros)
     lib = _cabi.load()
     K, n8 = qweight.shape
     N = n8 * 8
     G = K // qzeros.shape[0]
+    assert qweight.dtype == torch.int32 and qzeros.dtype == torch.int32 and scales.shape == (K // G, N)
+    assert qweight.is_contiguous() and qzeros.is_contiguous() and scales.is_contiguous()
+    qweight_t = torch.empty((((N + 255) // 256) * ((K + 127) // 128), 256, 16), dtype=torch.int32, device=qweight.device)
+    sz = torch.empty((K // G, N), dtype=torch.int32, device=qweight.device)
+    check(lib.b200_awq_repack(ptr(qweight_t), ptr(sz), ptr(qweight), ptr(scales), ptr(qzeros), K, N, G,
+                              dtype_code(scales.dtype), stream_ptr(qweight.device)), "b200_awq_repack")
+    return qweight_t, sz
+
+
+def awq_gemm_repacked(x: torch.Tensor, qweight_t: torch.Tensor, sz: torch.Tensor, group_size: int,
+                      bias: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Fused dequant + matmul on the streaming layout of `awq_repack`: x [M, K] @ W [K, N] (+bias)."""
+    require_cuda(x, qweight_t, sz)
+    lib = _cabi.load()
+    N = sz.shape[1]
+    K = sz.shape[0] * int(group_size)
+    assert qweight_t.dtype == torch.int32 and sz.dtype == torch.int32 and qweight_t.is_contiguous() and sz.is_contiguous()
+    assert qweight_t.numel() == ((N + 255) // 256) * ((K + 127) // 128) * 4096 and x.shape[-1] == K
+    assert x.dtype in (torch.float16, torch.bfloat16)
     x2 = x.reshape(-1, K).contiguous()
     M = x2.shape[0]
-    assert x.dtype == scales.dtype
     out = _out_buffer(out, M, N, x.dtype, x.device, "awq_gemm")
     if bias is not None:
         bias = bias.to(x.dtype).contiguous()
-    check(lib.b200_awq_gemm(ptr(out), ptr(x2), ptr(qweight), ptr(scales), ptr(qzeros), ptr(bias), M, N, K, G,
-                            dtype_code(x.dtype), stream_ptr(x.device)), "b200_awq_gemm")
+    ws = _awq_workspace(lib, x.device)
+    check(lib.b200_awq_gemm(ptr(out), ptr(x2), ptr(qweight_t), ptr(sz), ptr(bias), M, N, K, int(group_size),
+                            dtype_code(x.dtype), ptr(ws), ws.numel(), stream_ptr(x.device)), "b200_awq_gemm")
     return out
+
+
+def awq_gemm(x: torch.Tensor, qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor,
+             bias: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Fused dequant + matmul from the CHECKPOINT layout (awq.py:401-418): repacks on every call — for tests and one-off
+    use; a layer repacks once (B200AWQLinearMethod.process_weights_after_loading) and calls `awq_gemm_repacked`."""
+    assert x.dtype == scales.dtype
+    qweight_t, sz = awq_repack(qweight, scales, qzeros)
+    return awq_gemm_repacked(x, qweight_t, sz, qweight.shape[0] // qzeros.shape[0], bias=bias, out=out)
 
 
 # ---- element-wise ----------------------------------------------------------------------------------------

@@ -106,13 +106,31 @@ class B200AWQLinearMethod(LinearMethodBase):
             input_dim=0, output_dim=1, weight_loader=weight_loader))
 
     def process_weights_after_loading(self, layer: torch.nn.Module) -> None:
+        """The reference re-wraps the three tensors (awq.py:396-399).  Here the hook also produces the streaming layout of
+        the fused GEMM (kernels.awq_repack: channel-major packed words + {scale, zero} pairs).  The checkpoint-layout
+        tensors stay registered — they are what `awq_dequantize` and the parity tooling read — unless
+        B200_AWQ_DROP_CHECKPOINT_LAYOUT=1 frees them (a serving process that only ever calls apply())."""
+        import os
+
         layer.qweight = Parameter(layer.qweight.data, requires_grad=False)
         layer.qzeros = Parameter(layer.qzeros.data, requires_grad=False)
         layer.scales = Parameter(layer.scales.data, requires_grad=False)
+        if layer.qweight.is_cuda:
+            layer.awq_out_features = layer.qweight.shape[-1] * self.quant_config.pack_factor
+            qweight_t, sz = kernels.awq_repack(layer.qweight.data, layer.scales.data, layer.qzeros.data)
+            layer.register_buffer("qweight_t", qweight_t, persistent=False)
+            layer.register_buffer("awq_sz", sz, persistent=False)
+            if os.environ.get("B200_AWQ_DROP_CHECKPOINT_LAYOUT", "0") == "1":
+                empty = torch.empty(0, dtype=torch.int32, device=qweight_t.device)
+                layer.qweight = Parameter(empty, requires_grad=False)
+                layer.qzeros = Parameter(empty.clone(), requires_grad=False)
+                layer.scales = Parameter(torch.empty(0, dtype=layer.scales.dtype, device=qweight_t.device), requires_grad=False)
 
     def apply(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None,
               out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """`out` (optional, beyond the reference signature): destination of the [M, N] result (fused TP exchange)."""
-        out_shape = x.shape[:-1] + (layer.qweight.shape[-1] * self.quant_config.pack_factor,)
-        res = kernels.awq_gemm(x.reshape(-1, x.shape[-1]), layer.qweight, layer.scales, layer.qzeros, bias, out=out)
-        return res.reshape(out_shape)
+        if getattr(layer, "qweight_t", None) is None:
+            raise RuntimeError("B200AWQLinearMethod.apply before process_weights_after_loading (or not on a CUDA device)")
+        res = kernels.awq_gemm_repacked(x.reshape(-1, x.shape[-1]), layer.qweight_t, layer.awq_sz, layer.awq_group_size,
+                                        bias, out=out)
+        return res.reshape(x.shape[:-1] + (layer.awq_out_features,))

@@ -122,3 +122,53 @@ def test_awq_shape_errors(cuda_device):
         kernels.awq_gemm(x, torch.zeros((100, 16), dtype=torch.int32, device=dev),
                          torch.zeros((1, 128), dtype=torch.float16, device=dev),
                          torch.zeros((1, 16), dtype=torch.int32, device=dev))
+
+
+def test_awq_repack_is_a_pure_layout_change(cuda_device):
+    """qweight_t holds, per (256-channel tile, 128-k block), a [256 channels x 16 words] image whose words carry 8
+    consecutive k of one channel in the AWQ nibble order (16-byte chunks swizzled by (row >> 1) & 3); sz pairs the group's
+    scale with (magic + zero point).  Unpacking it in torch gives back every nibble / scale / zero of the checkpoint."""
+    K, N, G = 512, 264, 128
+    g = torch.Generator().manual_seed(4)
+    qweight = _full_range_words((K, N // 8), g)
+    qzeros = _full_range_words((K // G, N // 8), g)
+    order = torch.tensor([0, 4, 1, 5, 2, 6, 3, 7])
+    for dtype, magic in ((torch.float16, 0x6400), (torch.bfloat16, 0x4300)):
+        scales = torch.rand((K // G, N), generator=g).to(dtype)
+        qwt, sz = kernels.awq_repack(qweight.to(cuda_device), scales.to(cuda_device), qzeros.to(cuda_device))
+        qwt, sz = qwt.cpu(), sz.cpu()
+        nib = lambda words, pos: (words.unsqueeze(-1) >> (4 * pos)) & 0xF  # noqa: E731
+        q_ref = nib(qweight, order).reshape(K, N)           # logical [K, N] nibbles of the checkpoint layout
+        tiles, nkb = (N + 255) // 256, K // 128
+        img = qwt.view(tiles, nkb, 256, 4, 4)               # [tile, kb, row, swizzled chunk, word]
+        rows = torch.arange(256)
+        src_chunk = torch.arange(4).view(1, 4) ^ ((rows >> 1) & 3).view(256, 1)    # logical chunk c sits at c ^ swizzle
+        img = torch.gather(img, 3, src_chunk.view(1, 1, 256, 4, 1).expand(tiles, nkb, 256, 4, 4))
+        words = img.reshape(tiles, nkb, 256, 16).permute(0, 2, 1, 3).reshape(tiles * 256, K // 8)  # [channel, word j]
+        assert not words[N:].any(), "padding rows past N must be zero"
+        q_new = nib(words[:N], order).reshape(N, K).t()      # word (n, j), nibble ORDER[e] = k 8j + e
+        assert torch.equal(q_ref, q_new)
+        z_ref = nib(qzeros, order).reshape(K // G, N)
+        assert torch.equal(sz & 0xFFFF, scales.view(torch.int16).to(torch.int32) & 0xFFFF)
+        assert torch.equal((sz >> 16) & 0xFFFF, z_ref.to(torch.int32) | magic)
+
+
+@pytest.mark.parametrize("M,K,N", [(128, 8192, 256), (64, 16384, 512), (16, 4096, 264)])
+def test_awq_gemm_streamk_many_contributors(cuda_device, M, K, N):
+    """Few channel tiles, long K: every CTA holds a slice of ONE tile, so the owner sums dozens of partial accumulators
+    (the stream-K fix-up path); repeated to show the flag workspace is left clean."""
+    for rep in range(3):
+        out, ref = _gemm_case(cuda_device, M, K, N, 128, torch.float16, seed=rep)
+        assert_close_path(out, ref, f"awq_gemm stream-K M={M} K={K} N={N} rep {rep}")
+
+
+def test_awq_gemm_is_deterministic(cuda_device):
+    g = torch.Generator().manual_seed(1)
+    K, N, M = 5120, 3584, 128
+    qweight, qzeros = _full_range_words((K, N // 8), g).to(cuda_device), _full_range_words((K // 128, N // 8), g).to(cuda_device)
+    scales = (torch.rand((K // 128, N), generator=g) / 400).half().to(cuda_device)
+    x = torch.randn((M, K), generator=g).half().to(cuda_device)
+    qwt, sz = kernels.awq_repack(qweight, scales, qzeros)
+    a = kernels.awq_gemm_repacked(x, qwt, sz, 128).clone()
+    for _ in range(3):
+        assert torch.equal(kernels.awq_gemm_repacked(x, qwt, sz, 128), a)

@@ -37,12 +37,12 @@ def test_fused_exchange_matches_nccl_path(cuda_device):
 @pytest.mark.parametrize("tp,M", [(2, 64), (2, 7), (4, 64), (8, 100)])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 def test_exchange_kernel_loopback_all_ranks_on_one_gpu(cuda_device, tp, M, dtype):
-    """The exchange kernel itself on a single-GPU box: all `tp` ranks live in THIS process, each with its own buffer
-    set and stream on the same device, and the kernels meet through the same flag protocol they use over NVLink
-    (the pointer tables simply hold local addresses).  Checked against the un-fused chain: fp32 rank-order sum of the
-    partials -> fused_add_rmsnorm -> per-token int8 quant (bit-exact), for the int8 output (W8A8-int8 consumers) and
-    the normalised 16-bit output (FP8 / AWQ consumers).  A rank that never gets scheduled next to its peers makes the
-    barrier time out (B200_TP_TIMEOUT_MS) and the test fail — it cannot hang the box."""
+    """The exchange kernel itself on a single-GPU box: all `tp` ranks run in ONE cooperative launch (blockIdx.y = rank,
+    b200_tp_exchange_loopback), each with its own buffer set on the same device, and meet through the same flag protocol
+    they use over NVLink (the pointer tables simply hold local addresses).  Checked against the un-fused chain: fp32
+    rank-order sum of the partials -> fused_add_rmsnorm -> per-token int8 quant (bit-exact), for the int8 output
+    (W8A8-int8 consumers) and the normalised 16-bit output (FP8 / AWQ consumers).  The cooperative launch guarantees
+    co-residency of all ranks' CTAs, and the barrier still has its timeout (B200_TP_TIMEOUT_MS): it cannot hang the box."""
     import ctypes
 
     from sglang_npu_b200 import _cabi, kernels
@@ -51,7 +51,7 @@ def test_exchange_kernel_loopback_all_ranks_on_one_gpu(cuda_device, tp, M, dtype
     os.environ.setdefault("B200_TP_TIMEOUT_MS", "4000")
     lib = _cabi.load()
     dev = cuda_device
-    H, eps, max_blocks = 4096, 1e-5, 64
+    H, eps, max_blocks = 4096, 1e-5, 16
     g = torch.Generator(device=dev).manual_seed(tp * 100 + M)
     w = (1 + 0.1 * torch.randn(H, generator=g, device=dev)).to(dtype)
     partial = [torch.randn(M, H, generator=g, device=dev).to(dtype) for _ in range(tp)]
@@ -63,15 +63,15 @@ def test_exchange_kernel_loopback_all_ranks_on_one_gpu(cuda_device, tp, M, dtype
     epoch = [torch.zeros(max_blocks, dtype=torch.int32, device=dev) for _ in range(tp)]
     err = [torch.zeros(64, dtype=torch.int32, device=dev) for _ in range(tp)]
     residual = [residual0.clone() for _ in range(tp)]
+    scratch = torch.zeros(tp * 512, dtype=torch.uint8, device=dev)
     arr = lambda ts: (ctypes.c_void_p * tp)(*[t.data_ptr() for t in ts])  # noqa: E731
-    streams = [torch.cuda.Stream(device=dev) for _ in range(tp)]
-    torch.cuda.synchronize(dev)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    res_after = None
     for rep in range(2):  # twice: epochs / flags are reused across launches
-        for r in range(tp):
-            rc = lib.b200_tp_reduce_rmsnorm_quant_int8(arr(partial), arr(xq), arr(xs), arr(y), arr(flags), epoch[r].data_ptr(),
-                                                       residual[r].data_ptr(), w.data_ptr(), M, H, eps, tp, r, max_blocks,
-                                                       dtype_code(dtype), err[r].data_ptr(), streams[r].cuda_stream)
-            kernels.check(rc, "b200_tp_reduce_rmsnorm_quant_int8")
+        rc = lib.b200_tp_exchange_loopback(arr(partial), arr(xq), arr(xs), arr(y), arr(flags), arr(epoch), arr(residual),
+                                           w.data_ptr(), M, H, eps, tp, max_blocks, dtype_code(dtype), arr(err),
+                                           scratch.data_ptr(), scratch.numel(), stream)
+        kernels.check(rc, "b200_tp_exchange_loopback")
         torch.cuda.synchronize(dev)
         for r in range(tp):
             assert int(err[r][0]) == 0, f"rank {r}: barrier timed out (code {int(err[r][0]):#x})"
@@ -85,7 +85,7 @@ def test_exchange_kernel_loopback_all_ranks_on_one_gpu(cuda_device, tp, M, dtype
             rows = slice(min(M, r * per), min(M, (r + 1) * per))
             if rows.start == rows.stop:
                 continue
-            res_ref = (residual0 if rep == 0 else res_after)[rows].clone()  # noqa: F821
+            res_ref = (residual0 if rep == 0 else res_after)[rows].clone()
             act, yn = kernels.rmsnorm_quant_int8(ar[rows].clone(), w, eps, residual=res_ref, return_normed=True)
             for dst in range(tp):  # every rank received rank r's rows
                 assert torch.equal(xq[dst][rows], act.x_q), f"int8 rows of rank {r} differ on rank {dst}"

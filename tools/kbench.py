@@ -163,7 +163,7 @@ def bench_awq(args):
     """cfg 4 (Qwen2.5-32B) per-GPU shapes: decode M = 128, prefill M = 2048."""
     dev = torch.device("cuda")
     hidden, inter, hq, hkv, d = 5120, 27648, 40, 8, 128
-    for tp in (1, 2, 8):
+    for tp in ([args.tp] if args.tp else [1, 2, 8]):
         n_qkv = (hq // tp + 2 * max(1, hkv // tp)) * d
         shapes = [(hidden, n_qkv), (hq * d // tp, hidden), (hidden, 2 * inter // tp), (inter // tp, hidden)]
         for m in ([args.m] if args.m else [128, 2048]):
@@ -172,9 +172,10 @@ def bench_awq(args):
                 qw, sc, qz = synth.awq_weight(kk, n, 128, torch.float16, seed=1)
                 qw, sc, qz = qw.to(dev), sc.to(dev), qz.to(dev)
                 copies = max(2, int(300e6 // (qw.numel() * 4)) + 1)
-                qws = [qw.clone() for _ in range(copies)]
+                qwt, sz = kernels.awq_repack(qw, sc, qz)  # streaming layout, produced once at weight-loading time
+                qws = [qwt.clone() for _ in range(copies)]
                 x = torch.randn(m, kk, device=dev, dtype=torch.float16)
-                med = best = timeit_rot(lambda c: (lambda: kernels.awq_gemm(x, qws[c], sc, qz)), copies)
+                med = best = timeit_rot(lambda c: (lambda: kernels.awq_gemm_repacked(x, qws[c], sz, 128)), copies)
                 byts = qw.numel() * 4 + sc.numel() * 2 + qz.numel() * 4
                 tot_t += med
                 tot_b += byts
@@ -249,6 +250,7 @@ if __name__ == "__main__":
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--m", type=int, default=0)
     ap.add_argument("--ragged", action="store_true")
+    ap.add_argument("--tp", type=int, default=0, help="awq: one TP degree instead of 1, 2 and 8")
     ap.add_argument("--extra-splits", type=int, default=0, dest="extra_splits",
                     help="decode: over-provision the split grid (a graph captured under a longer context bound)")
     ap.add_argument("--fp8kv", action="store_true", help="decode: FP8 (e4m3) KV cache")
