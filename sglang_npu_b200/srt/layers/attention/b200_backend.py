@@ -88,9 +88,7 @@ class B200AttnBackend(AttentionBackend):
     def __init__(self, model_runner, skip_prefill: bool = False):
         super().__init__()
         self.device = torch.device(model_runner.device)
-        if self.device.type != "cuda":
-            raise RuntimeError("B200AttnBackend requires a CUDA device (no CPU fallback in this backend)")
-        kernels._cabi.load()  # fail loudly at construction if the extension is missing
+        self._require_device(self.device)
         self.skip_prefill = skip_prefill
         self.req_to_token = model_runner.req_to_token_pool.req_to_token
         tp = getattr(model_runner, "tp_size", 1) or 1
@@ -103,7 +101,7 @@ class B200AttnBackend(AttentionBackend):
         self.v_head_dim = model_runner.token_to_kv_pool.get_value_buffer(0).shape[-1]
         if self.v_head_dim != self.head_dim:
             raise NotImplementedError("B200AttnBackend: v_head_dim != head_dim (MLA-style) is out of scope")
-        self.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
+        self.sm_count = self._device_sm_count(self.device)
         self.forced_chunk = int(os.environ.get("B200_DECODE_KV_CHUNK", "0"))
         self.min_shared_prefix = int(os.environ.get("B200_MIN_SHARED_PREFIX", "1024"))
         self._max_chunk = 1024 if model_runner.token_to_kv_pool.dtype == torch.float8_e4m3fn else 2048
@@ -117,6 +115,16 @@ class B200AttnBackend(AttentionBackend):
         self._stage_rows_idx = None
         max_bs = model_runner.req_to_token_pool.size
         self.qo_indptr = torch.zeros((max_bs + 1,), dtype=torch.int32, device=self.device)
+
+    @staticmethod
+    def _require_device(device: torch.device) -> None:
+        if device.type != "cuda":
+            raise RuntimeError("B200AttnBackend requires a CUDA device (no CPU fallback in this backend)")
+        kernels._cabi.load()  # fail loudly at construction if the extension is missing
+
+    @staticmethod
+    def _device_sm_count(device: torch.device) -> int:
+        return torch.cuda.get_device_properties(device).multi_processor_count
 
     # ---- metadata -------------------------------------------------------------------------
     def _shared_prefix_supported(self) -> bool:
