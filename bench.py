@@ -309,6 +309,9 @@ def parse_args():
     ap.add_argument("--prefix", type=int, default=6144, help="prefill: cached prefix tokens per request")
     ap.add_argument("--layers", type=int, default=0, help="debug only: fewer layers (marks the line invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--timeline-out", default="", dest="timeline_out",
+                    help="decode: after the timed region, write rank 0's per-kernel device times of 3 graph replays "
+                         "(torch.profiler / CUPTI; works under torchrun where ncu does not) to this CSV")
     ap.add_argument("--kv-dtype", default=DEFAULTS["kv_dtype"], choices=["bf16", "fp8"], dest="kv_dtype",
                     help="fp8 = --kv-cache-dtype fp8_e4m3 variant")
     args = ap.parse_args()
@@ -375,6 +378,35 @@ def time_wrapped(modules_and_names, fn):
         for mod, name, orig in saved:
             setattr(mod, name, orig)
     return rec
+
+
+def kernel_timeline(fn, reps: int, out_path, barrier):
+    """Per-kernel device time of `reps` calls of fn() on this rank (CUPTI through torch.profiler; kernels inside a
+    replayed CUDA graph are recorded too).  Every rank runs the calls (collectives need all of them); only the rank
+    given an out_path writes the CSV: kernel, launches, total_us, avg_us, share.  With programmatic dependent launch
+    on, a kernel's CUPTI duration includes the time it spent waiting under its predecessor's tail (B200_PDL=0 gives
+    each kernel's own time)."""
+    from torch.profiler import ProfilerActivity, profile
+
+    barrier()
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        for _ in range(reps):
+            fn()
+        barrier()
+    if out_path is None:
+        return
+    agg = {}
+    for ev in prof.events():
+        if getattr(ev, "device_type", None) is not None and str(ev.device_type).endswith("CUDA") and ev.device_time_total > 0:
+            a = agg.setdefault(ev.name, [0, 0.0])
+            a[0] += 1
+            a[1] += ev.device_time_total
+    tot = sum(a[1] for a in agg.values()) or 1.0
+    with open(out_path, "w") as fh:
+        fh.write(f"# {reps} graph replays, rank 0, device time per kernel (us); total {tot:.1f} us\n")
+        fh.write("kernel,launches,total_us,avg_us,share\n")
+        for name, (n, us) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+            fh.write(f"\"{name[:160]}\",{n},{us:.1f},{us / n:.2f},{us / tot:.4f}\n")
 
 
 def tensor_peak_probe(kind: str, dev):
@@ -531,6 +563,9 @@ def main():
         h2d = sum(t.numel() * t.element_size() for t in (host.input_ids, host.req_pool_indices, host.seq_lens))
         d2h = bs * 8 + 8  # sampled ids + the allocator's page counter
         reset_loop()
+
+        if args.timeline_out:
+            kernel_timeline(lambda: runner.replay_decode(**d_in), 3, args.timeline_out if rank == 0 else None, barrier)
 
         # ---- (3) roofline of the dominant kernel, measured live with CUDA events on the launch stream --------
         import sglang_npu_b200.srt.layers.attention.b200_backend as bmod
