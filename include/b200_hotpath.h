@@ -163,6 +163,8 @@ int b200_decode_attn_shared_prefix(void* o, int8_t* oq, float* oq_scale, const v
  * tokens 0..i (causal) or all new tokens (causal = 0).  Prefix keys come through the
  * page table; new keys come from k_new/v_new when non-NULL (contiguous activations,
  * token stride given) else also through the page table (they were written first).
+ * num_q_tokens / num_kv_slots: rows of q and of k_cache / v_cache (the extents a TMA descriptor needs); 0 = unknown,
+ * which keeps the launch on the cp.async gather kernel.
  */
 int b200_extend_attn(void* o, const void* q, const void* k_new, const void* v_new,
                      const void* k_cache, const void* v_cache,
@@ -174,7 +176,7 @@ int b200_extend_attn(void* o, const void* q, const void* k_new, const void* v_ne
                      int64_t q_token_stride, int64_t o_token_stride,
                      int64_t knew_token_stride, int64_t vnew_token_stride,
                      int64_t kv_token_stride, float sm_scale, float logit_cap, int causal,
-                     int dtype, void* stream);
+                     int dtype, void* stream, int64_t num_q_tokens, int64_t num_kv_slots);
 
 /* ---- LSE merge ----------------------------------------------------------------------------
  * Replaces merge_state / merge_state_v2 (sgl-kernel/csrc/attention/cascade.cu:20-55,

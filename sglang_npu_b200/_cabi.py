@@ -60,7 +60,7 @@ _SIGNATURES = {
                                        c_size_t, c_int, _P],
     "b200_extend_attn": [_P, _P, _P, _P, _P, _P, _P, c_int64, _P, c_int, _P, _P, c_int, c_int,
                          c_int, c_int, c_int, c_int64, c_int64, c_int64, c_int64, c_int64, c_float,
-                         c_float, c_int, c_int, _P],
+                         c_float, c_int, c_int, _P, c_int64, c_int64],
     "b200_merge_state": [_P, _P, _P, _P, _P, _P, c_int64, c_int, c_int, c_int, _P],
     "b200_per_token_quant_int8": [_P, _P, _P, c_int64, c_int64, c_int64, c_int, _P],
     "b200_int8_scaled_mm_workspace_bytes": [c_int64, c_int64, c_int64, POINTER(c_size_t)],

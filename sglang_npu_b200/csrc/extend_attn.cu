@@ -273,7 +273,7 @@ B200_API int b200_extend_attn(
     const int32_t* qo_indptr, const int32_t* prefix_lens, int batch, int max_extend_len, int num_q_heads,
     int num_kv_heads, int head_dim, int64_t q_token_stride, int64_t o_token_stride, int64_t knew_token_stride,
     int64_t vnew_token_stride, int64_t kv_token_stride, float sm_scale, float logit_cap, int causal, int dtype,
-    void* stream) {
+    void* stream, int64_t num_q_tokens, int64_t num_kv_slots) {
   using namespace b200;
   B200_REQUIRE(batch >= 0 && max_extend_len >= 0, "extend_attn: negative sizes");
   if (batch == 0 || max_extend_len == 0) return B200_OK;
@@ -301,8 +301,18 @@ B200_API int b200_extend_attn(
   // tcgen05 / TMEM tiles (extend_attn_umma.cu) unless the whole batch is a handful of query rows, where 128-row
   // MMA tiles would be mostly padding; B200_EXTEND_LEGACY=1 forces the mma.sync kernel (A/B measurements)
   static const bool legacy = getenv("B200_EXTEND_LEGACY") != nullptr && getenv("B200_EXTEND_LEGACY")[0] == '1';
-  if (!legacy && max_extend_len > 16 && (head_dim == 128 || head_dim == 64) && (dtype == B200_BF16 || dtype == B200_F16))
+  if (!legacy && max_extend_len > 16 && (head_dim == 128 || head_dim == 64) && (dtype == B200_BF16 || dtype == B200_F16)) {
+    // two query tiles per CTA + TMA (extend_attn_fa.cu) from 129 query rows per request up, when all K/V is read
+    // through the page table and the caller gave the tensor extents TMA needs; B200_EXTEND_FA=0 keeps the
+    // one-tile kernel (A/B measurements)
+    static const bool fa = getenv("B200_EXTEND_FA") == nullptr || getenv("B200_EXTEND_FA")[0] != '0';
+    if (fa && max_extend_len > 128 && k_new == nullptr && num_q_tokens > 0 && num_kv_slots > 0 &&
+        q_token_stride % 8 == 0 && kv_token_stride % 8 == 0) {
+      const int rc = launch_extend_fa(a, max_extend_len, head_dim, dtype, num_q_tokens, num_kv_slots, st);
+      if (rc != B200_ERR_UNSUPPORTED) return rc;
+    }
     return launch_extend_umma(a, max_extend_len, head_dim, dtype, st);
+  }
   if (dtype == B200_BF16) {
     if (head_dim == 128) return launch_extend<__nv_bfloat16, 128>(a, max_extend_len, st);
     if (head_dim == 64) return launch_extend<__nv_bfloat16, 64>(a, max_extend_len, st);

@@ -35,6 +35,10 @@ struct ExtendArgs {
   int seg_rows = 0, seg_prefix = 0;  // q rows (= decode batch) and shared-prefix length: passed by value, no device arrays
 };
 
+// two-query-tile TMA kernel (extend_attn_fa.cu); B200_ERR_UNSUPPORTED (no error text) for what it does not cover
+int launch_extend_fa(const ExtendArgs& a, int max_extend_len, int head_dim, int dtype, int64_t num_q_tokens,
+                     int64_t num_kv_slots, cudaStream_t stream);
+
 // tcgen05 path (extend_attn_umma.cu); returns B200_ERR_UNSUPPORTED for shapes it does not cover
 int launch_extend_umma(const ExtendArgs& a, int max_extend_len, int head_dim, int dtype, cudaStream_t stream);
 

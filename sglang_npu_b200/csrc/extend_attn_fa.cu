@@ -15,7 +15,7 @@
 //   * TMEM (512 columns): S0 | S1 | O0 | O1.  P (bf16/f16) is written back over the first 64 columns of its own S
 //     tile with tcgen05.st and is the A operand of P V straight from tensor memory — no shared-memory P tile, no
 //     bank conflicts, 64 KB of shared memory returned to the K/V rings (2 K + 3 V stages);
-//   * the row of S (128 fp32) is held in registers (setmaxnreg: 232 for the softmax warps, 48 for the rest), so the row
+//   * the row of S (128 fp32) is held in registers (setmaxnreg: 232 for the softmax warps, 40 for the rest), so the row
 //     max and the exponentials read TMEM once; the max a row is normalised to only moves when the tile max exceeds
 //     it by 2^8 (O is then rescaled in TMEM by the same thread; rare after the first tiles);
 //   * a fixed fraction of the exponentials is evaluated on the FMA pipe (Cody-Waite + cubic, 7.5e-5 relative —
@@ -205,7 +205,7 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   constexpr uint32_t kOCol = 256;  // S0 / P0 at column 0, S1 / P1 at 128, O0 at 256, O1 at 256 + D
 
   if (warp < 4) {
-    fa_reg_dealloc<48>();
+    fa_reg_dealloc<40>();  // 128 x (168 - 40) registers returned = 256 x (232 - 168) taken below
     if (warp == 0) {
       // ---- TMA producer ----------------------------------------------------------------------------------------
       const int64_t req = load_index(a.req_pool_indices, b, a.index_is_int64);

@@ -20,6 +20,7 @@ struct GemmArgs {
   int kb_per_split;  // K blocks per cluster rank
   int splits;        // cluster size along z (1, 2, 4, 8)
   int out_is_bf16;
+  int m_blocks;     // stream-K: token blocks of BN per 128-channel weight tile (>= 1)
   int64_t sm_rs, sm_cs;  // scale_m[m * sm_rs + kb * sm_cs]          (F8Block)
   int64_t sn_rs, sn_cs;  // scale_n[(n / 128) * sn_rs + kb * sn_cs]   (F8Block)
   unsigned long long* trace;  // diagnostics (b200_debug_set_trace) or null

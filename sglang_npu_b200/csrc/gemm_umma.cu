@@ -610,6 +610,13 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 //     and adds their partials in CTA order.  int32 sums are exact and the fp32 order is fixed, so the result is
 //     bit-deterministic; the flags are reset by their consumer (self-cleaning workspace).
 // All G <= #SM CTAs are co-resident (one per SM by shared-memory footprint), so the flag wait cannot deadlock.
+// Token blocks (g.m_blocks = MB > 1, M <= MB * BN <= 512): the "tile" of the scheme above becomes a (weight tile, token
+// block) pair — unit u = ((tile * MB + mb) * num_kb + kb) — so a batch wider than BN multiplies the units instead of
+// widening them.  On 1/TP-size weight shards (TP 4: M = 256, 12 .. 56 weight tiles) one BN = 256 tile was shared by
+// ~12 CTAs whose 128 KB partials the owner summed one after the other (30 us per GEMM, profiles/r02e_timeline_*_n4*);
+// with BN = 64 x 4 token blocks a CTA holds ~10 units, a tile has ~3 sharers and a partial is 32 KB.  The weight
+// tile is re-read once per token block, from L2 (the blocks of a tile are adjacent in unit order).
+constexpr int kSkMaxM = 512;
 template <int BN>
 struct StreamK {
   static constexpr int kStageBytes = 128 * kBK + BN * kBK;
@@ -630,7 +637,7 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
   constexpr int kWBytes = 128 * kBK;
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint32_t s_tmem_base;
-  __shared__ __align__(16) float s_scale_m[BN];
+  __shared__ __align__(16) float s_scale_m[kSkMaxM];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar = base + L::kBarOff;
   const uint32_t fix_bar = bar + (2 * STAGES + 4) * 8;
@@ -673,6 +680,7 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
   const int G = gridDim.x;
   const int c = blockIdx.x;
   const int nkb = g.num_kb;
+  const int MB = g.m_blocks;
   const int u0 = (int)((int64_t)c * total_units / G);
   const int u1 = (int)((int64_t)(c + 1) * total_units / G);
 
@@ -680,28 +688,28 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
     if (lane == 0) {
       const int n_units = u1 - u0;
       const int pre = min(n_units, STAGES);
-      int tile = u0 / nkb, kb = u0 - tile * nkb;
+      int vt = u0 / nkb, kb = u0 - vt * nkb;  // vt = tile * MB + mb
       // weights do not depend on the previous kernel: fill the ring with weight boxes before the PDL wait
       for (int i = 0; i < pre; ++i) {
         mbar_expect_tx(full_bar(i), L::kStageBytes);
-        tma_load_2d(base + i * L::kStageBytes, &tmap_w, full_bar(i), kb * kBK, tile * 128, kEvictFirst);
-        if (++kb == nkb) { kb = 0; ++tile; }
+        tma_load_2d(base + i * L::kStageBytes, &tmap_w, full_bar(i), kb * kBK, (vt / MB) * 128, MB > 1 ? kEvictNormal : kEvictFirst);
+        if (++kb == nkb) { kb = 0; ++vt; }
       }
       pdl_wait();
       trace_mark(tr, 2);
-      tile = u0 / nkb, kb = u0 - tile * nkb;
+      vt = u0 / nkb, kb = u0 - vt * nkb;
       for (int i = 0; i < pre; ++i) {
-        tma_load_2d(base + i * L::kStageBytes + kWBytes, &tmap_x, full_bar(i), kb * kBK, 0, kEvictLast);
-        if (++kb == nkb) { kb = 0; ++tile; }
+        tma_load_2d(base + i * L::kStageBytes + kWBytes, &tmap_x, full_bar(i), kb * kBK, (vt % MB) * BN, kEvictLast);
+        if (++kb == nkb) { kb = 0; ++vt; }
       }
       for (int i = pre; i < n_units; ++i) {
         const int s = i % STAGES;
         mbar_wait(empty_bar(s), ((i / STAGES) & 1) ^ 1);
         mbar_expect_tx(full_bar(s), L::kStageBytes);
         const uint32_t sa = base + s * L::kStageBytes;
-        tma_load_2d(sa, &tmap_w, full_bar(s), kb * kBK, tile * 128, kEvictFirst);
-        tma_load_2d(sa + kWBytes, &tmap_x, full_bar(s), kb * kBK, 0, kEvictLast);
-        if (++kb == nkb) { kb = 0; ++tile; }
+        tma_load_2d(sa, &tmap_w, full_bar(s), kb * kBK, (vt / MB) * 128, MB > 1 ? kEvictNormal : kEvictFirst);
+        tma_load_2d(sa + kWBytes, &tmap_x, full_bar(s), kb * kBK, (vt % MB) * BN, kEvictLast);
+        if (++kb == nkb) { kb = 0; ++vt; }
       }
     } else {
       pdl_wait();
@@ -745,18 +753,20 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
     const int row = q * 32 + lane;
     const bool has_bias = g.bias != nullptr;
     const bool bf = g.out_is_bf16 != 0;
-    const int m_cols = min(BN, (g.M + 15) & ~15);  // token columns that hold data, in groups of 16
     // per-token scales of this launch -> shared memory (the inner loops below touch no global memory but their stores)
-    for (int i = threadIdx.x - 128; i < BN; i += 128) s_scale_m[i] = (!kDense16 && i < g.M) ? g.scale_m[i] : 0.f;
+    for (int i = threadIdx.x - 128; i < MB * BN; i += 128) s_scale_m[i] = (!kDense16 && i < g.M) ? g.scale_m[i] : 0.f;
     epi_bar_sync();
     uint32_t fix_phase = 0;
     int seg = 0;
     for (int u = u0; u < u1; ++seg) {
-      const int tile = u / nkb;
-      const int kb_begin = u - tile * nkb;
-      const int seg_end = min(u1, (tile + 1) * nkb);
+      const int vt = u / nkb;  // (weight tile, token block)
+      const int tile = vt / MB;
+      const int t0 = (vt - tile * MB) * BN;  // first token of the block
+      const int m_cols = min(BN, (g.M - t0 + 15) & ~15);  // token columns that hold data, in groups of 16
+      const int kb_begin = u - vt * nkb;
+      const int seg_end = min(u1, (vt + 1) * nkb);
       const bool starts = kb_begin == 0;
-      const bool ends = seg_end == (tile + 1) * nkb;
+      const bool ends = seg_end == (vt + 1) * nkb;
       const int buf = seg & 1;
       mbar_wait(tmem_full_bar(buf), (seg >> 1) & 1);
       tc_fence_after();
@@ -783,7 +793,7 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
         // owner of the tile: peers are the CTAs after this one whose ranges start inside the tile
         int n_peers = 0;
         if (!ends) {
-          const int tile_end = (tile + 1) * nkb;
+          const int tile_end = (vt + 1) * nkb;
           while (c + 1 + n_peers < G && (int)((int64_t)(c + 1 + n_peers) * total_units / G) < tile_end) ++n_peers;
           for (int p = 0; p < n_peers; ++p)
             while (ld_acquire_u32(flags + c + 1 + p) == 0u) {
@@ -836,8 +846,8 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
               }
             }
             if (last) {
-              finalize_store16<MODE>(r, s_scale_m + c0, sn, has_bias, bias, bf, outp + (int64_t)c0 * g.N,
-                                     accp ? accp + (int64_t)c0 * g.N : nullptr, g.N, g.M - c0, n_ok);
+              finalize_store16<MODE>(r, s_scale_m + t0 + c0, sn, has_bias, bias, bf, outp + (int64_t)(t0 + c0) * g.N,
+                                     accp ? accp + (int64_t)(t0 + c0) * g.N : nullptr, g.N, g.M - t0 - c0, n_ok);
             } else {
               tmem_st16(taddr + c0, r);
             }
@@ -917,8 +927,21 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmA
 // workspace of the stream-K decode path: [flags, kSkFlagBytes][partials: G x BN x 128 x 4 B]
 static int streamk_bn(int64_t M) { return M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256; }
 static size_t streamk_workspace_bytes(int64_t M) {
-  if (M > 256) return 0;
+  if (M > kSkMaxM) return 0;
   return (size_t)kSkFlagBytes + (size_t)sm_count() * streamk_bn(M) * 128 * 4;
+}
+// Token-block width of the stream-K kernel for the scaled (int8 / per-channel FP8) GEMMs: up to 64 tokens one block as
+// wide as the batch; wider batches are cut into 128-token blocks when that still leaves every CTA >= 16 units of
+// weight stream (few sharers per tile anyway) or the batch is compute-heavy (M > 256), else into 64-token blocks.
+// Measured on the Llama-3.1-8B shard shapes, layer total of the four GEMMs (profiles/r02f_kbench_int8_tokenblocks.jsonl):
+// TP 4 / M 256: 114.7 us with one 256-token block, 57.9 us with 128, 51.5 us with 64; TP 8 / M 512: 102 / 48.6 / 55.4;
+// TP 1 / M 256: 112 / 99 / 133.  B200_SK_BN overrides the width for M > 64 (tuning runs).
+static int streamk_block_bn(int64_t M, int64_t weight_units, int sms) {
+  static const int forced = getenv("B200_SK_BN") ? atoi(getenv("B200_SK_BN")) : 0;
+  if (M <= 64) return streamk_bn(M);
+  if (forced == 64 || forced == 128 || forced == 256) return forced >= M ? streamk_bn(M) : forced;
+  if (M > 256) return 128;
+  return weight_units * ceil_div(M, 128) >= 16ll * sms ? 128 : 64;
 }
 
 template <int MODE, int BN>
@@ -941,6 +964,7 @@ static int run_gemm(GemmArgs g, const void* a, const void* b, int64_t M, int64_t
   g.num_kb = (int)ceil_div(K, kBK);
   g.trace = g_trace;
   g.trace_slots = (int)g_trace_slots;
+  g.m_blocks = 1;
   static const int debug = getenv("B200_GEMM_DEBUG") ? atoi(getenv("B200_GEMM_DEBUG")) : 0;
   g.debug = debug;
   CUtensorMap ta, tb;
@@ -950,18 +974,22 @@ static int run_gemm(GemmArgs g, const void* a, const void* b, int64_t M, int64_t
     // measured (profiles/r01e_gemm_decode.jsonl): below 64 tokens the epilogue is negligible and the cluster kernel's
     // two CTAs per SM start streaming earlier; from 64 tokens up the balanced persistent kernel wins
     static const int streamk_min_m = getenv("B200_GEMM_STREAMK_MIN_M") ? atoi(getenv("B200_GEMM_STREAMK_MIN_M")) : 33;
-    if (M <= 256 && M >= streamk_min_m && ws != nullptr && streamk) {
+    // 256 < M <= 512 (a TP-8 decode batch): weight streaming still wins while the 128x256 tiles of the prefill kernel
+    // would not fill the SMs once (1/8-size shards: 12 .. 64 tiles)
+    const bool sk_wide = M > 256 && M <= kSkMaxM && ceil_div(M, 128) * ceil_div(N, kPfBN) < sm_count();
+    if ((M <= 256 || sk_wide) && M >= streamk_min_m && ws != nullptr && streamk) {
       const size_t need = streamk_workspace_bytes(M);
       if (ws_bytes < need)
         return fail(B200_ERR_WORKSPACE, "scaled_mm: workspace of %zu bytes, %zu needed", ws_bytes, need);
       B200_REQUIRE(((uintptr_t)ws % 16) == 0, "scaled_mm: workspace must be 16-byte aligned");
-      const int bn = streamk_bn(M);
-      const int64_t units = ceil_div(N, 128) * g.num_kb;
+      const int bn = streamk_block_bn(M, ceil_div(N, 128) * g.num_kb, sm_count());
+      g.m_blocks = (int)ceil_div(M, bn);
+      const int64_t units = ceil_div(N, 128) * g.m_blocks * g.num_kb;
       B200_REQUIRE(units < (1ll << 30), "scaled_mm: too many work units");
       // Grid: one CTA per SM.  When there are fewer tiles than SMs, prefer P = #SM / tiles CTAs per tile with ranges
       // aligned to tile boundaries (one segment per CTA, P - 1 peers per owner) if that still fills >= 85% of the SMs.
       const int sms = sm_count();
-      const int tiles = (int)ceil_div(N, 128);
+      const int tiles = (int)ceil_div(N, 128) * g.m_blocks;
       int ctas = (int)(units < sms ? units : sms);
       if (tiles < sms) {
         const int per_tile = sms / tiles < g.num_kb ? sms / tiles : g.num_kb;
@@ -1062,6 +1090,7 @@ static int run_dense16(GemmArgs g, const void* a, const void* b, int64_t M, int6
   g.num_kb = (int)ceil_div(K * 2, kBK);
   g.trace = g_trace;
   g.trace_slots = (int)g_trace_slots;
+  g.m_blocks = 1;
   g.splits = 1;
   g.kb_per_split = g.num_kb;
   const size_t need = streamk_workspace_bytes(M);

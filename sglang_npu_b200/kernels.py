@@ -257,7 +257,7 @@ def extend_attention_fwd(q: torch.Tensor, k_new: Optional[torch.Tensor], v_new: 
         req_to_token.stride(0), ptr(req_pool_indices), _is64(req_pool_indices), ptr(qo_indptr),
         ptr(prefix_lens), bs, int(max_extend_len), hq, hkv, d, q.stride(0), o.stride(0),
         kn_stride, vn_stride, k_buffer.stride(0), float(sm_scale), float(logit_cap), int(causal),
-        dtype_code(q.dtype), stream_ptr(q.device)), "b200_extend_attn")
+        dtype_code(q.dtype), stream_ptr(q.device), T, k_buffer.shape[0]), "b200_extend_attn")
 
 
 # ---- LSE merge ---------------------------------------------------------------------------------

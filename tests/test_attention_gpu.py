@@ -164,6 +164,41 @@ def test_extend_prefix_and_ragged(cuda_device, hq, hkv, d, page):
     assert_close_path(o, ref, f"extend hq{hq} hkv{hkv} d{d} page{page}")
 
 
+@pytest.mark.parametrize("page", [1, 16])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("causal", [True, False])
+def test_extend_two_tile_tma_kernel(cuda_device, page, dtype, causal):
+    """Requests with more than 128 new tokens take extend_attn_fa.cu (256 query rows per CTA, TMA page boxes):
+    one- and two-tile blocks, ragged last KV tiles, prefixes that are not tile multiples, 1-row boxes (page 1)."""
+    lens = [257, 206, 812, 1024, 130]
+    prefix = [0, 77, 300, 24, 1] if causal else [0, 0, 0, 0, 0]
+    o, ref = _extend_case(cuda_device, lens, prefix, 8, 2, 128, page, dtype, causal=causal)
+    assert_close_path(o, ref, f"extend two-tile page{page} {dtype} causal={causal}")
+
+
+def test_extend_two_tile_matches_one_tile_kernel_subprocess(cuda_device):
+    """B200_EXTEND_FA=0 (read once per process) keeps the one-tile cp.async kernel: both kernels against the oracle on
+    the same batch, and against each other."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import torch, sys\n"
+        "from tests.test_attention_gpu import _extend_case\n"
+        "o, ref = _extend_case(torch.device('cuda:0'), [700, 300], [100, 0], 32, 8, 128, 16, torch.bfloat16)\n"
+        "torch.save(o.cpu(), sys.argv[1])\n"
+    )
+    outs = []
+    for fa in ("1", "0"):
+        path = f"/tmp/b200_extend_fa_{fa}_{os.getpid()}.pt"
+        env = dict(os.environ, B200_EXTEND_FA=fa, PYTHONPATH=root)
+        res = subprocess.run([sys.executable, "-c", code, path], capture_output=True, text=True, env=env, cwd=root, timeout=600)
+        assert res.returncode == 0, res.stdout + res.stderr
+        outs.append(torch.load(path))
+        os.remove(path)
+    assert_close_path(outs[0], outs[1].float(), "two-tile vs one-tile extend kernel", max_abs=1e-2)
+
+
 def test_extend_without_saving_kv_reads_activations(cuda_device):
     o, ref = _extend_case(cuda_device, [100, 70], [30, 0], 8, 2, 128, 16, torch.bfloat16, save_kv=False)
     assert_close_path(o, ref, "extend save_kv_cache=False")

@@ -115,6 +115,43 @@ def test_int8_scaled_mm_prefill_shapes(cuda_device, M, N, K):
     assert torch.equal(out.view(torch.int16), ref.view(torch.int16))
 
 
+# TP shard shapes (Llama-3.1-8B at tp 4 / tp 8) at the decode batches of the weak-scaling bench (64 tokens per GPU): the
+# stream-K kernel cuts the batch into 64-token blocks, incl. a ragged last block and 256 < M <= 512
+@pytest.mark.parametrize("M", [65, 200, 256, 300, 512])
+@pytest.mark.parametrize("N,K", [(1536, 4096), (4096, 1024), (7168, 4096), (4096, 3584), (768, 4096), (4096, 512)])
+def test_int8_scaled_mm_token_blocks_tp_shards(cuda_device, M, N, K):
+    out, acc, ref, ref_acc = _run_mm(cuda_device, M, N, K, with_bias=(M == 200), out_dtype=torch.bfloat16)
+    assert torch.equal(acc, ref_acc), "int32 accumulators must be bit-exact"
+    assert torch.equal(out.view(torch.int16), ref.view(torch.int16))
+
+
+@pytest.mark.parametrize("bn", [128, 256])
+def test_int8_stream_k_wider_token_blocks_subprocess(cuda_device, bn):
+    """B200_SK_BN (read once per process) selects 128- / 256-token blocks instead of 64: same bits."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import torch\n"
+        "from oracle import quant_oracle as qo\n"
+        "from sglang_npu_b200 import kernels\n"
+        "g = torch.Generator().manual_seed(3)\n"
+        "for (M, N, K) in [(130, 1536, 4096), (256, 4096, 1024), (300, 7168, 4096), (512, 768, 4096), (500, 4096, 3584)]:\n"
+        "    a = torch.randint(-127, 128, (M, K), generator=g, dtype=torch.int32).to(torch.int8)\n"
+        "    w = torch.randint(-127, 128, (N, K), generator=g, dtype=torch.int32).to(torch.int8)\n"
+        "    sa, sb = torch.rand(M, generator=g), torch.rand(N, generator=g)\n"
+        "    out, acc = kernels.int8_scaled_mm(a.cuda(), w.cuda().t(), sa.cuda(), sb.cuda(), torch.bfloat16, return_acc=True)\n"
+        "    assert torch.equal(acc.cpu(), qo.int8_accumulate(a, w)), (M, N, K)\n"
+        "    ref = qo.int8_scaled_mm(a, w, sa, sb, torch.bfloat16, None)\n"
+        "    assert torch.equal(out.cpu().view(torch.int16), ref.view(torch.int16)), (M, N, K)\n"
+        "print('ok')\n"
+    )
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, B200_SK_BN=str(bn), PYTHONPATH=root)
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, cwd=root, timeout=600)
+    assert res.returncode == 0 and "ok" in res.stdout, res.stdout + res.stderr
+
+
 def test_int8_split_k_workspace_is_self_cleaning(cuda_device):
     """Back-to-back calls reuse the split-K workspace; results must not drift."""
     for i in range(3):

@@ -104,8 +104,10 @@ def bench_decode(args):
 
 def bench_gemm_int8(args):
     dev = torch.device("cuda")
-    shapes = [(4096, 6144), (4096, 4096), (4096, 28672), (14336, 4096)]
+    tp = args.tp or 1  # Llama-3.1-8B shard shapes [K, N] of one TP rank
+    shapes = [(4096, 6144 // tp), (4096 // tp, 4096), (4096, 28672 // tp), (14336 // tp, 4096)]
     for m in ([args.m] if args.m else [1, 16, 64, 128, 256, 512, 2048, 8192]):
+        tot = 0.0
         for (kk, n) in shapes:
             a = torch.randint(-127, 128, (m, kk), device=dev, dtype=torch.int8)
             copies = max(2, int(300e6 // (n * kk)) + 1)
@@ -115,8 +117,10 @@ def bench_gemm_int8(args):
             med = best = timeit_rot(lambda c: (lambda: kernels.int8_scaled_mm(a, ws[c].t(), sa, sb, torch.bfloat16,
                                                                               cluster_splitk=args.cluster)), copies)
             byts = n * kk + m * kk + m * n * 2
-            print(json.dumps(dict(kernel="int8_scaled_mm", path="cluster" if args.cluster else "streamk", m=m, n=n, k=kk, ms_med=round(med, 4), ms_best=round(best, 4),
+            tot += med
+            print(json.dumps(dict(kernel="int8_scaled_mm", path="cluster" if args.cluster else "streamk", tp=tp, sk_bn=os.environ.get("B200_SK_BN", "default"), m=m, n=n, k=kk, ms_med=round(med, 4), ms_best=round(best, 4),
                                   gbs=round(byts / med / 1e6, 1), tops=round(2 * m * n * kk / med / 1e9, 1))), flush=True)
+        print(json.dumps(dict(kernel="int8_scaled_mm layer total", tp=tp, sk_bn=os.environ.get("B200_SK_BN", "default"), m=m, us=round(tot * 1e3, 1))), flush=True)
 
 
 def bench_gemm_fp8(args):
