@@ -48,9 +48,7 @@ constexpr int kFaThreads = 384;
 constexpr int kFaKStages = 2;
 constexpr int kFaVStages = 3;
 constexpr float kFaRescale = 8.f;  // log2 domain
-#ifndef B200_FA_POLY_PER8
-#define B200_FA_POLY_PER8 2        // of every 8 exponentials, this many run on the FMA pipe
-#endif
+constexpr int kFaPolyDefault = 2;   // of every 8 exponentials, this many run on the FMA pipe (B200_FA_POLY overrides)
 
 template <int D>
 struct FaSmem {
@@ -130,7 +128,7 @@ __device__ __forceinline__ void st_shared_zero16(uint32_t addr) {
 
 }  // namespace
 
-template <typename T, int D>
+template <typename T, int D, int POLY>
 __global__ void __launch_bounds__(kFaThreads, 1)
 extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k16,
                       const __grid_constant__ CUtensorMap tm_k1, const __grid_constant__ CUtensorMap tm_v16,
@@ -413,7 +411,7 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
           float a0, a1;
           fa_fma2(a0, a1, __uint_as_float(s[32 * c + i]), __uint_as_float(s[32 * c + i + 1]), sc, neg_m);
           float p0, p1;
-          if ((i & 7) < B200_FA_POLY_PER8) {
+          if ((i & 7) < POLY) {
             p0 = fa_exp2_fma(a0);
             p1 = fa_exp2_fma(a1);
           } else {
@@ -501,7 +499,7 @@ int fa_tmap(CUtensorMap* out, const void* base, uint64_t rows, uint64_t row_byte
   return B200_OK;
 }
 
-template <typename T, int D>
+template <typename T, int D, int POLY>
 int launch_fa(const ExtendArgs& a, int max_extend_len, int64_t num_q_tokens, int64_t num_kv_slots, cudaStream_t stream) {
   using L = FaSmem<D>;
   CUtensorMap tq, tk16, tk1, tv16, tv1;
@@ -512,7 +510,7 @@ int launch_fa(const ExtendArgs& a, int max_extend_len, int64_t num_q_tokens, int
   if (st == B200_OK) st = fa_tmap(&tv16, a.v_cache, (uint64_t)num_kv_slots, kv_row, (uint64_t)a.kv_token_stride * 2, 16);
   if (st == B200_OK) st = fa_tmap(&tv1, a.v_cache, (uint64_t)num_kv_slots, kv_row, (uint64_t)a.kv_token_stride * 2, 1);
   if (st != B200_OK) return st;
-  auto kern = extend_attn_fa_kernel<T, D>;
+  auto kern = extend_attn_fa_kernel<T, D, POLY>;
   B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
   dim3 grid((max_extend_len + 2 * kFaBM - 1) / (2 * kFaBM), a.num_q_heads, a.batch);
   return launch_k(kern, grid, dim3(kFaThreads), L::kBytes, stream, 1, true, tq, tk16, tk1, tv16, tv1, a);
@@ -526,8 +524,17 @@ int launch_extend_fa(const ExtendArgs& a, int max_extend_len, int head_dim, int 
                      int64_t num_kv_slots, cudaStream_t stream) {
   if (a.k_new != nullptr || a.part_o != nullptr || head_dim != 128 || num_q_tokens <= 0 || num_kv_slots <= 0)
     return B200_ERR_UNSUPPORTED;
-  if (dtype == B200_BF16) return launch_fa<__nv_bfloat16, 128>(a, max_extend_len, num_q_tokens, num_kv_slots, stream);
-  if (dtype == B200_F16) return launch_fa<__half, 128>(a, max_extend_len, num_q_tokens, num_kv_slots, stream);
+  static const int poly = getenv("B200_FA_POLY") ? atoi(getenv("B200_FA_POLY")) : kFaPolyDefault;
+#define B200_FA_LAUNCH(TT)                                                                                        \
+  switch (poly) {                                                                                                 \
+    case 0: return launch_fa<TT, 128, 0>(a, max_extend_len, num_q_tokens, num_kv_slots, stream);                  \
+    case 4: return launch_fa<TT, 128, 4>(a, max_extend_len, num_q_tokens, num_kv_slots, stream);                  \
+    case 6: return launch_fa<TT, 128, 6>(a, max_extend_len, num_q_tokens, num_kv_slots, stream);                  \
+    default: return launch_fa<TT, 128, kFaPolyDefault>(a, max_extend_len, num_q_tokens, num_kv_slots, stream);    \
+  }
+  if (dtype == B200_BF16) { B200_FA_LAUNCH(__nv_bfloat16) }
+  if (dtype == B200_F16) { B200_FA_LAUNCH(__half) }
+#undef B200_FA_LAUNCH
   return B200_ERR_UNSUPPORTED;
 }
 

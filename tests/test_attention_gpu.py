@@ -196,7 +196,7 @@ def test_extend_two_tile_matches_one_tile_kernel_subprocess(cuda_device):
         assert res.returncode == 0, res.stdout + res.stderr
         outs.append(torch.load(path))
         os.remove(path)
-    assert_close_path(outs[0], outs[1].float(), "two-tile vs one-tile extend kernel", max_abs=1e-2)
+    assert_close_path(outs[0], outs[1].float(), "two-tile vs one-tile extend kernel")  # two bf16 roundings: 1 ulp at |o| ~ 2
 
 
 def test_extend_without_saving_kv_reads_activations(cuda_device):

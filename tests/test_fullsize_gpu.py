@@ -142,8 +142,11 @@ def test_extend_attention_cfg3(cuda_device, prefix, new):
     assert_close_path(o[rows], ref, f"extend cfg3 prefix={prefix} new={new}")
     # (b) determinism + chunk invariance over ALL rows: the same tokens extended as two halves (second half sees the
     # first through the cache) agree with the single launch
-    o_again = layer(q, k, v, fb, save_kv_cache=False).view(new, hq, d)
+    o_again = layer(q, k, v, fb, save_kv_cache=False, kv_in_cache=True).view(new, hq, d)
     assert torch.equal(o, o_again)
+    # the same chunk with its K/V read from the activations instead of the cache: the one-tile cp.async kernel
+    o_act = layer(q, k, v, fb, save_kv_cache=False).view(new, hq, d)
+    assert_close_path(o_act, o.float(), "new tokens from the activations vs from the cache")
     half = new // 2
     fb1 = harness.extend_batch(runner, backend, pb.req_pool_indices, torch.tensor([prefix + half]), torch.tensor([prefix]),
                                slots[prefix: prefix + half])
