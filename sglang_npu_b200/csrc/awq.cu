@@ -281,7 +281,7 @@ awq_streamk_kernel(const __grid_constant__ CUtensorMap tmap_x, const AwqSkArgs g
 
   if (warp == 0) {
     // ---- packed words: independent of the previous kernel, so the ring fills before the PDL wait --------------------
-    if (lane == 0) {
+    if (elect_one()) {
       for (int i = 0; i < u1 - u0; ++i) {
         const int s = i % SW;
         mbar_wait(w_empty(s), ((i / SW) & 1) ^ 1);
@@ -294,7 +294,7 @@ awq_streamk_kernel(const __grid_constant__ CUtensorMap tmap_x, const AwqSkArgs g
   } else if (warp == 3) {
     // ---- x chunks (64 k each, two per unit): written by the previous kernel --------------------------------------------
     pdl_wait();
-    if (lane == 0) {
+    if (elect_one()) {
       int kb = u0 % nkb;
       for (int i = 0; i < u1 - u0; ++i) {
 #pragma unroll
@@ -311,7 +311,7 @@ awq_streamk_kernel(const __grid_constant__ CUtensorMap tmap_x, const AwqSkArgs g
     }
   } else if (warp == 1) {
     pdl_wait();
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = make_idesc(/*f32*/ 1, AwqMagic<T>::kFmt, AwqMagic<T>::kFmt, 128, BN);
       int it = 0, seg = 0;
       for (int u = u0; u < u1; ++seg) {

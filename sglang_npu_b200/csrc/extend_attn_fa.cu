@@ -9,13 +9,17 @@
 // costs the pipe ~1050 cycles (Q K^T + P V) and the warpgroup >= 1024 cycles of MUFU.EX2 alone (16 / clk / SM), plus
 // its FMA / conversion / shared-memory work with a single warp per scheduler to hide latency — the pipe sat at 38 %
 // (profiles/r01h_extend_attn_ncu_full.txt).  Here:
-//   * one CTA = 256 query rows of one (request, q head) = two 128-row tiles that share every K/V tile: the tensor
-//     pipe alternates  P0 V -> Q0 K^T -> P1 V -> Q1 K^T  while the two softmax warpgroups (one per tile, two warps per
-//     scheduler) work on the S tile the pipe produced one slot earlier;
-//   * TMEM (512 columns): S0 | S1 | O0 | O1.  P (bf16/f16) is written back over the first 64 columns of its own S
-//     tile with tcgen05.st and is the A operand of P V straight from tensor memory — no shared-memory P tile, no
-//     bank conflicts, 64 KB of shared memory returned to the K/V rings (2 K + 3 V stages);
-//   * the row of S (128 fp32) is held in registers (setmaxnreg: 232 for the softmax warps, 40 for the rest), so the row
+//   * one CTA = 256 query rows of one (request, q head) = two 128-row tiles that share every K/V tile, with one
+//     softmax warpgroup per tile (two warps per scheduler);
+//   * KV tiles of 64 positions and TWO S buffers per query tile: Q K^T of tile j+1 is issued before P V of tile j,
+//     so a softmax warpgroup finds its next S tile waiting and the tensor pipe finds the next P waiting — the
+//     barrier round trips (commit -> softmax -> arrive -> issue) are off the critical path.  (A first version with
+//     128-position tiles and a single S buffer per query tile had each warpgroup wait for its own P V + Q K^T
+//     block: tensor pipe 48 % active, MUFU 48 %, neither saturated — profiles/r02i_extend_fa_ncu.txt.)
+//   * TMEM (512 columns): S0[2] | S1[2] | O0 | O1 (64 + 64 + 64 + 64 + 128 + 128).  P (bf16/f16) is written back over
+//     the first 32 columns of its own S buffer with tcgen05.st and is the A operand of P V straight from tensor
+//     memory — no shared-memory P tile, no bank conflicts, its shared memory goes to the K/V rings (4 K + 5 V stages);
+//   * the row of S (64 fp32) is held in registers (setmaxnreg: 232 for the softmax warps, 40 for the rest), so the row
 //     max and the exponentials read TMEM once; the max a row is normalised to only moves when the tile max exceeds
 //     it by 2^8 (O is then rescaled in TMEM by the same thread; rare after the first tiles);
 //   * a fixed fraction of the exponentials is evaluated on the FMA pipe (Cody-Waite + cubic, 7.5e-5 relative —
@@ -43,22 +47,24 @@ using namespace sm100;
 namespace {
 
 constexpr int kFaBM = 128;       // query rows per tile (two tiles per CTA)
-constexpr int kFaBN = 128;       // KV positions per tile
+constexpr int kFaBN = 64;        // KV positions per tile
 constexpr int kFaThreads = 384;
-constexpr int kFaKStages = 2;
-constexpr int kFaVStages = 3;
+constexpr int kFaKStages = 4;
+constexpr int kFaVStages = 5;
 constexpr float kFaRescale = 8.f;  // log2 domain
 constexpr int kFaPolyDefault = 2;   // of every 8 exponentials, this many run on the FMA pipe (B200_FA_POLY overrides)
 
 template <int D>
 struct FaSmem {
-  static constexpr int kBlk = 128 * 128;             // one [128 rows x 128 B] column block
-  static constexpr int kTile = 128 * D * 2;          // Q / K / V tile bytes
+  static constexpr int kQBlk = kFaBM * 128;          // one [128 rows x 128 B] column block of a Q tile
+  static constexpr int kQTile = kFaBM * D * 2;
+  static constexpr int kBlk = kFaBN * 128;           // one [64 rows x 128 B] column block of a K / V tile
+  static constexpr int kTile = kFaBN * D * 2;        // K / V tile bytes
   static constexpr int kQ = 0;                       // two query tiles
-  static constexpr int kK = 2 * kTile;
+  static constexpr int kK = 2 * kQTile;
   static constexpr int kV = kK + kFaKStages * kTile;
   static constexpr int kBar = kV + kFaVStages * kTile;
-  static constexpr int kBytes = kBar + 32 * 8 + 1024;
+  static constexpr int kBytes = kBar + 40 * 8 + 1024;
 };
 
 template <int N>
@@ -145,10 +151,12 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   auto v_full = [&](int s) { return bar + (2 * kFaKStages + s) * 8; };
   auto v_empty = [&](int s) { return bar + (2 * kFaKStages + kFaVStages + s) * 8; };
   constexpr int kB0 = 2 * kFaKStages + 2 * kFaVStages;
-  auto s_full = [&](int t) { return bar + (kB0 + t) * 8; };
-  auto p_full = [&](int t) { return bar + (kB0 + 2 + t) * 8; };
-  auto o_full = [&](int t) { return bar + (kB0 + 4 + t) * 8; };
-  const uint32_t q_full = bar + (kB0 + 6) * 8;
+  // per (query tile, S buffer): tile j uses buffer j & 1, phase (j >> 1) & 1 — with one barrier per query tile a
+  // warpgroup that is a tile ahead could complete two phases before the other side tests the first
+  auto s_full = [&](int t, int j) { return bar + (kB0 + 2 * t + (j & 1)) * 8; };
+  auto p_full = [&](int t, int j) { return bar + (kB0 + 4 + 2 * t + (j & 1)) * 8; };
+  auto pv_done = [&](int t) { return bar + (kB0 + 8 + t) * 8; };  // P V of tile j: phase j (completions cannot run ahead)
+  const uint32_t q_full = bar + (kB0 + 10) * 8;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -186,9 +194,11 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         mbar_init(v_empty(s), 1);
       }
       for (int t = 0; t < 2; ++t) {
-        mbar_init(s_full(t), 1);
-        mbar_init(p_full(t), 4);  // one arrive per softmax warp
-        mbar_init(o_full(t), 1);
+        for (int bf = 0; bf < 2; ++bf) {
+          mbar_init(s_full(t, bf), 1);
+          mbar_init(p_full(t, bf), 4);  // one arrive per softmax warp
+        }
+        mbar_init(pv_done(t), 1);
       }
       mbar_init(q_full, 1);
       fence_barrier_init();
@@ -200,7 +210,7 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = s_tmem_base;
-  constexpr uint32_t kOCol = 256;  // S0 / P0 at column 0, S1 / P1 at 128, O0 at 256, O1 at 256 + D
+  constexpr uint32_t kOCol = 256;  // S_t[buf] / P_t[buf] at column 128 t + 64 buf, O0 at 256, O1 at 256 + D
 
   if (warp < 4) {
     fa_reg_dealloc<40>();  // 128 x (168 - 40) registers returned = 256 x (232 - 168) taken below
@@ -212,21 +222,21 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         prefetch_tmap(&tm_q);
         prefetch_tmap(&tm_k16);
         prefetch_tmap(&tm_v16);
-        mbar_expect_tx(q_full, (uint32_t)((n_t[1] > 0 ? 2 : 1) * L::kTile));
+        mbar_expect_tx(q_full, (uint32_t)((n_t[1] > 0 ? 2 : 1) * L::kQTile));
         for (int t = 0; t < (n_t[1] > 0 ? 2 : 1); ++t)
 #pragma unroll
           for (int blk = 0; blk < kBlocks; ++blk)
-            tma_load_2d(base + L::kQ + t * L::kTile + blk * L::kBlk, &tm_q, q_full, head * D * 2 + blk * 128,
+            tma_load_2d(base + L::kQ + t * L::kQTile + blk * L::kQBlk, &tm_q, q_full, head * D * 2 + blk * 128,
                         q_start + m0 + t * kFaBM, kEvictFirst);
       }
       const int col0 = kvh * D * 2;
       for (int j = 0; j < n_max; ++j) {
         const int kv0 = j * kFaBN;
-        // page-table slice of the tile: lane l holds the cache slots of rows l, 32 + l, 64 + l, 96 + l
-        int32_t sl[4];
-        bool vld[4];
+        // page-table slice of the tile: lane l holds the cache slots of rows l and 32 + l
+        int32_t sl[2];
+        bool vld[2];
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
+        for (int g = 0; g < 2; ++g) {
           const int pos = kv0 + 32 * g + lane;
           vld[g] = pos < kv_end_max;
           sl[g] = vld[g] ? __ldg(r2t_row + pos) : 0;
@@ -234,7 +244,7 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         // 16-row runs with consecutive slots become one box each
         uint32_t run16 = 0;
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
+        for (int g = 0; g < 2; ++g) {
           const int32_t first = __shfl_sync(0xffffffffu, sl[g], lane & 16);
           const uint32_t bal = __ballot_sync(0xffffffffu, vld[g] && sl[g] == first + (lane & 15));
           if ((bal & 0xFFFFu) == 0xFFFFu) run16 |= 1u << (2 * g);
@@ -254,7 +264,7 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
           mbar_wait(empty, ((j / ns) & 1) ^ 1);
           if (rows_valid < kFaBN) {  // rows past the end of the sequence: zeros (generic proxy), then publish
 #pragma unroll
-            for (int g = 0; g < 4; ++g)
+            for (int g = 0; g < 2; ++g)
               if (!vld[g])
 #pragma unroll
                 for (int blk = 0; blk < kBlocks; ++blk)
@@ -266,7 +276,7 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
           if (lane == 0) mbar_expect_tx(full, bytes);
           __syncwarp();
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
+          for (int g = 0; g < 2; ++g) {
             const int r = 2 * g + (lane >> 4);
             if ((run16 >> r) & 1u) {
               if ((lane & 15) == 0) {
@@ -282,50 +292,52 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
           }
         }
       }
-    } else if (warp == 1 && lane == 0) {
-      // ---- MMA issuer: P0 V -> Q0 K^T -> P1 V -> Q1 K^T per KV tile ------------------------------------------------
+    } else if (warp == 1) {
+      // ---- MMA issuer (whole warp runs the loop and the waits, one elected lane issues): per KV tile j   Q0 K(j+1)^T -> P0(j) V(j) -> Q1 K(j+1)^T -> P1(j) V(j) ------------------------
       constexpr uint32_t idesc_s = make_idesc(/*f32*/ 1, kFmt, kFmt, 128, kFaBN);
       constexpr uint32_t idesc_o = make_idesc(/*f32*/ 1, kFmt, kFmt, 128, D, /*A K-major*/ 0, /*B MN-major*/ 1);
       mbar_wait(q_full, 0);
       tc_fence_after();
-      for (int j = 0; j <= n_max; ++j) {
+      auto issue_qk = [&](int t, int j) {  // S_t[j & 1] = Q_t K(j)^T; the buffer's previous reader P V(j-2) was issued earlier
+        const int ks = j % kFaKStages;
+        mbar_wait(k_full(ks), (j / kFaKStages) & 1);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint64_t da0 = smem_desc_k_sw128(base + L::kQ + t * L::kQTile);
+          const uint64_t db0 = smem_desc_k_sw128(base + L::kK + ks * L::kTile);
+          const uint32_t s_tmem = tmem_base + (uint32_t)(t * 128 + (j & 1) * kFaBN);
+#pragma unroll
+          for (int kk = 0; kk < D / 16; ++kk)  // descriptor address field counts 16-byte units
+            umma<kKindF16>(s_tmem, da0 + (uint64_t)((kk >> 2) * (L::kQBlk >> 4) + 2 * (kk & 3)),
+                           db0 + (uint64_t)((kk >> 2) * (L::kBlk >> 4) + 2 * (kk & 3)), idesc_s, kk != 0);
+          tc_commit(s_full(t, j));
+          if ((t == 1) || !(j < n_t[1])) tc_commit(k_empty(ks));  // last reader of K(j)
+        }
+        __syncwarp();
+      };
+      for (int t = 0; t < 2; ++t)
+        if (n_t[t] > 0) issue_qk(t, 0);
+      for (int j = 0; j < n_max; ++j) {
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
-          const int jj = j - 1;
-          if (jj >= 0 && jj < n_t[t]) {  // O_t += P_t(jj) V(jj)
-            const int vs = jj % kFaVStages;
-            mbar_wait(v_full(vs), (jj / kFaVStages) & 1);
-            mbar_wait(p_full(t), jj & 1);
+          if (j + 1 < n_t[t]) issue_qk(t, j + 1);
+          if (j < n_t[t]) {  // O_t += P_t(j) V(j)
+            const int vs = j % kFaVStages;
+            mbar_wait(v_full(vs), (j / kFaVStages) & 1);
+            mbar_wait(p_full(t, j), (j >> 1) & 1);
             tc_fence_after();
-            const uint32_t sv = base + L::kV + vs * L::kTile;
-            const uint32_t p_tmem = tmem_base + (uint32_t)t * kFaBN;
-            const uint32_t o_tmem = tmem_base + kOCol + (uint32_t)t * D;
-#pragma unroll
-            for (int kk = 0; kk < kFaBN / 16; ++kk) {
+            if (elect_one()) {
               // V tile: atoms of [8 kv x 64 d]; next 64 d = kBlk bytes (LBO), next 8 kv = 1024 bytes (SBO)
-              const uint64_t db = smem_desc_mn_sw128(sv + kk * 2048, L::kBlk, 1024);
-              fa_umma_ts(o_tmem, p_tmem + kk * 8, db, idesc_o, (jj | kk) != 0);
-            }
-            const bool last_user = (t == 1) || !(jj < n_t[1]);
-            if (last_user) tc_commit(v_empty(vs));
-            if (jj == n_t[t] - 1) tc_commit(o_full(t));
-          }
-          if (j < n_t[t]) {  // S_t = Q_t K(j)^T (overwrites P_t(j-1): issued after the P V that reads it)
-            const int ks = j % kFaKStages;
-            mbar_wait(k_full(ks), (j / kFaKStages) & 1);
-            tc_fence_after();
-            const uint32_t sq = base + L::kQ + t * L::kTile;
-            const uint32_t sk = base + L::kK + ks * L::kTile;
-            const uint32_t s_tmem = tmem_base + (uint32_t)t * kFaBN;
+              const uint64_t db0 = smem_desc_mn_sw128(base + L::kV + vs * L::kTile, L::kBlk, 1024);
+              const uint32_t p_tmem = tmem_base + (uint32_t)(t * 128 + (j & 1) * kFaBN);
+              const uint32_t o_tmem = tmem_base + kOCol + (uint32_t)t * D;
 #pragma unroll
-            for (int kk = 0; kk < D / 16; ++kk) {
-              const uint64_t da = smem_desc_k_sw128(sq + (kk >> 2) * L::kBlk) + 2 * (kk & 3);
-              const uint64_t db = smem_desc_k_sw128(sk + (kk >> 2) * L::kBlk) + 2 * (kk & 3);
-              umma<kKindF16>(s_tmem, da, db, idesc_s, kk != 0);
+              for (int kk = 0; kk < kFaBN / 16; ++kk)
+                fa_umma_ts(o_tmem, p_tmem + kk * 8, db0 + (uint64_t)(kk * (2048 >> 4)), idesc_o, (j | kk) != 0);
+              tc_commit(pv_done(t));
+              if ((t == 1) || !(j < n_t[1])) tc_commit(v_empty(vs));  // last reader of V(j)
             }
-            tc_commit(s_full(t));
-            const bool last_user = (t == 1) || !(j < n_t[1]);
-            if (last_user) tc_commit(k_empty(ks));
+            __syncwarp();
           }
         }
       }
@@ -340,7 +352,6 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     const int n_tiles = n_t[t];
     const int kv_end = kv_end_t[t];
     const uint32_t t_lane = tmem_base + ((uint32_t)(qd * 32) << 16);
-    const uint32_t t_s = t_lane + (uint32_t)t * kFaBN;
     const uint32_t t_o = t_lane + kOCol + (uint32_t)t * D;
     const int lim = min(a.causal ? prefix + r0 + row : kv_total - 1, kv_end - 1);  // last KV position this row may see
     const bool use_cap = a.logit_cap > 0.f;
@@ -353,32 +364,29 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     for (int j = 0; j < n_tiles; ++j) {
       const int kv0 = j * kFaBN;
       const bool need_mask = (kv0 + kFaBN > kv_end) || (a.causal && kv0 + kFaBN - 1 > prefix + r0);
-      mbar_wait(s_full(t), j & 1);
+      const uint32_t t_s = t_lane + (uint32_t)(t * 128 + (j & 1) * kFaBN);
+      mbar_wait(s_full(t, j), (j >> 1) & 1);
       tc_fence_after();
-      uint32_t s[128];
+      uint32_t s[kFaBN];
       {
         uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
         uint32_t(&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
-        uint32_t(&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
-        uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
         tmem_ld32(t_s, s0);
         tmem_ld32(t_s + 32, s1);
-        tmem_ld32(t_s + 64, s2);
-        tmem_ld32(t_s + 96, s3);
         tmem_ld_wait();
       }
       if (use_cap) {
 #pragma unroll
-        for (int i = 0; i < 128; ++i) s[i] = __float_as_uint(cap_out * tanh_approx(__uint_as_float(s[i]) * cap_in));
+        for (int i = 0; i < kFaBN; ++i) s[i] = __float_as_uint(cap_out * tanh_approx(__uint_as_float(s[i]) * cap_in));
       }
       if (need_mask) {
 #pragma unroll
-        for (int i = 0; i < 128; ++i)
+        for (int i = 0; i < kFaBN; ++i)
           if (kv0 + i > lim) s[i] = 0xff800000u;  // -inf
       }
       float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
-      for (int i = 0; i < 128; i += 4) {
+      for (int i = 0; i < kFaBN; i += 4) {
         mx0 = fa_max3(mx0, __uint_as_float(s[i]), __uint_as_float(s[i + 1]));
         mx1 = fa_max3(mx1, __uint_as_float(s[i + 2]), __uint_as_float(s[i + 3]));
       }
@@ -386,7 +394,9 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       const bool grow = m_tile > m_used + kFaRescale;  // also the first finite tile (m_used = -inf)
       if (__any_sync(0xffffffffu, grow)) {
         if (j > 0) {
-          // P V of tile j-1 retired before Q K^T of tile j was issued, so O is quiescent until p_full below
+          // O is touched only here: P V of tile j-1 must have retired (P V of tile j waits for p_full below)
+          mbar_wait(pv_done(t), (j - 1) & 1);
+          tc_fence_after();
           const float alpha = grow ? fast_exp2(m_used - m_tile) : 1.f;
           l0 *= alpha;
           l1 *= alpha;
@@ -404,7 +414,7 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       }
       const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < kFaBN / 32; ++c) {
         uint32_t w[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
@@ -426,12 +436,14 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(p_full(t));
+      if (lane == 0) mbar_arrive(p_full(t, j));
     }
 
     // ---- epilogue: O / l -> global ----------------------------------------------------------------------------------
     if (n_tiles > 0) {
-      mbar_wait(o_full(t), 0);
+      // a parity wait is only exact one phase ahead: S of the last tile proves P V(n-3) retired, not P V(n-2)
+      if (n_tiles >= 2) mbar_wait(pv_done(t), (n_tiles - 2) & 1);
+      mbar_wait(pv_done(t), (n_tiles - 1) & 1);
       tc_fence_after();
       const float l_run = l0 + l1;
       const float inv = l_run > 0.f ? 1.f / l_run : 0.f;

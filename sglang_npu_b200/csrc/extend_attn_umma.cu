@@ -314,7 +314,7 @@ __global__ void __launch_bounds__(kUxThreads, 1) extend_attn_umma_kernel(const E
     if (lane == 0) mbar_arrive(full((n_tiles - 1) & 1));
   } else if (warp == 4) {
     // ---- MMA issuer --------------------------------------------------------------------------------------------
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc_s = make_idesc(/*f32*/ 1, kFmt, kFmt, 128, kUxBN);
       constexpr uint32_t idesc_o = make_idesc(/*f32*/ 1, kFmt, kFmt, 128, D, /*A K-major*/ 0, /*B MN-major*/ 1);
       auto issue_qk = [&](int j) {

@@ -107,7 +107,7 @@ gemm_block_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __gr
   const int u1 = (int)((int64_t)(c + 1) * total_units / G);
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       const int n_units = u1 - u0;
       const int pre = min(n_units, STAGES);
       int tile = u0 / nkb, kb = u0 - tile * nkb;
@@ -138,7 +138,7 @@ gemm_block_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __gr
     }
   } else if (warp == 1) {
     pdl_wait();
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = make_idesc(/*f32*/ 1, /*e4m3*/ 0, 0, 128, BN);
       const int n_units = u1 - u0;
       for (int it = 0; it < n_units; ++it) {
@@ -367,7 +367,7 @@ gemm_block_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   const int nkb = g.num_kb;
   if (warp < 4) {
     reg_dealloc<40>();
-    if (warp == 0 && lane == 0) {
+    if (warp == 0 && elect_one()) {
       uint32_t it = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         const int n_tile = t / tiles_m;
@@ -382,7 +382,7 @@ gemm_block_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           tma_load_2d(sa + 128 * kBK, &tmap_b, full_bar(s), i * kBK, b_row0, kEvictNormal);
         }
       }
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 1 && elect_one()) {
       constexpr uint32_t idesc = make_idesc(/*f32*/ 1, /*e4m3*/ 0, 0, 128, kBpBN);
       uint32_t it = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {

@@ -165,7 +165,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   float facc[kBlock ? BN : 1];
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       // weights are read once (evict-first); activations are re-read by every CTA (evict-last)
       const uint64_t pol_a = SWAP ? kEvictFirst : kEvictLast;
       const uint64_t pol_b = SWAP ? kEvictLast : kEvictFirst;
@@ -199,7 +199,7 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   } else if (warp == 1) {
     pdl_wait();
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = MODE == kModeI8 ? make_idesc(/*s32*/ 2, /*int8*/ 1, 1, 128, BN)
                                                  : make_idesc(/*f32*/ 1, /*e4m3*/ 0, 0, 128, BN);
       for (int i = 0; i < nkb; ++i) {
@@ -495,7 +495,7 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 
   const int nkb = g.num_kb;
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       uint32_t it = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         const int n_tile = t / tiles_m;
@@ -512,7 +512,7 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = MODE == kModeI8 ? make_idesc(/*s32*/ 2, /*int8*/ 1, 1, 128, kPfBN)
                                                  : make_idesc(/*f32*/ 1, /*e4m3*/ 0, 0, 128, kPfBN);
       uint32_t it = 0;
@@ -685,7 +685,7 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
   const int u1 = (int)((int64_t)(c + 1) * total_units / G);
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       const int n_units = u1 - u0;
       const int pre = min(n_units, STAGES);
       int vt = u0 / nkb, kb = u0 - vt * nkb;  // vt = tile * MB + mb
@@ -716,7 +716,7 @@ gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_con
     }
   } else if (warp == 1) {
     pdl_wait();
-    if (lane == 0) {
+    if (elect_one()) {
       // kind::f16 operand formats: 0 = f16, 1 = bf16; a 128-byte K block is 64 16-bit elements = 4 UMMAs of K = 16
       constexpr uint32_t idesc = MODE == kModeI8     ? make_idesc(/*s32*/ 2, /*int8*/ 1, 1, 128, BN)
                                  : MODE == kModeBF16 ? make_idesc(/*f32*/ 1, /*bf16*/ 1, 1, 128, BN)

@@ -44,6 +44,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
+// One lane of a CONVERGED warp (elect.sync).  Use this — not `lane == 0` — to guard the regions that issue
+// tcgen05.mma / tcgen05.commit / cp.async.bulk: under elect.sync ptxas knows the region runs on a single thread and
+// emits those instructions straight; under `if (lane == 0)` it wraps EVERY one of them in its own elect-and-loop
+// sequence (ELECT, op, 2 x PLOP3, BRA.U.ANY: a branch per MMA / per TMA copy), which starves the tensor pipe on short
+// MMAs (measured on the extend kernel: the issuing thread spent 85 % of its time in those wrappers).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
+  return pred != 0;
+}
+
 // ---- TMA ----------------------------------------------------------------------------------
 constexpr uint64_t kEvictNormal = 0x1000000000000000ull;
 constexpr uint64_t kEvictFirst = 0x12F0000000000000ull;
