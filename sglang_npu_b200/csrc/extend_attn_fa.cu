@@ -18,7 +18,7 @@
 //     block: tensor pipe 48 % active, MUFU 48 %, neither saturated — profiles/r02i_extend_fa_ncu.txt.)
 //   * TMEM (512 columns): S0[2] | S1[2] | O0 | O1 (64 + 64 + 64 + 64 + 128 + 128).  P (bf16/f16) is written back over
 //     the first 32 columns of its own S buffer with tcgen05.st and is the A operand of P V straight from tensor
-//     memory — no shared-memory P tile, no bank conflicts, its shared memory goes to the K/V rings (4 K + 5 V stages);
+//     memory — no shared-memory P tile, no bank conflicts, its shared memory goes to the K/V rings (4 K + 4 V stages);
 //   * the row of S (64 fp32) is held in registers (setmaxnreg: 232 for the softmax warps, 40 for the rest), so the row
 //     max and the exponentials read TMEM once; the max a row is normalised to only moves when the tile max exceeds
 //     it by 2^8 (O is then rescaled in TMEM by the same thread; rare after the first tiles);
@@ -30,7 +30,7 @@
 //     column block, anything else (page_size 1, a tile's ragged tail) falls back to [1 x 128 B] boxes; rows past
 //     the end of the sequence are zero-filled by the producer warp, so V never feeds stale NaNs into P V.  All 32
 //     lanes of the producer warp issue copies; the page ids of a tile come from four coalesced loads.
-// Warps: 0 = TMA producer, 1 = MMA issuer + TMEM allocator, 2-3 idle, 4-7 softmax / correction / epilogue of query
+// Warps: 0 = TMA producer, 1 / 2 = MMA issuer of query tile 0 / 1 (1 also allocates TMEM), 3 idle, 4-7 softmax / correction / epilogue of query
 // tile 0, 8-11 of query tile 1 (TMEM lane quarter = warp % 4).
 #include <cstdlib>
 #include <mutex>
@@ -50,7 +50,7 @@ constexpr int kFaBM = 128;       // query rows per tile (two tiles per CTA)
 constexpr int kFaBN = 64;        // KV positions per tile
 constexpr int kFaThreads = 384;
 constexpr int kFaKStages = 4;
-constexpr int kFaVStages = 5;
+constexpr int kFaVStages = 4;
 constexpr float kFaRescale = 8.f;  // log2 domain
 constexpr int kFaPolyDefault = 2;   // of every 8 exponentials, this many run on the FMA pipe (B200_FA_POLY overrides)
 
@@ -181,17 +181,22 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
   }
   const int n_max = max(n_t[0], n_t[1]);
   const int kv_end_max = n_t[1] > 0 ? max(kv_end_t[0], kv_end_t[1]) : kv_end_t[0];
+  // Both query tiles walk the same n_max KV tiles (tile 0's last two lie entirely above its causal diagonal: every
+  // score is masked, P = 0): each K / V stage then has exactly one reader per valid query tile, and the two MMA
+  // warps need no per-tile bookkeeping about who reads what.
+  const int n_valid = n_t[1] > 0 ? 2 : 1;
+  n_t[0] = n_max;
   const int kvh = head / (a.num_q_heads / a.num_kv_heads);
 
   if (warp == 1) {
     if (lane == 0) {
       for (int s = 0; s < kFaKStages; ++s) {
         mbar_init(k_full(s), 1);
-        mbar_init(k_empty(s), 1);
+        mbar_init(k_empty(s), n_valid);  // one commit per MMA warp that reads the stage
       }
       for (int s = 0; s < kFaVStages; ++s) {
         mbar_init(v_full(s), 1);
-        mbar_init(v_empty(s), 1);
+        mbar_init(v_empty(s), n_valid);
       }
       for (int t = 0; t < 2; ++t) {
         for (int bf = 0; bf < 2; ++bf) {
@@ -230,17 +235,24 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
                         q_start + m0 + t * kFaBM, kEvictFirst);
       }
       const int col0 = kvh * D * 2;
-      for (int j = 0; j < n_max; ++j) {
-        const int kv0 = j * kFaBN;
-        // page-table slice of the tile: lane l holds the cache slots of rows l and 32 + l
-        int32_t sl[2];
-        bool vld[2];
+      // page-table slice of a tile: lane l holds the cache slots of rows l and 32 + l; fetched one tile ahead so the
+      // global-load latency is off the issue path
+      auto load_slots = [&](int j, int32_t (&sl)[2]) {
 #pragma unroll
         for (int g = 0; g < 2; ++g) {
-          const int pos = kv0 + 32 * g + lane;
-          vld[g] = pos < kv_end_max;
-          sl[g] = vld[g] ? __ldg(r2t_row + pos) : 0;
+          const int pos = j * kFaBN + 32 * g + lane;
+          sl[g] = pos < kv_end_max ? __ldg(r2t_row + pos) : 0;
         }
+      };
+      int32_t sl_next[2];
+      load_slots(0, sl_next);
+      for (int j = 0; j < n_max; ++j) {
+        const int kv0 = j * kFaBN;
+        int32_t sl[2] = {sl_next[0], sl_next[1]};
+        if (j + 1 < n_max) load_slots(j + 1, sl_next);
+        bool vld[2];
+#pragma unroll
+        for (int g = 0; g < 2; ++g) vld[g] = kv0 + 32 * g + lane < kv_end_max;
         // 16-row runs with consecutive slots become one box each
         uint32_t run16 = 0;
 #pragma unroll
@@ -250,18 +262,33 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
           if ((bal & 0xFFFFu) == 0xFFFFu) run16 |= 1u << (2 * g);
           if ((bal >> 16) == 0xFFFFu) run16 |= 1u << (2 * g + 1);
         }
+        int32_t first_slot[4];  // slot of the first row of each run, in every lane
+#pragma unroll
+        for (int r = 0; r < 4; ++r) first_slot[r] = __shfl_sync(0xffffffffu, sl[r >> 1], (r & 1) * 16);
         const int rows_valid = min(kFaBN, kv_end_max - kv0);
         const uint32_t bytes = (uint32_t)rows_valid * D * 2;
 #pragma unroll
         for (int which = 0; which < 2; ++which) {  // 0: K tile j, 1: V tile j
-          const int ns = which ? kFaVStages : kFaKStages;
-          const int st = j % ns;
+          const int st = j & 3;
           const uint32_t full = which ? v_full(st) : k_full(st);
           const uint32_t empty = which ? v_empty(st) : k_empty(st);
           const uint32_t dst = base + (which ? L::kV : L::kK) + st * L::kTile;
           const CUtensorMap* m16 = which ? &tm_v16 : &tm_k16;
           const CUtensorMap* m1 = which ? &tm_v1 : &tm_k1;
-          mbar_wait(empty, ((j / ns) & 1) ^ 1);
+          mbar_wait(empty, ((j >> 2) & 1) ^ 1);
+          if (run16 == 0xFu) {
+            // the common case (page_size >= 16, full tile): eight boxes issued straight by one elected lane
+            if (elect_one()) {
+              mbar_expect_tx(full, (uint32_t)L::kTile);
+#pragma unroll
+              for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int blk = 0; blk < kBlocks; ++blk)
+                  tma_load_2d(dst + blk * L::kBlk + r * 16 * 128, m16, full, col0 + blk * 128, first_slot[r], kEvictNormal);
+            }
+            __syncwarp();
+            continue;
+          }
           if (rows_valid < kFaBN) {  // rows past the end of the sequence: zeros (generic proxy), then publish
 #pragma unroll
             for (int g = 0; g < 2; ++g)
@@ -292,54 +319,55 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
           }
         }
       }
-    } else if (warp == 1) {
-      // ---- MMA issuer (whole warp runs the loop and the waits, one elected lane issues): per KV tile j   Q0 K(j+1)^T -> P0(j) V(j) -> Q1 K(j+1)^T -> P1(j) V(j) ------------------------
+    } else if (warp - 1 < n_valid) {
+      // ---- MMA issuers: warp 1 for query tile 0, warp 2 for query tile 1 (two schedulers: a single warp spent ~370
+      //      instructions per KV tile on waits / descriptors / issue and could not keep the pipe fed).  Per tile j:
+      //      Q_t K(j+1)^T -> P_t(j) V(j); tcgen05 ops of one thread execute in order, which is all the S / P buffer
+      //      reuse needs.  The whole warp runs the loop and the waits, one elected lane issues.
+      const int t = warp - 1;
       constexpr uint32_t idesc_s = make_idesc(/*f32*/ 1, kFmt, kFmt, 128, kFaBN);
       constexpr uint32_t idesc_o = make_idesc(/*f32*/ 1, kFmt, kFmt, 128, D, /*A K-major*/ 0, /*B MN-major*/ 1);
+      static_assert(kFaKStages == 4 && kFaVStages == 4, "stage index / phase below use j & 3, j >> 2");
+      const uint64_t dq = smem_desc_k_sw128(base + L::kQ + t * L::kQTile);
+      const uint64_t dk = smem_desc_k_sw128(base + L::kK);                  // + stage * (kTile >> 4)
+      // V tile: atoms of [8 kv x 64 d]; next 64 d = kBlk bytes (LBO), next 8 kv = 1024 bytes (SBO)
+      const uint64_t dv = smem_desc_mn_sw128(base + L::kV, L::kBlk, 1024);
+      const uint32_t s_tmem0 = tmem_base + (uint32_t)(t * 128);
+      const uint32_t o_tmem = tmem_base + kOCol + (uint32_t)t * D;
       mbar_wait(q_full, 0);
-      tc_fence_after();
-      auto issue_qk = [&](int t, int j) {  // S_t[j & 1] = Q_t K(j)^T; the buffer's previous reader P V(j-2) was issued earlier
-        const int ks = j % kFaKStages;
-        mbar_wait(k_full(ks), (j / kFaKStages) & 1);
+      auto issue_qk = [&](int j) {  // S_t[j & 1] = Q_t K(j)^T; the buffer's previous reader P V(j-2) was issued earlier
+        const int ks = j & 3;
+        mbar_wait(k_full(ks), (j >> 2) & 1);
         tc_fence_after();
         if (elect_one()) {
-          const uint64_t da0 = smem_desc_k_sw128(base + L::kQ + t * L::kQTile);
-          const uint64_t db0 = smem_desc_k_sw128(base + L::kK + ks * L::kTile);
-          const uint32_t s_tmem = tmem_base + (uint32_t)(t * 128 + (j & 1) * kFaBN);
+          const uint64_t db0 = dk + (uint64_t)(ks * (L::kTile >> 4));
+          const uint32_t s_tmem = s_tmem0 + (uint32_t)((j & 1) * kFaBN);
 #pragma unroll
           for (int kk = 0; kk < D / 16; ++kk)  // descriptor address field counts 16-byte units
-            umma<kKindF16>(s_tmem, da0 + (uint64_t)((kk >> 2) * (L::kQBlk >> 4) + 2 * (kk & 3)),
+            umma<kKindF16>(s_tmem, dq + (uint64_t)((kk >> 2) * (L::kQBlk >> 4) + 2 * (kk & 3)),
                            db0 + (uint64_t)((kk >> 2) * (L::kBlk >> 4) + 2 * (kk & 3)), idesc_s, kk != 0);
           tc_commit(s_full(t, j));
-          if ((t == 1) || !(j < n_t[1])) tc_commit(k_empty(ks));  // last reader of K(j)
+          tc_commit(k_empty(ks));
         }
         __syncwarp();
       };
-      for (int t = 0; t < 2; ++t)
-        if (n_t[t] > 0) issue_qk(t, 0);
+      issue_qk(0);
       for (int j = 0; j < n_max; ++j) {
+        if (j + 1 < n_max) issue_qk(j + 1);
+        const int vs = j & 3;
+        mbar_wait(v_full(vs), (j >> 2) & 1);
+        mbar_wait(p_full(t, j), (j >> 1) & 1);
+        tc_fence_after();
+        if (elect_one()) {  // O_t += P_t(j) V(j)
+          const uint64_t db0 = dv + (uint64_t)(vs * (L::kTile >> 4));
+          const uint32_t p_tmem = s_tmem0 + (uint32_t)((j & 1) * kFaBN);
 #pragma unroll
-        for (int t = 0; t < 2; ++t) {
-          if (j + 1 < n_t[t]) issue_qk(t, j + 1);
-          if (j < n_t[t]) {  // O_t += P_t(j) V(j)
-            const int vs = j % kFaVStages;
-            mbar_wait(v_full(vs), (j / kFaVStages) & 1);
-            mbar_wait(p_full(t, j), (j >> 1) & 1);
-            tc_fence_after();
-            if (elect_one()) {
-              // V tile: atoms of [8 kv x 64 d]; next 64 d = kBlk bytes (LBO), next 8 kv = 1024 bytes (SBO)
-              const uint64_t db0 = smem_desc_mn_sw128(base + L::kV + vs * L::kTile, L::kBlk, 1024);
-              const uint32_t p_tmem = tmem_base + (uint32_t)(t * 128 + (j & 1) * kFaBN);
-              const uint32_t o_tmem = tmem_base + kOCol + (uint32_t)t * D;
-#pragma unroll
-              for (int kk = 0; kk < kFaBN / 16; ++kk)
-                fa_umma_ts(o_tmem, p_tmem + kk * 8, db0 + (uint64_t)(kk * (2048 >> 4)), idesc_o, (j | kk) != 0);
-              tc_commit(pv_done(t));
-              if ((t == 1) || !(j < n_t[1])) tc_commit(v_empty(vs));  // last reader of V(j)
-            }
-            __syncwarp();
-          }
+          for (int kk = 0; kk < kFaBN / 16; ++kk)
+            fa_umma_ts(o_tmem, p_tmem + kk * 8, db0 + (uint64_t)(kk * (2048 >> 4)), idesc_o, (j | kk) != 0);
+          tc_commit(pv_done(t));
+          tc_commit(v_empty(vs));
         }
+        __syncwarp();
       }
     }
   } else {
