@@ -20,6 +20,8 @@
 //  * the 4 warps' (m, l, O) are merged through shared memory; with one chunk per request the
 //    CTA writes the final output, else fp32 partial (o, lse) go to the workspace and
 //    decode_merge_kernel combines the chunks (log-sum-exp merge).
+#include <mutex>
+
 #include "common.cuh"
 #include "extend_attn.cuh"
 #include <type_traits>
@@ -906,6 +908,30 @@ B200_API int b200_decode_attn_workspace_bytes(int batch, int num_q_heads, int he
   return B200_OK;
 }
 
+
+// Side stream + fork / join events of the shared-prefix overlap, one set per device ordinal (created under a mutex on
+// first use on that device; a process that drives several GPUs gets a stream that belongs to each).
+struct SideStream {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+};
+static int side_stream_for_current_device(SideStream* out) {
+  static std::mutex mu;
+  static SideStream per_device[64];
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < 64, "decode_attn_shared_prefix: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  SideStream& s = per_device[dev];
+  if (s.stream == nullptr) {
+    B200_CUDA_OK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    B200_CUDA_OK(cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming));
+    B200_CUDA_OK(cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming));
+  }
+  *out = s;
+  return B200_OK;
+}
+
 static int decode_attn_impl(void* o, const void* q, const void* k_cache, const void* v_cache,
                             const int32_t* req_to_token, int64_t req_to_token_stride,
                             const void* req_pool_indices, const void* seq_lens,
@@ -995,19 +1021,19 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
     // B200_SHARED_PREFIX_OVERLAP=0: serial.
     static const bool overlap = getenv("B200_SHARED_PREFIX_OVERLAP") == nullptr || getenv("B200_SHARED_PREFIX_OVERLAP")[0] != '0';
     if (overlap) {
-      static cudaStream_t side = nullptr;
-      static cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-      if (side == nullptr) {
-        B200_CUDA_OK(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
-        B200_CUDA_OK(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
-        B200_CUDA_OK(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
-      }
-      B200_CUDA_OK(cudaEventRecord(ev_fork, st));
-      B200_CUDA_OK(cudaStreamWaitEvent(side, ev_fork, 0));
-      const int rc = launch_extend_umma(e, batch, head_dim, dtype, side);
+      SideStream ss;
+      int rc = side_stream_for_current_device(&ss);
       if (rc != B200_OK) return rc;
-      B200_CUDA_OK(cudaEventRecord(ev_join, side));
-      join = ev_join;
+      B200_CUDA_OK(cudaEventRecord(ss.fork, st));
+      B200_CUDA_OK(cudaStreamWaitEvent(ss.stream, ss.fork, 0));
+      rc = launch_extend_umma(e, batch, head_dim, dtype, ss.stream);
+      // join on every path after the fork: an un-joined side stream would break an enclosing graph capture
+      B200_CUDA_OK(cudaEventRecord(ss.join, ss.stream));
+      if (rc != B200_OK) {
+        cudaStreamWaitEvent(st, ss.join, 0);
+        return rc;
+      }
+      join = ss.join;
     } else {
       const int rc = launch_extend_umma(e, batch, head_dim, dtype, st);
       if (rc != B200_OK) return rc;
