@@ -155,6 +155,21 @@ int b200_decode_attn_shared_prefix(void* o, int8_t* oq, float* oq_scale, const v
                                    int shared_prefix_len, int seg_len, int kv_chunk, int max_splits, void* workspace,
                                    size_t workspace_bytes, int dtype, void* stream);
 
+/* Shared-prefix decode over an FP8 (e4m3) KV cache (config 5 with --kv-cache-dtype fp8_e4m3, memory_pool.py:385-391).
+ * The caller first up-casts the shared tokens into a 16-bit staging copy with b200_fp8_kv_gather_dequant
+ * (k_stage / v_stage [shared_prefix_len, Hkv, D] of `dtype`, values already multiplied by k_scale / v_scale);
+ * stage_table[0 .. shared_prefix_len) names its rows (normally 0, 1, 2, ...) and *stage_index (same integer type as
+ * req_pool_indices) is 0.  Pass 1 (tensor cores) reads the staging copy, pass 2 (b200_decode_attn_fp8kv's kernel) the
+ * e4m3 cache from token shared_prefix_len on; one merge.  Same result as b200_decode_attn_fp8kv. */
+int b200_decode_attn_shared_prefix_fp8kv(
+    void* o, int8_t* oq, float* oq_scale, const void* q, const void* k_cache, const void* v_cache, const void* k_stage,
+    const void* v_stage, const int32_t* stage_table, const void* stage_index, int64_t stage_token_stride,
+    const int32_t* req_to_token, int64_t req_to_token_stride, const void* req_pool_indices, const void* seq_lens,
+    int index_is_int64, int batch, int num_q_heads, int num_kv_heads, int head_dim, int64_t q_token_stride,
+    int64_t o_token_stride, int64_t kv_token_stride, float sm_scale, float logit_cap, float k_scale, float v_scale,
+    int shared_prefix_len, int seg_len, int kv_chunk, int max_splits, void* workspace, size_t workspace_bytes, int dtype,
+    void* stream);
+
 /* ---- extend (prefill) attention ------------------------------------------------------
  * Replaces extend_attention_fwd (triton_ops/extend_attention.py:302-440) and the
  * oracle's _run_sdpa_forward_extend (torch_native_backend.py:27-110).  Request b has

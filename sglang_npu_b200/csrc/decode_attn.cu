@@ -941,7 +941,9 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
                             int kv_chunk, int max_splits, void* workspace,
                             size_t workspace_bytes, int dtype, int8_t* oq, float* oq_scale, void* stream,
                             bool kv_fp8 = false, float k_scale = 1.f, float v_scale = 1.f, int shared_prefix = 0,
-                            int seg_len = 0) {
+                            int seg_len = 0, const void* k_stage = nullptr, const void* v_stage = nullptr,
+                            const int32_t* stage_table = nullptr, const void* stage_index = nullptr,
+                            int64_t stage_token_stride = 0) {
   using namespace b200;
   B200_REQUIRE(batch >= 0, "decode_attn: negative batch");
   if (batch == 0) return B200_OK;
@@ -962,7 +964,11 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
                "decode_attn: pointer alignment");
   int n_seg = 0;
   if (shared_prefix > 0) {
-    B200_REQUIRE(!kv_fp8, "decode_attn_shared_prefix: FP8 KV is not supported by the prefix kernel");
+    // FP8 cache: the tensor-core prefix pass reads the shared tokens from a 16-bit staging copy (stage_table names
+    // its rows for "request" *stage_index), the per-request pass reads the e4m3 cache
+    B200_REQUIRE(!kv_fp8 || (k_stage && v_stage && stage_table && stage_index && stage_token_stride % 8 == 0 &&
+                             ((uintptr_t)k_stage | (uintptr_t)v_stage) % 16 == 0),
+                 "decode_attn_shared_prefix_fp8kv: the 16-bit staging copy of the shared prefix is required");
     B200_REQUIRE(seg_len >= 128 && seg_len % 128 == 0, "decode_attn_shared_prefix: seg_len %d must be a multiple of 128",
                  seg_len);
     n_seg = (shared_prefix + seg_len - 1) / seg_len;
@@ -985,6 +991,7 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
   a.group = num_q_heads / num_kv_heads;
   a.head_blocks = (a.group + 15) / 16;
   a.q_token_stride = q_token_stride; a.o_token_stride = o_token_stride; a.kv_token_stride = kv_token_stride;
+  const float sm_scale_plain = sm_scale;  // for K values that already carry k_scale (the staged prefix)
   sm_scale *= k_scale;  // logits of the stored K/k_scale values, scaled back
   a.sm_scale = sm_scale; a.scale_log2 = sm_scale * kLog2e; a.logit_cap = logit_cap;
   a.out_scale = v_scale;
@@ -1012,6 +1019,11 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
     e.q_token_stride = q_token_stride; e.o_token_stride = o_token_stride;
     e.knew_token_stride = 0; e.vnew_token_stride = 0; e.kv_token_stride = kv_token_stride;
     e.scale_log2 = a.scale_log2; e.sm_scale = a.sm_scale; e.logit_cap = logit_cap; e.causal = 0;
+    if (kv_fp8) {  // staged prefix: up-cast and multiplied by k_scale / v_scale already
+      e.k_cache = k_stage; e.v_cache = v_stage; e.req_to_token = stage_table; e.req_to_token_stride = 0;
+      e.req_pool_indices = stage_index; e.kv_token_stride = stage_token_stride;
+      e.sm_scale = sm_scale_plain; e.scale_log2 = sm_scale_plain * kLog2e;
+    }
     e.part_o = a.part_o; e.part_lse = a.part_lse; e.part_stride = ws_splits; e.seg_len = seg_len;
     e.seg_rows = batch; e.seg_prefix = shared_prefix;
     // The prefix pass is tensor-bound (16 MB of HBM reads at cfg 5) and the per-request pass HBM-bound; they are
@@ -1040,11 +1052,11 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
     }
   }
   if (dtype == B200_BF16) {
-    if (head_dim == 128) return kv_fp8 ? launch_decode<__nv_bfloat16, 128, true>(a, st) : launch_decode<__nv_bfloat16, 128, false>(a, st, join);
-    if (head_dim == 64) return kv_fp8 ? launch_decode<__nv_bfloat16, 64, true>(a, st) : launch_decode<__nv_bfloat16, 64, false>(a, st, join);
+    if (head_dim == 128) return kv_fp8 ? launch_decode<__nv_bfloat16, 128, true>(a, st, join) : launch_decode<__nv_bfloat16, 128, false>(a, st, join);
+    if (head_dim == 64) return kv_fp8 ? launch_decode<__nv_bfloat16, 64, true>(a, st, join) : launch_decode<__nv_bfloat16, 64, false>(a, st, join);
   } else if (dtype == B200_F16) {
-    if (head_dim == 128) return kv_fp8 ? launch_decode<__half, 128, true>(a, st) : launch_decode<__half, 128, false>(a, st, join);
-    if (head_dim == 64) return kv_fp8 ? launch_decode<__half, 64, true>(a, st) : launch_decode<__half, 64, false>(a, st, join);
+    if (head_dim == 128) return kv_fp8 ? launch_decode<__half, 128, true>(a, st, join) : launch_decode<__half, 128, false>(a, st, join);
+    if (head_dim == 64) return kv_fp8 ? launch_decode<__half, 64, true>(a, st, join) : launch_decode<__half, 64, false>(a, st, join);
   } else {
     return fail(B200_ERR_UNSUPPORTED, "decode_attn: dtype %d not supported (bf16/f16 only)", dtype);
   }
@@ -1106,4 +1118,20 @@ B200_API int b200_decode_attn_shared_prefix(void* o, int8_t* oq, float* oq_scale
                           index_is_int64, batch, num_q_heads, num_kv_heads, head_dim, q_token_stride, o_token_stride,
                           kv_token_stride, sm_scale, logit_cap, kv_chunk, max_splits, workspace, workspace_bytes, dtype,
                           oq, oq_scale, stream, false, 1.f, 1.f, shared_prefix_len, seg_len);
+}
+
+B200_API int b200_decode_attn_shared_prefix_fp8kv(
+    void* o, int8_t* oq, float* oq_scale, const void* q, const void* k_cache, const void* v_cache, const void* k_stage,
+    const void* v_stage, const int32_t* stage_table, const void* stage_index, int64_t stage_token_stride,
+    const int32_t* req_to_token, int64_t req_to_token_stride, const void* req_pool_indices, const void* seq_lens,
+    int index_is_int64, int batch, int num_q_heads, int num_kv_heads, int head_dim, int64_t q_token_stride,
+    int64_t o_token_stride, int64_t kv_token_stride, float sm_scale, float logit_cap, float k_scale, float v_scale,
+    int shared_prefix_len, int seg_len, int kv_chunk, int max_splits, void* workspace, size_t workspace_bytes, int dtype,
+    void* stream) {
+  B200_REQUIRE(shared_prefix_len > 0, "decode_attn_shared_prefix_fp8kv: shared_prefix_len must be positive");
+  return decode_attn_impl(o, q, k_cache, v_cache, req_to_token, req_to_token_stride, req_pool_indices, seq_lens,
+                          index_is_int64, batch, num_q_heads, num_kv_heads, head_dim, q_token_stride, o_token_stride,
+                          kv_token_stride, sm_scale, logit_cap, kv_chunk, max_splits, workspace, workspace_bytes, dtype,
+                          oq, oq_scale, stream, true, k_scale, v_scale, shared_prefix_len, seg_len, k_stage, v_stage,
+                          stage_table, stage_index, stage_token_stride);
 }

@@ -18,7 +18,7 @@ from ._cabi import check as _check, dtype_code, ptr, require_cuda, stream_ptr
 
 
 _LAUNCHES = 0
-_KERNELS_PER_CALL = {"b200_decode_attn_shared_prefix": 3, "b200_decode_attn": 2, "b200_decode_attn_int8": 2, "b200_decode_attn_fp8kv": 2, "b200_decode_attn_workspace_bytes": 0,
+_KERNELS_PER_CALL = {"b200_decode_attn_shared_prefix": 3, "b200_decode_attn_shared_prefix_fp8kv": 3, "b200_decode_attn": 2, "b200_decode_attn_int8": 2, "b200_decode_attn_fp8kv": 2, "b200_decode_attn_workspace_bytes": 0,
                      "b200_int8_scaled_mm_workspace_bytes": 0, "b200_argmax_workspace_bytes": 0}
 
 
@@ -209,21 +209,41 @@ def decode_attention_shared_prefix_fwd(q: torch.Tensor, k_buffer: torch.Tensor, 
                                        o: torch.Tensor, req_to_token: torch.Tensor, req_pool_indices: torch.Tensor,
                                        seq_lens: torch.Tensor, shared_prefix_len: int, seg_len: int,
                                        workspace: torch.Tensor, kv_chunk: int, max_splits: int, sm_scale: float,
-                                       logit_cap: float = 0.0, int8_out: bool = False):
+                                       logit_cap: float = 0.0, int8_out: bool = False, stage=None,
+                                       k_scale: Optional[float] = None, v_scale: Optional[float] = None):
     """Decode attention for a batch whose requests all start with the same `shared_prefix_len` KV slots (request 0's
-    page-table row names them); same result as decode_attention_fwd.  See b200_decode_attn_shared_prefix."""
+    page-table row names them); same result as decode_attention_fwd.  See b200_decode_attn_shared_prefix.
+    FP8 (e4m3) k/v_buffer: `stage` = (k_stage, v_stage, stage_table, stage_index) — the 16-bit staging copy of the
+    shared tokens made by fp8_kv_gather_dequant (b200_decode_attn_shared_prefix_fp8kv)."""
     require_cuda(q, k_buffer, v_buffer, o, req_to_token, req_pool_indices, seq_lens, workspace)
     lib = _cabi.load()
     bs, hq, d = q.shape
     hkv = k_buffer.shape[1]
     assert q.stride(2) == 1 and q.stride(1) == d and o.stride(2) == 1 and o.stride(1) == d
     assert k_buffer.stride(2) == 1 and k_buffer.stride(1) == d and v_buffer.stride() == k_buffer.stride()
-    assert k_buffer.dtype == q.dtype
     assert req_to_token.dtype == torch.int32 and req_to_token.stride(1) == 1
     assert req_pool_indices.dtype == seq_lens.dtype
     assert req_pool_indices.is_contiguous() and seq_lens.is_contiguous()
     oq = torch.empty((bs, hq * d), device=q.device, dtype=torch.int8) if int8_out else None
     oscale = torch.empty((bs, 1), device=q.device, dtype=torch.float32) if int8_out else None
+    if k_buffer.dtype in _FP8_STORE:
+        assert v_buffer.dtype in _FP8_STORE and stage is not None, "FP8 KV: the staged shared prefix is required"
+        k_stage, v_stage, stage_table, stage_index = stage
+        require_cuda(k_stage, v_stage, stage_table, stage_index)
+        assert k_stage.dtype == q.dtype and v_stage.dtype == q.dtype and k_stage.shape[0] >= shared_prefix_len
+        assert k_stage.shape[1:] == (hkv, d) and k_stage.is_contiguous() and v_stage.is_contiguous()
+        assert stage_table.dtype == torch.int32 and stage_table.numel() >= shared_prefix_len
+        assert stage_index.dtype == req_pool_indices.dtype
+        check(lib.b200_decode_attn_shared_prefix_fp8kv(
+            ptr(o), ptr(oq), ptr(oscale), ptr(q), ptr(k_buffer), ptr(v_buffer), ptr(k_stage), ptr(v_stage),
+            ptr(stage_table), ptr(stage_index), k_stage.stride(0), ptr(req_to_token), req_to_token.stride(0),
+            ptr(req_pool_indices), ptr(seq_lens), _is64(seq_lens), bs, hq, hkv, d, q.stride(0), o.stride(0),
+            k_buffer.stride(0), float(sm_scale), float(logit_cap), 1.0 if k_scale is None else float(k_scale),
+            1.0 if v_scale is None else float(v_scale), int(shared_prefix_len), int(seg_len), int(kv_chunk),
+            int(max_splits), ptr(workspace), workspace.numel() * workspace.element_size(), dtype_code(q.dtype),
+            stream_ptr(q.device)), "b200_decode_attn_shared_prefix_fp8kv")
+        return Int8Activation(oq, oscale, q.dtype) if int8_out else None
+    assert k_buffer.dtype == q.dtype
     check(lib.b200_decode_attn_shared_prefix(
         ptr(o), ptr(oq), ptr(oscale), ptr(q), ptr(k_buffer), ptr(v_buffer), ptr(req_to_token),
         req_to_token.stride(0), ptr(req_pool_indices), ptr(seq_lens), _is64(seq_lens), bs, hq, hkv, d,

@@ -113,6 +113,8 @@ class B200AttnBackend(AttentionBackend):
         self._graph_max_bs = 0
         self._stage_kv = None
         self._stage_rows_idx = None
+        self._sp_stage_meta = None
+        self._sp_stage_kv = None
         max_bs = model_runner.req_to_token_pool.size
         self.qo_indptr = torch.zeros((max_bs + 1,), dtype=torch.int32, device=self.device)
 
@@ -128,7 +130,19 @@ class B200AttnBackend(AttentionBackend):
 
     # ---- metadata -------------------------------------------------------------------------
     def _shared_prefix_supported(self) -> bool:
-        return self._kv_dtype in (torch.bfloat16, torch.float16)
+        return self._kv_dtype in (torch.bfloat16, torch.float16, torch.float8_e4m3fn)
+
+    def _shared_prefix_stage(self, shared: int, index_dtype: torch.dtype):
+        """FP8 KV cache: the index tensors of the staged shared prefix (device-side fills only: capturable)."""
+        st = self._sp_stage_meta
+        if st is None or st["shared"] != shared or st["index"].dtype != index_dtype:
+            st = dict(shared=shared,
+                      prefix_lens=torch.full((1,), shared, dtype=torch.int32, device=self.device),
+                      offsets=torch.zeros((1,), dtype=torch.int32, device=self.device),
+                      table=torch.arange(shared, dtype=torch.int32, device=self.device),
+                      index=torch.zeros((1,), dtype=index_dtype, device=self.device))
+            self._sp_stage_meta = st
+        return st
 
     def _decode_workspace(self, bs: int, max_splits: int, graph: bool = False) -> Optional[torch.Tensor]:
         if max_splits <= 1:
@@ -274,13 +288,34 @@ class B200AttnBackend(AttentionBackend):
         md = self.forward_metadata
         pool = forward_batch.token_to_kv_pool
         if md.shared_prefix_len > 0:
+            extra = {}
+            if pool.dtype != q.dtype:
+                # FP8 KV cache: up-cast the shared tokens once per layer into a 16-bit staging copy (2 x prefix x Hkv x D
+                # bytes read, twice that written: ~4 us at config 5 per GPU) for the tensor-core prefix pass; every
+                # request's own tokens are read as e4m3 by the FP8-KV decode kernel
+                if pool.dtype != torch.float8_e4m3fn:
+                    raise NotImplementedError(f"B200AttnBackend: KV cache dtype {pool.dtype} is not supported")
+                shared = md.shared_prefix_len
+                st = self._shared_prefix_stage(shared, forward_batch.req_pool_indices.dtype)
+                shape = (shared, layer.tp_k_head_num, layer.qk_head_dim)
+                if self._sp_stage_kv is None or self._sp_stage_kv[0].shape != shape or self._sp_stage_kv[0].dtype != q.dtype:
+                    self._sp_stage_kv = (torch.empty(shape, dtype=q.dtype, device=q.device),
+                                         torch.empty(shape, dtype=q.dtype, device=q.device))
+                sk, sv = self._sp_stage_kv
+                ks, vs = self._kv_scales(layer)
+                kernels.fp8_kv_gather_dequant(sk, sv, pool.get_key_buffer(layer.layer_id),
+                                              pool.get_value_buffer(layer.layer_id),
+                                              forward_batch.req_to_token_pool.req_to_token,
+                                              forward_batch.req_pool_indices[:1], st["prefix_lens"], st["offsets"], shared,
+                                              ks, vs)
+                extra = dict(stage=(sk, sv, st["table"], st["index"]), k_scale=ks, v_scale=vs)
             act = kernels.decode_attention_shared_prefix_fwd(
                 q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
                 pool.get_key_buffer(layer.layer_id), pool.get_value_buffer(layer.layer_id),
                 o.view(-1, layer.tp_q_head_num, layer.v_head_dim),
                 forward_batch.req_to_token_pool.req_to_token, forward_batch.req_pool_indices,
                 forward_batch.seq_lens, md.shared_prefix_len, md.seg_len, md.workspace, md.kv_chunk, md.max_splits,
-                layer.scaling, layer.logit_cap or 0.0, int8_out=int8_out)
+                layer.scaling, layer.logit_cap or 0.0, int8_out=int8_out, **extra)
             return act if int8_out else o
         act = kernels.decode_attention_fwd(
             q.view(-1, layer.tp_q_head_num, layer.qk_head_dim),
