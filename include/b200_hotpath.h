@@ -146,14 +146,15 @@ int b200_decode_attn_fp8kv(void* o, int8_t* oq, float* oq_scale, const void* q, 
  *   2. the split-KV decode kernel over each request's own tokens [shared_prefix_len, seq_len);
  *   3. one LSE merge over the segment partials and the decode partials (the decode stage-2 kernel).
  * Requires seq_lens[b] > shared_prefix_len for every b.  Workspace: b200_decode_attn_workspace_bytes(batch, Hq, D,
- * ceil(shared_prefix_len / seg_len) + max_splits).  oq / oq_scale as in b200_decode_attn_int8, or NULL. */
+ * ceil(shared_prefix_len / seg_len) + max_splits).  oq / oq_scale as in b200_decode_attn_int8, or NULL.
+ * num_kv_slots: rows of k_cache / v_cache (TMA extent for the two-query-tile prefix kernel); 0 = unknown. */
 int b200_decode_attn_shared_prefix(void* o, int8_t* oq, float* oq_scale, const void* q, const void* k_cache,
                                    const void* v_cache, const int32_t* req_to_token, int64_t req_to_token_stride,
                                    const void* req_pool_indices, const void* seq_lens, int index_is_int64, int batch,
                                    int num_q_heads, int num_kv_heads, int head_dim, int64_t q_token_stride,
                                    int64_t o_token_stride, int64_t kv_token_stride, float sm_scale, float logit_cap,
                                    int shared_prefix_len, int seg_len, int kv_chunk, int max_splits, void* workspace,
-                                   size_t workspace_bytes, int dtype, void* stream);
+                                   size_t workspace_bytes, int dtype, void* stream, int64_t num_kv_slots);
 
 /* Shared-prefix decode over an FP8 (e4m3) KV cache (config 5 with --kv-cache-dtype fp8_e4m3, memory_pool.py:385-391).
  * The caller first up-casts the shared tokens into a 16-bit staging copy with b200_fp8_kv_gather_dequant

@@ -57,7 +57,7 @@ _SIGNATURES = {
                                c_size_t, c_int, _P],
     "b200_decode_attn_shared_prefix": [_P, _P, _P, _P, _P, _P, _P, c_int64, _P, _P, c_int, c_int, c_int, c_int, c_int,
                                        c_int64, c_int64, c_int64, c_float, c_float, c_int, c_int, c_int, c_int, _P,
-                                       c_size_t, c_int, _P],
+                                       c_size_t, c_int, _P, c_int64],
     "b200_decode_attn_shared_prefix_fp8kv": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_int64, _P, c_int64, _P, _P, c_int,
                                              c_int, c_int, c_int, c_int, c_int64, c_int64, c_int64, c_float, c_float,
                                              c_float, c_float, c_int, c_int, c_int, c_int, _P, c_size_t, c_int, _P],

@@ -932,6 +932,19 @@ static int side_stream_for_current_device(SideStream* out) {
   return B200_OK;
 }
 
+// prefix pass of the shared-prefix decode: the two-query-tile TMA kernel when the K/V extent is known and the batch
+// fills more than one 128-row tile, else the one-tile cp.async kernel
+static int launch_prefix_pass(const b200::ExtendArgs& e, int batch, int head_dim, int dtype, int64_t kv_rows,
+                              cudaStream_t stream) {
+  using namespace b200;
+  static const bool fa = getenv("B200_EXTEND_FA") == nullptr || getenv("B200_EXTEND_FA")[0] != '0';
+  if (fa && kv_rows > 0 && batch > 128 && e.q_token_stride % 8 == 0 && e.kv_token_stride % 8 == 0) {
+    const int rc = launch_extend_fa(e, batch, head_dim, dtype, batch, kv_rows, stream);
+    if (rc != B200_ERR_UNSUPPORTED) return rc;
+  }
+  return launch_extend_umma(e, batch, head_dim, dtype, stream);
+}
+
 static int decode_attn_impl(void* o, const void* q, const void* k_cache, const void* v_cache,
                             const int32_t* req_to_token, int64_t req_to_token_stride,
                             const void* req_pool_indices, const void* seq_lens,
@@ -943,7 +956,7 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
                             bool kv_fp8 = false, float k_scale = 1.f, float v_scale = 1.f, int shared_prefix = 0,
                             int seg_len = 0, const void* k_stage = nullptr, const void* v_stage = nullptr,
                             const int32_t* stage_table = nullptr, const void* stage_index = nullptr,
-                            int64_t stage_token_stride = 0) {
+                            int64_t stage_token_stride = 0, int64_t num_kv_slots = 0) {
   using namespace b200;
   B200_REQUIRE(batch >= 0, "decode_attn: negative batch");
   if (batch == 0) return B200_OK;
@@ -1031,6 +1044,8 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
     // record/wait: capturable in a CUDA graph).  Measured gain is small (0.1198 -> 0.1167 ms at cfg 5 per GPU): the
     // prefix grid fills the chip and the decode pass needs every SM to saturate HBM, so mostly the tails overlap.
     // B200_SHARED_PREFIX_OVERLAP=0: serial.
+    // rows of the tensor the prefix pass reads K/V from (TMA extent): the staging copy, or the cache
+    const int64_t prefix_rows = kv_fp8 ? (int64_t)shared_prefix : num_kv_slots;
     static const bool overlap = getenv("B200_SHARED_PREFIX_OVERLAP") == nullptr || getenv("B200_SHARED_PREFIX_OVERLAP")[0] != '0';
     if (overlap) {
       SideStream ss;
@@ -1038,7 +1053,7 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
       if (rc != B200_OK) return rc;
       B200_CUDA_OK(cudaEventRecord(ss.fork, st));
       B200_CUDA_OK(cudaStreamWaitEvent(ss.stream, ss.fork, 0));
-      rc = launch_extend_umma(e, batch, head_dim, dtype, ss.stream);
+      rc = launch_prefix_pass(e, batch, head_dim, dtype, prefix_rows, ss.stream);
       // join on every path after the fork: an un-joined side stream would break an enclosing graph capture
       B200_CUDA_OK(cudaEventRecord(ss.join, ss.stream));
       if (rc != B200_OK) {
@@ -1047,7 +1062,7 @@ static int decode_attn_impl(void* o, const void* q, const void* k_cache, const v
       }
       join = ss.join;
     } else {
-      const int rc = launch_extend_umma(e, batch, head_dim, dtype, st);
+      const int rc = launch_prefix_pass(e, batch, head_dim, dtype, prefix_rows, st);
       if (rc != B200_OK) return rc;
     }
   }
@@ -1112,12 +1127,13 @@ B200_API int b200_decode_attn_shared_prefix(void* o, int8_t* oq, float* oq_scale
                                             int64_t o_token_stride, int64_t kv_token_stride, float sm_scale,
                                             float logit_cap, int shared_prefix_len, int seg_len, int kv_chunk,
                                             int max_splits, void* workspace, size_t workspace_bytes, int dtype,
-                                            void* stream) {
+                                            void* stream, int64_t num_kv_slots) {
   B200_REQUIRE(shared_prefix_len > 0, "decode_attn_shared_prefix: shared_prefix_len must be positive");
   return decode_attn_impl(o, q, k_cache, v_cache, req_to_token, req_to_token_stride, req_pool_indices, seq_lens,
                           index_is_int64, batch, num_q_heads, num_kv_heads, head_dim, q_token_stride, o_token_stride,
                           kv_token_stride, sm_scale, logit_cap, kv_chunk, max_splits, workspace, workspace_bytes, dtype,
-                          oq, oq_scale, stream, false, 1.f, 1.f, shared_prefix_len, seg_len);
+                          oq, oq_scale, stream, false, 1.f, 1.f, shared_prefix_len, seg_len, nullptr, nullptr, nullptr,
+                          nullptr, 0, num_kv_slots);
 }
 
 B200_API int b200_decode_attn_shared_prefix_fp8kv(

@@ -166,12 +166,20 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
 
   pdl_trigger();
   pdl_wait();
-  const int q_start = a.qo_indptr[b];
-  const int ext_len = a.qo_indptr[b + 1] - q_start;
+  // Segment mode (shared-prefix decode, decode_attn.cu): blockIdx.z = segment s of request 0's prefix; the query rows
+  // are the decode batch (one row per request), the KV range is [s * seg_len, min(prefix, (s+1) * seg_len)) of request
+  // 0's page-table row, no causal mask, and the result is a normalised fp32 partial + log2-LSE in the decode merge's
+  // workspace instead of o.
+  const bool seg_mode = a.part_o != nullptr;
+  const int rb = seg_mode ? 0 : b;
+  const int q_start = seg_mode ? 0 : a.qo_indptr[rb];
+  const int ext_len = seg_mode ? a.seg_rows : a.qo_indptr[rb + 1] - q_start;
   const int m0 = mblk * (2 * kFaBM);
   if (m0 >= ext_len) return;  // CTA-uniform, before any barrier / TMEM use
-  const int prefix = a.prefix_lens[b];
-  const int kv_total = prefix + ext_len;
+  const int kv_begin = seg_mode ? b * a.seg_len : 0;
+  const int prefix = seg_mode ? min(a.seg_prefix - kv_begin, a.seg_len) : a.prefix_lens[b];
+  if (seg_mode && prefix <= 0) return;
+  const int kv_total = seg_mode ? prefix : prefix + ext_len;
   int kv_end_t[2], n_t[2];
 #pragma unroll
   for (int t = 0; t < 2; ++t) {
@@ -221,8 +229,8 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     fa_reg_dealloc<40>();  // 128 x (168 - 40) registers returned = 256 x (232 - 168) taken below
     if (warp == 0) {
       // ---- TMA producer ----------------------------------------------------------------------------------------
-      const int64_t req = load_index(a.req_pool_indices, b, a.index_is_int64);
-      const int32_t* r2t_row = a.req_to_token + req * a.req_to_token_stride;
+      const int64_t req = load_index(a.req_pool_indices, rb, a.index_is_int64);
+      const int32_t* r2t_row = a.req_to_token + req * a.req_to_token_stride + kv_begin;
       if (lane == 0) {
         prefetch_tmap(&tm_q);
         prefetch_tmap(&tm_k16);
@@ -476,10 +484,28 @@ extend_attn_fa_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       const float l_run = l0 + l1;
       const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
       const bool row_ok = r0 + row < ext_len;
+      if (seg_mode) {
+        const int64_t pidx = ((int64_t)(r0 + row) * a.num_q_heads + head) * a.part_stride + b;
+        float* prow = a.part_o + pidx * D;
+        if (row_ok) a.part_lse[pidx] = l_run > 0.f ? m_used + log2f(l_run) : -INFINITY;
+#pragma unroll 1
+        for (int c0 = 0; c0 < D; c0 += 32) {
+          uint32_t r[32];
+          tmem_ld32(t_o + c0, r);
+          tmem_ld_wait();
+          if (row_ok) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4)
+              *reinterpret_cast<float4*>(prow + c0 + i) =
+                  make_float4(__uint_as_float(r[i]) * inv, __uint_as_float(r[i + 1]) * inv, __uint_as_float(r[i + 2]) * inv,
+                              __uint_as_float(r[i + 3]) * inv);
+          }
+        }
+      }
       T* orow = reinterpret_cast<T*>(a.o) + (int64_t)(q_start + r0 + row) * a.o_token_stride + (int64_t)head * D;
       const bool aligned = (reinterpret_cast<uintptr_t>(orow) & 15) == 0;
 #pragma unroll 1
-      for (int c0 = 0; c0 < D; c0 += 32) {
+      for (int c0 = 0; c0 < D && !seg_mode; c0 += 32) {
         uint32_t r[32];
         tmem_ld32(t_o + c0, r);
         tmem_ld_wait();
@@ -552,17 +578,18 @@ int launch_fa(const ExtendArgs& a, int max_extend_len, int64_t num_q_tokens, int
   if (st != B200_OK) return st;
   auto kern = extend_attn_fa_kernel<T, D, POLY>;
   B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
-  dim3 grid((max_extend_len + 2 * kFaBM - 1) / (2 * kFaBM), a.num_q_heads, a.batch);
+  dim3 grid((max_extend_len + 2 * kFaBM - 1) / (2 * kFaBM), a.num_q_heads, a.batch);  // segment mode: batch = segments
   return launch_k(kern, grid, dim3(kFaThreads), L::kBytes, stream, 1, true, tq, tk16, tk1, tv16, tv1, a);
 }
 
 }  // namespace
 
-// Two-query-tile TMA kernel.  Covers head_dim 128, every KV position read through the page table (k_new == NULL), no
-// segment mode; anything else returns B200_ERR_UNSUPPORTED and the caller takes extend_attn_umma.cu.
+// Two-query-tile TMA kernel.  Covers head_dim 128 and every KV position read through the page table (k_new == NULL),
+// incl. the segment mode of the shared-prefix decode; anything else returns B200_ERR_UNSUPPORTED and the caller takes
+// extend_attn_umma.cu.
 int launch_extend_fa(const ExtendArgs& a, int max_extend_len, int head_dim, int dtype, int64_t num_q_tokens,
                      int64_t num_kv_slots, cudaStream_t stream) {
-  if (a.k_new != nullptr || a.part_o != nullptr || head_dim != 128 || num_q_tokens <= 0 || num_kv_slots <= 0)
+  if (a.k_new != nullptr || head_dim != 128 || num_q_tokens <= 0 || num_kv_slots <= 0)
     return B200_ERR_UNSUPPORTED;
   static const int poly = getenv("B200_FA_POLY") ? atoi(getenv("B200_FA_POLY")) : kFaPolyDefault;
 #define B200_FA_LAUNCH(TT)                                                                                        \

@@ -191,7 +191,7 @@ def decode_attention_fwd(q: torch.Tensor, k_buffer: torch.Tensor, v_buffer: torc
 
 
 def plan_shared_prefix_segments(shared_prefix_len: int, batch: int, num_q_heads: int, sm_count: int = 148,
-                                sm_fraction: Optional[float] = None) -> int:
+                                sm_fraction: Optional[float] = None, head_dim: int = 128) -> int:
     """Segment length (multiple of 128) for the prefix pass of the shared-prefix decode.  The pass runs one CTA per SM
     (512 TMEM columns, 198 KB smem), ceil(batch/128) * Hq CTAs per segment: take as many segments as fit in ONE wave
     (2.05 waves measured 0.140 ms vs 0.122 ms for one), at least 512 tokens each.  Leaving SMs free for the forked
@@ -199,7 +199,10 @@ def plan_shared_prefix_segments(shared_prefix_len: int, batch: int, num_q_heads:
     0.117 ms): that pass needs every SM to saturate HBM, so the two passes' SM-time simply adds up."""
     if sm_fraction is None:
         sm_fraction = float(os.environ.get("B200_PREFIX_SM_FRACTION", "1.0"))
-    ctas_per_seg = max(1, (batch + 127) // 128) * num_q_heads
+    # query rows per CTA of the prefix pass: 256 for the two-query-tile kernel (head_dim 128, more than one 128-row tile
+    # of requests; extend_attn_fa.cu), else 128 (extend_attn_umma.cu) — launch_prefix_pass in csrc/decode_attn.cu
+    rows = 256 if (batch > 128 and head_dim == 128 and os.environ.get("B200_EXTEND_FA", "1") != "0") else 128
+    ctas_per_seg = max(1, (batch + rows - 1) // rows) * num_q_heads
     n_seg = max(1, int(sm_count * sm_fraction) // ctas_per_seg)
     seg = (shared_prefix_len + n_seg - 1) // n_seg
     return max(512, (seg + 127) // 128 * 128)
@@ -249,7 +252,7 @@ def decode_attention_shared_prefix_fwd(q: torch.Tensor, k_buffer: torch.Tensor, 
         req_to_token.stride(0), ptr(req_pool_indices), ptr(seq_lens), _is64(seq_lens), bs, hq, hkv, d,
         q.stride(0), o.stride(0), k_buffer.stride(0), float(sm_scale), float(logit_cap), int(shared_prefix_len),
         int(seg_len), int(kv_chunk), int(max_splits), ptr(workspace),
-        workspace.numel() * workspace.element_size(), dtype_code(q.dtype), stream_ptr(q.device)),
+        workspace.numel() * workspace.element_size(), dtype_code(q.dtype), stream_ptr(q.device), k_buffer.shape[0]),
         "b200_decode_attn_shared_prefix")
     return Int8Activation(oq, oscale, q.dtype) if int8_out else None
 

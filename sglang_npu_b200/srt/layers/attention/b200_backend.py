@@ -177,7 +177,7 @@ class B200AttnBackend(AttentionBackend):
                 shared = shared // 128 * 128  # whole KV tiles for the prefix pass; the remainder stays per-request
                 chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, max(max_len - shared, 1),
                                                    self.sm_count, self.forced_chunk, self._max_chunk, exact)
-                seg = kernels.plan_shared_prefix_segments(shared, bs, self.num_head, self.sm_count)
+                seg = kernels.plan_shared_prefix_segments(shared, bs, self.num_head, self.sm_count, head_dim=self.head_dim)
                 n_seg = (shared + seg - 1) // seg
                 self.forward_metadata = ForwardMetadata(
                     kv_chunk=chunk, max_splits=splits, shared_prefix_len=shared, seg_len=seg,
@@ -231,7 +231,7 @@ class B200AttnBackend(AttentionBackend):
         if shared >= self.min_shared_prefix and bs >= 2 and self._shared_prefix_supported():
             chunk, splits = plan_decode_splits(bs, self.num_kv_head, group, max(self.max_context_len - shared, 1),
                                                self.sm_count, self.forced_chunk, self._max_chunk, exact=False)
-            seg = kernels.plan_shared_prefix_segments(shared, bs, self.num_head, self.sm_count)
+            seg = kernels.plan_shared_prefix_segments(shared, bs, self.num_head, self.sm_count, head_dim=self.head_dim)
             n_seg = (shared + seg - 1) // seg
             self.forward_metadata = ForwardMetadata(kv_chunk=chunk, max_splits=splits, shared_prefix_len=shared, seg_len=seg,
                                                     workspace=self._decode_workspace(bs, n_seg + splits, graph=True))

@@ -91,8 +91,11 @@ def test_fp8_kv_oracles_are_consistent_with_the_16bit_oracles():
 def test_shared_prefix_segment_planner():
     from sglang_npu_b200.kernels import plan_shared_prefix_segments as plan
 
-    # cfg 5 per GPU: 2 row blocks x 8 heads = 16 CTAs per segment -> 9 segments fill one wave of 148 SMs
+    # cfg 5 per GPU, head_dim 128: the two-query-tile prefix kernel takes 256 requests per CTA -> 8 CTAs per segment ->
+    # 18 segments fill one wave of 148 SMs; head_dim 64 stays on 128-row CTAs: 16 CTAs per segment -> 9 segments
     seg = plan(30720, 256, 8, sm_count=148, sm_fraction=1.0)
+    assert seg % 128 == 0 and (30720 + seg - 1) // seg == 18
+    seg = plan(30720, 256, 8, sm_count=148, sm_fraction=1.0, head_dim=64)
     assert seg % 128 == 0 and (30720 + seg - 1) // seg == 9
     # never shorter than 512 tokens, always a multiple of 128, one segment when a segment already fills the chip
     assert plan(1024, 4, 2, sm_count=148, sm_fraction=1.0) == 512

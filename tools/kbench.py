@@ -85,14 +85,27 @@ def bench_decode(args):
         fn = lambda: kernels.decode_attention_fwd(q, k, v, o, r2t, rpi, sl, ws, ch, splits, d ** -0.5)
         if args.shared:  # shared-prefix (cascade) decode next to the plain kernel on the same batch
             uch, usp = plan_decode_splits(bs, hkv, hq // hkv, max(lens) - args.shared, 148, chunk)
-            seg = kernels.plan_shared_prefix_segments(args.shared, bs, hq)
+            seg = kernels.plan_shared_prefix_segments(args.shared, bs, hq, head_dim=d)
             nseg = (args.shared + seg - 1) // seg
             ws2 = torch.empty(kernels.decode_attn_workspace_bytes(bs, hq, d, nseg + usp), dtype=torch.uint8, device=dev)
-            fn2 = lambda: kernels.decode_attention_shared_prefix_fwd(q, k, v, o, r2t, rpi, sl, args.shared, seg, ws2,
-                                                                     uch, usp, d ** -0.5)
+            if args.fp8kv:  # staged prefix (gather + up-cast, timed with the decode) for the tensor-core pass
+                sk = torch.empty((args.shared, hkv, d), dtype=torch.bfloat16, device=dev)
+                sv = torch.empty_like(sk)
+                pl1 = torch.full((1,), args.shared, dtype=torch.int32, device=dev)
+                off1 = torch.zeros(1, dtype=torch.int32, device=dev)
+                tab = torch.arange(args.shared, dtype=torch.int32, device=dev)
+                idx0 = torch.zeros(1, dtype=rpi.dtype, device=dev)
+
+                def fn2():
+                    kernels.fp8_kv_gather_dequant(sk, sv, k, v, r2t, rpi[:1], pl1, off1, args.shared)
+                    kernels.decode_attention_shared_prefix_fwd(q, k, v, o, r2t, rpi, sl, args.shared, seg, ws2, uch, usp,
+                                                               d ** -0.5, stage=(sk, sv, tab, idx0))
+            else:
+                fn2 = lambda: kernels.decode_attention_shared_prefix_fwd(q, k, v, o, r2t, rpi, sl, args.shared, seg, ws2,
+                                                                         uch, usp, d ** -0.5)
             med2, best2 = timeit(fn2)
             unique = (args.shared + sum(n - args.shared for n in lens)) * 2 * hkv * d * k.element_size()
-            print(json.dumps(dict(kernel="decode_attn_shared_prefix", bs=bs, ctx=ctx, shared=args.shared, seg_len=seg,
+            print(json.dumps(dict(kernel="decode_attn_shared_prefix" + ("_fp8kv" if args.fp8kv else ""), bs=bs, ctx=ctx, shared=args.shared, seg_len=seg,
                                   segments=nseg, chunk=uch, splits=usp, ms_med=round(med2, 4), ms_best=round(best2, 4),
                                   unique_gbs=round(unique / med2 / 1e6, 1), logical_gbs=round(kv_bytes / med2 / 1e6, 1),
                                   prefix_tflops=round(4.0 * hq * d * bs * args.shared / med2 / 1e9, 1))), flush=True)
