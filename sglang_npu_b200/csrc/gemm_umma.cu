@@ -453,7 +453,11 @@ gemm_umma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 constexpr int kPfBN = 256;
 constexpr int kPfStages = 4;
 
-template <int MODE>
+// MC: the CTAs run as pairs (cluster 1x1x2) on two m-tiles of the SAME n-tile; each CTA loads its own A tile and HALF of
+// the shared B tile, multicast into both CTAs' shared memory.  Per K block a CTA then pulls 32 KB over the L2 -> SM
+// fabric instead of 48 KB (a 128x256 tile at 2.6 POP/s asks ~92 B/clk per SM from the fabric).  A stage is free when BOTH
+// CTAs have consumed it: the MMA threads commit to the empty barrier of both CTAs (multicast commit, count 2).
+template <int MODE, bool MC>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const GemmArgs g, const int tiles_m, const int num_tiles) {
@@ -477,7 +481,7 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kPfStages; ++s) {
       mbar_init(full_bar(s), 1);
-      mbar_init(empty_bar(s), 1);
+      mbar_init(empty_bar(s), MC ? 2 : 1);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(tmem_full_bar(b), 1);
@@ -487,19 +491,25 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   }
   if (warp == 2) tmem_alloc<512>(smem_u32(&s_tmem_base));
   tc_fence_before();
-  __syncthreads();
+  if constexpr (MC) cluster_sync();  // the peer's barriers exist before anything is multicast at them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = s_tmem_base;
   pdl_trigger();
   pdl_wait();
 
   const int nkb = g.num_kb;
+  // tile walk: without MC, tile t of this CTA; with MC, pair-tile t = (n_tile, pair of m-tiles), this CTA takes m-tile
+  // 2 * pair + rank (an odd tiles_m leaves rank 1 a tile of zero rows: TMA fills zeros, the epilogue stores nothing)
+  const int rank = MC ? (int)cluster_ctarank() : 0;
+  const int tiles_mp = MC ? (tiles_m + 1) / 2 : tiles_m;
+  auto tile_m = [&](int t) { return MC ? 2 * (t % tiles_mp) + rank : t % tiles_mp; };
   if (warp == 0) {
     if (elect_one()) {
       uint32_t it = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        const int n_tile = t / tiles_m;
-        const int a_row0 = (t - n_tile * tiles_m) * 128;
+        const int n_tile = t / tiles_mp;
+        const int a_row0 = tile_m(t) * 128;
         const int b_row0 = n_tile * kPfBN;
         for (int i = 0; i < nkb; ++i, ++it) {
           const int s = it % kPfStages;
@@ -507,7 +517,11 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           mbar_expect_tx(full_bar(s), L::kStage);
           const uint32_t sa = base + s * L::kStage;
           tma_load_2d(sa, &tmap_a, full_bar(s), i * kBK, a_row0, kEvictLast);
-          tma_load_2d(sa + L::kA, &tmap_b, full_bar(s), i * kBK, b_row0, kEvictNormal);
+          if constexpr (MC)  // tmap_b boxes are 128 rows here: this CTA's half, into both CTAs
+            tma_load_2d_mc(sa + L::kA + rank * (128 * kBK), &tmap_b, full_bar(s), i * kBK, b_row0 + rank * 128, (uint16_t)3,
+                           kEvictNormal);
+          else
+            tma_load_2d(sa + L::kA, &tmap_b, full_bar(s), i * kBK, b_row0, kEvictNormal);
         }
       }
     }
@@ -531,7 +545,8 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           const uint64_t db = smem_desc_k_sw128(sa + L::kA);
 #pragma unroll
           for (int k = 0; k < kBK / 32; ++k) umma<kKind>(d_tmem, da + 2 * k, db + 2 * k, idesc, (i | k) != 0);
-          tc_commit(empty_bar(s));
+          if constexpr (MC) tc_commit_mc(empty_bar(s), (uint16_t)3);
+          else tc_commit(empty_bar(s));
         }
         tc_commit(tmem_full_bar(buf));
       }
@@ -543,8 +558,8 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     int j = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++j) {
       const int buf = j & 1;
-      const int n_tile = t / tiles_m;
-      const int m = (t - n_tile * tiles_m) * 128 + row;
+      const int n_tile = t / tiles_mp;
+      const int m = tile_m(t) * 128 + row;
       const int b_row0 = n_tile * kPfBN;
       const bool m_ok = m < g.M;
       const float smv = m_ok ? g.scale_m[m] : 0.f;
@@ -591,8 +606,216 @@ gemm_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     }
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (MC) cluster_sync();  // no CTA leaves while its peer may still multicast into it / arrive at its barriers
+  else __syncthreads();
   if (warp == 2) tmem_dealloc<512>(tmem_base);
+}
+
+// ---- prefill: CTA pairs on one 256 x 256 tile (tcgen05.mma.cta_group::2) ------------------------------------------------
+// The 128x256 single-CTA tile above asks ~92 B/clk per SM from the L2 -> SM fabric (A 16 KB + B 32 KB per 128-byte K
+// block) and measures 15.7 TB/s of fabric traffic with the tensor pipe 73 % active and the MMA thread waiting for
+// stages (profiles/r02s_gemm_prefill_ncu.txt).  Here two CTAs of a cluster (2,1,1) — two SMs of one TPC — form ONE
+// 256(M) x 256(N) MMA: each CTA holds its own 128 token rows of A and HALF of the weight tile (128 of the 256
+// channels); the leader's thread issues tcgen05.mma.cta_group::2, the tensor cores of both SMs read A from their own
+// shared memory and B from both.  Per K block a CTA ingests 32 KB instead of 48 KB for the same MACs, and the stage
+// shrinks to 32 KB: six stages instead of four in the same shared memory.
+//   full[s]       lives in the LEADER: both producers arrive.expect_tx on it, both CTAs' TMA loads complete_tx on it;
+//   empty[s]      in each CTA (its producer waits on it): the leader's MMA thread commits to both (multicast);
+//   tmem_full[b]  in each CTA (its epilogue warps wait on it): multicast commit;
+//   tmem_empty[b] in the LEADER: the epilogue warps of BOTH CTAs arrive on it (count 8).
+constexpr int kP2Stages = 6;
+constexpr int kP2StageBytes = 2 * 128 * kBK;  // A rows of this CTA + this CTA's half of the weight tile
+constexpr int kP2BarOff = kP2Stages * kP2StageBytes;
+constexpr int kP2Bytes = kP2BarOff + (2 * kP2Stages + 4) * 8 + 1024;
+
+// Remote arrives in their default (release at CTA scope) form: `.release.cluster` compiles to MEMBAR.ALL.GPU + ERRBAR
+// per call, which throttled the non-leader's producer to one stage per fence (tensor pipe 37 % active).
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];\n" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx_remote(uint32_t cluster_addr, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;\n" ::"r"(cluster_addr), "r"(bytes)
+               : "memory");
+}
+// TMA tile load of a CTA pair: lands in THIS CTA's shared memory, completes bytes on the barrier at `cluster_bar`
+// (a shared::cluster address: the leader's)
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t smem_dst, const CUtensorMap* m, uint32_t cluster_bar, int c0, int c1,
+                                                 uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+      "[%0], [%1, {%3, %4}], [%2], %5;\n" ::"r"(smem_dst),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(cluster_bar), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+template <int KIND>
+__device__ __forceinline__ void umma_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, bool accumulate) {
+  const uint32_t acc = accumulate ? 1u : 0u;
+  if constexpr (KIND == kKindI8) {
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n}\n" ::"r"(d_tmem),
+                 "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
+                 : "memory");
+  } else {
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::2.kind::f8f6f4 [%0], %1, %2, %3, p;\n}\n" ::"r"(
+                     d_tmem),
+                 "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
+                 : "memory");
+  }
+}
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {  // arrives on the barrier at this offset in BOTH CTAs
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n" ::"r"(bar),
+               "h"((uint16_t)3)
+               : "memory");
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_prefill_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                         const GemmArgs g, const int tiles_m2, const int num_tiles) {
+  constexpr int kKind = MODE == kModeI8 ? kKindI8 : kKindF8;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint32_t s_tmem_base;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar = base + kP2BarOff;
+  auto full_bar = [&](int s) { return bar + s * 8; };
+  auto empty_bar = [&](int s) { return bar + (kP2Stages + s) * 8; };
+  auto tmem_full_bar = [&](int b) { return bar + (2 * kP2Stages + b) * 8; };
+  auto tmem_empty_bar = [&](int b) { return bar + (2 * kP2Stages + 2 + b) * 8; };
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int rank = (int)cluster_ctarank();
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_a);
+    prefetch_tmap(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kP2Stages; ++s) {
+      mbar_init(full_bar(s), 2);   // one arrive.expect_tx per producer of the pair (used in the leader)
+      mbar_init(empty_bar(s), 1);  // one multicast commit of the leader's MMA thread
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(tmem_full_bar(b), 1);
+      mbar_init(tmem_empty_bar(b), 8);  // four epilogue warps of each CTA (used in the leader)
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(&s_tmem_base)), "n"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
+  }
+  tc_fence_before();
+  cluster_sync();  // both CTAs' barriers and TMEM exist before anything crosses the pair
+  tc_fence_after();
+  const uint32_t tmem_base = s_tmem_base;
+  pdl_trigger();
+  pdl_wait();
+
+  const int nkb = g.num_kb;
+  if (warp == 0) {
+    if (elect_one()) {
+      uint32_t it = 0;
+      for (int t = blockIdx.x >> 1; t < num_tiles; t += gridDim.x >> 1) {
+        const int n_tile = t / tiles_m2;
+        const int a_row0 = (2 * (t - n_tile * tiles_m2) + rank) * 128;
+        const int b_row0 = n_tile * 256 + rank * 128;
+        for (int i = 0; i < nkb; ++i, ++it) {
+          const int s = it % kP2Stages;
+          mbar_wait(empty_bar(s), ((it / kP2Stages) & 1) ^ 1);
+          const uint32_t lead_full = mapa(full_bar(s), 0);
+          if (rank == 0) mbar_expect_tx(full_bar(s), kP2StageBytes);
+          else mbar_expect_tx_remote(lead_full, kP2StageBytes);
+          const uint32_t sa = base + s * kP2StageBytes;
+          tma_load_2d_pair(sa, &tmap_a, lead_full, i * kBK, a_row0, kEvictLast);
+          tma_load_2d_pair(sa + 128 * kBK, &tmap_b, lead_full, i * kBK, b_row0, kEvictNormal);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0 && elect_one()) {
+      constexpr uint32_t idesc = MODE == kModeI8 ? make_idesc(/*s32*/ 2, /*int8*/ 1, 1, 256, 256)
+                                                 : make_idesc(/*f32*/ 1, /*e4m3*/ 0, 0, 256, 256);
+      uint32_t it = 0;
+      int j = 0;
+      for (int t = blockIdx.x >> 1; t < num_tiles; t += gridDim.x >> 1, ++j) {
+        const int buf = j & 1;
+        mbar_wait(tmem_empty_bar(buf), ((j >> 1) & 1) ^ 1);  // both CTAs' epilogues have drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * 256;
+        for (int i = 0; i < nkb; ++i, ++it) {
+          const int s = it % kP2Stages;
+          mbar_wait(full_bar(s), (it / kP2Stages) & 1);
+          tc_fence_after();
+          const uint32_t sa = base + s * kP2StageBytes;
+          const uint64_t da = smem_desc_k_sw128(sa);
+          const uint64_t db = smem_desc_k_sw128(sa + 128 * kBK);
+#pragma unroll
+          for (int k = 0; k < kBK / 32; ++k) umma_pair<kKind>(d_tmem, da + 2 * k, db + 2 * k, idesc, (i | k) != 0);
+          tc_commit_pair(empty_bar(s));
+        }
+        tc_commit_pair(tmem_full_bar(buf));
+      }
+    }
+  } else if (warp >= 4) {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const bool has_bias = g.bias != nullptr;
+    int j = 0;
+    for (int t = blockIdx.x >> 1; t < num_tiles; t += gridDim.x >> 1, ++j) {
+      const int buf = j & 1;
+      const int n_tile = t / tiles_m2;
+      const int m = (2 * (t - n_tile * tiles_m2) + rank) * 128 + row;
+      const int b_row0 = n_tile * 256;
+      const bool m_ok = m < g.M;
+      const float smv = m_ok ? g.scale_m[m] : 0.f;
+      mbar_wait(tmem_full_bar(buf), (j >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256;
+#pragma unroll 2
+      for (int c0 = 0; c0 < 256; c0 += 16) {
+        const int n0 = b_row0 + c0;
+        if (n0 >= g.N) break;  // warp-uniform
+        uint32_t r[16];
+        tmem_ld16(taddr + c0, r);
+        tmem_ld_wait();
+        if (m_ok) {
+          const int valid = min(16, g.N - n0);  // N % 8 == 0: a 16-column group is full or exactly half full
+          float v[16];
+#pragma unroll
+          for (int jj = 0; jj < 16; ++jj) {
+            float bias = 0.f, sn = 0.f;
+            if (jj < valid) {
+              sn = __ldg(g.scale_n + n0 + jj);
+              if (has_bias) bias = load_bias(g.bias, n0 + jj, g.out_is_bf16);
+            }
+            v[jj] = finalize<MODE>(r[jj], smv, sn, has_bias, bias);
+          }
+          uint32_t p[8];
+#pragma unroll
+          for (int jj = 0; jj < 8; ++jj)
+            p[jj] = g.out_is_bf16 ? pack2<__nv_bfloat16>(v[2 * jj], v[2 * jj + 1]) : pack2<__half>(v[2 * jj], v[2 * jj + 1]);
+          uint8_t* dstp = reinterpret_cast<uint8_t*>(g.out) + ((int64_t)m * g.N + n0) * 2;
+          *reinterpret_cast<uint4*>(dstp) = make_uint4(p[0], p[1], p[2], p[3]);
+          if (valid > 8) *reinterpret_cast<uint4*>(dstp + 16) = make_uint4(p[4], p[5], p[6], p[7]);
+          if (MODE == kModeI8 && g.acc_out) {
+            int32_t* ad = g.acc_out + (int64_t)m * g.N + n0;
+#pragma unroll
+            for (int jj = 0; jj < 16; jj += 4)
+              if (jj < valid) *reinterpret_cast<uint4*>(ad + jj) = make_uint4(r[jj], r[jj + 1], r[jj + 2], r[jj + 3]);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (rank == 0) mbar_arrive(tmem_empty_bar(buf));
+        else mbar_arrive_remote(mapa(tmem_empty_bar(buf), 0));
+      }
+    }
+  }
+  tc_fence_before();
+  cluster_sync();  // no CTA leaves (or frees TMEM) while the pair's MMAs / barrier traffic may still touch it
+  if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "n"(512) : "memory");
 }
 
 // ---- decode: persistent stream-K weight streaming -----------------------------------------------------------------------
@@ -1061,11 +1284,55 @@ static int run_gemm(GemmArgs g, const void* a, const void* b, int64_t M, int64_t
     static const bool persist = getenv("B200_GEMM_PERSIST") == nullptr || getenv("B200_GEMM_PERSIST")[0] != '0';
     if (N >= kPfBN && persist) {
       if ((rc = cached_tmap(&ta, a, (uint64_t)M, (uint64_t)K, 128)) != B200_OK) return rc;
-      if ((rc = cached_tmap(&tb, b, (uint64_t)N, (uint64_t)K, (uint32_t)kPfBN)) != B200_OK) return rc;
       const int tiles_m = (int)ceil_div(M, 128);
-      const int num_tiles = tiles_m * (int)ceil_div(N, kPfBN);
       using L = GemmSmemLayout<kPfBN, kPfStages>;
-      auto kern = gemm_prefill_kernel<MODE>;
+      // CTA pairs with the weight tile multicast across the pair (see the kernel) from two m-tiles up;
+      // B200_GEMM_MC=0: one CTA per tile (A/B runs)
+      // B200_GEMM_PAIR=0 / B200_GEMM_MC=0 select the older kernels (A/B runs)
+      static const bool pair = getenv("B200_GEMM_PAIR") == nullptr || getenv("B200_GEMM_PAIR")[0] != '0';
+      if (pair && tiles_m >= 2) {
+        if ((rc = cached_tmap(&tb, b, (uint64_t)N, (uint64_t)K, 128)) != B200_OK) return rc;
+        const int tiles_m2 = (int)ceil_div(tiles_m, 2);
+        const int num_pairs = tiles_m2 * (int)ceil_div(N, 256);
+        auto kern = gemm_prefill_pair_kernel<MODE>;
+        B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kP2Bytes));
+        const int pairs = num_pairs < sm_count() / 2 ? num_pairs : sm_count() / 2;
+        // a kernel that uses cta_group::2 must be launched with an even cluster x dimension (a (1,1,2) cluster is
+        // rejected as "cluster misconfiguration")
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(2 * pairs));
+        cfg.blockDim = dim3(kGemmThreads);
+        cfg.dynamicSmemBytes = kP2Bytes;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[2];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        int na = 1;
+        if (pdl_enabled()) {
+          attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+          attr[na].val.programmaticStreamSerializationAllowed = 1;
+          ++na;
+        }
+        cfg.attrs = attr;
+        cfg.numAttrs = na;
+        B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, ta, tb, g, tiles_m2, num_pairs));
+        return B200_OK;
+      }
+      static const bool mc = getenv("B200_GEMM_MC") == nullptr || getenv("B200_GEMM_MC")[0] != '0';
+      if (mc && tiles_m >= 2) {
+        if ((rc = cached_tmap(&tb, b, (uint64_t)N, (uint64_t)K, 128)) != B200_OK) return rc;
+        const int num_pairs = (int)ceil_div(tiles_m, 2) * (int)ceil_div(N, kPfBN);
+        auto kern = gemm_prefill_kernel<MODE, true>;
+        B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
+        const int pairs = num_pairs < sm_count() / 2 ? num_pairs : sm_count() / 2;
+        return launch_k(kern, dim3((unsigned)pairs, 1, 2), dim3(kGemmThreads), L::kBytes, st, 2, true, ta, tb, g, tiles_m,
+                        num_pairs);
+      }
+      if ((rc = cached_tmap(&tb, b, (uint64_t)N, (uint64_t)K, (uint32_t)kPfBN)) != B200_OK) return rc;
+      const int num_tiles = tiles_m * (int)ceil_div(N, kPfBN);
+      auto kern = gemm_prefill_kernel<MODE, false>;
       B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
       const int ctas = num_tiles < sm_count() ? num_tiles : sm_count();
       return launch_k(kern, dim3((unsigned)ctas), dim3(kGemmThreads), L::kBytes, st, 1, true, ta, tb, g, tiles_m, num_tiles);
