@@ -581,7 +581,7 @@ def main():
         rec = time_wrapped([(bmod.kernels, name)], eager_passes)
         pairs = rec[name]
         durs = sorted(a.elapsed_time(b) for a, b, _, _ in pairs[len(pairs) // 3:])  # drop the first pass
-        attn_ms = sum(durs) / len(durs)
+        attn_ms = durs[len(durs) // 2]  # median over every layer of two passes
         # algorithmic bytes per launch: KV (unique bytes when a prefix is shared) + q/o + page ids
         sp = args.shared_prefix
         kv_tokens = sp + bs * (ctx - sp)
@@ -700,7 +700,7 @@ def main():
             by_shape.setdefault((kk, nn_), []).append(e0.elapsed_time(e1))
         gemms = []
         for (kk, nn_), ds in by_shape.items():
-            ms = sum(ds) / len(ds)
+            ms = sorted(ds)[len(ds) // 2]  # median: a power-cap clock dip during one pass must not skew the figure
             gemms.append({"k": kk, "n": nn_, "ms": ms, "tflops": 2 * T * kk * nn_ / (ms * 1e-3) / 1e12})
         gemms.sort(key=lambda g_: -g_["k"] * g_["n"])
         dom = gemms[0]
@@ -708,7 +708,8 @@ def main():
         tot_flops = sum(2 * T * g_["k"] * g_["n"] for g_ in gemms)
         att = rec.get("extend_attention_fwd", [])
         att = att[len(att) // 3:]
-        attn_ms = sum(a.elapsed_time(b) for a, b, _, _ in att) / max(len(att), 1)
+        att_d = sorted(a.elapsed_time(b) for a, b, _, _ in att)
+        attn_ms = att_d[len(att_d) // 2] if att_d else 0.0
         attn_flops = 4 * cfg.head_dim * hq_local * reqs * (new * prefix + new * (new + 1) // 2)
         probe, probe_what = tensor_peak_probe("int8" if args.quant == "int8" else "fp8", dev) \
             if args.quant != "awq" else (peaks["bf16_tflops"], "MEASURED_PEAKS.json bf16_tflops (f16 operands after dequant)")
