@@ -74,6 +74,11 @@ __device__ __forceinline__ void fa_reg_alloc() { asm volatile("setmaxnreg.inc.sy
 
 // (d0, d1) = (a0, a1) * (b, b) + (c, c) as one packed FFMA2
 __device__ __forceinline__ void fa_fma2(float& d0, float& d1, float a0, float a1, float b, float c) {
+#ifdef B200_FA_SCALAR_MATH
+  d0 = fmaf(a0, b, c);
+  d1 = fmaf(a1, b, c);
+  return;
+#endif
   asm("{\n.reg .b64 va, vb, vc;\n"
       "mov.b64 va, {%2, %3};\nmov.b64 vb, {%4, %4};\nmov.b64 vc, {%5, %5};\n"
       "fma.rn.f32x2 vc, va, vb, vc;\n"
@@ -82,6 +87,11 @@ __device__ __forceinline__ void fa_fma2(float& d0, float& d1, float a0, float a1
       : "f"(a0), "f"(a1), "f"(b), "f"(c));
 }
 __device__ __forceinline__ void fa_add2(float& s0, float& s1, float a0, float a1) {
+#ifdef B200_FA_SCALAR_MATH
+  s0 += a0;
+  s1 += a1;
+  return;
+#endif
   asm("{\n.reg .b64 va, vs;\n"
       "mov.b64 va, {%2, %3};\nmov.b64 vs, {%0, %1};\n"
       "add.rn.f32x2 vs, vs, va;\n"

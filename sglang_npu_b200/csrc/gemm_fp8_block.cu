@@ -25,9 +25,16 @@
 
 namespace b200 {
 
-// acc.{x,y} += bits(x0, x1) * s.{x,y} as ONE packed fp32x2 FMA (sm_100 FFMA2): the promotion loops are FFMA-issue
-// bound next to the TMEM loads, this halves their instruction count.  Same rounding as two scalar fmaf.
+// acc.{x,y} += bits(x0, x1) * s.{x,y}.  Two scalar FFMAs by default: the packed fp32x2 FMA (sm_100 FFMA2, one
+// instruction for both, -DB200_PACKED_PROMOTION) halves the instruction count but measured SLOWER in the promotion
+// loops — prefill at M=8192: 1.59-1.73 PFLOP/s packed vs 1.99-2.10 scalar, down_proj (K=14336) 1.44 vs 2.03
+// (profiles/r02z_kbench_fp8_block_scalar_vs_packed.jsonl).  Same rounding either way.
 __device__ __forceinline__ void ffma2(float& a0, float& a1, uint32_t x0, uint32_t x1, float s0, float s1) {
+#ifndef B200_PACKED_PROMOTION
+  a0 = fmaf(__uint_as_float(x0), s0, a0);
+  a1 = fmaf(__uint_as_float(x1), s1, a1);
+  return;
+#endif
   asm("{\n.reg .b64 va, vb, vc;\n"
       "mov.b64 va, {%2, %3};\nmov.b64 vb, {%4, %5};\nmov.b64 vc, {%0, %1};\n"
       "fma.rn.f32x2 vc, va, vb, vc;\n"
@@ -420,10 +427,24 @@ gemm_block_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
       const float* sn_p = g.scale_n + (int64_t)(n_ok ? (n0 >> 7) : 0) * g.sn_rs;
 #pragma unroll
       for (int j = 0; j < 128; ++j) facc[j] = 0.f;
-      float s_next = __ldg(sm_p) * __ldg(sn_p);
+      // Scales of K block i are LOADED two blocks ahead and MULTIPLIED only when block i is promoted: the activation
+      // scale of a thread's row is its own cache line (32 lines per warp load, an L2 round trip), and a product
+      // formed right behind the loads parked every promotion warp on that latency once per K block (17 % of all
+      // warp samples on that one FMUL, tensor pipe 44 % active: profiles/r02z_fp8_block_prefill_ncu.txt).
+      float a1 = __ldg(sm_p), w1 = __ldg(sn_p);
+      float a2 = 0.f, w2 = 0.f;
+      if (nkb > 1) {
+        a2 = __ldg(sm_p + g.sm_cs);
+        w2 = __ldg(sn_p + g.sn_cs);
+      }
       for (int i = 0; i < nkb; ++i, ++it) {
-        const float s = s_next;
-        if (i + 1 < nkb) s_next = __ldg(sm_p + (i + 1) * g.sm_cs) * __ldg(sn_p + (i + 1) * g.sn_cs);
+        const float s = a1 * w1;
+        a1 = a2;
+        w1 = w2;
+        if (i + 2 < nkb) {
+          a2 = __ldg(sm_p + (i + 2) * g.sm_cs);
+          w2 = __ldg(sn_p + (i + 2) * g.sn_cs);
+        }
         const int buf = it & 1;
         mbar_wait(empty_bar(it % kBpStages), (it / kBpStages) & 1);
         tc_fence_after();
