@@ -581,7 +581,55 @@ def main():
         rec = time_wrapped([(bmod.kernels, name)], eager_passes)
         pairs = rec[name]
         durs = sorted(a.elapsed_time(b) for a, b, _, _ in pairs[len(pairs) // 3:])  # drop the first pass
-        attn_ms = durs[len(durs) // 2]  # median over every layer of two passes
+        attn_ms_eager = durs[len(durs) // 2]  # median over every layer of two passes
+
+        # The same launch group the way the step runs it — from a CUDA graph, launches chained by programmatic
+        # dependent launch: every layer's attention (its own KV buffers: 1.07 GB per launch, L2-cold) captured back to
+        # back in one graph, CUDA events around each of three replays.  The eager figure above carries the host launch
+        # gap between the split-KV kernel and its merge; it is kept as `ms_per_launch_eager`.
+        def attn_graph_ms():
+            from sglang_npu_b200.srt.model_executor.forward_batch_info import ForwardMode
+
+            fb = runner._make_batch(ForwardMode.DECODE, d_in["input_ids"], d_in["req_pool_indices"], d_in["seq_lens"],
+                                    d_in["out_cache_loc"])
+            layers = [lyr for lyr in runner.model.layers]
+            q = torch.randn((bs, hq_local * cfg.head_dim), device=dev).to(act_dtype)
+
+            def run():
+                runner.attn_backend.init_forward_metadata_capture_cuda_graph(bs, bs, d_in["req_pool_indices"],
+                                                                            d_in["seq_lens"], None, ForwardMode.DECODE, None)
+                for lyr in layers:
+                    lyr.attn(q, None, None, fb, save_kv_cache=False, int8_out=bool(getattr(lyr, "fused_int8", False) and getattr(lyr, "fuse_attn_quant", False)),
+                             kv_in_cache=True)
+
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                run()
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            g_att = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g_att):
+                run()
+            g_att.replay()
+            torch.cuda.synchronize(dev)
+            reps = []
+            for _ in range(3):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                g_att.replay()
+                e1.record()
+                torch.cuda.synchronize(dev)
+                reps.append(e0.elapsed_time(e1) / len(layers))
+            return sorted(reps)[1]
+
+        try:
+            attn_ms = attn_graph_ms()
+            attn_how = ("CUDA events around graph replays of every layer's attention launch group back to back (median of 3 "
+                        "replays / layers); ms_per_launch_eager = the same group timed launch by launch in eager passes")
+        except Exception as e:  # keep the line: fall back to the eager figure and say so
+            attn_ms = attn_ms_eager
+            attn_how = f"eager passes, CUDA events per launch group (graph timing failed: {str(e)[:80]})"
         # algorithmic bytes per launch: KV (unique bytes when a prefix is shared) + q/o + page ids
         sp = args.shared_prefix
         kv_tokens = sp + bs * (ctx - sp)
@@ -596,6 +644,7 @@ def main():
                     "frac": achieved / peaks["hbm_gbs"],
                     "peak_kind": f"{peak_kind} (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)",
                     "frac_of_nominal_8TBs": achieved / 8000.0, "bytes_per_launch": attn_bytes, "ms_per_launch": attn_ms,
+                    "ms_per_launch_eager": attn_ms_eager, "timing": attn_how,
                     "share_of_step": attn_ms * n_layers / ms_per_step, "traffic": None}
         if sp:
             roofline["bytes_note"] = "UNIQUE KV bytes (the shared prefix counted once); logical bytes = " \
