@@ -301,3 +301,72 @@ def test_decode_int8_out_equals_unfused_quant(cuda_device, hq, hkv, d, forced_ch
     assert isinstance(act, kernels.Int8Activation)
     assert torch.equal(act.x_q.cpu(), xq.cpu())
     assert torch.equal(act.x_scale.cpu().view(torch.int32), xs.cpu().view(torch.int32))
+
+
+def _capped_attention_rows(q, k_all, v_all, positions, hq, hkv, d, cap):
+    """softmax(cap * tanh(q k^T * scale / cap)) v in fp32 for single query rows; row i sees keys [0, positions[i]].
+    The logit-cap formula of the reference's Triton kernels (triton_ops/extend_attention.py:164-165, :242-243;
+    decode_attention.py:122-123) — torch_native ignores logit_cap, so this restatement is the yardstick."""
+    grp = hq // hkv
+    out = torch.empty(q.shape[0], hq, d)
+    for i, p in enumerate(positions):
+        k = k_all[: p + 1].float()
+        v = v_all[: p + 1].float()
+        qi = q[i].float().view(hkv, grp, d)
+        s = torch.einsum("hgd,thd->hgt", qi, k) * d ** -0.5
+        s = cap * torch.tanh(s / cap)
+        out[i] = torch.einsum("hgt,thd->hgd", torch.softmax(s, dim=-1), v).reshape(hq, d)
+    return out
+
+
+@pytest.mark.parametrize("new,prefix", [(300, 77), (100, 0)])
+def test_logit_cap_extend_and_decode(cuda_device, new, prefix):
+    """logit_cap > 0 (Gemma-style soft capping): the two-tile TMA extend kernel (300 new tokens), the one-tile kernel
+    (100) and the decode kernel apply cap * tanh(s / cap) before the softmax."""
+    dev = cuda_device
+    hq, hkv, d, page, cap = 8, 2, 128, 16, 5.0
+    total = prefix + new
+    pb = synth.make_paged_batch([total + 1], page, seed=41)
+    runner, backend = harness.build_runner(dev, pb.req_to_token, pb.num_slots, page, hq, hkv, d, torch.bfloat16, ctx=total + 1)
+    pool = runner.token_to_kv_pool
+    kc, vc = synth.randn_kv_device(pb.num_slots, page, hkv, d, torch.bfloat16, dev, seed=42)
+    pool.k_buffer[0].copy_(kc * 2)  # larger scores so the cap bites
+    pool.v_buffer[0].copy_(vc)
+    g = torch.Generator().manual_seed(43)
+    q = (torch.randn(new, hq * d, generator=g) * 2).to(torch.bfloat16).to(dev)
+    k = (torch.randn(new, hkv * d, generator=g) * 2).to(torch.bfloat16).to(dev)
+    v = torch.randn(new, hkv * d, generator=g).to(torch.bfloat16).to(dev)
+    slots = pb.req_to_token[pb.req_pool_indices[0], : total + 1].long()
+    fb = harness.extend_batch(runner, backend, pb.req_pool_indices, torch.tensor([total]), torch.tensor([prefix]),
+                              slots[prefix:total])
+    layer = harness.make_layer(hq, hkv, d, logit_cap=cap)
+    o = layer(q, k, v, fb).view(new, hq, d)
+    torch.cuda.synchronize()
+    k_all = pool.k_buffer[0][slots.to(dev)].cpu()
+    v_all = pool.v_buffer[0][slots.to(dev)].cpu()
+    rows = sorted(set([0, 1, new // 2, new - 2, new - 1] + list(range(120, min(new, 140)))))
+    rows = [r for r in rows if r < new]
+    ref = _capped_attention_rows(q.cpu().view(new, hq, d)[rows], k_all, v_all, [prefix + r for r in rows], hq, hkv, d, cap)
+    assert_close_path(o[rows], ref, f"extend with logit_cap, {new} new tokens")
+    uncapped = _attn_rows_plain(q.cpu().view(new, hq, d)[rows], k_all, v_all, [prefix + r for r in rows], hq, hkv, d)
+    assert (uncapped - ref).abs().max().item() > 5e-2, "the cap must change the result for this test to mean anything"
+    # one decode step on top
+    qd = (torch.randn(1, hq * d, generator=g) * 2).to(torch.bfloat16).to(dev)
+    kd = (torch.randn(1, hkv * d, generator=g) * 2).to(torch.bfloat16).to(dev)
+    vd = torch.randn(1, hkv * d, generator=g).to(torch.bfloat16).to(dev)
+    fbd = harness.decode_batch(runner, backend, pb.req_pool_indices, torch.tensor([total + 1]), slots[total: total + 1])
+    od = layer(qd, kd, vd, fbd).view(1, hq, d)
+    torch.cuda.synchronize()
+    k_all = pool.k_buffer[0][slots.to(dev)].cpu()
+    v_all = pool.v_buffer[0][slots.to(dev)].cpu()
+    refd = _capped_attention_rows(qd.cpu().view(1, hq, d), k_all, v_all, [total], hq, hkv, d, cap)
+    assert_close_path(od, refd, "decode with logit_cap")
+
+
+def _attn_rows_plain(q, k_all, v_all, positions, hq, hkv, d):
+    grp = hq // hkv
+    out = torch.empty(q.shape[0], hq, d)
+    for i, p in enumerate(positions):
+        s = torch.einsum("hgd,thd->hgt", q[i].float().view(hkv, grp, d), k_all[: p + 1].float()) * d ** -0.5
+        out[i] = torch.einsum("hgt,thd->hgd", torch.softmax(s, dim=-1), v_all[: p + 1].float()).reshape(hq, d)
+    return out
