@@ -336,6 +336,15 @@ int b200_rmsnorm_quant_int8(int8_t* xq, float* scale, void* y_out, void* residua
                             const void* weight, int64_t M, int64_t H, float eps, int dtype, void* stream);
 int b200_silu_and_mul_quant_int8(int8_t* xq, float* scale, const void* x, int64_t M, int64_t H, int dtype,
                                  void* stream);
+
+/* The same two fusions for the block-scaled FP8 linears (fp8.py:444-487 quantises the activation per (token, 128)
+ * group before the GEMM: fp8_kernel.py:209-297).  xq [M, H] e4m3, scales [M, H / 128] fp32 row-major; bit-identical
+ * to b200_rmsnorm / b200_silu_and_mul followed by b200_per_token_group_quant_fp8(group 128, eps = quant_eps).
+ * H % 128 == 0.  residual (may be NULL) is updated in place like fused_add_rmsnorm. */
+int b200_rmsnorm_group_quant_fp8(void* xq, float* scales, void* residual, const void* x, const void* weight,
+                                 int64_t M, int64_t H, float eps, float quant_eps, int dtype, void* stream);
+int b200_silu_and_mul_group_quant_fp8(void* xq, float* scales, const void* x, int64_t M, int64_t H, float quant_eps,
+                                      int dtype, void* stream);
 int b200_rope_neox_set_kv(void* q, void* k, const void* v, const float* cos_sin_cache, const int64_t* positions,
                           void* k_cache, void* v_cache, const void* loc, int loc_is_int64, int64_t num_tokens,
                           int num_q_heads, int num_kv_heads, int head_dim, int rot_dim, int64_t q_token_stride,

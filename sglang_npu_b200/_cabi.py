@@ -61,6 +61,8 @@ _SIGNATURES = {
     "b200_decode_attn_shared_prefix_fp8kv": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_int64, _P, c_int64, _P, _P, c_int,
                                              c_int, c_int, c_int, c_int, c_int64, c_int64, c_int64, c_float, c_float,
                                              c_float, c_float, c_int, c_int, c_int, c_int, _P, c_size_t, c_int, _P],
+    "b200_rmsnorm_group_quant_fp8": [_P, _P, _P, _P, _P, c_int64, c_int64, c_float, c_float, c_int, _P],
+    "b200_silu_and_mul_group_quant_fp8": [_P, _P, _P, c_int64, c_int64, c_float, c_int, _P],
     "b200_extend_attn": [_P, _P, _P, _P, _P, _P, _P, c_int64, _P, c_int, _P, _P, c_int, c_int,
                          c_int, c_int, c_int, c_int64, c_int64, c_int64, c_int64, c_int64, c_float,
                          c_float, c_int, c_int, _P, c_int64, c_int64],

@@ -2,12 +2,16 @@
 //   b200_rmsnorm_quant_int8      (fused_add_)rmsnorm  -> per-token int8 quant   (feeds qkv_proj / gate_up_proj)
 //   b200_silu_and_mul_quant_int8 silu_and_mul         -> per-token int8 quant   (feeds down_proj)
 //   b200_rope_neox_set_kv        NeoX RoPE on q,k (in place) + set_kv_buffer of (rotated k, v)
+//   b200_rmsnorm_group_quant_fp8 / b200_silu_and_mul_group_quant_fp8: the same two pairs for the block-scaled FP8
+//                                linears (per-(token, 128) e4m3 quant: the absmax is local to 16 lanes)
 // Each one is bit-identical to running the two un-fused kernels back to back (elementwise.cu then quant.cu /
 // kv_write.cu): the intermediate activation is rounded to the activation dtype before the absmax and the
 // int8 rounding, exactly as when it round-trips through HBM.  What the fusion removes is a launch and an
 // activation round-trip per linear — at decode sizes these steps are latency-bound, not bandwidth-bound.
 // Reference kernels they stand in for: sgl-kernel/csrc/elementwise/{fused_add_rms_norm_kernel,activation,
 // rope}.cu, python/sglang/srt/layers/quantization/int8_kernel.py:20-83, mem_cache/memory_pool.py:369-407.
+#include <cuda_fp8.h>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -264,6 +268,137 @@ __global__ void __launch_bounds__(256) rope_set_kv_kernel(T* __restrict__ q, T* 
   }
 }
 
+
+// ---- block-FP8 activation quantisation fused behind the producer ---------------------------------------------------
+// Same arithmetic as per_token_group_quant_fp8_kernel (quant.cu): s = max(absmax, eps) / 448, q = sat_e4m3(y / s), on
+// the T-rounded activation the un-fused kernel would have read back from HBM; a 128-column group = 16 lanes x 8.
+__device__ __forceinline__ uint32_t fs_pack_fp8x4(float a, float b, float c, float d) {
+  const __nv_fp8x2_storage_t lo = __nv_cvt_float2_to_fp8x2(make_float2(a, b), __NV_SATFINITE, __NV_E4M3);
+  const __nv_fp8x2_storage_t hi = __nv_cvt_float2_to_fp8x2(make_float2(c, d), __NV_SATFINITE, __NV_E4M3);
+  return (uint32_t)lo | ((uint32_t)hi << 16);
+}
+__device__ __forceinline__ uint2 group_quant8(const float (&y)[8], float eps, float* scale_out, bool write_scale) {
+  float amax = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(y[i]));
+  const uint32_t half_mask = 0xFFFFu << (threadIdx.x & 16);  // the 16 lanes of this group (the other half-warp may be idle)
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(half_mask, amax, o));
+  amax = fmaxf(amax, eps);
+  const float s = __fdiv_rn(amax, 448.f);
+  if (write_scale) *scale_out = s;
+  float q[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) q[i] = fminf(fmaxf(__fdiv_rn(y[i], s), -448.f), 448.f);
+  return make_uint2(fs_pack_fp8x4(q[0], q[1], q[2], q[3]), fs_pack_fp8x4(q[4], q[5], q[6], q[7]));
+}
+
+// One CTA per token row, H % 128 == 0.  Thread t owns columns [8t, 8t+8) (+2048 per pass): a group is 16 consecutive
+// lanes of one warp, so the group absmax is four shuffles.
+template <typename T>
+__global__ void __launch_bounds__(256) rmsnorm_group_quant_fp8_kernel(uint8_t* __restrict__ xq, float* __restrict__ scales,
+                                                                      T* __restrict__ residual, const T* __restrict__ x,
+                                                                      const T* __restrict__ w, int64_t H, float eps,
+                                                                      float quant_eps) {
+  extern __shared__ float row_f[];  // H floats
+  __shared__ float red[8];
+  pdl_trigger();
+  pdl_wait();
+  const int64_t row = blockIdx.x;
+  const T* xr = x + row * H;
+  T* rr = residual ? residual + row * H : nullptr;
+  float ss = 0.f;
+  for (int64_t c = threadIdx.x * 8; c < H; c += 256 * 8) {
+    float f[8];
+    load8f<T>(xr + c, f);
+    if (rr) {
+      float r[8];
+      load8f<T>(rr + c, r);
+      int4 nv;
+      uint32_t* nu = reinterpret_cast<uint32_t*>(&nv);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        f[2 * i] += r[2 * i];
+        f[2 * i + 1] += r[2 * i + 1];
+        nu[i] = pack2<T>(f[2 * i], f[2 * i + 1]);
+      }
+      *reinterpret_cast<int4*>(rr + c) = nv;  // residual = T(x + residual)
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      row_f[c + i] = f[i];
+      ss += f[i] * f[i];
+    }
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) tot += red[i];
+  const float rstd = rsqrtf(tot / (float)H + eps);
+  const int64_t groups = H / 128;
+  for (int64_t c = threadIdx.x * 8; c < H; c += 256 * 8) {  // H % 128 == 0: a half-warp is all in or all out
+    float wv[8], y[8];
+    load8f<T>(w + c, wv);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 t2 = unpack2<T>(pack2<T>(row_f[c + 2 * i] * rstd * wv[2 * i], row_f[c + 2 * i + 1] * rstd * wv[2 * i + 1]));
+      y[2 * i] = t2.x;
+      y[2 * i + 1] = t2.y;
+    }
+    const int64_t g = c >> 7;
+    *reinterpret_cast<uint2*>(xq + row * H + c) = group_quant8(y, quant_eps, scales + row * groups + g, (threadIdx.x & 15) == 0);
+  }
+}
+
+// x [M, 2H] gate | up -> e4m3 [M, H] + scales [M, H / 128].  A warp quantises two groups; grid-stride over groups.
+template <typename T>
+__global__ void __launch_bounds__(256) silu_mul_group_quant_fp8_kernel(uint8_t* __restrict__ xq, float* __restrict__ scales,
+                                                                       const T* __restrict__ x, int64_t M, int64_t H,
+                                                                       float quant_eps) {
+  pdl_trigger();
+  pdl_wait();
+  const int64_t groups = H / 128;
+  const int64_t total = M * groups;  // groups overall; half-warp hw handles group hw, hw + stride, ...
+  const int64_t hw0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 4;
+  const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 4;
+  const int li = threadIdx.x & 15;
+  // both half-warps of a warp must run the same number of iterations (full-mask shuffles): pad with an inactive pass
+  const int64_t iters = (total + stride - 1) / stride;
+  for (int64_t it = 0; it < iters; ++it) {
+    const int64_t gi = hw0 + it * stride;
+    const bool active = gi < total;
+    const int64_t row = active ? gi / groups : 0;
+    const int64_t g = active ? gi - row * groups : 0;
+    const int64_t c = g * 128 + li * 8;
+    float y[8];
+    if (active) {
+      const int4 gv = *reinterpret_cast<const int4*>(x + row * 2 * H + c);
+      const int4 uv = *reinterpret_cast<const int4*>(x + row * 2 * H + H + c);
+      const uint32_t* gu = reinterpret_cast<const uint32_t*>(&gv);
+      const uint32_t* uu = reinterpret_cast<const uint32_t*>(&uv);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 g2 = unpack2<T>(gu[k]);
+        const float2 u2 = unpack2<T>(uu[k]);
+        // same arithmetic as silu_and_mul_kernel (elementwise.cu): F.silu(gate) rounded to T before the multiply
+        const float s0 = DT<T>::to_f(DT<T>::from_f(g2.x / (1.f + __expf(-g2.x))));
+        const float s1 = DT<T>::to_f(DT<T>::from_f(g2.y / (1.f + __expf(-g2.y))));
+        const float2 t2 = unpack2<T>(pack2<T>(s0 * u2.x, s1 * u2.y));  // the T-rounded activation
+        y[2 * k] = t2.x;
+        y[2 * k + 1] = t2.y;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) y[k] = 0.f;
+    }
+    float sdummy;
+    const uint2 q = group_quant8(y, quant_eps, active ? scales + row * groups + g : &sdummy, li == 0);
+    if (active) *reinterpret_cast<uint2*>(xq + row * H + c) = q;
+  }
+}
+
 }  // namespace b200
 
 using namespace b200;
@@ -349,4 +484,51 @@ B200_API int b200_rope_neox_set_kv(void* q, void* k, const void* v, const float*
                     num_q_heads, num_kv_heads, head_dim, rot_dim, q_token_stride, k_token_stride, v_token_stride,
                     k_cache_token_stride, v_cache_token_stride);
   return fail(B200_ERR_UNSUPPORTED, "rope_neox_set_kv: dtype %d not supported", dtype);
+}
+
+B200_API int b200_rmsnorm_group_quant_fp8(void* xq, float* scales, void* residual, const void* x, const void* weight,
+                                            int64_t M, int64_t H, float eps, float quant_eps, int dtype, void* stream) {
+  B200_REQUIRE(M >= 0 && H > 0, "rmsnorm_group_quant_fp8: bad sizes");
+  if (M == 0) return B200_OK;
+  B200_REQUIRE(xq && scales && x && weight, "rmsnorm_group_quant_fp8: null pointer");
+  B200_REQUIRE(H % 128 == 0 && H <= 16384, "rmsnorm_group_quant_fp8: H %lld must be a multiple of 128 and <= 16384",
+               (long long)H);
+  B200_REQUIRE(((uintptr_t)x | (uintptr_t)weight | (uintptr_t)residual) % 16 == 0 && (uintptr_t)xq % 8 == 0,
+               "rmsnorm_group_quant_fp8: alignment");
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t smem = (size_t)H * sizeof(float);
+  if (dtype == B200_BF16) {
+    auto kern = rmsnorm_group_quant_fp8_kernel<__nv_bfloat16>;
+    if (smem > 48 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    return launch_k(kern, dim3((unsigned)M), dim3(256), smem, st, 1, true, (uint8_t*)xq, scales, (__nv_bfloat16*)residual,
+                    (const __nv_bfloat16*)x, (const __nv_bfloat16*)weight, H, eps, quant_eps);
+  }
+  if (dtype == B200_F16) {
+    auto kern = rmsnorm_group_quant_fp8_kernel<__half>;
+    if (smem > 48 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    return launch_k(kern, dim3((unsigned)M), dim3(256), smem, st, 1, true, (uint8_t*)xq, scales, (__half*)residual,
+                    (const __half*)x, (const __half*)weight, H, eps, quant_eps);
+  }
+  return fail(B200_ERR_UNSUPPORTED, "rmsnorm_group_quant_fp8: dtype %d not supported", dtype);
+}
+
+B200_API int b200_silu_and_mul_group_quant_fp8(void* xq, float* scales, const void* x, int64_t M, int64_t H,
+                                                 float quant_eps, int dtype, void* stream) {
+  B200_REQUIRE(M >= 0 && H > 0, "silu_and_mul_group_quant_fp8: bad sizes");
+  if (M == 0) return B200_OK;
+  B200_REQUIRE(xq && scales && x, "silu_and_mul_group_quant_fp8: null pointer");
+  B200_REQUIRE(H % 128 == 0, "silu_and_mul_group_quant_fp8: H must be a multiple of 128");
+  B200_REQUIRE((uintptr_t)x % 16 == 0 && (uintptr_t)xq % 8 == 0, "silu_and_mul_group_quant_fp8: alignment");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t half_warps = M * (H / 128);
+  int64_t blocks = ceil_div(half_warps, 16);
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  if (dtype == B200_BF16)
+    return launch_k(silu_mul_group_quant_fp8_kernel<__nv_bfloat16>, dim3((unsigned)blocks), dim3(256), 0, st, 1, true,
+                    (uint8_t*)xq, scales, (const __nv_bfloat16*)x, M, H, quant_eps);
+  if (dtype == B200_F16)
+    return launch_k(silu_mul_group_quant_fp8_kernel<__half>, dim3((unsigned)blocks), dim3(256), 0, st, 1, true, (uint8_t*)xq,
+                    scales, (const __half*)x, M, H, quant_eps);
+  return fail(B200_ERR_UNSUPPORTED, "silu_and_mul_group_quant_fp8: dtype %d not supported", dtype);
 }

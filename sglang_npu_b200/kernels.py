@@ -693,6 +693,56 @@ def silu_and_mul_quant_int8(x: torch.Tensor) -> Int8Activation:
     return Int8Activation(x_q, scale, x.dtype)
 
 
+class Fp8GroupActivation(tuple):
+    """(x_q e4m3 [M, K], x_scale fp32 [M, K / 128], out_dtype): an activation already quantised per (token, 128) group by
+    its producer kernel; B200Fp8LinearMethod.apply() takes it in place of the 16-bit activation."""
+
+    def __new__(cls, x_q, x_scale, out_dtype):
+        return super().__new__(cls, (x_q, x_scale, out_dtype))
+
+    x_q = property(lambda self: self[0])
+    x_scale = property(lambda self: self[1])
+    out_dtype = property(lambda self: self[2])
+
+    @property
+    def shape(self):
+        return self[0].shape
+
+
+def rmsnorm_group_quant_fp8(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: Optional[torch.Tensor] = None,
+                            quant_eps: float = 1e-10) -> Fp8GroupActivation:
+    """(fused_add_)rmsnorm followed by sgl_per_token_group_quant_fp8(group 128) in ONE launch; `residual` is updated
+    in place (residual += x)."""
+    require_cuda(x, weight, residual)
+    lib = _cabi.load()
+    H = x.shape[-1]
+    assert x.is_contiguous() and (residual is None or residual.is_contiguous()) and H % 128 == 0
+    M = x.numel() // H
+    x_q = torch.empty((M, H), device=x.device, dtype=torch.float8_e4m3fn)
+    x_s = torch.empty((M, H // 128), device=x.device, dtype=torch.float32)
+    check(lib.b200_rmsnorm_group_quant_fp8(ptr(x_q), ptr(x_s), ptr(residual), ptr(x), ptr(weight), M, H, float(eps),
+                                           float(quant_eps), dtype_code(x.dtype), stream_ptr(x.device)),
+          "b200_rmsnorm_group_quant_fp8")
+    return Fp8GroupActivation(x_q, x_s, x.dtype)
+
+
+def silu_and_mul_group_quant_fp8(x: torch.Tensor, quant_eps: float = 1e-10) -> Fp8GroupActivation:
+    """silu_and_mul followed by sgl_per_token_group_quant_fp8(group 128) in ONE launch; x is [M, 2H] gate|up."""
+    require_cuda(x)
+    lib = _cabi.load()
+    H = x.shape[-1] // 2
+    x2 = x.reshape(-1, 2 * H)
+    if not x2.is_contiguous():
+        x2 = x2.contiguous()
+    M = x2.shape[0]
+    assert H % 128 == 0
+    x_q = torch.empty((M, H), device=x.device, dtype=torch.float8_e4m3fn)
+    x_s = torch.empty((M, H // 128), device=x.device, dtype=torch.float32)
+    check(lib.b200_silu_and_mul_group_quant_fp8(ptr(x_q), ptr(x_s), ptr(x2), M, H, float(quant_eps), dtype_code(x.dtype),
+                                                stream_ptr(x.device)), "b200_silu_and_mul_group_quant_fp8")
+    return Fp8GroupActivation(x_q, x_s, x.dtype)
+
+
 def rope_neox_set_kv(positions: torch.Tensor, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, head_dim: int,
                      cos_sin_cache: torch.Tensor, k_cache: Optional[torch.Tensor], v_cache: Optional[torch.Tensor],
                      loc: Optional[torch.Tensor]) -> None:

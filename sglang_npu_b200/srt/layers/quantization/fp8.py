@@ -120,6 +120,9 @@ class B200Fp8LinearMethod(LinearMethodBase):
               out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """`out` (optional, beyond the reference signature): destination of the [M, N] result — the symmetric buffer
         of the fused TP exchange for row-parallel layers."""
+        if isinstance(x, kernels.Fp8GroupActivation):  # quantised by the producer kernel (fused rmsnorm / silu-mul)
+            return kernels.fp8_blockwise_scaled_mm(x.x_q, layer.weight.t(), x.x_scale, layer.weight_scale_inv.t(),
+                                                   out_dtype=x.out_dtype, bias=bias, out=out)
         input_2d = x.view(-1, x.shape[-1])
         q_input, x_scale = kernels.sgl_per_token_group_quant_fp8(input_2d, self.quant_config.weight_block_size[1])
         res = kernels.fp8_blockwise_scaled_mm(q_input, layer.weight.t(), x_scale, layer.weight_scale_inv.t(),

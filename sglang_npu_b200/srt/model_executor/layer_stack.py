@@ -91,6 +91,10 @@ class DecoderLayer(nn.Module):
         self.fused_int8 = (type(self.qkv_proj.quant_method).__name__ == "B200W8A8Int8LinearMethod"
                            and os.environ.get("B200_FUSE_STEPS", "1") != "0")
         self.fuse_attn_quant = os.environ.get("B200_FUSE_ATTN_QUANT", "1") != "0"  # A/B switch
+        # block-scaled FP8 ([128, 128]) linears: norm + group quant and silu-mul + group quant in one launch each
+        self.fused_fp8 = (type(self.qkv_proj.quant_method).__name__ == "B200Fp8LinearMethod"
+                          and os.environ.get("B200_FUSE_STEPS", "1") != "0" and cfg.hidden_size % 128 == 0
+                          and (cfg.intermediate_size // tp) % 128 == 0)
         self.input_layernorm = nn.Parameter(torch.ones(cfg.hidden_size, dtype=dtype), requires_grad=False)
         self.post_attention_layernorm = nn.Parameter(torch.ones(cfg.hidden_size, dtype=dtype), requires_grad=False)
 
@@ -101,6 +105,8 @@ class DecoderLayer(nn.Module):
             return self.forward_fused_int8(positions, hidden_states, forward_batch, residual, cos_sin_cache)
         if comm is not None:
             return self.forward_fused_tp(positions, hidden_states, forward_batch, residual, cos_sin_cache, comm)
+        if self.fused_fp8:
+            return self.forward_fused_fp8(positions, hidden_states, forward_batch, residual, cos_sin_cache)
         eps = self.cfg.rms_norm_eps
         if residual is None:
             residual = hidden_states
@@ -123,6 +129,30 @@ class DecoderLayer(nn.Module):
         hidden_states, _ = self.down_proj(act)
         return hidden_states, residual
 
+
+    def forward_fused_fp8(self, positions, hidden_states, forward_batch, residual, cos_sin_cache):
+        """Block-FP8 layer with the activation quantisers fused behind their producers (bit-identical to the un-fused
+        pairs): 11 launches per layer instead of 15."""
+        eps = self.cfg.rms_norm_eps
+        if residual is None:
+            residual = hidden_states
+            act = kernels.rmsnorm_group_quant_fp8(hidden_states, self.input_layernorm, eps)
+        else:
+            act = kernels.rmsnorm_group_quant_fp8(hidden_states, self.input_layernorm, eps, residual=residual)
+        qkv, _ = self.qkv_proj(act)
+        q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
+        pool = forward_batch.token_to_kv_pool
+        cast_kv = pool.dtype != q.dtype
+        kernels.rope_neox_set_kv(positions, q, k, v, self.cfg.head_dim, cos_sin_cache,
+                                 None if cast_kv else pool.get_key_buffer(self.attn.layer_id),
+                                 None if cast_kv else pool.get_value_buffer(self.attn.layer_id),
+                                 None if cast_kv else forward_batch.out_cache_loc)
+        attn_out = self.attn(q, k, v, forward_batch, save_kv_cache=cast_kv, kv_in_cache=not cast_kv)
+        hidden_states, _ = self.o_proj(attn_out)
+        act = kernels.rmsnorm_group_quant_fp8(hidden_states, self.post_attention_layernorm, eps, residual=residual)
+        gate_up, _ = self.gate_up_proj(act)
+        hidden_states, _ = self.down_proj(kernels.silu_and_mul_group_quant_fp8(gate_up))
+        return hidden_states, residual
 
     def _forward_fused_int8(self, positions, hidden_states, forward_batch, residual, cos_sin_cache):
         """Same layer with the §8f #2 fusions: norm+quant, rope+KV-write, silu-mul+quant (10 launches, not 15)."""

@@ -273,3 +273,44 @@ def test_vocab_parallel_argmax_keys(cuda_device, rows, V, tp):
     mx = logits.float().amax(dim=-1, keepdim=True)
     first = torch.where(logits.float() == mx, torch.arange(V, device=cuda_device).expand(rows, V), V).amin(dim=-1)
     assert torch.equal(out, first), (out, first, exp)
+
+
+@pytest.mark.parametrize("M,H", [(1, 4096), (64, 4096), (7, 5120), (300, 8192), (3, 128), (5, 4224)])
+@pytest.mark.parametrize("with_residual", [False, True])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_rmsnorm_group_quant_fp8_equals_unfused(cuda_device, M, H, with_residual, dtype):
+    """(fused_add_)rmsnorm -> per-(token, 128) e4m3 quant in one launch: same bits as the two kernels back to back
+    (H = 4224 leaves the last pass with one active half-warp per warp)."""
+    g = torch.Generator().manual_seed(M * 5 + H)
+    x = torch.randn(M, H, generator=g).to(dtype).to(cuda_device)
+    r = torch.randn(M, H, generator=g).to(dtype).to(cuda_device)
+    w = (1 + 0.1 * torch.randn(H, generator=g)).to(dtype).to(cuda_device)
+    if M > 2:
+        x[2] = 0  # all-zero row: every group clamps at eps
+        r[2] = 0
+    x1, r1 = x.clone(), r.clone()
+    if with_residual:
+        kernels.fused_add_rmsnorm(x1, r1, w, 1e-5)
+        y1 = x1
+    else:
+        y1 = kernels.rmsnorm(x1, w, 1e-5)
+    q1, s1 = kernels.sgl_per_token_group_quant_fp8(y1, 128)
+    r2 = r.clone()
+    act = kernels.rmsnorm_group_quant_fp8(x, w, 1e-5, residual=r2 if with_residual else None)
+    torch.cuda.synchronize()
+    assert torch.equal(act.x_q.view(torch.uint8), q1.view(torch.uint8))
+    assert torch.equal(act.x_scale.view(torch.int32), s1.view(torch.int32))
+    if with_residual:
+        assert torch.equal(r2, r1)
+
+
+@pytest.mark.parametrize("M,H", [(1, 14336), (64, 14336), (5, 27648), (300, 3584), (2, 128), (8192, 1792)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_silu_and_mul_group_quant_fp8_equals_unfused(cuda_device, M, H, dtype):
+    x = torch.randn(M, 2 * H, generator=torch.Generator().manual_seed(H + M)).to(dtype).to(cuda_device)
+    y = kernels.silu_and_mul(x)
+    q1, s1 = kernels.sgl_per_token_group_quant_fp8(y, 128)
+    act = kernels.silu_and_mul_group_quant_fp8(x)
+    torch.cuda.synchronize()
+    assert torch.equal(act.x_q.view(torch.uint8), q1.view(torch.uint8))
+    assert torch.equal(act.x_scale.view(torch.int32), s1.view(torch.int32))

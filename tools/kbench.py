@@ -117,8 +117,10 @@ def bench_decode(args):
 
 def bench_gemm_int8(args):
     dev = torch.device("cuda")
-    tp = args.tp or 1  # Llama-3.1-8B shard shapes [K, N] of one TP rank
+    tp = args.tp or 1  # Llama-3.1-8B (or --big: Llama-3.1-70B) shard shapes [K, N] of one TP rank
     shapes = [(4096, 6144 // tp), (4096 // tp, 4096), (4096, 28672 // tp), (14336 // tp, 4096)]
+    if args.big:
+        shapes = [(8192, 10240 // tp), (8192 // tp, 8192), (8192, 57344 // tp), (28672 // tp, 8192)]
     for m in ([args.m] if args.m else [1, 16, 64, 128, 256, 512, 2048, 8192]):
         tot = 0.0
         for (kk, n) in shapes:
@@ -272,6 +274,7 @@ if __name__ == "__main__":
                     help="decode: over-provision the split grid (a graph captured under a longer context bound)")
     ap.add_argument("--fp8kv", action="store_true", help="decode: FP8 (e4m3) KV cache")
     ap.add_argument("--shared", type=int, default=0, help="decode: every request shares this many leading tokens")
+    ap.add_argument("--big", action="store_true", help="gemm_int8: Llama-3.1-70B shapes instead of 8B")
     ap.add_argument("--cluster", action="store_true", help="gemm_int8: cluster split-K kernel instead of stream-K")
     ap.add_argument("--chan", action="store_true", help="gemm_fp8: per-channel scales (fp8_scaled_mm) instead of block scales")
     args = ap.parse_args()
