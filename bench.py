@@ -310,7 +310,7 @@ def parse_args():
     ap.add_argument("--layers", type=int, default=0, help="debug only: fewer layers (marks the line invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--timeline-out", default="", dest="timeline_out",
-                    help="decode: after the timed region, write rank 0's per-kernel device times of 3 graph replays "
+                    help="after the timed region, write rank 0's per-kernel device times of 3 graph replays (decode) / 2 steps (prefill) "
                          "(torch.profiler / CUPTI; works under torchrun where ncu does not) to this CSV")
     ap.add_argument("--kv-dtype", default=DEFAULTS["kv_dtype"], choices=["bf16", "fp8"], dest="kv_dtype",
                     help="fp8 = --kv-cache-dtype fp8_e4m3 variant")
@@ -730,6 +730,9 @@ def main():
         e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
         e2e_value = T / (e2e_ms / args.steps * 1e-3)
         h2d, d2h = host.nbytes(), reqs * 8
+
+        if args.timeline_out:
+            kernel_timeline(step, 2, args.timeline_out if rank == 0 else None, barrier)
 
         # ---- roofline: the four GEMMs of a layer, timed live; the largest (gate_up) is the dominant kernel -------
         gemm_fn = {"int8": "int8_scaled_mm", "fp8": "fp8_blockwise_scaled_mm", "fp8_chan": "fp8_scaled_mm",
