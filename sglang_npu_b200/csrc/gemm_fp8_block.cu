@@ -62,8 +62,11 @@ struct BlkSk {
   static_assert(kBufs <= kStages, "accumulator ring deeper than the smem ring");
 };
 
-template <int BN>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+// EW promotion warps: 4 (one per TMEM lane quarter, all BN columns each) or 8 (two per quarter, BN/2 columns each — a
+// warp's unit is a serial chain barrier -> tcgen05.ld -> FMAs, two warps per SM sub-partition overlap each other's
+// latencies).  A column's K blocks are still summed in order by one thread: results do not depend on EW.
+template <int BN, int EW>
+__global__ void __launch_bounds__(128 + 32 * EW, 1)
 gemm_block_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                           const GemmArgs g, const int total_units, uint32_t* __restrict__ flags,
                           float* __restrict__ partials) {
@@ -71,7 +74,11 @@ gemm_block_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __gr
   constexpr int STAGES = L::kStages;
   constexpr int BUFS = L::kBufs;
   constexpr int kWBytes = 128 * kBK;
-  constexpr int CH = BN >= 32 ? 32 : 16;  // TMEM columns per tcgen05.ld
+  constexpr int HB = BN / (EW / 4);        // accumulator columns (tokens) per promotion warp
+  constexpr int CH = HB >= 32 ? 32 : 16;  // TMEM columns per tcgen05.ld
+  static_assert(EW == 4 || EW == 8, "one or two promotion warps per TMEM lane quarter");
+  static_assert(HB >= 16, "a promotion warp reads at least 16 columns");
+  auto epi_sync = [] { asm volatile("bar.sync 1, %0;\n" ::"n"(32 * EW) : "memory"); };
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint32_t s_tmem_base;
   __shared__ __align__(16) float s_tab[2][kScaleChunk][BN];  // a_s[token, kb] * w_s[tile, kb], two chunks of units
@@ -97,7 +104,7 @@ gemm_block_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __gr
       mbar_init(full_bar(s), 1);
       mbar_init(empty_bar(s), 1);
     }
-    for (int b = 0; b < BUFS; ++b) mbar_init(tempty_bar(b), 4);  // one arrive per epilogue warp
+    for (int b = 0; b < BUFS; ++b) mbar_init(tempty_bar(b), EW);  // one arrive per promotion warp
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<L::kTmemCols>(smem_u32(&s_tmem_base));
@@ -169,18 +176,22 @@ gemm_block_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __gr
     pdl_wait();
     const int q = warp & 3;
     const int row = q * 32 + lane;  // output channel within the tile = TMEM lane
+    const int col0 = ((warp - 4) >> 2) * HB;  // first token column of this warp
     const int t = threadIdx.x - 128;  // token whose combined scale this thread computes per unit
     const bool has_bias = g.bias != nullptr;
     const int m_cols = min(BN, (g.M + 15) & ~15);
-    float facc[BN];
+    float facc[HB];
 #pragma unroll
-    for (int j = 0; j < BN; ++j) facc[j] = 0.f;
+    for (int j = 0; j < HB; ++j) facc[j] = 0.f;
     // Combined scales a_s[token t, kb] * w_s[tile, kb]: thread t fetches them a CHUNK of units ahead (global-load
     // latency is ~a unit's worth of cycles, so a one-unit-deep prefetch would pace the loop) into a double-buffered
     // shared table; the promotion loop reads them with broadcast LDS.128.
     const int n_units = u1 - u0;
     int lt = u0 / nkb, lkb = u0 - lt * nkb;  // (tile, kb) of the next unit whose scale is to be fetched
-    float sreg[kScaleChunk];
+    // The loaded factors stay RAW in registers until store_chunk, a chunk of units later: a multiply placed next to the
+    // loads makes the warp sit out the whole global-load latency (several microseconds while every SM's TMA ring is
+    // pulling weights) once per chunk — that, not the FMAs, paced this kernel at 5.2 TB/s.
+    float va[kScaleChunk], vb[kScaleChunk];
     auto fetch_chunk = [&]() {
       // addresses first, then ALL loads back to back (one memory latency per chunk, not one per unit)
       int64_t oa[kScaleChunk], ob[kScaleChunk];
@@ -192,27 +203,27 @@ gemm_block_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __gr
         ob[j] = lt * g.sn_rs + lkb * g.sn_cs;
         if (ok[j] && ++lkb == nkb) { lkb = 0; ++lt; }
       }
-      const bool tok = t < g.M && t < BN;
-      float va[kScaleChunk], vb[kScaleChunk];
+      const bool tok = t < g.M && t < BN;  // only the threads that fill the table load anything
 #pragma unroll
       for (int j = 0; j < kScaleChunk; ++j) {
         va[j] = (ok[j] && tok) ? __ldg(g.scale_m + oa[j]) : 0.f;
-        vb[j] = ok[j] ? __ldg(g.scale_n + ob[j]) : 0.f;
+        vb[j] = (ok[j] && tok) ? __ldg(g.scale_n + ob[j]) : 0.f;
       }
-#pragma unroll
-      for (int j = 0; j < kScaleChunk; ++j) sreg[j] = va[j] * vb[j];
     };
     auto store_chunk = [&](int b) {
       if (t < BN) {
 #pragma unroll
-        for (int j = 0; j < kScaleChunk; ++j) s_tab[b][j][t] = sreg[j];
+        for (int j = 0; j < kScaleChunk; ++j) {
+          asm volatile("" : "+f"(va[j]), "+f"(vb[j]));  // first use of the loaded values is HERE, not at the loads
+          s_tab[b][j][t] = va[j] * vb[j];
+        }
       }
     };
     if (n_units > 0) {
       fetch_chunk();
       store_chunk(0);
     }
-    epi_bar_sync();
+    epi_sync();
     if (threadIdx.x == 128) trace_mark(tr, 12);  // first chunk of scales in shared memory
     int seg_kb0 = u0 - (u0 / nkb) * nkb;  // first K block of the running segment
     int tile = u0 / nkb, kb = seg_kb0;
@@ -226,19 +237,28 @@ gemm_block_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __gr
       mbar_wait(empty_bar(it % STAGES), (it / STAGES) & 1);
       tc_fence_after();
       if (threadIdx.x == 128) trace_mark(tr, it == 0 ? 5 : 7);  // 5: first unit accumulated, 7: latest one
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN;
-      const float* sc = s_tab[cb][cj];
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN + col0;
+      const float* sc = s_tab[cb][cj] + col0;
+      const bool dbg_no_read = (g.debug & 0x20) != 0;  // timing experiments (B200_GEMM_DEBUG): wrong results
+      const bool dbg_no_fma = (g.debug & 0x10) != 0;
+      if (col0 >= m_cols || dbg_no_read) {  // nothing of this buffer is this warp's (M <= BN / 2, two warps per quarter)
+        if (lane == 0) mbar_arrive(tempty_bar(buf));
+      }
 #pragma unroll
-      for (int c0 = 0; c0 < BN; c0 += CH) {
-        if (c0 < m_cols) {  // warp-uniform
+      for (int c0 = 0; c0 < HB; c0 += CH) {
+        if (col0 + c0 < m_cols && !dbg_no_read) {  // warp-uniform
           uint32_t r[CH];
           if constexpr (CH == 32) tmem_ld32(taddr + c0, r);
           else tmem_ld16(taddr + c0, r);
           tmem_ld_wait();
-          if (c0 + CH >= m_cols) {  // last read of this buffer: hand it back to the MMA thread before the FMAs
-            tc_fence_before();
+          if (col0 + c0 + CH >= m_cols || c0 + CH >= HB) {  // this warp's last read of the buffer: hand it back
+            tc_fence_before();                             // to the MMA thread before the FMAs
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty_bar(buf));
+          }
+          if (dbg_no_fma) {
+            facc[c0] += __uint_as_float(r[0]);
+            continue;
           }
 #pragma unroll
           for (int j = 0; j < CH; j += 4) {
@@ -250,7 +270,7 @@ gemm_block_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __gr
       }
       if (cj == kScaleChunk - 1 && more) {
         store_chunk(cb ^ 1);
-        epi_bar_sync();
+        epi_sync();
       }
       const int cur_tile = tile, cur_kb = kb;
       if (++kb == nkb) { kb = 0; ++tile; }
@@ -262,13 +282,15 @@ gemm_block_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __gr
       const bool starts = seg_kb0 == 0;
       if (!starts) {
         // contribution: fp32 partial sums -> partials[c][col][row]; a warp store covers 128 contiguous bytes
-        float* dst = partials + (size_t)c * BN * 128 + row;
+        float* dst = partials + ((size_t)c * BN + col0) * 128 + row;
 #pragma unroll
-        for (int j = 0; j < BN; ++j)
-          if (j < m_cols) __stcg(dst + j * 128, facc[j]);
-        epi_bar_sync();  // orders every epilogue thread's stores before the release below (cumulativity)
-        if (threadIdx.x == 128) st_release_u32(flags + c, 1u);
-        if (threadIdx.x == 128) trace_mark(tr, 6);
+        for (int j = 0; j < HB; ++j)
+          if (col0 + j < m_cols) __stcg(dst + j * 128, facc[j]);
+        // The flag is released by warp 3, not here: st.release.gpu is a MEMBAR.ALL.GPU, which under the initial flood of
+        // weight requests takes microseconds — long enough for the MMA thread to run out of TMEM buffers and for this
+        // SM's weight stream to stop (CTAs with a short first segment finished 4-5 us after the others).  bar.arrive
+        // orders this thread's stores before the barrier's completion and does not wait.
+        asm volatile("bar.arrive 2, %0;\n" ::"n"(32 * EW + 32) : "memory");
       } else {
         int n_peers = 0;
         if (!ends) {  // owner of a tile that continues in the following CTAs: add their partials in CTA order
@@ -278,10 +300,10 @@ gemm_block_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __gr
             while (ld_acquire_u32(flags + c + 1 + p) == 0u) {
             }
             if (threadIdx.x == 128) trace_mark(tr, 8);
-            const float* src = partials + (size_t)(c + 1 + p) * BN * 128 + row;
+            const float* src = partials + ((size_t)(c + 1 + p) * BN + col0) * 128 + row;
 #pragma unroll
-            for (int j0 = 0; j0 < BN; j0 += 16) {
-              if (j0 < m_cols) {  // 16 independent loads in flight, then the adds (fixed order: bit-deterministic)
+            for (int j0 = 0; j0 < HB; j0 += 16) {
+              if (col0 + j0 < m_cols) {  // 16 independent loads in flight, then the adds (fixed order: bit-deterministic)
                 float tmp[16];
 #pragma unroll
                 for (int j = 0; j < 16; ++j) tmp[j] = __ldcg(src + (j0 + j) * 128);
@@ -297,25 +319,37 @@ gemm_block_streamk_kernel(const __grid_constant__ CUtensorMap tmap_w, const __gr
           uint16_t* p = reinterpret_cast<uint16_t*>(g.out) + n;
           const bool bf = g.out_is_bf16 != 0;
 #pragma unroll
-          for (int j = 0; j < BN; ++j) {
-            if (j < g.M) {
+          for (int j = 0; j < HB; ++j) {
+            if (col0 + j < g.M) {
               const float v = has_bias ? __fadd_rn(facc[j], bias) : facc[j];
-              p[(int64_t)j * g.N] = bf ? __bfloat16_as_ushort(__float2bfloat16_rn(v)) : __half_as_ushort(__float2half_rn(v));
+              p[(int64_t)(col0 + j) * g.N] = bf ? __bfloat16_as_ushort(__float2bfloat16_rn(v)) : __half_as_ushort(__float2half_rn(v));
             }
           }
         }
         if (n_peers > 0) {
-          epi_bar_sync();  // every epilogue thread has consumed the peers' partials
+          epi_sync();  // every epilogue thread has consumed the peers' partials
           if (threadIdx.x == 128)
             for (int p = 0; p < n_peers; ++p) flags[c + 1 + p] = 0u;
         }
       }
 #pragma unroll
-      for (int j = 0; j < BN; ++j) facc[j] = 0.f;
+      for (int j = 0; j < HB; ++j) facc[j] = 0.f;
       seg_kb0 = 0;  // the next unit (if any) opens the next tile at K block 0
       }
     }
     if (threadIdx.x == 128) trace_mark(tr, 9);
+  } else if (warp == 3) {
+    pdl_wait();
+    // Publisher of this CTA's contribution (its first segment, when that starts inside a tile): completes the barrier
+    // the promotion warps arrive on after their partial stores, then releases the flag (cumulativity covers their
+    // stores: same pattern as a CTA barrier followed by one releasing thread, without stalling the promotion).
+    if (u1 > u0 && u0 % nkb != 0) {
+      asm volatile("bar.sync 2, %0;\n" ::"n"(32 * EW + 32) : "memory");
+      if (lane == 0) {
+        st_release_u32(flags + c, 1u);
+        trace_mark(tr, 6);
+      }
+    }
   } else {
     pdl_wait();
   }
@@ -494,16 +528,16 @@ gemm_block_prefill_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------------------
-template <int BN>
+template <int BN, int EW>
 static int launch_blk_sk(const CUtensorMap& tw, const CUtensorMap& tx, const GemmArgs& g, int total_units, int ctas,
                          void* ws, cudaStream_t st) {
   using L = BlkSk<BN>;
-  auto kern = gemm_block_streamk_kernel<BN>;
+  auto kern = gemm_block_streamk_kernel<BN, EW>;
   B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
   uint32_t* flags = reinterpret_cast<uint32_t*>(ws);
   float* partials = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ws) + kSkFlagBytes);
-  return launch_k(kern, dim3((unsigned)ctas), dim3(kGemmThreads), L::kBytes, st, 1, true, tw, tx, g, total_units, flags,
-                  partials);
+  return launch_k(kern, dim3((unsigned)ctas), dim3(128 + 32 * EW), L::kBytes, st, 1, true, tw, tx, g, total_units,
+                  flags, partials);
 }
 
 int launch_block_fp8_streamk(GemmArgs g, const void* a, const void* b, int64_t M, int64_t N, int64_t K, void* ws,
@@ -522,11 +556,20 @@ int launch_block_fp8_streamk(GemmArgs g, const void* a, const void* b, int64_t M
   int rc;
   if ((rc = cached_tmap(&tw, b, (uint64_t)N, (uint64_t)K, 128)) != B200_OK) return rc;
   if ((rc = cached_tmap(&tx, a, (uint64_t)M, (uint64_t)K, (uint32_t)bn)) != B200_OK) return rc;
+  // two promotion warps per TMEM lane quarter from 33 tokens up (B200_BLK_SK_EW=4 keeps one, for A/B timing)
+  static const int ew_env = [] {
+    const char* e = std::getenv("B200_BLK_SK_EW");
+    return e ? std::atoi(e) : 0;
+  }();
+  const bool wide = ew_env == 8 || (ew_env != 4 && bn >= 64);
   switch (bn) {
-    case 16: return launch_blk_sk<16>(tw, tx, g, (int)units, ctas, ws, st);
-    case 32: return launch_blk_sk<32>(tw, tx, g, (int)units, ctas, ws, st);
-    case 64: return launch_blk_sk<64>(tw, tx, g, (int)units, ctas, ws, st);
-    default: return launch_blk_sk<128>(tw, tx, g, (int)units, ctas, ws, st);
+    case 16: return launch_blk_sk<16, 4>(tw, tx, g, (int)units, ctas, ws, st);
+    case 32: return wide ? launch_blk_sk<32, 8>(tw, tx, g, (int)units, ctas, ws, st)
+                         : launch_blk_sk<32, 4>(tw, tx, g, (int)units, ctas, ws, st);
+    case 64: return wide ? launch_blk_sk<64, 8>(tw, tx, g, (int)units, ctas, ws, st)
+                         : launch_blk_sk<64, 4>(tw, tx, g, (int)units, ctas, ws, st);
+    default: return wide ? launch_blk_sk<128, 8>(tw, tx, g, (int)units, ctas, ws, st)
+                         : launch_blk_sk<128, 4>(tw, tx, g, (int)units, ctas, ws, st);
   }
 }
 
