@@ -1,5 +1,5 @@
 #!/bin/bash
-# round-2 multi-GPU session: bash tools/r2_session_mgpu.sh N   (N = 2, 4 or 8; run under gpurun --gpus N)
+# round-2 multi-GPU session: bash tools/sessions/r2_session_mgpu.sh N   (N = 2, 4 or 8; run under gpurun --gpus N)
 # headline weak-scaling line + kernel timeline, the fused-exchange check, config 4 (AWQ TP=N) and, at N=8, config 5.
 set -u
 N=${1:-2}
