@@ -307,7 +307,7 @@ int b200_argmax(int64_t* out, const void* x, int64_t rows, int64_t V, int64_t ro
 /* Vocab-parallel greedy sampling (replaces the all-gather of the full logits, logits_processor.py:430-500, before
  * sampler.py's argmax): b200_argmax_key stores, per row, a non-negative int64 key = (order-preserving value bits,
  * ~(index_offset + local index)); the TP ranks combine keys with ONE max all-reduce of 8 bytes per row
- * (b200_allreduce / torch.distributed) and b200_argmax_key_decode turns the winning key into the token id
+ * (torch.distributed) and b200_argmax_key_decode turns the winning key into the token id
  * (equal maxima resolve to the lowest global index, like torch.argmax over the gathered logits). */
 int b200_argmax_key(int64_t* key_out, const void* x, int64_t rows, int64_t V, int64_t row_stride, int dtype,
                     int64_t index_offset, void* workspace, size_t workspace_bytes, void* stream);
@@ -419,6 +419,16 @@ int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, void* con
                                       void* epoch, void* residual, const void* weight, int64_t M, int64_t H,
                                       float eps, int tp_size, int tp_rank, int max_blocks, int dtype,
                                       void* err_flag, void* stream);
+/* Plain all-reduce(sum) of the ranks' [M, H] partials over the same symmetric buffers and flag protocol: the exchange
+ * above without residual, norm or quantisation (two-shot: this rank sums its token slice over all ranks in rank order
+ * — fp32, one rounding, identical bits on every rank — and stores it into every rank's `out_ptrs[r]`).  Replaces
+ * tensor_model_parallel_all_reduce where no fusion applies (python/sglang/srt/distributed/communication_op.py:11-13 ->
+ * parallel_state.py:463-542 GroupCoordinator.all_reduce; its small-message kernel is the one/two-shot custom all-reduce,
+ * sgl-kernel/csrc/allreduce/custom_all_reduce.cuh:417-453; binding analogue pynccl.py:126-148).  `out_ptrs` may not
+ * alias `partial_ptrs`.  Same flag words / epoch / err_flag and the same call-sequence rule as above. */
+int b200_tp_all_reduce(const void* const* partial_ptrs, void* const* out_ptrs, void* const* flag_ptrs, void* epoch,
+                       int64_t M, int64_t H, int tp_size, int tp_rank, int max_blocks, int dtype, void* err_flag,
+                       void* stream);
 /* Test entry: all `tp_size` ranks of ONE exchange in a single cooperative launch on one device (blockIdx.y = rank; the
  * pointer tables hold local addresses; epoch / residual / err are per rank).  `args_scratch`: >= tp_size * 512 bytes of
  * device memory.  Lets a single-GPU box execute the exchange kernel's protocol and arithmetic. */

@@ -108,6 +108,7 @@ _SIGNATURES = {
     "b200_comm_ipc_close": [_P],
     "b200_tp_reduce_rmsnorm_quant_int8": [_P, _P, _P, _P, _P, _P, _P, _P, c_int64, c_int64, c_float, c_int, c_int,
                                           c_int, c_int, _P, _P],
+    "b200_tp_all_reduce": [_P, _P, _P, _P, c_int64, c_int64, c_int, c_int, c_int, c_int, _P, _P],
     "b200_tp_exchange_loopback": [_P, _P, _P, _P, _P, _P, _P, _P, c_int64, c_int64, c_float, c_int, c_int, c_int, _P, _P,
                                   c_size_t, _P],
     "b200_comm_check": [_P, _P],

@@ -147,6 +147,7 @@ __device__ __forceinline__ void tp_reduce_norm_quant_body(const TpArgs& a, float
   if (threadIdx.x == 0) trace_mark(tr, 2);
   const int64_t H = a.H;
   const int tp = a.tp;
+  const bool plain = a.weight == nullptr;  // b200_tp_all_reduce: the summed rows go out as they are (no norm, no quant)
   // the grid is capped (every CTA of every rank must be resident for the barriers): a CTA walks rows b, b + grid, ...
   for (int64_t ri = b; ri < rows_per; ri += gridDim.x) {
     const int64_t row = (int64_t)a.rank * rows_per + ri;
@@ -173,6 +174,14 @@ __device__ __forceinline__ void tp_reduce_norm_quant_body(const TpArgs& a, float
           for (int i = 0; i < 8; ++i) s[i] += f[i];
         }
       }
+      if (plain) {  // two-shot all-reduce: this rank's token slice, summed in rank order, to every rank
+        int4 sv;
+        uint32_t* su = reinterpret_cast<uint32_t*>(&sv);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) su[i] = pack2<T>(s[2 * i], s[2 * i + 1]);
+        for (int r = 0; r < tp; ++r) *reinterpret_cast<int4*>(reinterpret_cast<T*>(a.y[r]) + row * H + c) = sv;
+        continue;
+      }
       float f[8];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {  // the all-reduce result as a T tensor (what the un-fused path hands to the norm)
@@ -196,6 +205,7 @@ __device__ __forceinline__ void tp_reduce_norm_quant_body(const TpArgs& a, float
 #pragma unroll
       for (int i = 0; i < 8; ++i) row_f[c + i] = f[i];
     }
+    if (plain) continue;  // (uniform over the CTA)
     __syncthreads();
     // Sum of squares in EXACTLY the order of rmsnorm_quant_int8_kernel (256 threads, thread j runs over the 8-column
     // groups j, j + 256, ... sequentially, then a warp tree, then 8 warp sums in order): fp32 addition is not
@@ -350,7 +360,10 @@ static int build_tp_args(TpArgs& a, int64_t& grid, const void* const* partial_pt
                tp_size, tp_rank);
   B200_REQUIRE(M > 0 && H > 0 && H % 8 == 0 && H * 4 <= 200 * 1024, "tp exchange: bad sizes M %lld H %lld", (long long)M,
                (long long)H);
-  B200_REQUIRE(partial_ptrs && flag_ptrs && epoch && weight && err_flag, "tp exchange: null pointer");
+  B200_REQUIRE(partial_ptrs && flag_ptrs && epoch && err_flag, "tp exchange: null pointer");
+  // weight == null is the plain all-reduce (b200_tp_all_reduce): 16-bit output only, nothing to add or normalise
+  B200_REQUIRE(weight != nullptr || (y_ptrs != nullptr && xq_ptrs == nullptr && residual == nullptr),
+               "tp exchange: a norm weight is required unless only the summed rows are requested");
   B200_REQUIRE(xq_ptrs != nullptr || y_ptrs != nullptr, "tp exchange: no output requested");
   B200_REQUIRE((xq_ptrs == nullptr) == (xscale_ptrs == nullptr), "tp exchange: xq and xscale go together");
   const int64_t rows_per = ceil_div(M, tp_size);
@@ -411,6 +424,14 @@ B200_API int b200_tp_reduce_rmsnorm_quant_int8(const void* const* partial_ptrs, 
     return launch_k(kern, dim3((unsigned)grid), dim3(kCommThreads), smem, st, 1, true, a);
   }
   return fail(B200_ERR_UNSUPPORTED, "tp exchange: dtype %d not supported (bf16/f16)", dtype);
+}
+
+B200_API int b200_tp_all_reduce(const void* const* partial_ptrs, void* const* out_ptrs, void* const* flag_ptrs, void* epoch,
+                                int64_t M, int64_t H, int tp_size, int tp_rank, int max_blocks, int dtype, void* err_flag,
+                                void* stream) {
+  // sum over ranks of the [M, H] partials, every rank receiving all rows: the exchange kernel without its norm / quant
+  return b200_tp_reduce_rmsnorm_quant_int8(partial_ptrs, nullptr, nullptr, out_ptrs, flag_ptrs, epoch, nullptr, nullptr, M, H,
+                                           0.f, tp_size, tp_rank, max_blocks, dtype, err_flag, stream);
 }
 
 B200_API int b200_tp_exchange_loopback(const void* const* partial_ptrs, void* const* xq_ptrs, void* const* xscale_ptrs,

@@ -135,6 +135,22 @@ class B200TPComm:
         partial sums + residual add + RMSNorm, every rank receiving the normalised [M, hidden] rows."""
         return self.reduce_rmsnorm_quant_int8(M, weight, eps, residual, quant=False, normed=True)
 
+    def all_reduce(self, M: int) -> torch.Tensor:
+        """Plain all-reduce(sum) of every rank's `self.partial(M)`: the [M, hidden] sum (rank-order fp32 sum, one rounding,
+        the same bits on every rank) in this rank's `y` buffer — valid until the next exchange through this object.
+        The custom small-message all-reduce of the reference (custom_all_reduce.cuh:417-453) without a fused consumer."""
+        lib = _cabi.load()
+        pa = self._ptr_arrays
+        kernels.check(lib.b200_tp_all_reduce(pa["partial"], pa["y"], pa["flags"], self._base + self._off["epoch"], M,
+                                             self.hidden, self.tp, self.rank, MAX_BLOCKS, dtype_code(self.dtype),
+                                             self._base + self._off["err"], stream_ptr(self.device)),
+                      "b200_tp_all_reduce")
+        return self._y(M)
+
+    def can_all_reduce(self, x: torch.Tensor) -> bool:
+        return (x.is_cuda and x.dtype == self.dtype and x.dim() >= 1 and x.shape[-1] == self.hidden and x.is_contiguous()
+                and 0 < x.numel() // self.hidden <= self.max_tokens)
+
     def check(self) -> None:
         """Synchronise the current stream and raise if an exchange kernel of this rank gave up waiting for a peer
         (B200_TP_TIMEOUT_MS).  Call it where the reference would surface an NCCL timeout: after a step, before results

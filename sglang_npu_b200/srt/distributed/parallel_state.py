@@ -8,6 +8,8 @@ PyNccl path.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -37,8 +39,6 @@ def destroy_tensor_parallel():
 
 def init_tp_comm(max_tokens: int, hidden: int, dtype, device):
     """Create the fused exchange (csrc/tp_comm.cu) for this TP group; B200_TP_FUSED_EXCHANGE=0 keeps NCCL."""
-    import os
-
     global _TP_COMM
     if _TP_SIZE == 1 or os.environ.get("B200_TP_FUSED_EXCHANGE", "1") == "0" or not torch.cuda.is_available():
         return None
@@ -65,8 +65,18 @@ def get_tensor_model_parallel_world_size() -> int:
 
 
 def tensor_model_parallel_all_reduce(x: torch.Tensor) -> torch.Tensor:
-    """In-place sum over the TP group (communication_op.py:11-13)."""
+    """In-place sum over the TP group (communication_op.py:11-13).  With a symmetric-memory exchange object installed
+    (init_tp_comm) a [.., hidden] activation that fits it goes through b200_tp_all_reduce — the counterpart of the
+    reference's custom small-message all-reduce (parallel_state.py:463-542 picks it ahead of NCCL the same way);
+    everything else (other widths / dtypes, CPU tensors, gloo groups) takes torch.distributed.  The choice depends on
+    shapes only, so every rank makes the same one."""
     if _TP_SIZE == 1:
+        return x
+    comm = _TP_COMM
+    if comm is not None and os.environ.get("B200_CUSTOM_ALLREDUCE", "1") != "0" and comm.can_all_reduce(x):
+        M = x.numel() // comm.hidden
+        comm.partial(M).copy_(x.view(M, comm.hidden))
+        x.copy_(comm.all_reduce(M).view_as(x))
         return x
     dist.all_reduce(x, op=dist.ReduceOp.SUM, group=_TP_GROUP)
     return x

@@ -95,6 +95,32 @@ def main():
         say(rank, check="exchange_parity", M=M, residual=residual is not None, tp=world, bit_exact=True, yardstick="nccl" if world == 2 else "fp32 rank-order sum of the gathered partials",
             ok=bool(flag.item()))
 
+    # ---- 1b. plain all-reduce (b200_tp_all_reduce, and through tensor_model_parallel_all_reduce) ----------------------
+    ps._TP_COMM = comm  # what init_tp_comm() installs for the layer stack
+    for M in [1, 33, 256, 512]:
+        part = torch.randn((M, H), generator=g, device=dev).to(dt)
+        gathered = [torch.empty_like(part) for _ in range(world)]
+        dist.all_gather(gathered, part)
+        acc = gathered[0].float()
+        for r in range(1, world):
+            acc = acc + gathered[r].float()
+        exact = acc.to(dt)  # the contract: rank-order fp32 sum, one rounding
+        nccl = part.clone()
+        dist.all_reduce(nccl)
+        comm.partial(M).copy_(part)
+        out = comm.all_reduce(M).clone()
+        via_api = ps.tensor_model_parallel_all_reduce(part.clone().view(M, 1, H)).view(M, H)
+        torch.cuda.synchronize()
+        good = (torch.equal(out.view(torch.int16), exact.view(torch.int16))
+                and torch.equal(via_api.view(torch.int16), exact.view(torch.int16))
+                and torch.allclose(out.float(), nccl.float(), rtol=2e-2, atol=2e-2))
+        flag = torch.tensor([int(good)], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok = ok and bool(flag.item())
+        say(rank, check="all_reduce_parity", M=M, tp=world, bit_exact_vs="fp32 rank-order sum of the gathered partials",
+            max_diff_vs_nccl=float((out.float() - nccl.float()).abs().max()), ok=bool(flag.item()))
+    ps._TP_COMM = None
+
     # CUDA-graph replay of three chained exchanges (what the decode graph does 65 times per step)
     M = 64
     part = torch.randn((M, H), generator=g, device=dev).to(dt)
