@@ -207,8 +207,15 @@ def main():
             dist.all_reduce(part)
             kernels.rmsnorm_quant_int8(part, w, eps, residual=res)
 
+        def plain_custom():  # b200_tp_all_reduce alone (input already in the symmetric buffer, like a GEMM output)
+            comm.all_reduce(M)
+
+        def plain_nccl():
+            dist.all_reduce(part)
+
         out = {}
-        for name, fn in (("fused_us", fused), ("nccl_us", nccl)):
+        for name, fn in (("fused_us", fused), ("nccl_us", nccl), ("all_reduce_custom_us", plain_custom),
+                         ("all_reduce_nccl_us", plain_nccl)):
             for _ in range(5):
                 fn()
             dist.barrier()
