@@ -41,7 +41,7 @@ struct TpArgs {
   float eps;
   uint32_t* err;                  // local: first barrier failure of this rank (0 = none), read by b200_comm_check
   unsigned long long timeout_ns;  // how long a barrier waits for a peer before giving up (%globaltimer)
-  int relaxed_start;              // A/B switch: start barrier with relaxed flags (the round-1 protocol)
+  int relaxed_start;              // start barrier with relaxed flags (default; 0 = sys-scope release / acquire, A/B)
   unsigned long long* trace;  // diagnostics (b200_debug_set_trace) or null
   int trace_slots;
 };
@@ -67,11 +67,6 @@ __device__ __forceinline__ int4 ld_peer_v4(const void* p) {
 __device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.relaxed.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
@@ -81,12 +76,22 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 
 // Block-level barrier across ranks: thread t < tp publishes `e` into peer t's slot [phase][rank][b] and waits for
 // peer t's value in the local slot [phase][t][b].
-//   Both phases are a PTX release / acquire pair at system scope.  ONE releasing thread per peer: the CTA barrier
-//   before it orders every thread's earlier accesses before the release (cumulativity), so the other ~500 threads do
-//   not fence.  At the start barrier what is released is this rank's GEMM output (made visible to this thread by the
-//   kernel boundary / griddepcontrol.wait); the acquiring side then reads the peer rows with L1-bypassing loads.
-//   (`relaxed_start` keeps the round-1 protocol — relaxed start flags, relying on completed-kernel writes being visible
-//   at their home L2 — for A/B timing only: B200_TP_RELAXED_START=1.)
+//   END barrier (phase 1): a PTX release / acquire pair at system scope.  ONE releasing thread per peer: the CTA barrier
+//   before it orders every thread's earlier accesses — the stores into the peers' buffers — before the release
+//   (cumulativity), so the other ~500 threads do not fence.  The release costs 3-4 us (it waits for the NVLink acks of
+//   those stores); that wait is the point of the barrier.
+//   START barrier (phase 0): what has to be visible to the peers is this rank's GEMM output, written by the PREVIOUS
+//   grid.  Default: relaxed sys-scope flags, the reference's own protocol (custom_all_reduce.cuh:168-171,
+//   "Start barrier shouldn't need fence": st/ld.volatile).  It rests on three facts, each held by a test or a rule of
+//   the programming model: (1) griddepcontrol.wait / the kernel boundary returns only when all memory operations of the
+//   prerequisite grid are performed and visible to this grid, i.e. they sit in THIS GPU's L2 or HBM; (2) memory homed on
+//   a GPU has one point of coherence, that GPU's L2 — a peer's NVLink load is served there and is never cached in the
+//   peer's L2 — so a load that leaves the peer AFTER it saw the flag sees the data; (3) the peer's loads do leave the
+//   peer: they are ld.volatile (L1 bypass, see ld_peer_v4) and sit behind the flag loop in program order as volatile
+//   asm.  A sys-scope release here instead (B200_TP_RELEASE_START=1, kept for A/B runs) is a MEMBAR.SYS with nothing of
+//   this grid to wait for and still costs 4.1 us per exchange (flag sent 4.77 us after kernel entry instead of 0.62 us:
+//   profiles/r02zb_tp_exchange_trace_n2.jsonl) — 8 us per layer.  tools/tp_exchange_check.py holds the exchange bit-exact
+//   against the rank-order sum of the gathered partials over repeated launches and graph replays at tp 2 / 4 / 8.
 //   A peer that does not arrive within `timeout_ns` (wall clock, %globaltimer; default 20 s — host skew, a lazy module
 //   load or a GC pause on a peer are legitimate reasons to be late) does NOT kill the context: the first failure is
 //   recorded in `err` (b200_comm_check reports it on the host), the wait is abandoned and the kernel completes with
@@ -101,9 +106,10 @@ __device__ __forceinline__ void rank_barrier(const TpArgs& a, int phase, int b, 
     const bool relaxed = phase == 0 && a.relaxed_start != 0;
     if (relaxed) st_relaxed_sys(theirs, e);
     else st_release_sys(theirs, e);
+    if (t == 0 && a.trace != nullptr && b < a.trace_slots) trace_mark(a.trace + (size_t)b * 16, 7 + 2 * phase);  // flag sent
     unsigned long long t0 = 0;
     uint32_t spins = 0;
-    while ((relaxed ? ld_relaxed_sys(mine) : ld_acquire_sys(mine)) != e) {
+    while (ld_acquire_sys(mine) != e) {  // acquire on the waiting side in both modes: it measured free (1.5 us either way)
       if ((++spins & 0x3ffu) == 0) {  // look at the clock every 1024 polls
         const unsigned long long now = globaltimer_ns();
         if (t0 == 0) t0 = now;
@@ -393,7 +399,14 @@ static int build_tp_args(TpArgs& a, int64_t& grid, const void* const* partial_pt
   a.err = reinterpret_cast<uint32_t*>(err_flag);
   static const unsigned long long timeout_ms =
       getenv("B200_TP_TIMEOUT_MS") ? strtoull(getenv("B200_TP_TIMEOUT_MS"), nullptr, 10) : 20000ull;
-  static const int relaxed_start = getenv("B200_TP_RELAXED_START") && getenv("B200_TP_RELAXED_START")[0] == '1';
+  // start barrier: relaxed flags unless B200_TP_RELEASE_START=1 (or the older spelling B200_TP_RELAXED_START=0)
+  static const int relaxed_start = [] {
+    const char* rel = getenv("B200_TP_RELEASE_START");
+    const char* old = getenv("B200_TP_RELAXED_START");
+    if (rel && rel[0] == '1') return 0;
+    if (old && old[0] == '0') return 0;
+    return 1;
+  }();
   a.timeout_ns = timeout_ms * 1000000ull;
   a.relaxed_start = relaxed_start;
   a.M = M; a.H = H; a.tp = tp_size; a.rank = tp_rank; a.max_blocks = max_blocks; a.eps = eps;

@@ -189,7 +189,8 @@ def main():
     torch.cuda.synchronize()
     t = tbuf.cpu()
     t = t[t[:, 0] != 0]
-    names = {1: "pdl_wait", 2: "start_barrier", 3: "row_reduced", 4: "stores_issued", 6: "end_barrier"}
+    names = {1: "pdl_wait", 7: "start_flag_sent", 2: "start_barrier", 3: "row_reduced", 4: "stores_issued",
+             9: "end_flag_sent", 6: "end_barrier"}
     row = {n: [int(((t[:, i] - t[:, 14]).float() / 1.965).median()), int(((t[:, i] - t[:, 14]).float() / 1.965).max())]
            for i, n in names.items()}
     say(rank, check="exchange_trace_ns_med_max", M=M, ctas=int(t.shape[0]), graph_us_per_pair=round(e0.elapsed_time(e1) / 80 * 1e3, 2), **row)
