@@ -111,14 +111,17 @@ def main():
         out = comm.all_reduce(M).clone()
         via_api = ps.tensor_model_parallel_all_reduce(part.clone().view(M, 1, H)).view(M, H)
         torch.cuda.synchronize()
-        good = (torch.equal(out.view(torch.int16), exact.view(torch.int16))
-                and torch.equal(via_api.view(torch.int16), exact.view(torch.int16))
-                and torch.allclose(out.float(), nccl.float(), rtol=2e-2, atol=2e-2))
+        exact_ok = (torch.equal(out.view(torch.int16), exact.view(torch.int16))
+                    and torch.equal(via_api.view(torch.int16), exact.view(torch.int16)))
+        # NCCL is only a sanity yardstick at tp > 2: its small-message ring rounds to bf16 at every hop (7 roundings of
+        # partial sums up to ~16, ulp 0.125, at tp 8), its in-switch reduction at larger sizes does not
+        nccl_diff = float((out.float() - nccl.float()).abs().max())
+        good = exact_ok and nccl_diff <= (0.0 if world == 2 else 0.5)
         flag = torch.tensor([int(good)], device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         ok = ok and bool(flag.item())
         say(rank, check="all_reduce_parity", M=M, tp=world, bit_exact_vs="fp32 rank-order sum of the gathered partials",
-            max_diff_vs_nccl=float((out.float() - nccl.float()).abs().max()), ok=bool(flag.item()))
+            bit_exact=exact_ok, max_diff_vs_nccl=nccl_diff, ok=bool(flag.item()))
     ps._TP_COMM = None
 
     # CUDA-graph replay of three chained exchanges (what the decode graph does 65 times per step)
