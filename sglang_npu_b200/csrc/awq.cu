@@ -584,7 +584,26 @@ static int run_awq_gemm(AwqSkArgs g, const void* x, const void* qweight_t, int64
   g.flags = reinterpret_cast<uint32_t*>(wsb + kAwqStateBytes);
   g.partials = reinterpret_cast<uint32_t*>(wsb + kAwqStateBytes + awq_flag_bytes());
   const int sms = sm_count();
-  const int ctas = (int)(units < sms ? units : sms);
+  int ctas = (int)(units < sms ? units : sms);
+  // Above 64 tokens a unit costs a CTA ~1.1 us whatever the grid does (the fp16 tensor pipe and the dequant chain, not
+  // the weight stream, pace it), and what a launch pays on top is the fix-up.  With no more tiles than SMs the grid is
+  // therefore tiles x P CTAs: ranges [c*U/G, (c+1)*U/G) then never straddle a tile, every tile is cut into exactly P
+  // contiguous K ranges, and each CTA publishes and reduces at most once.  P minimises the measured cost model
+  // ceil(nkb / P) * 1.1 + 0.025 * G + 0.1 * P + 3 us (P = 1: nkb * 1.1, no fix-up).  Per-shard GEMMs of cfg 4 at M = 128:
+  // layer total 152 -> 128 us (TP 2), 125 -> 93 (TP 4), 88 -> 70 (TP 8): profiles/r02zd_awq_ctas_per_tile_sweep.jsonl.
+  // B200_AWQ_CTAS_PER_TILE = p forces P (0 = one CTA per SM, the stream-K split of the larger shapes).
+  static const int per_tile_env = getenv("B200_AWQ_CTAS_PER_TILE") ? atoi(getenv("B200_AWQ_CTAS_PER_TILE")) : -1;
+  int per_tile = per_tile_env;
+  if (per_tile < 0 && M > 64 && tiles <= sms) {
+    const int pmax = sms / tiles < g.num_kb ? sms / tiles : g.num_kb;
+    float best = 1.1f * (float)g.num_kb;
+    per_tile = 1;
+    for (int p = 2; p <= pmax; ++p) {
+      const float c = 1.1f * (float)((g.num_kb + p - 1) / p) + 0.025f * (float)(tiles * p) + 0.1f * (float)p + 3.f;
+      if (c < best) { best = c; per_tile = p; }
+    }
+  }
+  if (per_tile > 0 && (int64_t)tiles * per_tile <= ctas) ctas = tiles * per_tile;
   CUtensorMap tx;
   int rc;
   g.qweight_t = reinterpret_cast<const uint8_t*>(qweight_t);

@@ -172,3 +172,36 @@ def test_awq_gemm_is_deterministic(cuda_device):
     a = kernels.awq_gemm_repacked(x, qwt, sz, 128).clone()
     for _ in range(3):
         assert torch.equal(kernels.awq_gemm_repacked(x, qwt, sz, 128), a)
+
+
+def test_awq_gemm_tile_aligned_grid_cfg4_tp4(cuda_device):
+    """Above 64 tokens and with no more 256-channel tiles than SMs the grid is tiles x P CTAs (awq.cu run_awq_gemm): every
+    tile is cut into exactly P contiguous K ranges.  The four per-GPU GEMMs of cfg 4 at TP 4 give P = 10..14 (7 tiles),
+    5 (20 tiles, 10 K blocks), 2 (54 tiles) and 7 with an uneven 54 / 7 split; twice each (flags reused)."""
+    for (K, N) in [(5120, 1792), (1280, 5120), (5120, 13824), (6912, 5120)]:
+        for rep in range(2):
+            out, ref = _gemm_case(cuda_device, 128, K, N, 128, torch.float16, seed=rep)
+            assert_close_path(out, ref, f"awq_gemm aligned grid K={K} N={N} rep {rep}")
+
+
+@pytest.mark.parametrize("per_tile", [0, 1, 3, 7])
+def test_awq_gemm_forced_ctas_per_tile_same_bits(cuda_device, per_tile):
+    """B200_AWQ_CTAS_PER_TILE (read once per process, hence the subprocess): whatever the K split, partials are summed in
+    CTA order, so the result must agree with the oracle — and P = 1 (no fix-up at all) is the yardstick the others are
+    held to within fp32 re-association of the K sum."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, torch; sys.path.insert(0, %r)\n"
+        "from tests.test_awq_gpu import _gemm_case\n"
+        "from tests.util import assert_close_path\n"
+        "for (K, N) in [(3456, 5120), (5120, 896)]:\n"
+        "    out, ref = _gemm_case(torch.device('cuda:0'), 128, K, N, 128, torch.float16, seed=5)\n"
+        "    assert_close_path(out, ref, f'awq forced split K={K} N={N}')\n"
+        "print('ok')\n" % (root,))
+    env = dict(os.environ, B200_AWQ_CTAS_PER_TILE=str(per_tile))
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, cwd=root, timeout=600)
+    assert res.returncode == 0 and "ok" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]
