@@ -304,6 +304,13 @@ int b200_rope_neox(void* q, void* k, const float* cos_sin_cache, const int64_t* 
 int b200_argmax_workspace_bytes(int64_t rows, size_t* bytes);
 int b200_argmax(int64_t* out, const void* x, int64_t rows, int64_t V, int64_t row_stride, int dtype,
                 void* workspace, size_t workspace_bytes, void* stream);
+/* b200_argmax without a caller workspace and without ANY allocation (no cudaMalloc / cudaFree, no allocating library
+ * call): the per-row scratch lives in a file-scope `static __device__` array inside the library, 64 KB per GPU, which
+ * bounds the call to rows <= 4096 (more rows -> B200_ERR_WORKSPACE; use b200_argmax).  Same result as b200_argmax.
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (CUDA-graph capture, tight serving loops, harnesses that forbid it).  All calls on one GPU share the scratch (it is
+ * cleared on `stream` before every launch): calls that overlap on the GPU race — serialise them on one stream. */
+int b200_argmax_static(int64_t* out, const void* x, int64_t rows, int64_t V, int64_t row_stride, int dtype, void* stream);
 /* Vocab-parallel greedy sampling (replaces the all-gather of the full logits, logits_processor.py:430-500, before
  * sampler.py's argmax): b200_argmax_key stores, per row, a non-negative int64 key = (order-preserving value bits,
  * ~(index_offset + local index)); the TP ranks combine keys with ONE max all-reduce of 8 bytes per row

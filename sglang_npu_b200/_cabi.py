@@ -87,6 +87,7 @@ _SIGNATURES = {
                        c_int, _P],
     "b200_argmax_workspace_bytes": [c_int64, POINTER(c_size_t)],
     "b200_argmax": [_P, _P, c_int64, c_int64, c_int64, c_int, _P, c_size_t, _P],
+    "b200_argmax_static": [_P, _P, c_int64, c_int64, c_int64, c_int, _P],
     "b200_argmax_key": [_P, _P, c_int64, c_int64, c_int64, c_int, c_int64, _P, c_size_t, _P],
     "b200_argmax_key_decode": [_P, _P, c_int64, _P],
     "b200_embedding": [_P, _P, _P, c_int64, c_int64, c_int64, c_int, _P, _P, _P],

@@ -3,6 +3,8 @@
 // {fused_add_rms_norm_kernel,activation,rope}.cu; numerics follow the layers' forward_native
 // (python/sglang/srt/layers/layernorm.py:135-172, activation.py:60-62, rotary_embedding.py:50-75)
 // evaluated in fp32.  HBM-bound: 16-byte accesses, one row per CTA.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -326,6 +328,50 @@ B200_API int b200_argmax_key_decode(int64_t* out, const int64_t* keys, int64_t r
   B200_REQUIRE(out && keys, "argmax_key_decode: null pointer");
   return launch_k(argmax_key_decode_kernel, dim3((unsigned)ceil_div(rows, 128)), dim3(128), 0, (cudaStream_t)stream, 1, true,
                   out, reinterpret_cast<const long long*>(keys), rows);
+}
+
+// ---- greedy argmax without any allocation: scratch in a file-scope device array ---------------------------------------------
+// For callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+// The scratch of b200_argmax (one u64 key + one u32 counter, padded to 16 bytes, per row) lives in g_argmax_scratch:
+// 4096 rows x 16 B = 64 KB, held by every GPU that loads the library until the process exits.  In host code the array's
+// name is only a host-side stand-in, so the device address is looked up ONCE per device with cudaGetSymbolAddress (with
+// that device current) and that pointer is what the kernel gets.  Every call on a device shares the array: it is cleared
+// on the caller's stream before each launch (an earlier call that was aborted may have left keys behind), and two calls
+// that overlap on the GPU (different streams, no dependency) race on it.
+constexpr int64_t kArgmaxStaticMaxRows = 4096;
+static __device__ __align__(256) unsigned char g_argmax_scratch[kArgmaxStaticMaxRows * 16];
+
+static int argmax_static_scratch(void** ptr) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static void* addr[kMaxDevices] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < kMaxDevices, "argmax_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    B200_CUDA_OK(cudaGetSymbolAddress(&p, g_argmax_scratch));  // this device's instance of the array
+    B200_REQUIRE(p != nullptr && ((uintptr_t)p % 256) == 0, "argmax_static: bad scratch address");
+    addr[dev] = p;
+  }
+  *ptr = addr[dev];
+  return B200_OK;
+}
+
+B200_API int b200_argmax_static(int64_t* out, const void* x, int64_t rows, int64_t V, int64_t row_stride, int dtype,
+                                void* stream) {
+  B200_REQUIRE(rows >= 0, "argmax_static: bad sizes");
+  if (rows > kArgmaxStaticMaxRows)
+    return fail(B200_ERR_WORKSPACE, "argmax_static: %lld rows exceed the built-in scratch of %lld rows (use b200_argmax "
+                "with a caller-owned workspace)", (long long)rows, (long long)kArgmaxStaticMaxRows);
+  if (rows == 0) return B200_OK;
+  void* scratch = nullptr;
+  int rc = argmax_static_scratch(&scratch);
+  if (rc != B200_OK) return rc;
+  const size_t bytes = (size_t)rows * 16;
+  B200_CUDA_OK(cudaMemsetAsync(scratch, 0, bytes, (cudaStream_t)stream));  // keys and counters must start at zero
+  return run_argmax(out, nullptr, 0u, x, rows, V, row_stride, dtype, scratch, bytes, stream);
 }
 
 // ---- decode prologue: token embedding gather (+ positions = seq_lens - 1) -------------------------------------------------
