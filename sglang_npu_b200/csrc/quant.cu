@@ -93,6 +93,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) per_token_group_quant_fp8_kernel(
     uint8_t* __restrict__ xq, float* __restrict__ scales, const T* __restrict__ x, int64_t M, int64_t K,
     int64_t x_row_stride, int group_size, float eps, int64_t s_row_stride, int64_t s_col_stride) {
+  pdl_trigger();
+  pdl_wait();  // x is the previous kernel's output (decode: the attention merge, between it and the o_proj GEMM)
   const int lanes_per_group = group_size / 8;       // 16 for G=128
   const int groups_per_warp = 32 / lanes_per_group;
   const int groups_per_row = (int)(K / group_size);
@@ -131,6 +133,8 @@ __global__ void __launch_bounds__(256) per_token_quant_fp8_kernel(uint8_t* __res
                                                                   const T* __restrict__ x, int64_t K,
                                                                   int64_t x_row_stride) {
   __shared__ float sm[8];
+  pdl_trigger();
+  pdl_wait();
   const int64_t row = blockIdx.x;
   const T* xr = x + row * x_row_stride;
   float amax = 0.f;
@@ -195,15 +199,12 @@ B200_API int b200_per_token_group_quant_fp8(void* xq, float* scales, const void*
   const unsigned blocks = (unsigned)ceil_div(warps, 8);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == B200_BF16)
-    per_token_group_quant_fp8_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(
-        (uint8_t*)xq, scales, (const __nv_bfloat16*)x, M, K, x_row_stride, group_size, eps, scale_row_stride, scale_col_stride);
-  else if (dtype == B200_F16)
-    per_token_group_quant_fp8_kernel<__half><<<blocks, 256, 0, st>>>(
-        (uint8_t*)xq, scales, (const __half*)x, M, K, x_row_stride, group_size, eps, scale_row_stride, scale_col_stride);
-  else
-    return fail(B200_ERR_UNSUPPORTED, "per_token_group_quant_fp8: dtype %d not supported", dtype);
-  B200_LAUNCH_OK();
-  return B200_OK;
+    return launch_k(per_token_group_quant_fp8_kernel<__nv_bfloat16>, dim3(blocks), dim3(256), 0, st, 1, true, (uint8_t*)xq,
+                    scales, (const __nv_bfloat16*)x, M, K, x_row_stride, group_size, eps, scale_row_stride, scale_col_stride);
+  if (dtype == B200_F16)
+    return launch_k(per_token_group_quant_fp8_kernel<__half>, dim3(blocks), dim3(256), 0, st, 1, true, (uint8_t*)xq, scales,
+                    (const __half*)x, M, K, x_row_stride, group_size, eps, scale_row_stride, scale_col_stride);
+  return fail(B200_ERR_UNSUPPORTED, "per_token_group_quant_fp8: dtype %d not supported", dtype);
 }
 
 B200_API int b200_per_token_quant_fp8(void* xq, float* scale, const void* x, int64_t M, int64_t K,
@@ -215,11 +216,10 @@ B200_API int b200_per_token_quant_fp8(void* xq, float* scale, const void* x, int
                "per_token_quant_fp8: alignment");
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == B200_BF16)
-    per_token_quant_fp8_kernel<__nv_bfloat16><<<(unsigned)M, 256, 0, st>>>((uint8_t*)xq, scale, (const __nv_bfloat16*)x, K, x_row_stride);
-  else if (dtype == B200_F16)
-    per_token_quant_fp8_kernel<__half><<<(unsigned)M, 256, 0, st>>>((uint8_t*)xq, scale, (const __half*)x, K, x_row_stride);
-  else
-    return fail(B200_ERR_UNSUPPORTED, "per_token_quant_fp8: dtype %d not supported", dtype);
-  B200_LAUNCH_OK();
-  return B200_OK;
+    return launch_k(per_token_quant_fp8_kernel<__nv_bfloat16>, dim3((unsigned)M), dim3(256), 0, st, 1, true, (uint8_t*)xq, scale,
+                    (const __nv_bfloat16*)x, K, x_row_stride);
+  if (dtype == B200_F16)
+    return launch_k(per_token_quant_fp8_kernel<__half>, dim3((unsigned)M), dim3(256), 0, st, 1, true, (uint8_t*)xq, scale,
+                    (const __half*)x, K, x_row_stride);
+  return fail(B200_ERR_UNSUPPORTED, "per_token_quant_fp8: dtype %d not supported", dtype);
 }
