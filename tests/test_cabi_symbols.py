@@ -58,3 +58,11 @@ def test_cpu_tensors_are_rejected():
 
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         kernels.per_token_quant_int8(torch.zeros(2, 16, dtype=torch.bfloat16))
+
+
+def test_argmax_static_rejects_oversize_before_touching_cuda(lib):
+    """b200_argmax_static (scratch in a static device array, 4096 rows): the size check comes before any CUDA call."""
+    st = lib.b200_argmax_static(None, None, 4097, 128, 128, 1, None)
+    assert st == _cabi.B200_ERR_WORKSPACE
+    assert b"4096" in lib.b200_last_error()
+    assert lib.b200_argmax_static(None, None, 0, 128, 128, 1, None) == 0
