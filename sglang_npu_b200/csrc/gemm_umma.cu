@@ -1217,6 +1217,14 @@ static int run_gemm(GemmArgs g, const void* a, const void* b, int64_t M, int64_t
       if (tiles < sms) {
         const int per_tile = sms / tiles < g.num_kb ? sms / tiles : g.num_kb;
         if (tiles * per_tile * 100 >= sms * 85) ctas = tiles * per_tile;
+        // Short K on a quarter of the SMs or more (decode qkv / o_proj of an 8B model: 32-48 tiles of <= 512 KB): ONE CTA
+        // per tile.  A single SM streams its 512 KB in ~3 us, while the fix-up a K split brings (publish, flag, 32 KB
+        // per peer back through L2) costs ~5 us after the last MMA: 11.2 -> 9.6 us (qkv) and 10.6 -> 9.3 us (o_proj) at
+        // M = 64 (profiles/r02zj_int8_ctas_per_tile_sweep.jsonl).  Measured for 33 <= M <= 64 only, so limited to it.
+        if (g.m_blocks == 1 && M <= 64 && tiles >= 32 && g.num_kb <= 32) ctas = tiles;
+        // B200_SK_CTAS_PER_TILE = p (experiments): force p CTAs per tile (p - 1 peers per owner; 1 = no fix-up at all)
+        static const int force = getenv("B200_SK_CTAS_PER_TILE") ? atoi(getenv("B200_SK_CTAS_PER_TILE")) : 0;
+        if (force > 0 && force <= g.num_kb && tiles * force <= sms) ctas = tiles * force;
       }
       g.splits = 1;
       g.kb_per_split = g.num_kb;
